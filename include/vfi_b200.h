@@ -1,0 +1,123 @@
+/* vfi_b200.h -- C ABI of libvfi_b200.so: the B200 (sm_100a) replacement for the
+ * frame-interpolation hot path of the gaming-VFI benchmark study.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the
+ * reference tree).  All functions return 0 on success or a negative VFI_E_* code;
+ * vfi_last_error(h) gives the message.  Unless stated otherwise all buffers are DEVICE
+ * pointers owned by the caller; the library owns only the handle's weights + workspace.
+ * `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  A handle is
+ * not thread-safe; different handles are independent (the reference is single-threaded:
+ * scripts/run_benchmarks.py:142 hot loop).
+ * There is no CPU fallback: every call fails with VFI_E_CUDA when no sm_100 device exists.
+ */
+#ifndef VFI_B200_H
+#define VFI_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vfi_handle vfi_handle;
+
+#define VFI_OK 0
+#define VFI_E_ARG (-1)     /* bad argument (shape, null pointer, unsupported scale ...) */
+#define VFI_E_CUDA (-2)    /* CUDA runtime / driver error, message in vfi_last_error   */
+#define VFI_E_STATE (-3)   /* weights not loaded                                         */
+#define VFI_E_NOMEM (-4)
+
+#define VFI_PRECISION_FP32 0 /* CUDA-core fp32 convs: 1e-4 parity mode                   */
+#define VFI_PRECISION_BF16 1 /* tcgen05 bf16 implicit-GEMM convs, fp32 accumulate/flow   */
+
+#define VFI_ROUTE_RIFE 0
+#define VFI_ROUTE_VFIMAMBA 1
+#define VFI_ROUTE_SCENE_CHANGE 2
+
+#define VFI_IFNET_PARAMS 5664776
+
+/* lifetime ------------------------------------------------------------------------- */
+int vfi_create(int device, vfi_handle** out);
+void vfi_destroy(vfi_handle* h);
+const char* vfi_last_error(vfi_handle* h);
+/* number of kernels this handle has launched since creation (bench.py "gpu_launches") */
+long long vfi_launch_count(vfi_handle* h);
+
+/* IFNet weights.  Replaces Model.load_model(dir, -1) (models/sota/rife_wrapper.py:102-103,
+ * scripts/run_experiments.py:266).  `params` is a HOST array of VFI_IFNET_PARAMS floats:
+ * the v4.25 IFNet state_dict tensors flattened (PyTorch layouts: Conv2d [Co,Ci,kh,kw],
+ * ConvTranspose2d [Ci,Co,kh,kw]) in this order:
+ *   encode.cnn0.{weight,bias} cnn1 cnn2 cnn3,
+ *   for b in block0..block4: conv0.0.0.{weight,bias}, conv0.1.0.{weight,bias},
+ *       for j in 0..7: convblock.j.conv.{weight,bias}, convblock.j.beta,
+ *       lastconv.0.{weight,bias}
+ * `lrelu_slope` NULL => LeakyReLU(0.2) (v4.25); otherwise one slope for every activation. */
+int vfi_ifnet_load_weights(vfi_handle* h, const float* params, size_t n_params, const float* lrelu_slope);
+
+/* Replaces RIFEModel.interpolate's device work (rife_wrapper.py:127-152): to_tensor
+ * (models/base.py:175-186), pad_to_multiple reflect (base.py:203-225), Model.inference(
+ * img0,img1,timestep=t,scale) for each t (rife_wrapper.py:141-146), unpad (base.py:227)
+ * and to_numpy's *255/clip/truncate (base.py:188-201).
+ *   img0,img1 : B x H x W x 3 uint8 RGB          timesteps : HOST array of T floats
+ *   scale     : 1.0, 0.5 or 0.25 (rife_wrapper.py:144; run_experiments.py:192,214)
+ *   hud_mask  : nullable, B x H x W uint8; where non-zero the output pixel is copied from
+ *               img0 (t < 0.5) or img1 (adaptive_pipeline.py:399-409)
+ *   out       : B x T x H x W x 3 uint8          out_f32 : nullable, same shape, float [0,1] unclamped
+ *   flow_out  : nullable, B x T x H x W x 4 float final flow (debug / parity)             */
+int vfi_ifnet_infer(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int B, int H, int W,
+                    const float* timesteps, int T, float scale, int precision,
+                    const uint8_t* hud_mask, uint8_t* out, float* out_f32, float* flow_out, void* stream);
+
+/* The fused backward-warp + sigmoid-blend kernel on its own (IFNet.forward tail:
+ * warp(img0,flow[:, :2]), warp(img1,flow[:, 2:4]), sigmoid(mask), blend -- reached through
+ * rife_wrapper.py:146).  img0/img1: N x H x W x 3 uint8; flow: N x H x W x 4 float;
+ * mask: N x H x W float (pre-sigmoid); out: N x H x W x 3 uint8; out_f32 nullable.      */
+int vfi_warp_blend(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, const float* flow,
+                   const float* mask, int N, int H, int W, uint8_t* out, float* out_f32, void* stream);
+
+/* compute_psnr_simple (evaluation/metrics.py:299-315) for n same-shape uint8 frame pairs of
+ * `elems` bytes each.  sse_out: n x uint64 exact integer sum of squared differences;
+ * psnr_out: n x double (inf when sse == 0).  Either may be NULL.                          */
+int vfi_psnr_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t elems,
+                unsigned long long* sse_out, double* psnr_out, void* stream);
+
+/* compute_ssim_simple (evaluation/metrics.py:318-335; skimage structural_similarity on the
+ * cv2 gray images, 7x7 uniform window) when downscale == 1; AdaptiveRouter.detect_scene_change's
+ * score (adaptive_pipeline.py:140-160: gray, x0.25 INTER_LINEAR, SSIM) when downscale == 4.
+ * a,b: n x H x W x 3 uint8 RGB; out: n x double.                                           */
+int vfi_ssim_gray_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, int H, int W,
+                     int downscale, double* out, void* stream);
+
+/* AdaptiveRouter.compute_motion's reductions (adaptive_pipeline.py:130-138) over a dense flow
+ * field n x H x W x 2 float: out[3*i+0..2] = mean, max, std (population) of |flow|.        */
+int vfi_flow_stats(vfi_handle* h, const float* flow, int n, int H, int W, double* out, void* stream);
+
+/* detect_particles' frequency term (adaptive_pipeline.py:180-183): variance of the 3x3
+ * Laplacian (reflect-101) of the gray image.  rgb: n x H x W x 3; out: n x double.        */
+int vfi_laplacian_var(vfi_handle* h, const uint8_t* rgb, int n, int H, int W, double* out, void* stream);
+
+/* AdaptiveRouter.detect_hud (adaptive_pipeline.py:193-235) for one frame.  hist_ring:
+ * hist_len x 180 x 320 uint8 ring of gray thumbnails; *count (HOST, in/out) = frames pushed so
+ * far.  mask_out: H x W uint8 (0/1); coverage_out: 1 double (device).  With fewer than 5 frames
+ * the mask is all zero and coverage 0, as in the reference.                                */
+int vfi_hud_update(vfi_handle* h, const uint8_t* rgb, int H, int W, uint8_t* hist_ring, int hist_len,
+                   long long* count, double var_threshold, uint8_t* mask_out, double* coverage_out,
+                   void* stream);
+
+/* The decision tree of AdaptiveRouter.analyze (adaptive_pipeline.py:242-275) on HOST doubles.
+ * Returns the route in *route (VFI_ROUTE_*), confidence in *confidence, particle flag/score. */
+int vfi_route_decide(double ssim_score, double motion_mean, double motion_max, double motion_std,
+                     double laplacian_var, double scene_thr, double particle_thr, double motion_lo,
+                     double motion_hi, int* route, double* confidence, int* has_particles,
+                     double* particle_score);
+
+/* Unit-test hook: run ONE conv layer of the loaded IFNet on caller data in both precisions'
+ * layouts.  layer ids are listed in csrc/ifnet.h.  x: N x Hin x Win x Cin_pad (fp32 NHWC),
+ * y: N x Hout x Wout x Cout_pad fp32 NHWC out (for lastconv: N x 4Hin x 4Win x 16).       */
+int vfi_debug_conv(vfi_handle* h, int layer, int precision, const float* x, int N, int Hin, int Win,
+                   const float* residual, float* y, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

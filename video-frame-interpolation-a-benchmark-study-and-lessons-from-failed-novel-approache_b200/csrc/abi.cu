@@ -1,0 +1,343 @@
+// abi.cu -- the extern "C" boundary of libvfi_b200.so: handle lifetime, IFNet weight packing and the
+// inference schedule (Head once per pair, 5 IFBlocks batched over pairs x timesteps, fused tail).
+#include <math.h>
+
+#include "common.cuh"
+
+static const int BLOCK_C[5] = {192, 128, 96, 64, 32};
+
+int vfi_ws_reserve(vfi_handle* h, size_t bytes) {
+  if (bytes <= h->ws_bytes) return 0;
+  if (h->ws) { cudaDeviceSynchronize(); cudaFree(h->ws); h->ws = nullptr; h->ws_bytes = 0; }
+  size_t want = bytes + bytes / 8;
+  if (cudaMalloc(&h->ws, want) != cudaSuccess) {
+    cudaGetLastError();
+    VFI_FAIL(h, VFI_E_NOMEM, "workspace cudaMalloc(%zu) failed", want);
+  }
+  h->ws_bytes = want;
+  return 0;
+}
+int vfi_red_reserve(vfi_handle* h, size_t bytes) {
+  if (bytes <= h->red_bytes) return 0;
+  if (h->red) { cudaDeviceSynchronize(); cudaFree(h->red); h->red = nullptr; h->red_bytes = 0; }
+  if (cudaMalloc(&h->red, bytes) != cudaSuccess) {
+    cudaGetLastError();
+    VFI_FAIL(h, VFI_E_NOMEM, "scratch cudaMalloc(%zu) failed", bytes);
+  }
+  h->red_bytes = bytes;
+  return 0;
+}
+
+extern "C" __attribute__((visibility("default"))) int vfi_create(int device, vfi_handle** out) {
+  if (!out) return VFI_E_ARG;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) { cudaGetLastError(); return VFI_E_CUDA; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return VFI_E_CUDA;
+  if (prop.major != 10) return VFI_E_CUDA;  // sm_100a only: no fallback path exists
+  if (cudaSetDevice(device) != cudaSuccess) return VFI_E_CUDA;
+  vfi_handle* h = new vfi_handle();
+  h->device = device;
+  h->sm_count = prop.multiProcessorCount;
+  for (int i = 0; i < VFI_NUM_LAYERS; i++) h->layers[i] = Layer();
+  *out = h;
+  return VFI_OK;
+}
+
+static void free_layers(vfi_handle* h) {
+  for (int i = 0; i < VFI_NUM_LAYERS; i++) {
+    Layer& L = h->layers[i];
+    cudaFree(L.w32); cudaFree(L.bias); cudaFree(L.beta); cudaFree(L.wtc); cudaFree(L.bias_tc);
+    L.w32 = L.bias = L.beta = L.bias_tc = nullptr;
+    L.wtc = nullptr;
+  }
+}
+
+extern "C" __attribute__((visibility("default"))) void vfi_destroy(vfi_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  free_layers(h);
+  cudaFree(h->ws);
+  cudaFree(h->red);
+  delete h;
+}
+
+extern "C" __attribute__((visibility("default"))) const char* vfi_last_error(vfi_handle* h) { return h ? h->err.c_str() : "null handle"; }
+extern "C" __attribute__((visibility("default"))) long long vfi_launch_count(vfi_handle* h) { return h ? h->launches : 0; }
+
+static void layer_shape(int id, Layer& L) {
+  L = Layer();
+  L.act = true;
+  L.has_beta = false;
+  L.stride = 1;
+  L.kind = LK_CONV3;
+  if (id < 4) {
+    if (id == 0) { L.cin = 3; L.cout = 16; L.stride = 2; L.cin_pad = 4; }
+    else if (id < 3) { L.cin = 16; L.cout = 16; L.cin_pad = 16; }
+    else { L.kind = LK_DECONV4; L.cin = 16; L.cout = 4; L.cin_pad = 16; L.act = false; L.stride = 2; }
+  } else {
+    int b = (id - 4) / 11, j = (id - 4) % 11, c = BLOCK_C[b];
+    if (j == 0) { L.cin = b == 0 ? 15 : 28; L.cin_pad = b == 0 ? 16 : 32; L.cout = c / 2; L.stride = 2; }
+    else if (j == 1) { L.cin = L.cin_pad = c / 2; L.cout = c; L.stride = 2; }
+    else if (j < 10) { L.cin = L.cin_pad = c; L.cout = c; L.has_beta = true; }
+    else { L.kind = LK_DECONV4; L.cin = L.cin_pad = c; L.cout = 52; L.act = false; L.stride = 2; }
+  }
+  L.cout_pad = L.cout;
+}
+
+extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi_handle* h, const float* params, size_t n_params, const float* lrelu_slope) {
+  if (!h) return VFI_E_ARG;
+  if (!params || n_params != (size_t)VFI_IFNET_PARAMS)
+    VFI_FAIL(h, VFI_E_ARG, "expected %d parameters, got %zu", VFI_IFNET_PARAMS, n_params);
+  VFI_CUDA(h, cudaSetDevice(h->device));
+  free_layers(h);
+  h->weights_loaded = false;
+  h->slope = lrelu_slope ? *lrelu_slope : 0.2f;
+  size_t off = 0;
+  for (int id = 0; id < VFI_NUM_LAYERS; id++) {
+    Layer& L = h->layers[id];
+    layer_shape(id, L);
+    const int kk = L.kind == LK_CONV3 ? 9 : 16;
+    size_t nw = (size_t)L.cin * L.cout * kk;
+    if (off + nw + L.cout + (L.has_beta ? L.cout : 0) > n_params) VFI_FAIL(h, VFI_E_ARG, "parameter blob too short");
+    std::vector<float> w(params + off, params + off + nw);
+    off += nw;
+    std::vector<float> bias(params + off, params + off + L.cout);
+    off += L.cout;
+    std::vector<float> beta;
+    if (L.has_beta) { beta.assign(params + off, params + off + L.cout); off += L.cout; }
+    // fp32 layout [tap][cin_pad][cout_pad]
+    std::vector<float> w32((size_t)kk * L.cin_pad * L.cout_pad, 0.f);
+    for (int co = 0; co < L.cout; co++)
+      for (int ci = 0; ci < L.cin; ci++)
+        for (int t = 0; t < kk; t++) {
+          float v = L.kind == LK_CONV3 ? w[((size_t)co * L.cin + ci) * 9 + t] : w[((size_t)ci * L.cout + co) * 16 + t];
+          w32[((size_t)t * L.cin_pad + ci) * L.cout_pad + co] = v;
+        }
+    VFI_CUDA(h, cudaMalloc(&L.w32, w32.size() * 4));
+    VFI_CUDA(h, cudaMemcpy(L.w32, w32.data(), w32.size() * 4, cudaMemcpyHostToDevice));
+    std::vector<float> bpad(64 > L.cout_pad ? 64 : L.cout_pad, 0.f);
+    for (int i = 0; i < L.cout; i++) bpad[i] = bias[i];
+    VFI_CUDA(h, cudaMalloc(&L.bias, bpad.size() * 4));
+    VFI_CUDA(h, cudaMemcpy(L.bias, bpad.data(), bpad.size() * 4, cudaMemcpyHostToDevice));
+    if (L.has_beta) {
+      VFI_CUDA(h, cudaMalloc(&L.beta, beta.size() * 4));
+      VFI_CUDA(h, cudaMemcpy(L.beta, beta.data(), beta.size() * 4, cudaMemcpyHostToDevice));
+    }
+    const bool tc = (id == 1 || id == 2 || id >= 4);
+    if (tc) {
+      if (int rc = tc_build_layer(h, L, w)) return rc;
+    }
+  }
+  if (off != n_params) VFI_FAIL(h, VFI_E_ARG, "parameter blob length mismatch (%zu consumed)", off);
+  h->weights_loaded = true;
+  return VFI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+struct Carve {
+  uint8_t* base; size_t off;
+  template <typename T> T* take(size_t n) {
+    off = (off + 1023) & ~(size_t)1023;
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    return p;
+  }
+};
+
+static int run_conv(vfi_handle* h, const Layer& L, const void* in, const void* res, void* out, int N, int Hin,
+                    int Win, bool bf, bool out_phase, cudaStream_t s) {
+  if (bf) return k_conv_tc(h, L, (const bf16*)in, (const bf16*)res, out, N, Hin, Win, out_phase, h->slope, s);
+  return k_conv3_direct(h, L, in, res, out, N, Hin, Win, false, h->slope, s);
+}
+
+extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int B, int H, int W,
+                               const float* timesteps, int T, float scale, int precision, const uint8_t* hud_mask,
+                               uint8_t* out, float* out_f32, float* flow_out, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!h->weights_loaded) VFI_FAIL(h, VFI_E_STATE, "IFNet weights not loaded");
+  if (!img0 || !img1 || !out || !timesteps || B < 1 || T < 1 || T > 64 || H < 2 || W < 2)
+    VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  if (precision != VFI_PRECISION_FP32 && precision != VFI_PRECISION_BF16) VFI_FAIL(h, VFI_E_ARG, "bad precision");
+  int inv;
+  if (scale == 1.0f) inv = 1; else if (scale == 0.5f) inv = 2; else if (scale == 0.25f) inv = 4;
+  else VFI_FAIL(h, VFI_E_ARG, "scale must be 1.0, 0.5 or 0.25");
+  VFI_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool bf = precision == VFI_PRECISION_BF16;
+  const size_t esz = bf ? 2 : 4;
+  const int mult = 64 * inv > 32 ? 64 * inv : 32;
+  const int Hp = (H + mult - 1) / mult * mult, Wp = (W + mult - 1) / mult * mult;
+  if (Hp - H >= H || Wp - W >= W) VFI_FAIL(h, VFI_E_ARG, "frame too small for reflect padding to %d", mult);
+  const int N = B * T, NI = 2 * B;
+  int sl[5];
+  for (int i = 0; i < 5; i++) sl[i] = (16 >> i) * inv;
+
+  // ---- workspace ----
+  size_t xin_e = 0, a0_e = 0, f_e = 0, low_e = 0;
+  for (int i = 0; i < 5; i++) {
+    size_t hs = Hp / sl[i], wsz = Wp / sl[i];
+    int c = BLOCK_C[i];
+    xin_e = std::max(xin_e, (size_t)N * hs * wsz * (i == 0 ? 16 : 32));
+    a0_e = std::max(a0_e, (size_t)N * (hs / 2) * (wsz / 2) * (c / 2));
+    f_e = std::max(f_e, (size_t)N * (hs / 4) * (wsz / 4) * c);
+    low_e = std::max(low_e, (size_t)N * hs * wsz * 16);
+  }
+  const size_t px = (size_t)Hp * Wp;
+  Carve cv{nullptr, 0};
+  for (int pass = 0; pass < 2; pass++) {
+    cv.off = 0;
+    cv.base = pass ? (uint8_t*)h->ws : nullptr;
+    if (pass == 0) { /* sizing pass */ }
+    uint8_t* imgs = cv.take<uint8_t>(NI * px * 4);
+    uint8_t* feats = cv.take<uint8_t>(NI * px * 4 * esz);
+    uint8_t* ht0 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
+    uint8_t* ht1 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
+    float* tdev = cv.take<float>(64);
+    float* state = cv.take<float>((size_t)N * px * 16);
+    float* fm = cv.take<float>((size_t)N * px * 8);
+    uint8_t* xin = cv.take<uint8_t>(xin_e * esz);
+    uint8_t* a0 = cv.take<uint8_t>(a0_e * esz);
+    uint8_t* fa = cv.take<uint8_t>(f_e * esz);
+    uint8_t* fb = cv.take<uint8_t>(f_e * esz);
+    float* low = cv.take<float>(low_e);
+    if (pass == 0) {
+      if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc;
+      continue;
+    }
+    int rc;
+    VFI_CUDA(h, cudaMemcpyAsync(tdev, timesteps, T * sizeof(float), cudaMemcpyHostToDevice, s));
+    // to_tensor + reflect pad, both frames of every pair
+    if ((rc = k_pad_rgbx(h, img0, imgs, B, H, W, Hp, Wp, s))) return rc;
+    if ((rc = k_pad_rgbx(h, img1, imgs + (size_t)B * px * 4, B, H, W, Hp, Wp, s))) return rc;
+    // Head (encode) once per image, shared by all T timesteps
+    if ((rc = k_head_cnn0(h, h->layers[0], imgs, ht0, NI, Hp, Wp, bf, s))) return rc;
+    if ((rc = run_conv(h, h->layers[1], ht0, nullptr, ht1, NI, Hp / 2, Wp / 2, bf, false, s))) return rc;
+    if ((rc = run_conv(h, h->layers[2], ht1, nullptr, ht0, NI, Hp / 2, Wp / 2, bf, false, s))) return rc;
+    if ((rc = k_deconv4_direct(h, h->layers[3], ht0, feats, NI, Hp / 2, Wp / 2, bf, 0, s))) return rc;
+    for (int i = 0; i < 5; i++) {
+      const int sc = sl[i], hs = Hp / sc, wsz = Wp / sc;
+      const Layer* Lb = &h->layers[4 + 11 * i];
+      if ((rc = k_gather(h, imgs, feats, state, tdev, xin, B, T, Hp, Wp, sc, i == 0, bf, bf, s))) return rc;
+      if ((rc = run_conv(h, Lb[0], xin, nullptr, a0, N, hs, wsz, bf, bf, s))) return rc;
+      if ((rc = run_conv(h, Lb[1], a0, nullptr, fa, N, hs / 2, wsz / 2, bf, false, s))) return rc;
+      uint8_t *cur = fa, *nxt = fb;
+      for (int j = 0; j < 8; j++) {
+        if ((rc = run_conv(h, Lb[2 + j], cur, cur, nxt, N, hs / 4, wsz / 4, bf, false, s))) return rc;
+        std::swap(cur, nxt);
+      }
+      if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low, N, hs / 4, wsz / 4, false, h->slope, s);
+      else rc = k_deconv4_direct(h, Lb[10], cur, low, N, hs / 4, wsz / 4, false, 1, s);
+      if (rc) return rc;
+      if ((rc = k_upsample(h, low, state, fm, N, Hp, Wp, sc, i == 0, i == 4, s))) return rc;
+    }
+    if ((rc = k_final_blend(h, imgs, fm, hud_mask, tdev, out, out_f32, flow_out, B, T, H, W, Hp, Wp, s))) return rc;
+  }
+  return VFI_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int vfi_warp_blend(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, const float* flow,
+                              const float* mask, int N, int H, int W, uint8_t* out, float* out_f32, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!img0 || !img1 || !flow || !mask || !out || N < 1 || H < 1 || W < 1) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  VFI_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t px = (size_t)H * W;
+  Carve cv{nullptr, 0};
+  for (int pass = 0; pass < 2; pass++) {
+    cv.off = 0;
+    cv.base = pass ? (uint8_t*)h->ws : nullptr;
+    uint8_t* imgs = cv.take<uint8_t>(2 * (size_t)N * px * 4);
+    float* fm = cv.take<float>((size_t)N * px * 8);
+    float* tdev = cv.take<float>(64);
+    if (pass == 0) { if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc; continue; }
+    int rc;
+    VFI_CUDA(h, cudaMemsetAsync(tdev, 0, 64 * sizeof(float), s));
+    if ((rc = k_pad_rgbx(h, img0, imgs, N, H, W, H, W, s))) return rc;
+    if ((rc = k_pad_rgbx(h, img1, imgs + (size_t)N * px * 4, N, H, W, H, W, s))) return rc;
+    if ((rc = k_pack_fm(h, flow, mask, fm, N, H, W, H, W, s))) return rc;
+    if ((rc = k_final_blend(h, imgs, fm, nullptr, tdev, out, out_f32, nullptr, N, 1, H, W, H, W, s))) return rc;
+  }
+  return VFI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle* h, int layer, int precision, const float* x, int N, int Hin, int Win,
+                              const float* residual, float* y, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!h->weights_loaded) VFI_FAIL(h, VFI_E_STATE, "IFNet weights not loaded");
+  if (layer < 1 || layer >= VFI_NUM_LAYERS || !x || !y) VFI_FAIL(h, VFI_E_ARG, "bad layer/argument");
+  VFI_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const Layer& L = h->layers[layer];
+  const bool bf = precision == VFI_PRECISION_BF16;
+  const bool s2 = L.kind == LK_CONV3 && L.stride == 2;
+  const int Ho = L.kind == LK_DECONV4 ? 2 * Hin : (s2 ? Hin / 2 : Hin);
+  const int Wo = L.kind == LK_DECONV4 ? 2 * Win : (s2 ? Win / 2 : Win);
+  const size_t nin = (size_t)N * Hin * Win * L.cin_pad;
+  const size_t nout = (size_t)N * Ho * Wo * L.cout_pad;
+  if (!bf) {
+    if (L.kind == LK_CONV3) return k_conv3_direct(h, L, x, residual, y, N, Hin, Win, false, h->slope, s);
+    return k_deconv4_direct(h, L, x, y, N, Hin, Win, false, layer == 3 ? 0 : 1, s);
+  }
+  Carve cv{nullptr, 0};
+  for (int pass = 0; pass < 2; pass++) {
+    cv.off = 0;
+    cv.base = pass ? (uint8_t*)h->ws : nullptr;
+    bf16* xb = cv.take<bf16>(nin);
+    bf16* xp = cv.take<bf16>(nin);
+    bf16* rb = cv.take<bf16>(nout);
+    bf16* yb = cv.take<bf16>(nout);
+    if (pass == 0) { if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc; continue; }
+    int rc;
+    if ((rc = k_f32_to_act(h, x, xb, nin, true, s))) return rc;
+    if (layer == 3) {
+      if ((rc = k_deconv4_direct(h, L, xb, yb, N, Hin, Win, true, 0, s))) return rc;
+      return k_act_to_f32(h, yb, y, nout, true, s);
+    }
+    const bf16* in = xb;
+    if (s2) { if ((rc = k_plain_to_phase(h, xb, xp, N, Hin, Win, L.cin_pad, s))) return rc; in = xp; }
+    if (L.kind == LK_DECONV4) return k_conv_tc(h, L, in, nullptr, y, N, Hin, Win, false, h->slope, s);
+    if (L.has_beta) {
+      if (!residual) VFI_FAIL(h, VFI_E_ARG, "ResConv layer needs residual");
+      if ((rc = k_f32_to_act(h, residual, rb, nout, true, s))) return rc;
+    }
+    if ((rc = k_conv_tc(h, L, in, L.has_beta ? rb : nullptr, yb, N, Hin, Win, false, h->slope, s))) return rc;
+    return k_act_to_f32(h, yb, y, nout, true, s);
+  }
+  return VFI_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int vfi_route_decide(double ssim_score, double motion_mean, double motion_max, double motion_std,
+                                double laplacian_var, double scene_thr, double particle_thr, double motion_lo,
+                                double motion_hi, int* route, double* confidence, int* has_particles,
+                                double* particle_score) {
+  if (!route || !confidence) return VFI_E_ARG;
+  int hp = 0;
+  double ps = 0.0;
+  if (ssim_score < scene_thr) {  // adaptive_pipeline.py:242-254
+    *route = VFI_ROUTE_SCENE_CHANGE;
+    *confidence = 1.0 - ssim_score;
+  } else {
+    double fs = motion_std / 20.0; if (fs > 1.0) fs = 1.0;           // :178
+    double qs = laplacian_var / 500.0; if (qs > 1.0) qs = 1.0;       // :186
+    ps = sqrt(fs * qs);                                              // :189
+    hp = ps > particle_thr;
+    if (hp || motion_max > motion_hi) {                              // :266-268
+      *route = VFI_ROUTE_VFIMAMBA;
+      double c = ps + motion_max / 50.0;
+      *confidence = c < 1.0 ? c : 1.0;
+    } else if (motion_mean < motion_lo) {                            // :269-271
+      *route = VFI_ROUTE_RIFE;
+      *confidence = 1.0 - motion_mean / motion_lo;
+    } else {                                                         // :272-275
+      *route = VFI_ROUTE_RIFE;
+      *confidence = 0.7;
+    }
+  }
+  if (has_particles) *has_particles = hp;
+  if (particle_score) *particle_score = ps;
+  return VFI_OK;
+}

@@ -1,0 +1,133 @@
+// common.cuh -- handle, layer table and helpers shared by every translation unit of libvfi_b200.so
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/vfi_b200.h"
+
+typedef __nv_bfloat16 bf16;
+
+// ---- IFNet v4.25 layer table --------------------------------------
+// ids: 0..3 = Head cnn0..cnn3; block b: base = 4 + 11*b: +0 conv0a, +1 conv0b, +2..+9 ResConv, +10 lastconv
+#define VFI_NUM_LAYERS 59
+enum LayerKind { LK_CONV3 = 0, LK_DECONV4 = 1 };
+
+#define VFI_MAX_STEPS 32
+// One k-step of the implicit GEMM: one (tap, channel-chunk) A tile and the B rows that consume it.
+struct TcSeg {
+  int16_t b_row_off;  // first row inside this step's B tile
+  int16_t n;          // MMA N
+  int16_t tmem_col;   // accumulator column offset
+  int16_t accumulate; // 0 => first MMA into these columns (overwrite)
+};
+struct TcStep {
+  int16_t dy, dx;    // A tile coordinate offset (in the A tensor's own pixel grid)
+  int16_t plane;     // phase plane of a stride-2 input (0 for plain tensors)
+  int16_t c0;        // first input channel of the chunk
+  int32_t b_row;     // first row of this step's B tile in the packed weight matrix
+  int16_t b_rows;    // rows to fetch
+  int16_t nseg;
+  TcSeg seg[2];
+};
+
+struct Layer {
+  int kind, cin, cout, stride;
+  int cin_pad;    // channel count of the NHWC input tensor (multiple of 16; 4 for cnn0)
+  int cout_pad;   // channel stride of the output / padded weight columns (multiple of 4)
+  bool has_beta, act;
+  // fp32 path: conv [9][cin_pad][cout_pad]; deconv [16][cin_pad][cout_pad]
+  float* w32 = nullptr;
+  float* bias = nullptr;  // cout_pad floats (zero padded)
+  float* beta = nullptr;  // cout floats or null
+  // tcgen05 path
+  bf16* wtc = nullptr;    // packed [rows_total][cblk] K-major
+  int cblk = 0, rows_total = 0, nsteps = 0, n_total = 0, b_box = 0;
+  TcStep steps[VFI_MAX_STEPS];
+  float* bias_tc = nullptr;  // bias laid out by accumulator column (n_total floats)
+};
+
+struct vfi_handle {
+  int device = 0;
+  int sm_count = 148;
+  std::string err;
+  long long launches = 0;
+  bool weights_loaded = false;
+  float slope = 0.2f;
+  Layer layers[VFI_NUM_LAYERS];
+  // grow-only workspace arena
+  void* ws = nullptr;
+  size_t ws_bytes = 0;
+  // small scratch for reductions
+  void* red = nullptr;
+  size_t red_bytes = 0;
+  void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled entry point
+};
+
+#define VFI_FAIL(h, code, ...)                               \
+  do {                                                       \
+    char _b[512];                                            \
+    snprintf(_b, sizeof(_b), __VA_ARGS__);                   \
+    (h)->err = _b;                                           \
+    return (code);                                           \
+  } while (0)
+
+#define VFI_CUDA(h, expr)                                                                   \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess)                                                                  \
+      VFI_FAIL(h, VFI_E_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+  } while (0)
+
+#define VFI_LAUNCHED(h)                                                                     \
+  do {                                                                                      \
+    (h)->launches++;                                                                        \
+    cudaError_t _e = cudaGetLastError();                                                    \
+    if (_e != cudaSuccess)                                                                  \
+      VFI_FAIL(h, VFI_E_CUDA, "%s:%d launch: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \
+  } while (0)
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// arena helpers (abi.cu)
+int vfi_ws_reserve(vfi_handle* h, size_t bytes);
+int vfi_red_reserve(vfi_handle* h, size_t bytes);
+
+// ---- elementwise.cu -----------------------------------------------------------------------
+int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s);
+int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, int NI, int Hp, int Wp, bool bf, cudaStream_t s);
+int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const float* state, const float* tsteps_dev,
+             void* out, int B, int T, int Hp, int Wp, int s_int, bool first, bool bf, bool phase, cudaStream_t s);
+int k_upsample(vfi_handle* h, const float* low13, float* state, float* fm, int N, int Hp, int Wp, int s_int,
+               bool first, bool last, cudaStream_t s);
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const float* fm, const uint8_t* hud, const float* tsteps_dev,
+                  uint8_t* out, float* out_f32, float* flow_out, int B, int T, int H, int W, int Hp, int Wp,
+                  cudaStream_t s);
+int k_pack_fm(vfi_handle* h, const float* flow, const float* mask, float* fm, int N, int H, int W, int Hp, int Wp,
+              cudaStream_t s);
+int k_f32_to_act(vfi_handle* h, const float* src, void* dst, size_t n, bool bf, cudaStream_t s);
+int k_act_to_f32(vfi_handle* h, const void* src, float* dst, size_t n, bool bf, cudaStream_t s);
+int k_plain_to_phase(vfi_handle* h, const bf16* src, bf16* dst, int N, int H, int W, int C, cudaStream_t s);
+
+// ---- conv_fp32.cu -------------------------------------------------------------------------
+// in/out element type: float (bf=false) or bf16 (bf=true); accumulation always fp32.
+int k_conv3_direct(vfi_handle* h, const Layer& L, const void* in, const void* residual, void* out, int N, int Hin,
+                   int Win, bool bf, float slope, cudaStream_t s);
+// mode 0: out [N,2Hi,2Wi,cout_pad] (act type); mode 1: pixel-shuffled fp32 low13 [N,4Hi,4Wi,16]
+int k_deconv4_direct(vfi_handle* h, const Layer& L, const void* in, void* out, int N, int Hin, int Win, bool bf,
+                     int mode, cudaStream_t s);
+
+// ---- conv_tc.cu ---------------------------------------------------------------------------
+int tc_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch);  // packs wtc + step table
+// conv (mode 0/1) : in plain (stride 1) or phase planes (stride 2) bf16, out bf16 plain or phase (out_phase)
+// lastconv (deconv): in plain bf16, out = fp32 low13 [N,4Hin,4Win,16]
+int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
+              int Win, bool out_phase, float slope, cudaStream_t s);
+
+// ---- reduce.cu is reached only through the ABI functions -----------------------------------

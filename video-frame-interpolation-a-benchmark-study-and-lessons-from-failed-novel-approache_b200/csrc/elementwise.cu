@@ -1,0 +1,458 @@
+// elementwise.cu -- the HBM-bound kernels of the IFNet pass: reflect-pad, Head cnn0, block-input
+// gather (backward warp + bilinear /s + channel concat fused), bilinear xs upsample + flow
+// accumulate, and the final fused backward-warp + sigmoid-blend + u8 store.
+// Reference semantics: SURVEY.md Appendix A.2 (IFNet.forward / IFBlock.forward / warp()).
+#include "common.cuh"
+
+// ------------------------------------------------------------------------------------------
+// small typed load/store helpers
+template <typename T> struct Act;
+template <> struct Act<float> {
+  static __device__ __forceinline__ void load4(const float* p, float* v) {
+    float4 a = *reinterpret_cast<const float4*>(p);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  }
+  static __device__ __forceinline__ void store8(float* p, const float* v) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+  }
+  static __device__ __forceinline__ void store4(float* p, const float* v) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <> struct Act<bf16> {
+  static __device__ __forceinline__ void load4(const bf16* p, float* v) {
+    uint2 a = *reinterpret_cast<const uint2*>(p);
+    __nv_bfloat162 lo = *reinterpret_cast<__nv_bfloat162*>(&a.x);
+    __nv_bfloat162 hi = *reinterpret_cast<__nv_bfloat162*>(&a.y);
+    float2 f0 = __bfloat1622float2(lo), f1 = __bfloat1622float2(hi);
+    v[0] = f0.x; v[1] = f0.y; v[2] = f1.x; v[3] = f1.y;
+  }
+  static __device__ __forceinline__ uint32_t pack(float a, float b) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&t);
+  }
+  static __device__ __forceinline__ void store8(bf16* p, const float* v) {
+    uint4 u;
+    u.x = pack(v[0], v[1]); u.y = pack(v[2], v[3]); u.z = pack(v[4], v[5]); u.w = pack(v[6], v[7]);
+    *reinterpret_cast<uint4*>(p) = u;
+  }
+  static __device__ __forceinline__ void store4(bf16* p, const float* v) {
+    uint2 u;
+    u.x = pack(v[0], v[1]); u.y = pack(v[2], v[3]);
+    *reinterpret_cast<uint2*>(p) = u;
+  }
+};
+
+struct Bil {
+  int o00, o01, o10, o11;  // pixel offsets (y*W + x)
+  float w00, w01, w10, w11;
+};
+// grid_sample(bilinear, border, align_corners=True) at pixel coordinate (fx, fy)
+__device__ __forceinline__ Bil bil_setup(float fx, float fy, int W, int H) {
+  fx = fminf(fmaxf(fx, 0.f), (float)(W - 1));
+  fy = fminf(fmaxf(fy, 0.f), (float)(H - 1));
+  float flx = floorf(fx), fly = floorf(fy);
+  int x0 = (int)flx, y0 = (int)fly;
+  int x1 = min(x0 + 1, W - 1), y1 = min(y0 + 1, H - 1);
+  float wx = fx - flx, wy = fy - fly;
+  Bil b;
+  b.o00 = y0 * W + x0; b.o01 = y0 * W + x1; b.o10 = y1 * W + x0; b.o11 = y1 * W + x1;
+  b.w00 = (1.f - wx) * (1.f - wy); b.w01 = wx * (1.f - wy); b.w10 = (1.f - wx) * wy; b.w11 = wx * wy;
+  return b;
+}
+__device__ __forceinline__ void sample_rgbx(const uint8_t* img, const Bil& b, float* rgb) {
+  const uchar4* p = reinterpret_cast<const uchar4*>(img);
+  uchar4 a = __ldg(p + b.o00), c = __ldg(p + b.o01), d = __ldg(p + b.o10), e = __ldg(p + b.o11);
+  const float k = 1.0f / 255.0f;
+  rgb[0] = (b.w00 * a.x + b.w01 * c.x + b.w10 * d.x + b.w11 * e.x) * k;
+  rgb[1] = (b.w00 * a.y + b.w01 * c.y + b.w10 * d.y + b.w11 * e.y) * k;
+  rgb[2] = (b.w00 * a.z + b.w01 * c.z + b.w10 * d.z + b.w11 * e.z) * k;
+}
+template <typename T>
+__device__ __forceinline__ void sample_feat(const T* f, const Bil& b, float* o) {
+  float a[4], c[4], d[4], e[4];
+  Act<T>::load4(f + 4 * (size_t)b.o00, a);
+  Act<T>::load4(f + 4 * (size_t)b.o01, c);
+  Act<T>::load4(f + 4 * (size_t)b.o10, d);
+  Act<T>::load4(f + 4 * (size_t)b.o11, e);
+#pragma unroll
+  for (int i = 0; i < 4; i++) o[i] = b.w00 * a[i] + b.w01 * c[i] + b.w10 * d[i] + b.w11 * e[i];
+}
+
+// ------------------------------------------------------------------------------------------
+// to_tensor + pad_to_multiple(reflect) (models/base.py:175-186, :203-225) kept in uint8: RGB -> RGBX
+__global__ void pad_rgbx_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int B, int H, int W,
+                                int Hp, int Wp) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)B * Hp * Wp;
+  if (i >= total) return;
+  int x = (int)(i % Wp);
+  int y = (int)((i / Wp) % Hp);
+  int b = (int)(i / ((size_t)Wp * Hp));
+  int sx = x < W ? x : 2 * (W - 1) - x;
+  int sy = y < H ? y : 2 * (H - 1) - y;
+  const uint8_t* p = src + (((size_t)b * H + sy) * W + sx) * 3;
+  reinterpret_cast<uchar4*>(dst)[i] = make_uchar4(p[0], p[1], p[2], 0);
+}
+int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s) {
+  size_t total = (size_t)B * Hp * Wp;
+  pad_rgbx_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Head.cnn0: Conv2d(3,16,3,2,1) + LeakyReLU straight from the uint8 image (K = 27: CUDA cores).
+template <typename T>
+__global__ void head_cnn0_kernel(const uint8_t* __restrict__ imgs, const float* __restrict__ w /*[9][4][16]*/,
+                                 const float* __restrict__ bias, T* __restrict__ out, int NI, int Hp, int Wp,
+                                 float slope) {
+  __shared__ float sw[9 * 4 * 16];
+  __shared__ float sb[16];
+  for (int i = threadIdx.x; i < 9 * 4 * 16; i += blockDim.x) sw[i] = w[i];
+  if (threadIdx.x < 16) sb[threadIdx.x] = bias[threadIdx.x];
+  __syncthreads();
+  int Ho = Hp / 2, Wo = Wp / 2;
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)NI * Ho * Wo;
+  if (i >= total) return;
+  int x = (int)(i % Wo), y = (int)((i / Wo) % Ho), n = (int)(i / ((size_t)Wo * Ho));
+  const uchar4* img = reinterpret_cast<const uchar4*>(imgs) + (size_t)n * Hp * Wp;
+  float acc[16];
+#pragma unroll
+  for (int c = 0; c < 16; c++) acc[c] = sb[c];
+#pragma unroll
+  for (int r = 0; r < 3; r++) {
+    int iy = 2 * y + r - 1;
+    if (iy < 0 || iy >= Hp) continue;
+#pragma unroll
+    for (int q = 0; q < 3; q++) {
+      int ix = 2 * x + q - 1;
+      if (ix < 0 || ix >= Wp) continue;
+      uchar4 p = __ldg(img + (size_t)iy * Wp + ix);
+      float v[3] = {p.x / 255.0f, p.y / 255.0f, p.z / 255.0f};
+      const float* ww = sw + (r * 3 + q) * 64;
+#pragma unroll
+      for (int ci = 0; ci < 3; ci++)
+#pragma unroll
+        for (int c = 0; c < 16; c++) acc[c] = fmaf(v[ci], ww[ci * 16 + c], acc[c]);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 16; c++) acc[c] = acc[c] > 0.f ? acc[c] : acc[c] * slope;
+  T* o = out + i * 16;
+  Act<T>::store8(o, acc);
+  Act<T>::store8(o + 8, acc + 8);
+}
+int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, int NI, int Hp, int Wp, bool bf,
+                cudaStream_t s) {
+  size_t total = (size_t)NI * (Hp / 2) * (Wp / 2);
+  if (bf)
+    head_cnn0_kernel<bf16><<<cdiv(total, 128), 128, 0, s>>>(imgs, L.w32, L.bias, (bf16*)out, NI, Hp, Wp, h->slope);
+  else
+    head_cnn0_kernel<float><<<cdiv(total, 128), 128, 0, s>>>(imgs, L.w32, L.bias, (float*)out, NI, Hp, Wp, h->slope);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Block-input gather.  Produces IFBlock's conv0 input at 1/s resolution in ONE pass:
+//   block 0 : cat(img0, img1, f0, f1, t)                               -> 15 ch (+1 zero)
+//   block i : cat(warp(img0,F01), warp(img1,F10), warp(f0,F01), warp(f1,F10), t, mask, feat, flow/s)
+//                                                                       -> 28 ch (+4 zero)
+// followed by F.interpolate(1/s, bilinear, align_corners=False), which for s in {2,4,8,16,32}
+// is exactly the mean of the 2x2 full-resolution pixels at offsets s/2-1, s/2,
+// so only those pixels are ever warped.  The 28-channel full-resolution concat of the reference
+// never exists.  Output NHWC, plain or split into the 4 stride-2 phase planes the conv0a TMA reads.
+template <typename T, bool FIRST>
+__global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats,
+                              const float* __restrict__ state, const float* __restrict__ tsteps,
+                              T* __restrict__ out, int B, int Tn, int Hp, int Wp, int s, int phase) {
+  constexpr int C = FIRST ? 16 : 32;
+  const int Hs = Hp / s, Ws = Wp / s;
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)B * Tn * Hs * Ws;
+  if (i >= total) return;
+  int X = (int)(i % Ws), Y = (int)((i / Ws) % Hs), n = (int)(i / ((size_t)Ws * Hs));
+  int b = n / Tn;
+  float t = tsteps[n % Tn];
+  const size_t plane = (size_t)Hp * Wp;
+  const uint8_t* img0 = imgs + ((size_t)b) * plane * 4;
+  const uint8_t* img1 = imgs + ((size_t)(B + b)) * plane * 4;
+  const T* f0 = feats + ((size_t)b) * plane * 4;
+  const T* f1 = feats + ((size_t)(B + b)) * plane * 4;
+  const int ns = s == 1 ? 1 : 2;
+  const int by = s == 1 ? Y : s * Y + s / 2 - 1;
+  const int bx = s == 1 ? X : s * X + s / 2 - 1;
+  float acc[C];
+#pragma unroll
+  for (int c = 0; c < C; c++) acc[c] = 0.f;
+  for (int dy = 0; dy < ns; dy++)
+    for (int dx = 0; dx < ns; dx++) {
+      int y = by + dy, x = bx + dx;
+      float v[4];
+      if constexpr (FIRST) {
+        uchar4 p0 = __ldg(reinterpret_cast<const uchar4*>(img0) + (size_t)y * Wp + x);
+        uchar4 p1 = __ldg(reinterpret_cast<const uchar4*>(img1) + (size_t)y * Wp + x);
+        acc[0] += p0.x / 255.0f; acc[1] += p0.y / 255.0f; acc[2] += p0.z / 255.0f;
+        acc[3] += p1.x / 255.0f; acc[4] += p1.y / 255.0f; acc[5] += p1.z / 255.0f;
+        Act<T>::load4(f0 + 4 * ((size_t)y * Wp + x), v);
+        acc[6] += v[0]; acc[7] += v[1]; acc[8] += v[2]; acc[9] += v[3];
+        Act<T>::load4(f1 + 4 * ((size_t)y * Wp + x), v);
+        acc[10] += v[0]; acc[11] += v[1]; acc[12] += v[2]; acc[13] += v[3];
+      } else {
+        const float4* st = reinterpret_cast<const float4*>(state + (((size_t)n * Hp + y) * Wp + x) * 16);
+        float4 fl = __ldg(st), s1 = __ldg(st + 1), s2 = __ldg(st + 2), s3 = __ldg(st + 3);
+        Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
+        Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
+        float rgb[3];
+        sample_rgbx(img0, b0, rgb);
+        acc[0] += rgb[0]; acc[1] += rgb[1]; acc[2] += rgb[2];
+        sample_rgbx(img1, b1, rgb);
+        acc[3] += rgb[0]; acc[4] += rgb[1]; acc[5] += rgb[2];
+        sample_feat<T>(f0, b0, v);
+        acc[6] += v[0]; acc[7] += v[1]; acc[8] += v[2]; acc[9] += v[3];
+        sample_feat<T>(f1, b1, v);
+        acc[10] += v[0]; acc[11] += v[1]; acc[12] += v[2]; acc[13] += v[3];
+        acc[15] += s1.x;                                                 // mask (pre-sigmoid)
+        acc[16] += s1.y; acc[17] += s1.z; acc[18] += s1.w;              // feat 0..2
+        acc[19] += s2.x; acc[20] += s2.y; acc[21] += s2.z; acc[22] += s2.w;
+        acc[23] += s3.x;
+        acc[24] += fl.x; acc[25] += fl.y; acc[26] += fl.z; acc[27] += fl.w;
+      }
+    }
+  if (ns == 2) {
+#pragma unroll
+    for (int c = 0; c < C; c++) acc[c] *= 0.25f;
+  }
+  acc[14] = t;
+  if constexpr (!FIRST) {
+    const float inv = 1.0f / (float)s;
+    acc[24] *= inv; acc[25] *= inv; acc[26] *= inv; acc[27] *= inv;
+  }
+  size_t o;
+  if (phase) {
+    int H2 = Hs / 2, W2 = Ws / 2;
+    o = ((((size_t)n * 4 + (Y & 1) * 2 + (X & 1)) * H2 + (Y >> 1)) * W2 + (X >> 1)) * C;
+  } else {
+    o = i * C;
+  }
+#pragma unroll
+  for (int c = 0; c < C; c += 8) Act<T>::store8(out + o + c, acc + c);
+}
+
+int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const float* state, const float* tsteps_dev,
+             void* out, int B, int T, int Hp, int Wp, int s_int, bool first, bool bf, bool phase, cudaStream_t s) {
+  size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
+  int grid = cdiv(total, 128);
+#define GATHER_LAUNCH(TT, F)                                                                             \
+  gather_kernel<TT, F><<<grid, 128, 0, s>>>(imgs, (const TT*)feats, state, tsteps_dev, (TT*)out, B, T, Hp, Wp, \
+                                            s_int, phase ? 1 : 0)
+  if (bf) { if (first) GATHER_LAUNCH(bf16, true); else GATHER_LAUNCH(bf16, false); }
+  else    { if (first) GATHER_LAUNCH(float, true); else GATHER_LAUNCH(float, false); }
+#undef GATHER_LAUNCH
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// IFBlock tail: tmp = F.interpolate(lastconv(feat), scale_factor=s, bilinear, align_corners=False);
+// flow += tmp[:, :4] * s; mask = tmp[:, 4:5]; feat = tmp[:, 5:]          (Appendix A.2)
+// low13: [N, Hp/s, Wp/s, 16] fp32 (13 used).  state: [N,Hp,Wp,16] fp32 = flow(4) mask(1) feat(8).
+// LAST: only flow + mask are needed downstream -> compact fm [N,Hp,Wp,8].
+template <bool LAST>
+__global__ void upsample_kernel(const float* __restrict__ low, float* __restrict__ state, float* __restrict__ fm,
+                                int N, int Hp, int Wp, int s, int first) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)N * Hp * Wp;
+  if (i >= total) return;
+  int x = (int)(i % Wp), y = (int)((i / Wp) % Hp), n = (int)(i / ((size_t)Wp * Hp));
+  const int Hl = Hp / s, Wl = Wp / s;
+  // area_pixel_compute_source_index(scale = 1/s, align_corners=False): max(0, (dst+0.5)/s - 0.5)
+  const float rs = 1.0f / (float)s;
+  float sy = fmaxf(rs * ((float)y + 0.5f) - 0.5f, 0.f);
+  float sx = fmaxf(rs * ((float)x + 0.5f) - 0.5f, 0.f);
+  int y0 = (int)sy, x0 = (int)sx;
+  int y1 = y0 + (y0 < Hl - 1 ? 1 : 0), x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
+  float ly = sy - (float)y0, lx = sx - (float)x0;
+  float hy = 1.f - ly, hx = 1.f - lx;
+  const float4* p00 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y0) * Wl + x0) * 16);
+  const float4* p01 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y0) * Wl + x1) * 16);
+  const float4* p10 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y1) * Wl + x0) * 16);
+  const float4* p11 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y1) * Wl + x1) * 16);
+  constexpr int NV = LAST ? 2 : 4;
+  float4 r[NV];
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    float4 a = __ldg(p00 + k), b = __ldg(p01 + k), c = __ldg(p10 + k), d = __ldg(p11 + k);
+    r[k].x = hy * (hx * a.x + lx * b.x) + ly * (hx * c.x + lx * d.x);
+    r[k].y = hy * (hx * a.y + lx * b.y) + ly * (hx * c.y + lx * d.y);
+    r[k].z = hy * (hx * a.z + lx * b.z) + ly * (hx * c.z + lx * d.z);
+    r[k].w = hy * (hx * a.w + lx * b.w) + ly * (hx * c.w + lx * d.w);
+  }
+  const float fs = (float)s;
+  float4 fl = make_float4(r[0].x * fs, r[0].y * fs, r[0].z * fs, r[0].w * fs);
+  float4* st = reinterpret_cast<float4*>(state + i * 16);
+  if (!first) {
+    float4 o = st[0];
+    fl.x += o.x; fl.y += o.y; fl.z += o.z; fl.w += o.w;
+  }
+  if constexpr (LAST) {
+    float4* f = reinterpret_cast<float4*>(fm + i * 8);
+    f[0] = fl;
+    f[1] = make_float4(r[1].x, 0.f, 0.f, 0.f);
+  } else {
+    st[0] = fl; st[1] = r[1]; st[2] = r[2]; st[3] = r[3];
+  }
+}
+int k_upsample(vfi_handle* h, const float* low13, float* state, float* fm, int N, int Hp, int Wp, int s_int,
+               bool first, bool last, cudaStream_t s) {
+  size_t total = (size_t)N * Hp * Wp;
+  if (last) upsample_kernel<true><<<cdiv(total, 256), 256, 0, s>>>(low13, state, fm, N, Hp, Wp, s_int, first ? 1 : 0);
+  else upsample_kernel<false><<<cdiv(total, 256), 256, 0, s>>>(low13, state, fm, N, Hp, Wp, s_int, first ? 1 : 0);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// IFNet tail + wrapper epilogue, fused (north_star kernel (b)):
+//   warped0 = warp(img0, flow[:, :2]); warped1 = warp(img1, flow[:, 2:4]); m = sigmoid(mask)
+//   merged = warped0*m + warped1*(1-m)                                   (Appendix A.2)
+//   unpad (base.py:227-229); (x*255).clip(0,255).astype(uint8) truncation (base.py:188-201)
+//   HUD composite frame[mask] = (f0 if t<0.5 else f1)[mask]              (adaptive_pipeline.py:399-409)
+// One thread per 4 output pixels: fm is read as 2x float4 per pixel, the u8 result is written as
+// three 32-bit words (12 B, 4-byte aligned when W % 4 == 0).
+__device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img1, const float* fmp, int x, int y,
+                                         int Hp, int Wp, float* o /*3*/, float4* flow_o) {
+  float4 fl = __ldg(reinterpret_cast<const float4*>(fmp));
+  float mk = __ldg(fmp + 4);
+  Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
+  Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
+  float a[3], c[3];
+  sample_rgbx(img0, b0, a);
+  sample_rgbx(img1, b1, c);
+  float m = 1.0f / (1.0f + expf(-mk));
+#pragma unroll
+  for (int k = 0; k < 3; k++) o[k] = a[k] * m + c[k] * (1.0f - m);
+  *flow_o = fl;
+}
+__device__ __forceinline__ uint8_t quant_u8(float v) {
+  v = fminf(fmaxf(v * 255.0f, 0.f), 255.f);
+  return (uint8_t)(int)v;  // truncation, as numpy astype(uint8)
+}
+__global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const float* __restrict__ fm,
+                                   const uint8_t* __restrict__ hud, const float* __restrict__ tsteps,
+                                   uint8_t* __restrict__ out, float* __restrict__ out_f32,
+                                   float* __restrict__ flow_out, int B, int Tn, int H, int W, int Hp, int Wp) {
+  const int W4 = (W + 3) / 4;
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)B * Tn * H * W4;
+  if (i >= total) return;
+  int xq = (int)(i % W4), y = (int)((i / W4) % H), n = (int)(i / ((size_t)W4 * H));
+  int b = n / Tn;
+  float t = tsteps[n % Tn];
+  const size_t plane = (size_t)Hp * Wp;
+  const uint8_t* img0 = imgs + (size_t)b * plane * 4;
+  const uint8_t* img1 = imgs + (size_t)(B + b) * plane * 4;
+  const uint8_t* hsrc = t < 0.5f ? img0 : img1;
+  uint8_t px[12];
+  int x0 = xq * 4;
+  int cnt = min(4, W - x0);
+  for (int k = 0; k < cnt; k++) {
+    int x = x0 + k;
+    float o[3];
+    float4 fl;
+    blend_px(img0, img1, fm + (((size_t)n * Hp + y) * Wp + x) * 8, x, y, Hp, Wp, o, &fl);
+    size_t opix = ((size_t)n * H + y) * W + x;
+    if (out_f32) { out_f32[opix * 3] = o[0]; out_f32[opix * 3 + 1] = o[1]; out_f32[opix * 3 + 2] = o[2]; }
+    if (flow_out) reinterpret_cast<float4*>(flow_out)[opix] = fl;
+    uint8_t r = quant_u8(o[0]), g = quant_u8(o[1]), bl = quant_u8(o[2]);
+    if (hud && hud[((size_t)b * H + y) * W + x]) {
+      uchar4 sp = __ldg(reinterpret_cast<const uchar4*>(hsrc) + (size_t)y * Wp + x);
+      r = sp.x; g = sp.y; bl = sp.z;
+    }
+    px[3 * k] = r; px[3 * k + 1] = g; px[3 * k + 2] = bl;
+  }
+  uint8_t* op = out + (((size_t)n * H + y) * W + x0) * 3;
+  if (cnt == 4 && (W & 3) == 0) {
+    uint32_t* o32 = reinterpret_cast<uint32_t*>(op);
+    o32[0] = px[0] | (px[1] << 8) | (px[2] << 16) | ((uint32_t)px[3] << 24);
+    o32[1] = px[4] | (px[5] << 8) | (px[6] << 16) | ((uint32_t)px[7] << 24);
+    o32[2] = px[8] | (px[9] << 8) | (px[10] << 16) | ((uint32_t)px[11] << 24);
+  } else {
+    for (int k = 0; k < 3 * cnt; k++) op[k] = px[k];
+  }
+}
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const float* fm, const uint8_t* hud, const float* tsteps_dev,
+                  uint8_t* out, float* out_f32, float* flow_out, int B, int T, int H, int W, int Hp, int Wp,
+                  cudaStream_t s) {
+  size_t total = (size_t)B * T * H * ((W + 3) / 4);
+  final_blend_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, fm, hud, tsteps_dev, out, out_f32, flow_out, B, T, H, W,
+                                                      Hp, Wp);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// flow [N,H,W,4] + mask [N,H,W] -> fm [N,Hp,Wp,8] (standalone vfi_warp_blend entry)
+__global__ void pack_fm_kernel(const float* __restrict__ flow, const float* __restrict__ mask, float* __restrict__ fm,
+                               int N, int H, int W, int Hp, int Wp) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)N * Hp * Wp;
+  if (i >= total) return;
+  int x = (int)(i % Wp), y = (int)((i / Wp) % Hp), n = (int)(i / ((size_t)Wp * Hp));
+  float4 fl = make_float4(0, 0, 0, 0);
+  float mk = 0.f;
+  if (x < W && y < H) {
+    size_t p = ((size_t)n * H + y) * W + x;
+    fl = reinterpret_cast<const float4*>(flow)[p];
+    mk = mask[p];
+  }
+  reinterpret_cast<float4*>(fm)[i * 2] = fl;
+  reinterpret_cast<float4*>(fm)[i * 2 + 1] = make_float4(mk, 0, 0, 0);
+}
+int k_pack_fm(vfi_handle* h, const float* flow, const float* mask, float* fm, int N, int H, int W, int Hp, int Wp,
+              cudaStream_t s) {
+  size_t total = (size_t)N * Hp * Wp;
+  pack_fm_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, mask, fm, N, H, W, Hp, Wp);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// test-hook conversions
+__global__ void f32_to_bf16_kernel(const float* s, bf16* d, size_t n) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < n) d[i] = __float2bfloat16(s[i]);
+}
+__global__ void bf16_to_f32_kernel(const bf16* s, float* d, size_t n) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < n) d[i] = __bfloat162float(s[i]);
+}
+int k_f32_to_act(vfi_handle* h, const float* src, void* dst, size_t n, bool bf, cudaStream_t s) {
+  if (bf) { f32_to_bf16_kernel<<<cdiv(n, 256), 256, 0, s>>>(src, (bf16*)dst, n); VFI_LAUNCHED(h); }
+  else VFI_CUDA(h, cudaMemcpyAsync(dst, src, n * 4, cudaMemcpyDeviceToDevice, s));
+  return 0;
+}
+int k_act_to_f32(vfi_handle* h, const void* src, float* dst, size_t n, bool bf, cudaStream_t s) {
+  if (bf) { bf16_to_f32_kernel<<<cdiv(n, 256), 256, 0, s>>>((const bf16*)src, dst, n); VFI_LAUNCHED(h); }
+  else VFI_CUDA(h, cudaMemcpyAsync(dst, src, n * 4, cudaMemcpyDeviceToDevice, s));
+  return 0;
+}
+// plain NHWC -> 4 stride-2 phase planes [N,4,H/2,W/2,C]
+__global__ void plain_to_phase_kernel(const bf16* __restrict__ s, bf16* __restrict__ d, int N, int H, int W, int C) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t total = (size_t)N * H * W * C;
+  if (i >= total) return;
+  int c = (int)(i % C);
+  size_t p = i / C;
+  int x = (int)(p % W), y = (int)((p / W) % H), n = (int)(p / ((size_t)W * H));
+  size_t o = ((((size_t)n * 4 + (y & 1) * 2 + (x & 1)) * (H / 2) + (y >> 1)) * (W / 2) + (x >> 1)) * C + c;
+  d[o] = s[i];
+}
+int k_plain_to_phase(vfi_handle* h, const bf16* src, bf16* dst, int N, int H, int W, int C, cudaStream_t s) {
+  size_t total = (size_t)N * H * W * C;
+  plain_to_phase_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, N, H, W, C);
+  VFI_LAUNCHED(h);
+  return 0;
+}
