@@ -1,0 +1,196 @@
+"""Thin host wrapper over the C ABI: one vfi_handle per CUDA device, torch tensors for device memory
+and streams only.  Every method launches the sm_100a kernels; nothing here computes on the CPU."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _abi
+from . import ifnet_params
+
+_ENGINES = {}
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Engine:
+    def __init__(self, device=0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("vfi_b200 needs an sm_100 CUDA device; there is no CPU fallback")
+        self.device = torch.device("cuda", device)
+        self._lib = _abi.lib()
+        h = C.c_void_p()
+        rc = self._lib.vfi_create(device, C.byref(h))
+        if rc != 0:
+            raise _abi.VFIError(f"vfi_create(device={device}) failed ({rc}): needs an sm_100 (B200) GPU")
+        self._h = h
+        self.weights_loaded = False
+
+    @staticmethod
+    def get(device=0):
+        if isinstance(device, torch.device):
+            device = device.index if device.index is not None else torch.cuda.current_device()
+        if device not in _ENGINES:
+            _ENGINES[device] = Engine(device)
+        return _ENGINES[device]
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.vfi_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    @property
+    def launches(self):
+        return int(self._lib.vfi_launch_count(self._h))
+
+    def _check(self, rc, what):
+        _abi.check(self._h, rc, what)
+
+    def _u8(self, x):
+        if isinstance(x, np.ndarray):
+            x = torch.from_numpy(np.ascontiguousarray(x))
+        if x.dtype != torch.uint8:
+            raise TypeError("expected uint8 frames")
+        return x.to(self.device, non_blocking=True).contiguous()
+
+    # ---- IFNet ---------------------------------------------------------------------------
+    def load_weights(self, state_dict, lrelu_slope=None):
+        flat = ifnet_params.flatten(state_dict)
+        slope = C.byref(C.c_float(lrelu_slope)) if lrelu_slope is not None else None
+        with torch.cuda.device(self.device):
+            rc = self._lib.vfi_ifnet_load_weights(self._h, flat.ctypes.data_as(C.c_void_p), flat.size,
+                                                  C.cast(slope, C.c_void_p) if slope is not None else C.c_void_p(0))
+        self._check(rc, "vfi_ifnet_load_weights")
+        self.weights_loaded = True
+
+    def infer(self, img0, img1, timesteps, scale=1.0, precision=_abi.PRECISION_BF16, hud_mask=None,
+              want_float=False, want_flow=False, out=None):
+        """img0/img1: (B,H,W,3) or (H,W,3) uint8 (numpy or torch).  Returns uint8 (B,T,H,W,3) on the GPU
+        (plus float frames / final flow when asked)."""
+        img0, img1 = self._u8(img0), self._u8(img1)
+        if img0.dim() == 3:
+            img0, img1 = img0[None], img1[None]
+        B, H, W, _ = img0.shape
+        ts = (C.c_float * len(timesteps))(*[float(t) for t in timesteps])
+        T = len(timesteps)
+        with torch.cuda.device(self.device):
+            if out is None:
+                out = torch.empty((B, T, H, W, 3), dtype=torch.uint8, device=self.device)
+            of = torch.empty((B, T, H, W, 3), dtype=torch.float32, device=self.device) if want_float else None
+            fl = torch.empty((B, T, H, W, 4), dtype=torch.float32, device=self.device) if want_flow else None
+            hm = self._u8(hud_mask) if hud_mask is not None else None
+            rc = self._lib.vfi_ifnet_infer(self._h, _ptr(img0), _ptr(img1), B, H, W, C.cast(ts, C.c_void_p), T,
+                                           float(scale), int(precision), _ptr(hm), _ptr(out), _ptr(of), _ptr(fl),
+                                           _stream())
+        self._check(rc, "vfi_ifnet_infer")
+        res = (out,)
+        if want_float:
+            res += (of,)
+        if want_flow:
+            res += (fl,)
+        return res if len(res) > 1 else out
+
+    def warp_blend(self, img0, img1, flow, mask, want_float=False):
+        img0, img1 = self._u8(img0), self._u8(img1)
+        N, H, W, _ = img0.shape
+        flow = flow.to(self.device, torch.float32).contiguous()
+        mask = mask.to(self.device, torch.float32).contiguous()
+        with torch.cuda.device(self.device):
+            out = torch.empty((N, H, W, 3), dtype=torch.uint8, device=self.device)
+            of = torch.empty((N, H, W, 3), dtype=torch.float32, device=self.device) if want_float else None
+            rc = self._lib.vfi_warp_blend(self._h, _ptr(img0), _ptr(img1), _ptr(flow), _ptr(mask), N, H, W,
+                                          _ptr(out), _ptr(of), _stream())
+        self._check(rc, "vfi_warp_blend")
+        return (out, of) if want_float else out
+
+    def debug_conv(self, layer, precision, x, residual=None):
+        x = x.to(self.device, torch.float32).contiguous()
+        N, Hin, Win, _ = x.shape
+        from .ifnet_layers import layer_out_shape
+        oshape = layer_out_shape(layer, N, Hin, Win)
+        with torch.cuda.device(self.device):
+            y = torch.zeros(oshape, dtype=torch.float32, device=self.device)
+            r = residual.to(self.device, torch.float32).contiguous() if residual is not None else None
+            rc = self._lib.vfi_debug_conv(self._h, layer, precision, _ptr(x), N, Hin, Win, _ptr(r), _ptr(y), _stream())
+        self._check(rc, "vfi_debug_conv")
+        return y
+
+    # ---- metrics / routing reductions ----------------------------------------------------
+    def psnr_sse(self, a, b):
+        """Exact integer SSE per frame pair.  a, b: (n, ...) uint8, same shape."""
+        a, b = self._u8(a), self._u8(b)
+        n = a.shape[0]
+        elems = a[0].numel()
+        with torch.cuda.device(self.device):
+            sse = torch.empty(n, dtype=torch.int64, device=self.device)
+            ps = torch.empty(n, dtype=torch.float64, device=self.device)
+            rc = self._lib.vfi_psnr_u8(self._h, _ptr(a), _ptr(b), n, elems, _ptr(sse), _ptr(ps), _stream())
+        self._check(rc, "vfi_psnr_u8")
+        return sse, ps
+
+    def ssim(self, a, b, downscale=1):
+        a, b = self._u8(a), self._u8(b)
+        n, H, W, _ = a.shape
+        with torch.cuda.device(self.device):
+            out = torch.empty(n, dtype=torch.float64, device=self.device)
+            rc = self._lib.vfi_ssim_gray_u8(self._h, _ptr(a), _ptr(b), n, H, W, downscale, _ptr(out), _stream())
+        self._check(rc, "vfi_ssim_gray_u8")
+        return out
+
+    def flow_stats(self, flow):
+        """flow: (n,H,W,2) float32 -> (n,3) float64 [mean, max, std]."""
+        if isinstance(flow, np.ndarray):
+            flow = torch.from_numpy(np.ascontiguousarray(flow))
+        flow = flow.to(self.device, torch.float32, non_blocking=True).contiguous()
+        n, H, W, _ = flow.shape
+        with torch.cuda.device(self.device):
+            out = torch.empty((n, 3), dtype=torch.float64, device=self.device)
+            rc = self._lib.vfi_flow_stats(self._h, _ptr(flow), n, H, W, _ptr(out), _stream())
+        self._check(rc, "vfi_flow_stats")
+        return out
+
+    def laplacian_var(self, rgb):
+        rgb = self._u8(rgb)
+        n, H, W, _ = rgb.shape
+        with torch.cuda.device(self.device):
+            out = torch.empty(n, dtype=torch.float64, device=self.device)
+            rc = self._lib.vfi_laplacian_var(self._h, _ptr(rgb), n, H, W, _ptr(out), _stream())
+        self._check(rc, "vfi_laplacian_var")
+        return out
+
+
+class HudState:
+    """Device-resident ring of 180x320 gray thumbnails + the current mask (AdaptiveRouter.frame_history)."""
+
+    def __init__(self, engine, hist_len=10, var_threshold=10.0):
+        self.e = engine
+        self.hist_len = hist_len
+        self.var_threshold = float(var_threshold)
+        self.count = C.c_longlong(0)
+        self.ring = torch.zeros((hist_len, 180, 320), dtype=torch.uint8, device=engine.device)
+        self.mask = None
+        self.coverage = None
+
+    def __len__(self):
+        return min(int(self.count.value), self.hist_len)
+
+    def update(self, rgb):
+        rgb = self.e._u8(rgb)
+        H, W, _ = rgb.shape
+        with torch.cuda.device(self.e.device):
+            mask = torch.empty((H, W), dtype=torch.uint8, device=self.e.device)
+            cov = torch.empty(1, dtype=torch.float64, device=self.e.device)
+            rc = self.e._lib.vfi_hud_update(self.e._h, _ptr(rgb), H, W, _ptr(self.ring), self.hist_len,
+                                            C.byref(self.count), self.var_threshold, _ptr(mask), _ptr(cov), _stream())
+        self.e._check(rc, "vfi_hud_update")
+        self.mask, self.coverage = mask, cov
+        return mask, cov

@@ -1,0 +1,104 @@
+"""PSNR / SSIM of the reference's evaluation/metrics.py, computed by the B200 reduction kernels.
+
+compute_psnr_simple (reference :299-315) and compute_ssim_simple (:318-335) keep their signatures and
+results: PSNR from the exact integer sum of squared differences (so the float64 arithmetic that follows
+is numpy's own and the value is bit-identical), SSIM = skimage structural_similarity on the cv2 gray
+images (7x7 uniform window) to ~1e-12.  QualityEvaluator / QualityResults (:88-258) keep their surface;
+psnr/ssim are served by the kernels, the pyiqa-only metrics (lpips, ms_ssim, flolpips) are out of scope
+and reported as None / NaN.  Batched variants (psnr_batch / ssim_batch) are the throughput entry points.
+"""
+import dataclasses
+from typing import Dict, List, Optional
+
+import cv2
+import numpy as np
+import torch
+
+from ..engine import Engine
+
+
+def _match(pred: np.ndarray, gt: np.ndarray) -> np.ndarray:
+    if pred.shape != gt.shape:
+        pred = cv2.resize(pred, (gt.shape[1], gt.shape[0]))  # same default INTER_LINEAR as the reference
+    return pred
+
+
+def _psnr_from_sse(sse: int, n: int) -> float:
+    mse = np.float64(sse) / n          # == np.mean of the exact integer squares
+    if mse == 0:
+        return float('inf')
+    return float(10 * np.log10(255.0 ** 2 / mse))
+
+
+def compute_psnr_simple(pred: np.ndarray, gt: np.ndarray) -> float:
+    pred = _match(pred, gt)
+    sse, _ = Engine.get().psnr_sse(pred[None], gt[None])
+    return _psnr_from_sse(int(sse[0]), pred.size)
+
+
+def compute_ssim_simple(pred: np.ndarray, gt: np.ndarray) -> float:
+    pred = _match(pred, gt)
+    if pred.ndim == 2:                 # already gray: replicate so the integer gray conversion is the identity
+        pred, gt = (np.repeat(a[..., None], 3, axis=2) for a in (pred, gt))
+    return float(Engine.get().ssim(pred[None], gt[None], downscale=1)[0])
+
+
+def psnr_batch(pred, gt, device=0) -> np.ndarray:
+    """(n,H,W,3) uint8 numpy / CUDA tensors -> n PSNR values (float64, inf for identical frames)."""
+    sse, _ = Engine.get(device).psnr_sse(pred, gt)
+    n = int(np.prod(pred.shape[1:]))
+    return np.array([_psnr_from_sse(int(s), n) for s in sse.tolist()], dtype=np.float64)
+
+
+def ssim_batch(pred, gt, device=0) -> np.ndarray:
+    return Engine.get(device).ssim(pred, gt, downscale=1).cpu().numpy()
+
+
+@dataclasses.dataclass
+class QualityResults:
+    psnr: float
+    ssim: float
+    lpips: float
+    ms_ssim: Optional[float] = None
+    flolpips: Optional[float] = None
+    psnr_per_frame: Optional[List[float]] = None
+    lpips_per_frame: Optional[List[float]] = None
+
+    def to_dict(self) -> dict:
+        return {'psnr': self.psnr, 'ssim': self.ssim, 'lpips': self.lpips, 'ms_ssim': self.ms_ssim,
+                'flolpips': self.flolpips}
+
+
+class QualityEvaluator:
+    """Reference surface (evaluation/metrics.py:111-258).  psnr / ssim come from the kernels (the
+    definitions of compute_*_simple, which is also what the reference driver falls back to at
+    scripts/run_benchmarks.py:174-178 when pyiqa is unavailable); lpips / ms_ssim / flolpips need pyiqa's
+    networks and are not provided."""
+
+    def __init__(self, device: str = 'cuda'):
+        self.device = device
+        self._initialized = False
+
+    def _ensure_initialized(self):
+        if not self._initialized:
+            Engine.get()
+            self._initialized = True
+
+    def evaluate_pair(self, pred: np.ndarray, gt: np.ndarray) -> Dict[str, float]:
+        self._ensure_initialized()
+        return {'psnr': compute_psnr_simple(pred, gt), 'ssim': compute_ssim_simple(pred, gt), 'lpips': float('nan')}
+
+    def evaluate(self, pred_frames: List[np.ndarray], gt_frames: List[np.ndarray]) -> QualityResults:
+        self._ensure_initialized()
+        if len(pred_frames) != len(gt_frames):
+            raise ValueError(f"Number of predicted frames ({len(pred_frames)}) "
+                             f"doesn't match ground truth ({len(gt_frames)})")
+        same = len({f.shape for f in pred_frames} | {f.shape for f in gt_frames}) == 1
+        if same and pred_frames:
+            p, g = np.stack(pred_frames), np.stack(gt_frames)
+            ps, ss = psnr_batch(p, g).tolist(), ssim_batch(p, g).tolist()
+        else:
+            ps = [compute_psnr_simple(a, b) for a, b in zip(pred_frames, gt_frames)]
+            ss = [compute_ssim_simple(a, b) for a, b in zip(pred_frames, gt_frames)]
+        return QualityResults(psnr=float(np.mean(ps)), ssim=float(np.mean(ss)), lpips=float('nan'),
+                              psnr_per_frame=ps, lpips_per_frame=[float('nan')] * len(ps))

@@ -1,0 +1,269 @@
+"""AdaptiveVFI routing + RIFE fast path behind the reference's AdaptivePipeline interface.
+
+Drop-in for the reference's models/novel/adaptive_pipeline.py: ContentAnalysis :30-40, RoutingStats
+:43-71, AdaptiveRouter :74-286 (same six constructor thresholds :81-96, same public methods and
+state), AdaptivePipeline :289-483.  The per-pair statistics run as reduction kernels through the
+C ABI: scene-cut SSIM (vfi_ssim_gray_u8, downscale 4), |flow| mean/max/std (vfi_flow_stats),
+Laplacian variance (vfi_laplacian_var), HUD temporal-variance mask (vfi_hud_update); the decision
+tree is vfi_route_decide.  The dense flow field itself still comes from OpenCV's Farneback, called
+with the reference's parameters (:119-128) and uploaded -- SURVEY.md §8(f) row N1.
+Fixes kept minimal: the RIFE / VFIMamba imports point at models/sota.
+"""
+import dataclasses
+import time
+from collections import deque
+from typing import List, Optional, Tuple
+
+import cv2
+import numpy as np
+import torch
+
+from ..base import BaseModel, InferenceResult, ModelInfo
+from ... import _abi
+from ...engine import Engine, HudState
+
+
+@dataclasses.dataclass
+class ContentAnalysis:
+    motion_mean: float
+    motion_max: float
+    motion_std: float
+    has_particles: bool
+    is_scene_change: bool
+    hud_coverage: float
+    recommended_model: str
+    confidence: float
+
+
+@dataclasses.dataclass
+class RoutingStats:
+    total: int = 0
+    rife_count: int = 0
+    vfimamba_count: int = 0
+    scene_change_count: int = 0
+
+    def add(self, model: str):
+        self.total += 1
+        field = {'rife': 'rife_count', 'vfimamba': 'vfimamba_count', 'scene_change': 'scene_change_count'}.get(model)
+        if field:
+            setattr(self, field, getattr(self, field) + 1)
+
+    def to_dict(self) -> dict:
+        if not self.total:
+            return {'total': 0}
+        pct = lambda n: n / self.total * 100
+        return {'total': self.total, 'rife': self.rife_count, 'rife_pct': pct(self.rife_count),
+                'vfimamba': self.vfimamba_count, 'vfimamba_pct': pct(self.vfimamba_count),
+                'scene_change': self.scene_change_count, 'scene_change_pct': pct(self.scene_change_count)}
+
+
+def farneback_flow(frame0: np.ndarray, frame1: np.ndarray) -> np.ndarray:
+    """Dense flow source (third-party OpenCV, reference parameters adaptive_pipeline.py:119-128)."""
+    g0 = cv2.cvtColor(frame0, cv2.COLOR_RGB2GRAY)
+    g1 = cv2.cvtColor(frame1, cv2.COLOR_RGB2GRAY)
+    return cv2.calcOpticalFlowFarneback(g0, g1, None, pyr_scale=0.5, levels=3, winsize=15, iterations=3,
+                                        poly_n=5, poly_sigma=1.2, flags=0)
+
+
+class AdaptiveRouter:
+    """Analyses a frame pair and recommends a model; statistics are computed on the GPU."""
+
+    def __init__(self, motion_threshold_low: float = 5.0, motion_threshold_high: float = 25.0,
+                 scene_change_threshold: float = 0.65, particle_threshold: float = 0.4,
+                 hud_variance_threshold: float = 10.0, hud_history_frames: int = 10, *, device=None, flow_fn=None):
+        self.motion_threshold_low = motion_threshold_low
+        self.motion_threshold_high = motion_threshold_high
+        self.scene_change_threshold = scene_change_threshold
+        self.particle_threshold = particle_threshold
+        self.hud_variance_threshold = hud_variance_threshold
+        self.hud_history_frames = hud_history_frames
+        self.hud_mask: Optional[np.ndarray] = None
+        self._device = device
+        self._flow_fn = flow_fn or farneback_flow
+        self._engine = None
+        self._hud = None
+        self._hud_mask_dev = None
+        self._last = {}
+
+    # -- plumbing ------------------------------------------------------------------------
+    @property
+    def engine(self) -> Engine:
+        if self._engine is None:
+            self._engine = Engine.get(self._device if self._device is not None else 0)
+        return self._engine
+
+    def _hud_state(self) -> HudState:
+        if self._hud is None:
+            self._hud = HudState(self.engine, self.hud_history_frames, self.hud_variance_threshold)
+        return self._hud
+
+    @property
+    def frame_history(self) -> deque:
+        """The last <= hud_history_frames gray 320x180 thumbnails, oldest first (reference :105)."""
+        d = deque(maxlen=self.hud_history_frames)
+        if self._hud is not None:
+            n, c, L = len(self._hud), int(self._hud.count.value), self.hud_history_frames
+            ring = self._hud.ring.cpu().numpy()
+            for k in range(c - n, c):
+                d.append(ring[k % L])
+        return d
+
+    def _dev(self, frame):
+        return self.engine._u8(frame)
+
+    # -- the reference's public methods ----------------------------------------------------
+    def compute_motion(self, frame0: np.ndarray, frame1: np.ndarray) -> Tuple[float, float, float, np.ndarray]:
+        """(mean, max, std, |flow| map) -- reference :108-138."""
+        flow = torch.from_numpy(self._flow_fn(frame0, frame1)).to(self.engine.device)
+        st = self.engine.flow_stats(flow[None])[0].tolist()
+        mag = torch.sqrt(flow[..., 0] ** 2 + flow[..., 1] ** 2).cpu().numpy()
+        return st[0], st[1], st[2], mag
+
+    def detect_scene_change(self, frame0: np.ndarray, frame1: np.ndarray) -> Tuple[bool, float]:
+        """SSIM of the quarter-resolution gray pair < threshold -- reference :140-160."""
+        score = float(self.engine.ssim(self._dev(frame0)[None], self._dev(frame1)[None], downscale=4)[0])
+        return score < self.scene_change_threshold, score
+
+    def detect_particles(self, frame0: np.ndarray, flow_magnitude, flow_std: float) -> Tuple[bool, float]:
+        """sqrt(min(std/20,1) * min(var(Laplacian)/500,1)) > threshold -- reference :162-191."""
+        lv = float(self.engine.laplacian_var(self._dev(frame0)[None])[0])
+        self._last['laplacian_var'] = lv
+        _, _, hp, ps = _abi.route_decide(1.0, 0.0, 0.0, flow_std, lv, 0.0, self.particle_threshold, 1.0, 1e300)
+        return hp, ps
+
+    def detect_hud(self, frame: np.ndarray) -> Tuple[np.ndarray, float]:
+        """Static-region mask from the variance of the last five thumbnails -- reference :193-235."""
+        mask, cov = self._hud_state().update(self._dev(frame))
+        cov = float(cov[0])
+        if len(self._hud) < 5:
+            # the reference returns zeros here WITHOUT touching self.hud_mask (:207-209)
+            return np.zeros(frame.shape[:2], dtype=bool), 0.0
+        self._hud_mask_dev = mask
+        self.hud_mask = mask.cpu().numpy().astype(bool)
+        return self.hud_mask, cov
+
+    def analyze(self, frame0: np.ndarray, frame1: np.ndarray) -> ContentAnalysis:
+        """Scene cut (early return) -> motion -> particles -> HUD -> decision tree (reference :237-286)."""
+        e = self.engine
+        d0, d1 = self._dev(frame0), self._dev(frame1)
+        score = float(e.ssim(d0[None], d1[None], downscale=4)[0])
+        if score < self.scene_change_threshold:
+            return ContentAnalysis(0, 0, 0, False, True, 0, 'scene_change', 1.0 - score)
+        flow = self._flow_fn(frame0, frame1)
+        st = e.flow_stats(torch.from_numpy(flow)[None])
+        lv = e.laplacian_var(d0[None])
+        mean, mx, std = st[0].tolist()
+        lv = float(lv[0])
+        _, hud_cov = self._detect_hud_dev(d0, frame0.shape[:2])
+        route, conf, hp, ps = _abi.route_decide(score, mean, mx, std, lv, self.scene_change_threshold,
+                                                self.particle_threshold, self.motion_threshold_low,
+                                                self.motion_threshold_high)
+        self._last = {'ssim': score, 'laplacian_var': lv, 'particle_score': ps}
+        return ContentAnalysis(motion_mean=mean, motion_max=mx, motion_std=std, has_particles=hp,
+                               is_scene_change=False, hud_coverage=hud_cov,
+                               recommended_model=_abi.ROUTE_NAMES[route], confidence=conf)
+
+    def _detect_hud_dev(self, dframe, shape):
+        mask, cov = self._hud_state().update(dframe)
+        if len(self._hud) < 5:
+            return None, 0.0
+        self._hud_mask_dev = mask
+        self.hud_mask = None            # host copy made lazily by hud_mask_host()
+        return mask, float(cov[0])
+
+    def hud_mask_host(self):
+        if self.hud_mask is None and self._hud_mask_dev is not None:
+            self.hud_mask = self._hud_mask_dev.cpu().numpy().astype(bool)
+        return self.hud_mask
+
+
+class AdaptivePipeline(BaseModel):
+    """Routes pairs by content; RIFE fast path on the B200 kernels; HUD pixels copied from the nearer input."""
+
+    def __init__(self, device: str = 'cuda', motion_threshold_low: float = 5.0, motion_threshold_high: float = 25.0,
+                 enable_vfimamba: bool = True, sr_model_name: str = 'lanczos'):
+        super().__init__(device)
+        self.enable_vfimamba = enable_vfimamba
+        self.sr_model_name = sr_model_name
+        self.router = AdaptiveRouter(motion_threshold_low=motion_threshold_low,
+                                     motion_threshold_high=motion_threshold_high,
+                                     device=self.device if self.device.type == 'cuda' else None)
+        self.stats = RoutingStats()
+        self._rife = None
+        self._vfimamba = None
+        self._sr = None
+
+    @property
+    def info(self) -> ModelInfo:
+        return ModelInfo(name='AdaptivePipeline', type='novel', supports_vfi=True, supports_sr=True,
+                         supports_joint=False, parameters=27_700_000, requires_gpu=True,
+                         description="Novel adaptive routing: fast RIFE for easy content, quality VFIMamba for hard content")
+
+    def load(self) -> None:
+        print("Loading Adaptive Pipeline...")
+        from ..sota.rife_wrapper import RIFEModel
+        self._rife = RIFEModel(device=str(self.device))
+        self._rife.load()
+        if self.enable_vfimamba:
+            try:
+                from ..sota.vfimamba_wrapper import VFIMambaModel  # not part of this build: falls back below
+                self._vfimamba = VFIMambaModel(device=str(self.device))
+                self._vfimamba.load()
+            except Exception as e:  # same fallback as the reference (:358-361)
+                print(f"Warning: Could not load VFIMamba: {e}")
+                print("Will use RIFE for all frames")
+                self.enable_vfimamba = False
+        self._loaded = True
+        print("Adaptive Pipeline ready")
+
+    def interpolate(self, frame0: np.ndarray, frame1: np.ndarray, num_frames: int = 3,
+                    timestamps: Optional[List[float]] = None) -> List[np.ndarray]:
+        self.ensure_loaded()
+        analysis = self.router.analyze(frame0, frame1)
+        if analysis.is_scene_change:
+            self.stats.add('scene_change')
+            return [frame0.copy() for _ in range(num_frames)]
+        use_hud = analysis.hud_coverage > 0.01 and self.router._hud_mask_dev is not None
+        if analysis.recommended_model == 'vfimamba' and self.enable_vfimamba:
+            self.stats.add('vfimamba')
+            out = self._vfimamba.interpolate(frame0, frame1, num_frames, timestamps)
+            if use_hud:  # foreign model: composite on its host frames (reference :399-409)
+                ts = timestamps if timestamps is not None else self._rife.get_default_timestamps(num_frames)
+                m = self.router.hud_mask_host()
+                for fr, t in zip(out, ts):
+                    fr[m] = (frame0 if t < 0.5 else frame1)[m]
+            return out
+        self.stats.add('rife')
+        ts = timestamps if timestamps is not None else self._rife.get_default_timestamps(num_frames)
+        return self._rife._interpolate_masked(frame0, frame1, ts, self.router._hud_mask_dev if use_hud else None)
+
+    def upscale(self, frame: np.ndarray, scale: float = 1.333) -> np.ndarray:
+        h, w = frame.shape[:2]
+        return cv2.resize(frame, (int(w * scale), int(h * scale)), interpolation=cv2.INTER_LANCZOS4)
+
+    def process_pair(self, frame0: np.ndarray, frame1: np.ndarray, num_intermediate: int = 3,
+                     target_scale: float = 1.333) -> InferenceResult:
+        """Analyse (for extra_info) + adaptive interpolate (analyses again, as the reference :443,:382) + upscale."""
+        self.ensure_loaded()
+        if torch.cuda.is_available():
+            torch.cuda.reset_peak_memory_stats()
+        t0 = time.perf_counter()
+        analysis = self.router.analyze(frame0, frame1)
+        mids = self.interpolate(frame0, frame1, num_intermediate)
+        frames = [self.upscale(f, target_scale) for f in [frame0, *mids, frame1]]
+        ms = (time.perf_counter() - t0) * 1000
+        peak = torch.cuda.max_memory_allocated() / 1e6 if torch.cuda.is_available() else 0
+        return InferenceResult(frames=frames, inference_time_ms=ms, vram_peak_mb=peak, model_used=self.info.name,
+                               extra_info={'analysis': {'motion_mean': analysis.motion_mean,
+                                                        'motion_max': analysis.motion_max,
+                                                        'has_particles': analysis.has_particles,
+                                                        'is_scene_change': analysis.is_scene_change,
+                                                        'hud_coverage': analysis.hud_coverage,
+                                                        'recommended_model': analysis.recommended_model},
+                                           'routing_stats': self.stats.to_dict()})
+
+    def get_stats(self) -> dict:
+        return self.stats.to_dict()
+
+    def reset_stats(self) -> None:
+        self.stats = RoutingStats()
