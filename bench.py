@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""bench.py -- interpolated 1080p frames/s, RIFE v4.25 4x (t = 0.25/0.5/0.75), bf16, synthetic clip.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            (N > 1: launched under torchrun)
+    python bench.py --impl reference ...                           (CPU oracle on the host cores)
+
+One "step" = one pass of the hot path over one batch of `--pairs` frame pairs x 3 timesteps
+(BASELINE.json configs[1]; K*pairs = 300 pairs by default).  `value` is device-timed with the clip
+resident in HBM; `e2e` goes through RIFEModel.interpolate_batch with pinned HOST buffers (H2D + D2H
+inside the timed region).  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W = 1080, 1920
+TIMESTEPS = [0.25, 0.5, 0.75]
+METRIC = "interpolated_1080p_frames_per_sec_rife_4x"
+UNIT = "frames/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops", 1590.0), d.get("bf16_tflops_sustained", 1400.0), "measured"
+    return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+def tc_flops_per_batch(B, T, Hp, Wp):
+    """Algorithmic (dense, unpadded channels) FLOPs of every tcgen05 conv launch of one batch."""
+    from vfi_b200.ifnet_layers import layer_info
+    from vfi_b200.ifnet_params import BLOCK_C
+    fl = 0
+    for layer in (1, 2):  # Head cnn1/cnn2 on 2B images at half resolution
+        li = layer_info(layer)
+        fl += 2 * 2 * B * (Hp // 2) * (Wp // 2) * 9 * li["cin"] * li["cout"]
+    for b in range(5):
+        s = 16 >> b
+        hs, ws = Hp // s, Wp // s
+        base = 4 + 11 * b
+        n = B * T
+        li = layer_info(base)
+        fl += 2 * n * (hs // 2) * (ws // 2) * 9 * li["cin"] * li["cout"]
+        li = layer_info(base + 1)
+        fl += 2 * n * (hs // 4) * (ws // 4) * 9 * li["cin"] * li["cout"]
+        c = BLOCK_C[b]
+        fl += 8 * 2 * n * (hs // 4) * (ws // 4) * 9 * c * c
+        fl += 2 * n * (hs // 2) * (ws // 2) * 4 * c * 52  # ConvTranspose 4x4 s2: 4 taps per output pixel
+    return fl
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.idx = gpu_index
+        self.rows = []
+        self.stop = threading.Event()
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([x.strip() for x in o.split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) >= 6 and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def run_reference(args, rank, world):
+    """The reference's own CPU path for this hot path = the oracle restatement (the reference's IFNet lives in a
+    missing submodule; nothing of it can be installed).  One step = one Model.inference (1 pair, 1 timestep)."""
+    if rank != 0:
+        return
+    from oracle import ifnet_ref
+    import vfi_b200  # noqa: F401
+    from vfi_b200 import ifnet_params
+    from vfi_b200.synth import gen_clip
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    m = ifnet_ref.Model()
+    m.flownet.load_state_dict(ifnet_params.random_init(1234), strict=True)
+    fr = gen_clip(2, H, W, seed=1, cut_every=0, fast=None)
+    i0 = ifnet_ref.pad_reflect(ifnet_ref.to_tensor(fr[0]), 64)
+    i1 = ifnet_ref.pad_reflect(ifnet_ref.to_tensor(fr[1]), 64)
+
+    def step(k):
+        mid = m.inference(i0, i1, timestep=TIMESTEPS[k % 3], scale=1.0)[:, :, :H, :W]
+        return ifnet_ref.to_numpy_u8(mid)
+
+    for k in range(args.warmup):
+        step(k)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(k)
+    dt = time.perf_counter() - t0
+    v = args.steps / dt
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1000, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "RIFE v4.25 4x, 1080p synthetic clip, CPU oracle (reference IFNet source is a missing "
+                               "third-party submodule); one step = one inference (1 pair, 1 timestep)"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{args.steps} inferences of one 1080p pair, torch fp32, {cores} threads"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=75)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--pairs", type=int, default=4, help="frame pairs per step (batch)")
+    ap.add_argument("--pool", type=int, default=24, help="unique synthetic pairs resident in HBM")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch.distributed as dist
+    import vfi_b200  # noqa: F401
+    from vfi_b200 import _abi
+    from vfi_b200.models.sota.rife_wrapper import RIFEModel
+    from vfi_b200.synth import gen_clip
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    model = RIFEModel(device=f"cuda:{local}", precision=args.precision)
+    model.load()
+    eng = model._engine
+    B, T = args.pairs, len(TIMESTEPS)
+    # each rank works on its own shard of the clip (frame-pair sharding, no data-path collective)
+    clip = gen_clip(args.pool, H, W, seed=1 + rank, cut_every=0, fast=None)
+    f0_host = torch.from_numpy(clip[:-1]).pin_memory()
+    f1_host = torch.from_numpy(clip[1:]).pin_memory()
+    f0_dev, f1_dev = f0_host.to(dev), f1_host.to(dev)
+    out_dev = torch.empty((B, T, H, W, 3), dtype=torch.uint8, device=dev)
+    out_host = torch.empty((B, T, H, W, 3), dtype=torch.uint8).pin_memory()
+    prec = _abi.PRECISION_BF16 if args.precision == "bf16" else _abi.PRECISION_FP32
+
+    def batch_idx(k):
+        s = (k * B) % (args.pool - B + 1) if args.pool > B else 0
+        return slice(s, s + B)
+
+    def step_resident(k):
+        sl = batch_idx(k)
+        eng.infer(f0_dev[sl], f1_dev[sl], TIMESTEPS, 1.0, prec, out=out_dev)
+
+    def step_e2e(k):
+        sl = batch_idx(k)
+        a = f0_host[sl].to(dev, non_blocking=True)
+        b = f1_host[sl].to(dev, non_blocking=True)
+        o = model.interpolate_batch(a, b, TIMESTEPS, device_out=True)
+        out_host.copy_(o, non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for k in range(warmup):
+            fn(k)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = eng.launches
+        e0.record()
+        for k in range(steps):
+            fn(warmup + k)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms[0]), eng.launches - l0
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms, launches = timed(step_resident, args.steps, max(args.warmup, 3))
+    if rank == 0:
+        sampler.stop.set()
+    frames_per_step = B * T
+    value = world * frames_per_step * args.steps / (ms / 1000.0)
+
+    e2e_steps = max(3, min(args.steps, 25))
+    ms_e2e, _ = timed(step_e2e, e2e_steps, 3)
+    e2e = world * frames_per_step * e2e_steps / (ms_e2e / 1000.0)
+
+    # per-kernel-class device time over a profiled replay of the same steps (events around every launch)
+    roof = None
+    breakdown = None
+    if rank == 0:
+        eng.profile(True)
+        psteps = min(args.steps, 10)
+        for k in range(psteps):
+            step_resident(k)
+        prof = eng.profile_read()
+        eng.profile(False)
+        hbm, tf_burst, tf_sust, src = peaks()
+        tot = sum(v[0] for v in prof.values())
+        breakdown = {k: {"ms_per_step": v[0] / psteps, "launches_per_step": v[1] / psteps,
+                         "share": v[0] / tot if tot else 0} for k, v in prof.items() if v[1]}
+        tc_ms, tc_n = prof["conv_tcgen05"]
+        if tc_n and args.precision == "bf16":
+            fl = tc_flops_per_batch(B, T, 1088, 1920) * psteps
+            ach = fl / (tc_ms / 1000.0) / 1e12
+            roof = {"kernel": "conv_tc_kernel (all tcgen05 implicit-GEMM conv launches)", "bound": "tensor",
+                    "achieved": ach, "peak": tf_sust, "unit": "TFLOP/s", "frac": ach / tf_sust, "traffic": None,
+                    "peak_source": f"{src} bf16_tflops_sustained", "launches": tc_n // psteps,
+                    "avg_launch_us": tc_ms / tc_n * 1000.0,
+                    "algorithmic_gflop_per_step": fl / psteps / 1e9}
+            wb_ms, wb_n = prof["warp_blend"]
+            if wb_n:
+                by = B * T * H * W * (6 + 20 + 3)
+                roof["warp_blend"] = {"bound": "hbm", "achieved": by * psteps / (wb_ms / 1000.0) / 1e9, "peak": hbm,
+                                      "unit": "GB/s", "frac": by * psteps / (wb_ms / 1000.0) / 1e9 / hbm,
+                                      "bytes_per_px": 29}
+
+    cpu_base = None
+    if rank == 0 and not args.no_cpu_baseline:
+        from oracle import ifnet_ref
+        from vfi_b200 import ifnet_params
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        m = ifnet_ref.Model()
+        m.flownet.load_state_dict(ifnet_params.random_init(1234), strict=True)
+        i0 = ifnet_ref.pad_reflect(ifnet_ref.to_tensor(clip[0]), 64)
+        i1 = ifnet_ref.pad_reflect(ifnet_ref.to_tensor(clip[1]), 64)
+        m.inference(i0, i1, 0.5, 1.0)
+        n = 0
+        t0 = time.perf_counter()
+        while n < 6 or (time.perf_counter() - t0 < 10 and n < 24):
+            ifnet_ref.to_numpy_u8(m.inference(i0, i1, TIMESTEPS[n % 3], 1.0)[:, :, :H, :W])
+            n += 1
+        dt = time.perf_counter() - t0
+        cpu_base = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+                    "sample": f"{n} oracle inferences (1080p, fp32, {cores} torch threads) of the same clip"}
+
+    if rank == 0:
+        sampler.join(timeout=2)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": "RIFE v4.25 4x (t=0.25/0.5/0.75) on a synthetic 1080p clip, random-init weights "
+                                   "(BASELINE.json configs[1])",
+                       "pairs_per_step": B, "frames_per_step": frames_per_step, "pool_pairs": args.pool,
+                       "resolution": [H, W], "padded": [1088, 1920], "parallelism": f"frame-pair sharding x{world}",
+                       "l2_policy": "inputs+activations per step (>1 GB) exceed the 126 MB L2; batches rotate through the pool"},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(B * 2 * H * W * 3),
+                    "d2h_bytes_per_step": int(B * T * H * W * 3), "steps": e2e_steps,
+                    "api": "RIFEModel.interpolate_batch (pinned host uint8 in, pinned host uint8 out)"},
+            "gpu_launches": int(launches),
+            "clocks": sampler.summary(),
+            "roofline": roof, "kernel_breakdown": breakdown, "cpu_baseline": cpu_base,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -117,6 +117,14 @@ int vfi_route_decide(double ssim_score, double motion_mean, double motion_max, d
 int vfi_debug_conv(vfi_handle* h, int layer, int precision, const float* x, int N, int Hin, int Win,
                    const float* residual, float* y, void* stream);
 
+/* Per-kernel-class device timing for bench.py's roofline block.  While enabled every kernel launch is
+ * bracketed by CUDA events on its stream; vfi_profile_read synchronises, returns summed milliseconds and
+ * launch counts per class (0 pad, 1 head_cnn0, 2 conv_tcgen05, 3 conv_direct, 4 deconv_direct, 5 gather,
+ * 6 upsample, 7 warp_blend, 8 reduce, 9 misc) and clears the log. */
+#define VFI_PROFILE_CLASSES 10
+int vfi_profile_enable(vfi_handle* h, int on);
+int vfi_profile_read(vfi_handle* h, double* ms, long long* counts, int ncat);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,6 +11,8 @@ PRECISION_FP32, PRECISION_BF16 = 0, 1
 ROUTE_RIFE, ROUTE_VFIMAMBA, ROUTE_SCENE_CHANGE = 0, 1, 2
 ROUTE_NAMES = ("rife", "vfimamba", "scene_change")
 IFNET_PARAMS = 5664776
+PROFILE_CLASSES = ("pad", "head_cnn0", "conv_tcgen05", "conv_direct", "deconv_direct", "gather", "upsample",
+                   "warp_blend", "reduce", "misc")
 
 _vp, _i, _f, _d, _sz, _ll = C.c_void_p, C.c_int, C.c_float, C.c_double, C.c_size_t, C.c_longlong
 SIGNATURES = {
@@ -28,6 +30,8 @@ SIGNATURES = {
     "vfi_hud_update": (_i, [_vp, _vp, _i, _i, _vp, _i, C.POINTER(_ll), _d, _vp, _vp, _vp]),
     "vfi_route_decide": (_i, [_d, _d, _d, _d, _d, _d, _d, _d, _d, C.POINTER(_i), C.POINTER(_d),
                               C.POINTER(_i), C.POINTER(_d)]),
+    "vfi_profile_enable": (_i, [_vp, _i]),
+    "vfi_profile_read": (_i, [_vp, _vp, _vp, _i]),
     "vfi_debug_conv": (_i, [_vp, _i, _i, _vp, _i, _i, _i, _vp, _vp, _vp]),
 }
 

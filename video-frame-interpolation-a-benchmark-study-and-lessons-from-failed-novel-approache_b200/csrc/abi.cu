@@ -64,6 +64,40 @@ extern "C" __attribute__((visibility("default"))) void vfi_destroy(vfi_handle* h
   delete h;
 }
 
+void prof_begin(vfi_handle* h, int cat, cudaStream_t s) {
+  cudaEvent_t a, b;
+  cudaEventCreate(&a);
+  cudaEventCreate(&b);
+  h->prof_ev.push_back(a);
+  h->prof_ev.push_back(b);
+  h->prof_cat.push_back(cat);
+  cudaEventRecord(a, s);
+}
+void prof_end(vfi_handle* h, cudaStream_t s) { cudaEventRecord(h->prof_ev.back(), s); }
+
+extern "C" __attribute__((visibility("default"))) int vfi_profile_enable(vfi_handle* h, int on) {
+  if (!h) return VFI_E_ARG;
+  h->profile = on != 0;
+  return VFI_OK;
+}
+// Synchronises, sums the elapsed ms and launch counts per kernel class (ProfCat order) and clears the log.
+extern "C" __attribute__((visibility("default"))) int vfi_profile_read(vfi_handle* h, double* ms, long long* counts, int ncat) {
+  if (!h || !ms || !counts) return VFI_E_ARG;
+  for (int i = 0; i < ncat; i++) { ms[i] = 0; counts[i] = 0; }
+  VFI_CUDA(h, cudaDeviceSynchronize());
+  for (size_t i = 0; i < h->prof_cat.size(); i++) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, h->prof_ev[2 * i], h->prof_ev[2 * i + 1]);
+    int c = h->prof_cat[i];
+    if (c < ncat) { ms[c] += t; counts[c]++; }
+    cudaEventDestroy(h->prof_ev[2 * i]);
+    cudaEventDestroy(h->prof_ev[2 * i + 1]);
+  }
+  h->prof_ev.clear();
+  h->prof_cat.clear();
+  return VFI_OK;
+}
+
 extern "C" __attribute__((visibility("default"))) const char* vfi_last_error(vfi_handle* h) { return h ? h->err.c_str() : "null handle"; }
 extern "C" __attribute__((visibility("default"))) long long vfi_launch_count(vfi_handle* h) { return h ? h->launches : 0; }
 

@@ -68,6 +68,20 @@ struct vfi_handle {
   void* red = nullptr;
   size_t red_bytes = 0;
   void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled entry point
+  // optional per-kernel-class timing (vfi_profile_enable): event pairs around every launch
+  bool profile = false;
+  std::vector<cudaEvent_t> prof_ev;   // begin,end,begin,end...
+  std::vector<int> prof_cat;
+};
+
+enum ProfCat { PC_PAD = 0, PC_HEAD0, PC_CONV_TC, PC_CONV_DIRECT, PC_DECONV_DIRECT, PC_GATHER, PC_UPSAMPLE, PC_BLEND,
+               PC_REDUCE, PC_MISC, PC_COUNT };
+void prof_begin(vfi_handle* h, int cat, cudaStream_t s);
+void prof_end(vfi_handle* h, cudaStream_t s);
+struct ProfScope {
+  vfi_handle* h; cudaStream_t s;
+  ProfScope(vfi_handle* h_, int cat, cudaStream_t s_) : h(h_), s(s_) { if (h->profile) prof_begin(h, cat, s); }
+  ~ProfScope() { if (h->profile) prof_end(h, s); }
 };
 
 #define VFI_FAIL(h, code, ...)                               \

@@ -84,6 +84,7 @@ __global__ void conv3_direct_kernel(const T* __restrict__ in, const float* __res
 
 int k_conv3_direct(vfi_handle* h, const Layer& L, const void* in, const void* residual, void* out, int N, int Hin,
                    int Win, bool bf, float slope, cudaStream_t s) {
+  ProfScope _ps(h, PC_CONV_DIRECT, s);
   int Ho = L.stride == 2 ? Hin / 2 : Hin, Wo = L.stride == 2 ? Win / 2 : Win;
   int G = L.cout_pad / 4;
   int threads = 256;
@@ -162,6 +163,7 @@ __global__ void deconv4_direct_kernel(const T* __restrict__ in, const float* __r
 
 int k_deconv4_direct(vfi_handle* h, const Layer& L, const void* in, void* out, int N, int Hin, int Win, bool bf,
                      int mode, cudaStream_t s) {
+  ProfScope _ps(h, PC_DECONV_DIRECT, s);
   int G = L.cout_pad / 4;
   int threads = 256;
   int ppb = threads / G;

@@ -464,6 +464,7 @@ static int make_tmap_w(vfi_handle* h, CUtensorMap* out, const bf16* base, int cb
 
 int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
               int Win, bool out_phase, float slope, cudaStream_t s) {
+  ProfScope _ps(h, PC_CONV_TC, s);
   TcParams P;
   memset(&P, 0, sizeof(P));
   const bool s2 = (L.kind == LK_CONV3 && L.stride == 2);

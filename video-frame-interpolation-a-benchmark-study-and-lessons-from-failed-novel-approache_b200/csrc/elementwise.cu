@@ -96,6 +96,7 @@ __global__ void pad_rgbx_kernel(const uint8_t* __restrict__ src, uint8_t* __rest
   reinterpret_cast<uchar4*>(dst)[i] = make_uchar4(p[0], p[1], p[2], 0);
 }
 int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s) {
+  ProfScope _ps(h, PC_PAD, s);
   size_t total = (size_t)B * Hp * Wp;
   pad_rgbx_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp);
   VFI_LAUNCHED(h);
@@ -147,6 +148,7 @@ __global__ void head_cnn0_kernel(const uint8_t* __restrict__ imgs, const float* 
 }
 int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, int NI, int Hp, int Wp, bool bf,
                 cudaStream_t s) {
+  ProfScope _ps(h, PC_HEAD0, s);
   size_t total = (size_t)NI * (Hp / 2) * (Wp / 2);
   if (bf)
     head_cnn0_kernel<bf16><<<cdiv(total, 128), 128, 0, s>>>(imgs, L.w32, L.bias, (bf16*)out, NI, Hp, Wp, h->slope);
@@ -244,6 +246,7 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
 
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const float* state, const float* tsteps_dev,
              void* out, int B, int T, int Hp, int Wp, int s_int, bool first, bool bf, bool phase, cudaStream_t s) {
+  ProfScope _ps(h, PC_GATHER, s);
   size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
   int grid = cdiv(total, 128);
 #define GATHER_LAUNCH(TT, F)                                                                             \
@@ -308,6 +311,7 @@ __global__ void upsample_kernel(const float* __restrict__ low, float* __restrict
 }
 int k_upsample(vfi_handle* h, const float* low13, float* state, float* fm, int N, int Hp, int Wp, int s_int,
                bool first, bool last, cudaStream_t s) {
+  ProfScope _ps(h, PC_UPSAMPLE, s);
   size_t total = (size_t)N * Hp * Wp;
   if (last) upsample_kernel<true><<<cdiv(total, 256), 256, 0, s>>>(low13, state, fm, N, Hp, Wp, s_int, first ? 1 : 0);
   else upsample_kernel<false><<<cdiv(total, 256), 256, 0, s>>>(low13, state, fm, N, Hp, Wp, s_int, first ? 1 : 0);
@@ -387,6 +391,7 @@ __global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const float
 int k_final_blend(vfi_handle* h, const uint8_t* imgs, const float* fm, const uint8_t* hud, const float* tsteps_dev,
                   uint8_t* out, float* out_f32, float* flow_out, int B, int T, int H, int W, int Hp, int Wp,
                   cudaStream_t s) {
+  ProfScope _ps(h, PC_BLEND, s);
   size_t total = (size_t)B * T * H * ((W + 3) / 4);
   final_blend_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, fm, hud, tsteps_dev, out, out_f32, flow_out, B, T, H, W,
                                                       Hp, Wp);
@@ -413,6 +418,7 @@ __global__ void pack_fm_kernel(const float* __restrict__ flow, const float* __re
 }
 int k_pack_fm(vfi_handle* h, const float* flow, const float* mask, float* fm, int N, int H, int W, int Hp, int Wp,
               cudaStream_t s) {
+  ProfScope _ps(h, PC_MISC, s);
   size_t total = (size_t)N * Hp * Wp;
   pack_fm_kernel<<<cdiv(total, 256), 256, 0, s>>>(flow, mask, fm, N, H, W, Hp, Wp);
   VFI_LAUNCHED(h);

@@ -52,6 +52,18 @@ class Engine:
     def launches(self):
         return int(self._lib.vfi_launch_count(self._h))
 
+    def profile(self, on):
+        self._check(self._lib.vfi_profile_enable(self._h, 1 if on else 0), "vfi_profile_enable")
+
+    def profile_read(self):
+        """{class: (ms, launches)} since the last read; synchronises the device."""
+        n = len(_abi.PROFILE_CLASSES)
+        ms = (C.c_double * n)()
+        cnt = (C.c_longlong * n)()
+        self._check(self._lib.vfi_profile_read(self._h, C.cast(ms, C.c_void_p), C.cast(cnt, C.c_void_p), n),
+                    "vfi_profile_read")
+        return {k: (ms[i], int(cnt[i])) for i, k in enumerate(_abi.PROFILE_CLASSES)}
+
     def _check(self, rc, what):
         _abi.check(self._h, rc, what)
 
