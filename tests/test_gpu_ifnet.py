@@ -1,0 +1,133 @@
+"""Parity of the CUDA IFNet pass (through the C ABI) with the CPU oracle.
+Tolerances are BASELINE.json north_star's: fp32 mode max-abs 1e-4 on [0,1] frames; bf16 mode max-abs 2e-2 and
+PSNR-vs-oracle >= 45 dB.  At 1080p (too slow for the oracle inside a test) size-independent properties are used."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import vfi_b200  # noqa: F401
+from oracle import ifnet_ref
+from vfi_b200 import _abi
+from vfi_b200.ifnet_layers import layer_info
+from vfi_b200.synth import gen_clip
+
+pytestmark = pytest.mark.gpu
+TOL = {_abi.PRECISION_FP32: 1e-4, _abi.PRECISION_BF16: 2e-2}
+TS = [0.25, 0.5, 0.75]
+
+
+def _psnr(a, b):
+    return 10 * np.log10(1.0 / max(float(((a - b) ** 2).mean()), 1e-20))
+
+
+def _check(engine, oracle_model, fr0, fr1, ts, scale, prec):
+    ref_u8, ref_f = ifnet_ref.interpolate_ref(oracle_model, fr0, fr1, ts, scale=scale, return_float=True)
+    out, of = engine.infer(fr0[None], fr1[None], ts, scale, prec, want_float=True)
+    of, out = of[0].cpu().numpy(), out[0].cpu().numpy()
+    for i in range(len(ts)):
+        err = float(np.abs(of[i] - ref_f[i]).max())
+        assert err <= TOL[prec], f"t={ts[i]} max-abs {err} > {TOL[prec]}"
+        if prec == _abi.PRECISION_BF16:
+            assert _psnr(of[i], ref_f[i]) >= 45.0
+        # uint8 store = truncation of the float result (base.py:201); vs the oracle's u8 at most 1 + tol*255 levels
+        assert np.array_equal(out[i], (of[i] * 255).clip(0, 255).astype(np.uint8))
+        assert np.abs(out[i].astype(int) - ref_u8[i].astype(int)).max() <= int(TOL[prec] * 255) + 1
+
+
+@pytest.mark.parametrize("prec", [_abi.PRECISION_FP32, _abi.PRECISION_BF16])
+def test_golden_fixture(engine, golden, prec):
+    g = golden("ifnet_small.npz")
+    n, H, W, seed = g["clip"].tolist()
+    fr = gen_clip(n, H, W, seed=seed, cut_every=0, fast=None)
+    out, of = engine.infer(fr[0][None], fr[1][None], g["ts"].tolist(), 1.0, prec, want_float=True)
+    assert float(np.abs(of[0].cpu().numpy() - g["out_f32"]).max()) <= TOL[prec]
+
+
+@pytest.mark.parametrize("prec", [_abi.PRECISION_FP32, _abi.PRECISION_BF16])
+@pytest.mark.parametrize("H,W", [(128, 192), (270, 480), (100, 150)])     # aligned, 1080p/4, ragged (reflect pad both ways)
+def test_parity_scale1(engine, oracle_model, prec, H, W):
+    fr = gen_clip(1, H, W, seed=0, cut_every=0, fast=None)
+    _check(engine, oracle_model, fr[0], fr[1], TS, 1.0, prec)
+
+
+@pytest.mark.parametrize("prec", [_abi.PRECISION_FP32, _abi.PRECISION_BF16])
+@pytest.mark.parametrize("scale,H,W", [(0.5, 256, 384), (0.5, 200, 300), (0.25, 256, 512)])
+def test_parity_uhd_scales(engine, oracle_model, prec, scale, H, W):
+    fr = gen_clip(1, H, W, seed=7, cut_every=0, fast=None)
+    _check(engine, oracle_model, fr[0], fr[1], [0.5], scale, prec)
+
+
+def test_timestep_edge_values(engine, oracle_model):
+    fr = gen_clip(1, 128, 192, seed=3, cut_every=0, fast=None)
+    _check(engine, oracle_model, fr[0], fr[1], [0.0, 1.0, 0.125], 1.0, _abi.PRECISION_FP32)
+
+
+@pytest.mark.parametrize("prec", [_abi.PRECISION_FP32, _abi.PRECISION_BF16])
+def test_batch_equals_singles_bit_exact(engine, prec):
+    fr = gen_clip(3, 192, 256, seed=5, cut_every=0, fast=None)
+    batch = engine.infer(fr[:3], fr[1:4], TS, 1.0, prec).cpu().numpy()
+    for b in range(3):
+        one = engine.infer(fr[b][None], fr[b + 1][None], TS, 1.0, prec).cpu().numpy()
+        assert np.array_equal(batch[b], one[0])
+        for i, t in enumerate(TS):      # and each timestep on its own (Head sharing does not change results)
+            assert np.array_equal(engine.infer(fr[b][None], fr[b + 1][None], [t], 1.0, prec).cpu().numpy()[0, 0], one[0, i])
+
+
+def test_hud_mask_composite(engine):
+    fr = gen_clip(1, 128, 192, seed=2, cut_every=0, fast=None)
+    m = np.zeros((1, 128, 192), np.uint8)
+    m[0, :20, :50] = 1
+    plain = engine.infer(fr[0][None], fr[1][None], TS, 1.0, _abi.PRECISION_BF16).cpu().numpy()[0]
+    comp = engine.infer(fr[0][None], fr[1][None], TS, 1.0, _abi.PRECISION_BF16, hud_mask=m).cpu().numpy()[0]
+    mb = m[0].astype(bool)
+    for i, t in enumerate(TS):          # adaptive_pipeline.py:399-409
+        assert np.array_equal(comp[i][mb], (fr[0] if t < 0.5 else fr[1])[mb])
+        assert np.array_equal(comp[i][~mb], plain[i][~mb])
+
+
+def test_argument_errors(engine):
+    z = np.zeros((1, 64, 64, 3), np.uint8)
+    with pytest.raises(_abi.VFIError, match="scale"):
+        engine.infer(z, z, [0.5], 0.3, _abi.PRECISION_BF16)
+    with pytest.raises(_abi.VFIError):
+        engine.infer(z[:, :1], z[:, :1], [0.5], 1.0, _abi.PRECISION_BF16)       # too small to reflect-pad
+
+
+LAYERS = [1, 3, 4, 5, 6, 13, 14, 15, 16, 17, 25, 26, 27, 28, 36, 37, 38, 39, 47, 48, 49, 50, 57, 58]
+
+
+def _torch_layer(sd, layer, x, res, round_bf16):
+    li = layer_info(layer)
+    w, b = sd[li["key"] + ".weight"].cuda(), sd[li["key"] + ".bias"].cuda()
+    x = x[..., :li["cin"]].permute(0, 3, 1, 2).contiguous()
+    r16 = (lambda t: t.to(torch.bfloat16).float()) if round_bf16 else (lambda t: t)
+    w, x = r16(w), r16(x)
+    if li["kind"] == "conv":
+        y = F.conv2d(x, w, b, stride=li["stride"], padding=1)
+        if li["beta"]:
+            y = y * sd[li["beta_key"]].cuda() + r16(res.permute(0, 3, 1, 2))
+        if li["act"]:
+            y = F.leaky_relu(y, 0.2)
+        return y.permute(0, 2, 3, 1)
+    y = F.conv_transpose2d(x, w, b, stride=2, padding=1)
+    return (y if layer == 3 else F.pixel_shuffle(y, 2)).permute(0, 2, 3, 1)
+
+
+@pytest.mark.parametrize("prec", [_abi.PRECISION_FP32, _abi.PRECISION_BF16])
+@pytest.mark.parametrize("layer", LAYERS)
+def test_single_layer_vs_torch(engine, weights, layer, prec):
+    """Every conv kernel shape of the net against torch fp32 conv2d / conv_transpose2d on the same
+    (bf16-rounded, for the tcgen05 path) operands; odd spatial sizes exercise partial tiles."""
+    torch.backends.cudnn.allow_tf32 = False
+    li = layer_info(layer)
+    g = torch.Generator().manual_seed(layer)
+    Hin, Win = (26, 44) if li["stride"] == 2 and li["kind"] == "conv" else (23, 41)
+    x = torch.randn((2, Hin, Win, li["cin_pad"]), generator=g).cuda()
+    x[..., li["cin"]:] = 0
+    res = torch.randn((2, Hin, Win, li["cout"]), generator=g).cuda() if li["beta"] else None
+    y = engine.debug_conv(layer, prec, x, res)
+    ref = _torch_layer(weights, layer, x, res, prec == _abi.PRECISION_BF16)
+    err = (y[..., :ref.shape[-1]] - ref).abs().max().item()
+    tol = (1e-4 if prec == _abi.PRECISION_FP32 else 1.5e-2) * max(1.0, ref.abs().max().item())
+    assert err <= tol, f"layer {layer} ({li['key']}): {err} > {tol}"

@@ -1,0 +1,60 @@
+"""BASELINE.json full-size checks (1080p, 1440p) through size-independent properties + one oracle comparison."""
+import numpy as np
+import pytest
+import torch
+
+import vfi_b200  # noqa: F401
+from oracle import ifnet_ref
+from vfi_b200 import _abi
+from vfi_b200.synth import gen_clip
+
+pytestmark = pytest.mark.gpu
+TS = [0.25, 0.5, 0.75]
+
+
+@pytest.fixture(scope="module")
+def clip1080():
+    return gen_clip(2, 1080, 1920, seed=1, cut_every=0, fast=None)
+
+
+def test_config1_fp32_and_bf16_vs_oracle_1080p(engine, oracle_model, clip1080):
+    """configs[0]: one 1080p pair, t=0.5, random-init weights, oracle fp32 on the CPU."""
+    ref_u8, ref_f = ifnet_ref.interpolate_ref(oracle_model, clip1080[0], clip1080[1], [0.5], return_float=True)
+    for prec, tol in ((_abi.PRECISION_FP32, 1e-4), (_abi.PRECISION_BF16, 2e-2)):
+        out, of = engine.infer(clip1080[0][None], clip1080[1][None], [0.5], 1.0, prec, want_float=True)
+        d = of[0, 0].cpu().numpy() - ref_f[0]
+        assert float(np.abs(d).max()) <= tol
+        if prec == _abi.PRECISION_BF16:
+            assert 10 * np.log10(1.0 / float((d ** 2).mean())) >= 45.0
+
+
+def test_bf16_tracks_fp32_mode_1080p(engine, clip1080):
+    a = engine.infer(clip1080[:2], clip1080[1:3], TS, 1.0, _abi.PRECISION_FP32, want_float=True)[1]
+    b = engine.infer(clip1080[:2], clip1080[1:3], TS, 1.0, _abi.PRECISION_BF16, want_float=True)[1]
+    d = (a - b)
+    assert float(d.abs().max()) <= 2e-2
+    assert float(10 * torch.log10(1.0 / (d ** 2).mean())) >= 45.0
+
+
+def test_determinism_and_batch_invariance_1080p(engine, clip1080):
+    x = engine.infer(clip1080[:2], clip1080[1:3], TS, 1.0, _abi.PRECISION_BF16).clone()
+    y = engine.infer(clip1080[:2], clip1080[1:3], TS, 1.0, _abi.PRECISION_BF16)
+    assert torch.equal(x, y)
+    z = engine.infer(clip1080[1][None], clip1080[2][None], [0.75], 1.0, _abi.PRECISION_BF16)
+    assert torch.equal(z[0, 0], x[1, 2])
+
+
+def test_hud_all_ones_returns_inputs_1080p(engine, clip1080):
+    m = np.ones((1, 1080, 1920), np.uint8)
+    o = engine.infer(clip1080[0][None], clip1080[1][None], TS, 1.0, _abi.PRECISION_BF16, hud_mask=m).cpu().numpy()[0]
+    assert np.array_equal(o[0], clip1080[0]) and np.array_equal(o[1], clip1080[1]) and np.array_equal(o[2], clip1080[1])
+
+
+@pytest.mark.parametrize("H,W", [(1440, 2560)])
+def test_1440p_pads_to_64(engine, H, W):
+    """1440 is a multiple of 32 but not 64; the pass must pad to 1472 and still return HxW."""
+    fr = gen_clip(1, H, W, seed=3, cut_every=0, fast=None)
+    a = engine.infer(fr[0][None], fr[1][None], [0.5], 1.0, _abi.PRECISION_BF16, want_float=True)
+    b = engine.infer(fr[0][None], fr[1][None], [0.5], 1.0, _abi.PRECISION_FP32, want_float=True)
+    assert a[0].shape == (1, 1, H, W, 3)
+    assert float((a[1] - b[1]).abs().max()) <= 2e-2

@@ -218,8 +218,15 @@ class AdaptivePipeline(BaseModel):
 
     def interpolate(self, frame0: np.ndarray, frame1: np.ndarray, num_frames: int = 3,
                     timestamps: Optional[List[float]] = None) -> List[np.ndarray]:
+        return self._interpolate_routed(frame0, frame1, num_frames, timestamps)[0]
+
+    def _interpolate_routed(self, frame0, frame1, num_frames=3, timestamps=None):
+        """interpolate() that also hands back the ContentAnalysis it routed on."""
         self.ensure_loaded()
         analysis = self.router.analyze(frame0, frame1)
+        return self._route(analysis, frame0, frame1, num_frames, timestamps), analysis
+
+    def _route(self, analysis, frame0, frame1, num_frames, timestamps):
         if analysis.is_scene_change:
             self.stats.add('scene_change')
             return [frame0.copy() for _ in range(num_frames)]
@@ -261,6 +268,44 @@ class AdaptivePipeline(BaseModel):
                                                         'hud_coverage': analysis.hud_coverage,
                                                         'recommended_model': analysis.recommended_model},
                                            'routing_stats': self.stats.to_dict()})
+
+    def process_clip(self, frames, num_frames: int = 3, rank: int = 0, world: int = 1, group=None,
+                     on_pair=None) -> dict:
+        """Extra (not in the reference): interpolate a whole clip sharded by frame-pair index over `world`
+        ranks.  Each rank replays the HUD pushes it needs from the pairs before its range,
+        runs interpolate() on its own pairs, and the route counters are summed with ONE all-reduce.
+        frames: (n_pairs+1, H, W, 3) uint8.  on_pair(j, mids, analysis) receives each pair's result.
+        Returns {'range', 'routes' (clip-order int8, -1 where unknown), 'stats' (whole clip)}."""
+        from ... import sharding
+        self.ensure_loaded()
+        n_pairs = len(frames) - 1
+        cuts = {}
+
+        def is_cut(j):
+            if j not in cuts:
+                cuts[j] = self.router.detect_scene_change(frames[j], frames[j + 1])[0]
+            return cuts[j]
+
+        code = {'rife': _abi.ROUTE_RIFE, 'vfimamba': _abi.ROUTE_VFIMAMBA, 'scene_change': _abi.ROUTE_SCENE_CHANGE}
+        local = []
+
+        def process(j):
+            mids, a = self._interpolate_routed(frames[j], frames[j + 1], num_frames)
+            local.append(code[a.recommended_model])
+            if on_pair is not None:
+                on_pair(j, mids, a)
+
+        (lo, hi), _ = sharding.run_sharded(n_pairs, rank, world, is_cut,
+                                           lambda j: self.router._detect_hud_dev(self.router._dev(frames[j]), None),
+                                           process)
+        dev = self.device if self.device.type == 'cuda' else torch.device('cpu')
+        st = self.stats
+        vec = torch.tensor([st.total, st.rife_count, st.vfimamba_count, st.scene_change_count], dtype=torch.int64,
+                           device=dev)
+        vec = sharding.reduce_counters(vec, group).tolist()
+        routes = sharding.gather_flags(torch.tensor(local, dtype=torch.int8, device=dev), n_pairs, rank, world, group)
+        whole = RoutingStats(*vec)
+        return {'range': (lo, hi), 'routes': routes.cpu().numpy(), 'stats': whole.to_dict()}
 
     def get_stats(self) -> dict:
         return self.stats.to_dict()
