@@ -43,6 +43,10 @@ const char* vfi_last_error(vfi_handle* h);
 /* number of kernels this handle has launched since creation (bench.py "gpu_launches") */
 long long vfi_launch_count(vfi_handle* h);
 
+/* Tuning / test knob.  key "conv_v2": 1 (default) routes the stride-1 3x3 convs whose weights fit in shared
+ * memory through the resident-weight halo-tile kernel (csrc/conv_v2.cu), 0 keeps them on the TMA-per-tap kernel. */
+int vfi_set_option(vfi_handle* h, const char* key, int value);
+
 /* IFNet weights.  Replaces Model.load_model(dir, -1) (models/sota/rife_wrapper.py:102-103,
  * scripts/run_experiments.py:266).  `params` is a HOST array of VFI_IFNET_PARAMS floats:
  * the v4.25 IFNet state_dict tensors flattened (PyTorch layouts: Conv2d [Co,Ci,kh,kw],
@@ -113,7 +117,8 @@ int vfi_route_decide(double ssim_score, double motion_mean, double motion_max, d
 
 /* Unit-test hook: run ONE conv layer of the loaded IFNet on caller data in both precisions'
  * layouts.  layer ids are listed in csrc/ifnet.h.  x: N x Hin x Win x Cin_pad (fp32 NHWC),
- * y: N x Hout x Wout x Cout_pad fp32 NHWC out (for lastconv: N x 4Hin x 4Win x 16).       */
+ * y: N x Hout x Wout x Cout_pad fp32 NHWC out (for lastconv: N x 4Hin x 4Win x 16).
+ * residual (ResConv layers only): NULL => the layer input itself, as in the net.          */
 int vfi_debug_conv(vfi_handle* h, int layer, int precision, const float* x, int N, int Hin, int Win,
                    const float* residual, float* y, void* stream);
 

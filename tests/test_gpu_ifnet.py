@@ -106,7 +106,7 @@ def _torch_layer(sd, layer, x, res, round_bf16):
     if li["kind"] == "conv":
         y = F.conv2d(x, w, b, stride=li["stride"], padding=1)
         if li["beta"]:
-            y = y * sd[li["beta_key"]].cuda() + r16(res.permute(0, 3, 1, 2))
+            y = y * sd[li["beta_key"]].cuda() + (r16(res.permute(0, 3, 1, 2)) if res is not None else x)
         if li["act"]:
             y = F.leaky_relu(y, 0.2)
         return y.permute(0, 2, 3, 1)
@@ -131,3 +131,25 @@ def test_single_layer_vs_torch(engine, weights, layer, prec):
     err = (y[..., :ref.shape[-1]] - ref).abs().max().item()
     tol = (1e-4 if prec == _abi.PRECISION_FP32 else 1.5e-2) * max(1.0, ref.abs().max().item())
     assert err <= tol, f"layer {layer} ({li['key']}): {err} > {tol}"
+
+
+@pytest.mark.parametrize("layer", [1, 2, 39, 46, 50, 57])
+@pytest.mark.parametrize("Hin,Win", [(16, 8), (23, 41), (50, 100), (136, 240)])
+def test_conv_v2_halo_tile_kernel(engine, weights, layer, Hin, Win):
+    """csrc/conv_v2.cu (resident weights, one halo tile per 16 x 8KW outputs, shifted no-swizzle descriptors) against
+    torch and against the TMA-per-tap kernel on the same bf16 operands; partial tiles in both directions."""
+    torch.backends.cudnn.allow_tf32 = False
+    li = layer_info(layer)
+    g = torch.Generator().manual_seed(100 + layer)
+    x = torch.randn((3, Hin, Win, li["cin_pad"]), generator=g).cuda()
+    try:
+        engine.set_option("conv_v2", 1)
+        y2 = engine.debug_conv(layer, _abi.PRECISION_BF16, x, None)
+        engine.set_option("conv_v2", 0)
+        y1 = engine.debug_conv(layer, _abi.PRECISION_BF16, x, None)
+    finally:
+        engine.set_option("conv_v2", 1)
+    ref = _torch_layer(weights, layer, x, None, True)
+    scale = max(1.0, ref.abs().max().item())
+    assert (y2 - ref).abs().max().item() <= 1.5e-2 * scale
+    assert (y2 - y1).abs().max().item() <= 1.0e-2 * scale          # same operands, different accumulation order + bf16 store

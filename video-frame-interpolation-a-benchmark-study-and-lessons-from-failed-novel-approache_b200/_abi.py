@@ -20,6 +20,7 @@ SIGNATURES = {
     "vfi_destroy": (None, [_vp]),
     "vfi_last_error": (C.c_char_p, [_vp]),
     "vfi_launch_count": (_ll, [_vp]),
+    "vfi_set_option": (_i, [_vp, C.c_char_p, _i]),
     "vfi_ifnet_load_weights": (_i, [_vp, _vp, _sz, _vp]),
     "vfi_ifnet_infer": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _f, _i, _vp, _vp, _vp, _vp, _vp]),
     "vfi_warp_blend": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),

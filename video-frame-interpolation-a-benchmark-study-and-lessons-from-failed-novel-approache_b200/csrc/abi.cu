@@ -48,9 +48,10 @@ extern "C" __attribute__((visibility("default"))) int vfi_create(int device, vfi
 static void free_layers(vfi_handle* h) {
   for (int i = 0; i < VFI_NUM_LAYERS; i++) {
     Layer& L = h->layers[i];
-    cudaFree(L.w32); cudaFree(L.bias); cudaFree(L.beta); cudaFree(L.wtc); cudaFree(L.bias_tc);
+    cudaFree(L.w32); cudaFree(L.bias); cudaFree(L.beta); cudaFree(L.wtc); cudaFree(L.bias_tc); cudaFree(L.wv2);
     L.w32 = L.bias = L.beta = L.bias_tc = nullptr;
     L.wtc = nullptr;
+    L.wv2 = nullptr;
   }
 }
 
@@ -96,6 +97,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_profile_read(vfi_handl
   h->prof_ev.clear();
   h->prof_cat.clear();
   return VFI_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle* h, const char* key, int value) {
+  if (!h || !key) return VFI_E_ARG;
+  if (!strcmp(key, "conv_v2")) { h->opt_conv_v2 = value; return VFI_OK; }
+  VFI_FAIL(h, VFI_E_ARG, "unknown option %s", key);
 }
 
 extern "C" __attribute__((visibility("default"))) const char* vfi_last_error(vfi_handle* h) { return h ? h->err.c_str() : "null handle"; }
@@ -163,6 +170,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
     const bool tc = (id == 1 || id == 2 || id >= 4);
     if (tc) {
       if (int rc = tc_build_layer(h, L, w)) return rc;
+      if (int rc = v2_build_layer(h, L, w)) return rc;
     }
   }
   if (off != n_params) VFI_FAIL(h, VFI_E_ARG, "parameter blob length mismatch (%zu consumed)", off);
@@ -183,6 +191,8 @@ struct Carve {
 
 static int run_conv(vfi_handle* h, const Layer& L, const void* in, const void* res, void* out, int N, int Hin,
                     int Win, bool bf, bool out_phase, cudaStream_t s) {
+  if (bf && h->opt_conv_v2 && L.wv2 && !out_phase && (res == nullptr || res == in))
+    return k_conv_v2(h, L, (const bf16*)in, (bf16*)out, N, Hin, Win, h->slope, s);
   if (bf) return k_conv_tc(h, L, (const bf16*)in, (const bf16*)res, out, N, Hin, Win, out_phase, h->slope, s);
   return k_conv3_direct(h, L, in, res, out, N, Hin, Win, false, h->slope, s);
 }
@@ -313,7 +323,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
   const size_t nin = (size_t)N * Hin * Win * L.cin_pad;
   const size_t nout = (size_t)N * Ho * Wo * L.cout_pad;
   if (!bf) {
-    if (L.kind == LK_CONV3) return k_conv3_direct(h, L, x, residual, y, N, Hin, Win, false, h->slope, s);
+    if (L.kind == LK_CONV3)
+      return k_conv3_direct(h, L, x, L.has_beta && !residual ? x : residual, y, N, Hin, Win, false, h->slope, s);
     return k_deconv4_direct(h, L, x, y, N, Hin, Win, false, layer == 3 ? 0 : 1, s);
   }
   Carve cv{nullptr, 0};
@@ -334,11 +345,14 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
     const bf16* in = xb;
     if (s2) { if ((rc = k_plain_to_phase(h, xb, xp, N, Hin, Win, L.cin_pad, s))) return rc; in = xp; }
     if (L.kind == LK_DECONV4) return k_conv_tc(h, L, in, nullptr, y, N, Hin, Win, false, h->slope, s);
-    if (L.has_beta) {
-      if (!residual) VFI_FAIL(h, VFI_E_ARG, "ResConv layer needs residual");
-      if ((rc = k_f32_to_act(h, residual, rb, nout, true, s))) return rc;
+    const bf16* resp = nullptr;
+    if (L.has_beta) {  // ResConv: residual defaults to the layer input (x), as in the net
+      resp = xb;
+      if (residual) { if ((rc = k_f32_to_act(h, residual, rb, nout, true, s))) return rc; resp = rb; }
     }
-    if ((rc = k_conv_tc(h, L, in, L.has_beta ? rb : nullptr, yb, N, Hin, Win, false, h->slope, s))) return rc;
+    if (h->opt_conv_v2 && L.wv2 && !s2 && (resp == nullptr || resp == xb)) {
+      if ((rc = k_conv_v2(h, L, xb, yb, N, Hin, Win, h->slope, s))) return rc;
+    } else if ((rc = k_conv_tc(h, L, in, resp, yb, N, Hin, Win, false, h->slope, s))) return rc;
     return k_act_to_f32(h, yb, y, nout, true, s);
   }
   return VFI_OK;

@@ -51,6 +51,7 @@ struct Layer {
   int cblk = 0, rows_total = 0, nsteps = 0, n_total = 0, b_box = 0;
   TcStep steps[VFI_MAX_STEPS];
   float* bias_tc = nullptr;  // bias laid out by accumulator column (n_total floats)
+  bf16* wv2 = nullptr;       // conv_v2.cu resident-weight image [tap][cin/8][cout][8] (null: layer not v2-capable)
 };
 
 struct vfi_handle {
@@ -68,6 +69,7 @@ struct vfi_handle {
   void* red = nullptr;
   size_t red_bytes = 0;
   void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled entry point
+  int opt_conv_v2 = 1;          // vfi_set_option("conv_v2"): resident-weight halo-tile conv kernel where it applies
   // optional per-kernel-class timing (vfi_profile_enable): event pairs around every launch
   bool profile = false;
   std::vector<cudaEvent_t> prof_ev;   // begin,end,begin,end...
@@ -143,5 +145,12 @@ int tc_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch); 
 // lastconv (deconv): in plain bf16, out = fp32 low13 [N,4Hin,4Win,16]
 int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
               int Win, bool out_phase, float slope, cudaStream_t s);
+
+// ---- conv_v2.cu ---------------------------------------------------------------------------
+bool v2_supported(const Layer& L);
+int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch);
+// stride-1 3x3 conv (+ResConv epilogue), plain NHWC bf16 in/out
+int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, int H, int W, float slope,
+              cudaStream_t s);
 
 // ---- reduce.cu is reached only through the ABI functions -----------------------------------

@@ -52,6 +52,9 @@ class Engine:
     def launches(self):
         return int(self._lib.vfi_launch_count(self._h))
 
+    def set_option(self, key, value):
+        self._check(self._lib.vfi_set_option(self._h, key.encode(), int(value)), "vfi_set_option")
+
     def profile(self, on):
         self._check(self._lib.vfi_profile_enable(self._h, 1 if on else 0), "vfi_profile_enable")
 
