@@ -159,7 +159,9 @@ def main():
     dev = torch.device("cuda", local)
 
     model = RIFEModel(device=f"cuda:{local}", precision=args.precision)
-    model.load()
+    import contextlib
+    with contextlib.redirect_stdout(sys.stderr):   # the wrapper prints "Loading RIFE ..." like the reference; stdout is the JSON line only
+        model.load()
     eng = model._engine
     B, T = args.pairs, len(TIMESTEPS)
     # each rank works on its own shard of the clip (frame-pair sharding, no data-path collective)

@@ -31,13 +31,14 @@ struct V2Params {
   int npix;    // 18 * pitch
   int CS;      // chunk stride in 16-byte units (>= npix, padded against bank conflicts)
   int a_bytes, nstages, w_bytes, tmem_cols, acc_stride;
-  int act;
+  int act, chunk_shift;  // chunk_shift = log2(Cin/8) or -1
   float slope;
 };
 
 #define V2_THREADS 288
 #define V2_PRODUCERS 128
 #define V2_MAX_STAGES 4
+#define V2_UNROLL 11
 
 namespace {
 __device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -153,28 +154,28 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       bar_wait(&empty_bar[st], ph ^ 1);
       uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)st * P.a_bytes);
       const bf16* img = P.in + (size_t)n * P.H * P.W * P.Cin;
-      const int row_items = P.pitch * nchunk;
-      for (int py = warp; py < 18; py += 4) {
-        const int gy = gy0 + py;
-        const bool rowok = (gy >= 0) && (gy < P.H);
-        const bf16* rowp = img + (size_t)(rowok ? gy : 0) * P.W * P.Cin;
-        for (int i0 = lane; i0 < row_items; i0 += 128) {
-          uint4 v[4];
-          int px[4], jj[4];
+      // flattened (halo row, pixel, chunk) items, V2_UNROLL independent 16-byte loads in flight per thread
+      const int row_items = P.pitch * nchunk, total = 18 * row_items;
+      int py = 0, rem = threadIdx.x;  // item = py * row_items + rem
+      while (rem >= row_items) { rem -= row_items; py++; }
+      for (int i0 = threadIdx.x; i0 < total; i0 += V2_PRODUCERS * V2_UNROLL) {
+        uint4 v[V2_UNROLL];
+        int off[V2_UNROLL];
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
-            const int i = i0 + 32 * u;
-            px[u] = i / nchunk;
-            jj[u] = i - px[u] * nchunk;
-            const int gx = gx0 + px[u];
-            v[u] = make_uint4(0, 0, 0, 0);
-            if (i < row_items && rowok && gx >= 0 && gx < P.W)
-              v[u] = __ldg(reinterpret_cast<const uint4*>(rowp + (size_t)gx * P.Cin + jj[u] * 8));
-          }
-#pragma unroll
-          for (int u = 0; u < 4; u++)
-            if (i0 + 32 * u < row_items) dst[jj[u] * P.CS + py * P.pitch + px[u]] = v[u];
+        for (int u = 0; u < V2_UNROLL; u++) {
+          const int px = P.chunk_shift >= 0 ? (rem >> P.chunk_shift) : rem / nchunk;
+          const int j = rem - px * nchunk;
+          const int gy = gy0 + py, gx = gx0 + px;
+          const bool ok = (i0 + u * V2_PRODUCERS < total) && gy >= 0 && gy < P.H && gx >= 0 && gx < P.W;
+          off[u] = (i0 + u * V2_PRODUCERS < total) ? j * P.CS + py * P.pitch + px : -1;
+          v[u] = make_uint4(0, 0, 0, 0);
+          if (ok) v[u] = __ldg(reinterpret_cast<const uint4*>(img + ((size_t)gy * P.W + gx) * P.Cin + j * 8));
+          rem += V2_PRODUCERS;
+          while (rem >= row_items) { rem -= row_items; py++; }
         }
+#pragma unroll
+        for (int u = 0; u < V2_UNROLL; u++)
+          if (off[u] >= 0) dst[off[u]] = v[u];
       }
       fence_async_smem();
       bar_arrive(&full_bar[st]);
@@ -196,18 +197,19 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
         bar_wait(&full_bar[st], ph);
         tc_after();
         const uint32_t a_addr = s_u32(a_s + (size_t)st * P.a_bytes);
-        for (int j = 0; j < P.KW; j++) {
-          const uint32_t dcol = tmem_base + (uint32_t)(as * P.acc_stride + j * P.Cout);
-          uint32_t acc = 0;
-          for (int tap = 0; tap < 9; tap++) {
-            const int r = tap / 3, q = tap - 3 * r;
-            const uint32_t a0 = a_addr + (uint32_t)(r * P.pitch + q + 8 * j) * 16;
-            const uint32_t b0 = w_addr + (uint32_t)(tap * nchunk) * b_lbo;
-            for (int k = 0; k < ksteps; k++) {
-              mma_bf16(dcol, desc_ns(a0 + 2 * k * a_lbo, a_lbo, a_sbo), desc_ns(b0 + 2 * k * b_lbo, b_lbo, b_sbo), idesc,
-                       acc);
-              acc = 1;
-            }
+        // consecutive MMAs go to DIFFERENT accumulators (j innermost): back-to-back MMAs into the same TMEM columns
+        // serialise on the accumulate dependency (~200 cycles each at these small N), independent ones pipeline.
+        const uint32_t dcol0 = tmem_base + (uint32_t)(as * P.acc_stride);
+        for (int tap = 0; tap < 9; tap++) {
+          const int r = tap / 3, q = tap - 3 * r;
+          const uint32_t a0 = a_addr + (uint32_t)(r * P.pitch + q) * 16;
+          const uint32_t b0 = w_addr + (uint32_t)(tap * nchunk) * b_lbo;
+          for (int k = 0; k < ksteps; k++) {
+            const uint64_t bd = desc_ns(b0 + 2 * k * b_lbo, b_lbo, b_sbo);
+            const uint64_t ad = desc_ns(a0 + 2 * k * a_lbo, a_lbo, a_sbo);
+            const uint32_t acc = (tap | k) ? 1u : 0u;
+            for (int j = 0; j < P.KW; j++)
+              mma_bf16(dcol0 + (uint32_t)(j * P.Cout), ad + (uint64_t)(8 * j), bd, idesc, acc);  // +8 px = +128 B = +8 (16-B units)
           }
         }
         commit_to(&empty_bar[st]);
@@ -324,6 +326,8 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   P.slope = slope;
   P.w_bytes = 9 * L.cin * L.cout * 2;
   const int nchunk = L.cin / 8;
+  P.chunk_shift = -1;
+  for (int b = 0; b < 6; b++) if ((1 << b) == nchunk) P.chunk_shift = b;
   const size_t budget = 220 * 1024 - P.w_bytes - 1024;
   int kw = 4;
   for (; kw >= 1; kw >>= 1) {
