@@ -69,6 +69,7 @@ struct vfi_handle {
   void* red = nullptr;
   size_t red_bytes = 0;
   void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled entry point
+  int opt_v2_ablate = 0;        // debug only: see V2Params::ablate
   int opt_conv_v2 = 1;          // vfi_set_option("conv_v2"): resident-weight halo-tile conv kernel where it applies
   // optional per-kernel-class timing (vfi_profile_enable): event pairs around every launch
   bool profile = false;

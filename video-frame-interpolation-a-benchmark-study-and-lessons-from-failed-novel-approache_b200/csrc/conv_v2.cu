@@ -12,8 +12,8 @@
 //   D (TMEM)     : KW accumulators of Cout fp32 columns, double buffered (2*KW*Cout <= 512 columns).
 //   epilogue     : tcgen05.ld -> +bias -> (*beta + residual, taken from the SAME smem halo tile) -> LeakyReLU
 //                  -> bf16 NHWC store.
-// Warp roles (288 threads): warps 0-3 producers (LDG.128 -> STS.128, zero fill = conv padding), warp 4 TMEM
-// allocator + single-thread MMA issuer, warps 5-8 epilogue.
+// Warp roles (416 threads): warps 0-3 producers (cp.async 16 B, zero fill = conv padding, up to 3 tiles in flight),
+// warp 4 TMEM allocator + MMA issuer (converged warp, elected lane), warps 5-12 epilogue (two per TMEM lane group).
 // Layer semantics: SURVEY.md Appendix A.2 (conv(), ResConv).
 #include <algorithm>
 
@@ -25,20 +25,45 @@ struct V2Params {
   const bf16* wpack;
   const float* bias;
   const float* beta;  // null => plain conv
-  int N, H, W, Cin, Cout;
-  int KW, tiles_x, tiles_y, num_tiles;
-  int pitch;   // halo row pitch in pixels = 8*KW + 2
-  int npix;    // 18 * pitch
-  int CS;      // chunk stride in 16-byte units (>= npix, padded against bank conflicts)
-  int a_bytes, nstages, w_bytes, tmem_cols, acc_stride;
-  int act, chunk_shift;  // chunk_shift = log2(Cin/8) or -1
+  int N, H, W;
+  int tiles_x, tiles_y, num_tiles;
+  int nstages;
+  int ablate;  // debug (vfi_set_option "v2_ablate"): 1 skip loads, 2 skip MMAs, 4 skip epilogue math+stores, 8 skip TMEM loads
+  int act;
   float slope;
 };
 
-#define V2_THREADS 288
+#define V2_THREADS 416
 #define V2_PRODUCERS 128
 #define V2_MAX_STAGES 4
-#define V2_UNROLL 11
+#define V2_DEPTH 3
+
+// Compile-time geometry of one (Cin, Cout, KW) instance.
+template <int CIN, int COUT, int KW>
+struct V2Cfg {
+  static constexpr int NCHUNK = CIN / 8;
+  static constexpr int PITCH = 8 * KW + 2;    // halo row pitch in pixels
+  static constexpr int NPIX = 18 * PITCH;
+  // chunk stride in 16-byte units: >= NPIX, padded so the 8 lanes of a 16-byte store phase (chunk j, pixel p) hit
+  // 8 distinct bank groups: (j*CS + p) mod 8 distinct
+  static constexpr int cs() {
+    int c = NPIX;
+    if (NCHUNK >= 8) { while (c % 2 == 0) c++; }
+    else if (NCHUNK == 4) { while (c % 8 != 2) c++; }
+    else if (NCHUNK == 2) { while (c % 8 != 4) c++; }
+    return c;
+  }
+  static constexpr int CS = cs();
+  static constexpr int A_BYTES = (NCHUNK * CS * 16 + 127) & ~127;
+  static constexpr int W_BYTES = 9 * CIN * COUT * 2;
+  static constexpr int BB_BYTES = (2 * COUT * 4 + 127) & ~127;
+  static constexpr int ACC_STRIDE = KW * COUT;
+  static constexpr int TMEM_COLS = 2 * ACC_STRIDE <= 32 ? 32 : 2 * ACC_STRIDE <= 64 ? 64 : 2 * ACC_STRIDE <= 128 ? 128
+                                   : 2 * ACC_STRIDE <= 256 ? 256 : 512;
+  static constexpr int TOTAL_ITEMS = NPIX * NCHUNK;
+  static constexpr int UNROLL = (TOTAL_ITEMS + 2 * V2_PRODUCERS - 1) / (2 * V2_PRODUCERS);  // two load batches per tile
+  static_assert(2 * ACC_STRIDE <= 512, "TMEM budget");
+};
 
 namespace {
 __device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -58,6 +83,9 @@ __device__ __forceinline__ void bar_wait(uint64_t* b, uint32_t parity) {
 __device__ __forceinline__ void bar_arrive(uint64_t* b) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s_u32(b)) : "memory");
 }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -73,6 +101,22 @@ __device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// same, issued from a converged warp: `leader` is the elect.sync result, operands are warp-uniform
+__device__ __forceinline__ void mma_bf16_elect(uint32_t leader, uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, pe;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.ne.b32 pe, %5, 0;\n\t"
+      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred pe;\n\telect.sync _|pe, 0xffffffff;\n\tselp.u32 %0, 1, 0, pe;\n\t}" : "=r"(pred));
+  return pred;
 }
 __device__ __forceinline__ void ld16(uint32_t taddr, float* v) {
   uint32_t r[16];
@@ -103,35 +147,37 @@ __device__ __forceinline__ uint32_t pk_bf16(float a, float b) {
 }
 }  // namespace
 
+template <int CIN, int COUT, int KW>
 __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_constant__ V2Params P) {
+  using C = V2Cfg<CIN, COUT, KW>;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t full_bar[V2_MAX_STAGES], empty_bar[V2_MAX_STAGES], tfull_bar[2], tempty_bar[2];
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* w_s = smem;
-  float* bias_s = reinterpret_cast<float*>(smem + P.w_bytes);
-  float* beta_s = bias_s + P.Cout;
-  uint8_t* a_s = smem + P.w_bytes + ((2 * P.Cout * 4 + 127) & ~127);
+  float* bias_s = reinterpret_cast<float*>(smem + C::W_BYTES);
+  float* beta_s = bias_s + COUT;
+  uint8_t* a_s = smem + C::W_BYTES + C::BB_BYTES;
   const bool use_res = P.beta != nullptr;
 
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], V2_PRODUCERS); bar_init(&empty_bar[i], use_res ? 5 : 1); }
-    for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], 4); }
+    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], V2_PRODUCERS / 32); bar_init(&empty_bar[i], use_res ? 9 : 1); }
+    for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 4) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(&tmem_base_smem)),
-                 "r"((uint32_t)P.tmem_cols)
+                 "r"((uint32_t)C::TMEM_COLS)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   {
     const uint4* src = reinterpret_cast<const uint4*>(P.wpack);
     uint4* dst = reinterpret_cast<uint4*>(w_s);
-    for (int i = threadIdx.x; i < P.w_bytes / 16; i += V2_THREADS) dst[i] = __ldg(src + i);
-    for (int i = threadIdx.x; i < P.Cout; i += V2_THREADS) {
+    for (int i = threadIdx.x; i < C::W_BYTES / 16; i += V2_THREADS) dst[i] = __ldg(src + i);
+    for (int i = threadIdx.x; i < COUT; i += V2_THREADS) {
       bias_s[i] = P.bias[i];
       beta_s[i] = use_res ? P.beta[i] : 1.f;
     }
@@ -141,115 +187,154 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   __syncthreads();
   tc_after();
   const uint32_t tmem_base = tmem_base_smem;
-  const int nchunk = P.Cin >> 3;
 
   if (warp < 4) {
     // ================= producers: halo tile -> smem [chunk][pixel][8ch] =================
+    // cp.async (LDGSTS, 16 B, L2-only) straight into the UMMA layout; zero fill (src-size 0) is the conv padding.
+    // Up to V2_DEPTH tiles are in flight per thread: tile i is published (wait_group -> fence.proxy.async -> arrive)
+    // while tiles i+1..i+V2_DEPTH are still streaming in.
+    constexpr int ROW_ITEMS = C::PITCH * C::NCHUNK;
+    constexpr int PER_THREAD = (C::TOTAL_ITEMS + V2_PRODUCERS - 1) / V2_PRODUCERS;
+    const int depth = P.nstages - 1 < V2_DEPTH ? P.nstages - 1 : V2_DEPTH;  // stages >= tiles in flight + the one in MMA
     int it = 0;
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
       const int st = it % P.nstages;
       const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
       const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
-      const int gx0 = tx * 8 * P.KW - 1, gy0 = ty * 16 - 1;
-      bar_wait(&empty_bar[st], ph ^ 1);
-      uint4* dst = reinterpret_cast<uint4*>(a_s + (size_t)st * P.a_bytes);
-      const bf16* img = P.in + (size_t)n * P.H * P.W * P.Cin;
-      // flattened (halo row, pixel, chunk) items, V2_UNROLL independent 16-byte loads in flight per thread
-      const int row_items = P.pitch * nchunk, total = 18 * row_items;
-      int py = 0, rem = threadIdx.x;  // item = py * row_items + rem
-      while (rem >= row_items) { rem -= row_items; py++; }
-      for (int i0 = threadIdx.x; i0 < total; i0 += V2_PRODUCERS * V2_UNROLL) {
-        uint4 v[V2_UNROLL];
-        int off[V2_UNROLL];
-#pragma unroll
-        for (int u = 0; u < V2_UNROLL; u++) {
-          const int px = P.chunk_shift >= 0 ? (rem >> P.chunk_shift) : rem / nchunk;
-          const int j = rem - px * nchunk;
-          const int gy = gy0 + py, gx = gx0 + px;
-          const bool ok = (i0 + u * V2_PRODUCERS < total) && gy >= 0 && gy < P.H && gx >= 0 && gx < P.W;
-          off[u] = (i0 + u * V2_PRODUCERS < total) ? j * P.CS + py * P.pitch + px : -1;
-          v[u] = make_uint4(0, 0, 0, 0);
-          if (ok) v[u] = __ldg(reinterpret_cast<const uint4*>(img + ((size_t)gy * P.W + gx) * P.Cin + j * 8));
-          rem += V2_PRODUCERS;
-          while (rem >= row_items) { rem -= row_items; py++; }
-        }
-#pragma unroll
-        for (int u = 0; u < V2_UNROLL; u++)
-          if (off[u] >= 0) dst[off[u]] = v[u];
+      const int gx0 = tx * 8 * KW - 1, gy0 = ty * 16 - 1;
+      if (it >= depth) {
+        // publish the oldest in-flight tile BEFORE claiming a new stage, so publishing never waits on a stage release
+        if (depth == 3) asm volatile("cp.async.wait_group 2;" ::: "memory");
+        else if (depth == 2) asm volatile("cp.async.wait_group 1;" ::: "memory");
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) bar_arrive(&full_bar[(it - depth) % P.nstages]);
       }
-      fence_async_smem();
-      bar_arrive(&full_bar[st]);
+      bar_wait(&empty_bar[st], ph ^ 1);
+      const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
+      const bf16* img = P.in + (size_t)n * P.H * P.W * CIN;
+#pragma unroll
+      for (int u = 0; u < PER_THREAD; u++) {
+        const int i = (int)threadIdx.x + u * V2_PRODUCERS;
+        if (i < C::TOTAL_ITEMS && !(P.ablate & 1)) {
+          const int py = i / ROW_ITEMS, rem = i - py * ROW_ITEMS;
+          const int px = rem / C::NCHUNK, j = rem - px * C::NCHUNK;
+          const int gy = gy0 + py, gx = gx0 + px;
+          const bool ok = gy >= 0 && gy < P.H && gx >= 0 && gx < P.W;
+          const bf16* src = ok ? img + ((size_t)gy * P.W + gx) * CIN + j * 8 : img;
+          cp_async16(dst + (uint32_t)(j * C::CS + py * C::PITCH + px) * 16, src, ok ? 16u : 0u);
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
     }
+    // drain: publish the last `depth` tiles
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0)
+      for (int k = (it < depth ? it : depth); k > 0; k--) bar_arrive(&full_bar[(it - k) % P.nstages]);
   } else if (warp == 4) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
-      const uint32_t idesc = idesc_bf16(P.Cout);
-      const uint32_t a_lbo = (uint32_t)P.CS * 16, a_sbo = (uint32_t)P.pitch * 16;
-      const uint32_t b_lbo = (uint32_t)P.Cout * 16, b_sbo = 128;
-      const uint32_t w_addr = s_u32(w_s);
-      const int ksteps = P.Cin >> 4;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
-        const int st = it % P.nstages;
-        const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
-        const int as = it & 1;
-        bar_wait(&tempty_bar[as], (uint32_t)(((it >> 1) & 1) ^ 1));
-        bar_wait(&full_bar[st], ph);
-        tc_after();
-        const uint32_t a_addr = s_u32(a_s + (size_t)st * P.a_bytes);
-        // consecutive MMAs go to DIFFERENT accumulators (j innermost): back-to-back MMAs into the same TMEM columns
-        // serialise on the accumulate dependency (~200 cycles each at these small N), independent ones pipeline.
-        const uint32_t dcol0 = tmem_base + (uint32_t)(as * P.acc_stride);
-        for (int tap = 0; tap < 9; tap++) {
-          const int r = tap / 3, q = tap - 3 * r;
-          const uint32_t a0 = a_addr + (uint32_t)(r * P.pitch + q) * 16;
-          const uint32_t b0 = w_addr + (uint32_t)(tap * nchunk) * b_lbo;
-          for (int k = 0; k < ksteps; k++) {
-            const uint64_t bd = desc_ns(b0 + 2 * k * b_lbo, b_lbo, b_sbo);
-            const uint64_t ad = desc_ns(a0 + 2 * k * a_lbo, a_lbo, a_sbo);
-            const uint32_t acc = (tap | k) ? 1u : 0u;
-            for (int j = 0; j < P.KW; j++)
-              mma_bf16(dcol0 + (uint32_t)(j * P.Cout), ad + (uint64_t)(8 * j), bd, idesc, acc);  // +8 px = +128 B = +8 (16-B units)
+    // ================= MMA issuer: the warp stays converged, one elected lane issues =================
+    const uint32_t leader = elect_one();
+    constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(COUT >> 3) << 17) | (8u << 24);
+    constexpr uint32_t A_LBO = C::CS * 16, A_SBO = C::PITCH * 16, B_LBO = COUT * 16, B_SBO = 128;
+    constexpr int KSTEPS = CIN / 16;
+    const uint64_t bd0 = desc_ns(s_u32(w_s), B_LBO, B_SBO);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+      const int st = it % P.nstages;
+      const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
+      const int as = it & 1;
+      bar_wait(&tempty_bar[as], (uint32_t)(((it >> 1) & 1) ^ 1));
+      bar_wait(&full_bar[st], ph);
+      tc_after();
+      const uint64_t ad0 = desc_ns(s_u32(a_s + (size_t)st * C::A_BYTES), A_LBO, A_SBO);
+      if (!(P.ablate & 2)) {
+      const uint32_t dcol0 = tmem_base + (uint32_t)(as * C::ACC_STRIDE);
+      // consecutive MMAs target different accumulators (j innermost) so they pipeline; all descriptor offsets are
+      // compile-time immediates (16-byte units added to the start-address field)
+#pragma unroll
+      for (int tap = 0; tap < 9; tap++) {
+#pragma unroll
+        for (int k = 0; k < KSTEPS; k++) {
+#pragma unroll
+          for (int j = 0; j < KW; j++) {
+            constexpr int dummy = 0;
+            (void)dummy;
+            const uint32_t a_off = (uint32_t)((tap / 3) * C::PITCH + (tap % 3) + 8 * j + 2 * k * C::CS);
+            const uint32_t b_off = (uint32_t)((tap * C::NCHUNK + 2 * k) * COUT);
+            mma_bf16_elect(leader, dcol0 + (uint32_t)(j * COUT), ad0 + a_off, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
           }
         }
+      }
+      }
+      if (leader) {
         commit_to(&empty_bar[st]);
         commit_to(&tfull_bar[as]);
       }
+      __syncwarp();
     }
   } else {
-    // ================= epilogue =================
-    const int lg = warp & 3;
+    // ================= epilogue: 8 warps, two per TMEM lane group, each taking every other sub-tile =================
+    const int lg = warp & 3;                 // TMEM lane group this warp may access
+    const int half = (warp - 5) >> 2;        // 0: even sub-tiles, 1: odd sub-tiles
     const int m = lg * 32 + lane;
     const int ly = m >> 3, lx = m & 7;
+    const float4* bias4 = reinterpret_cast<const float4*>(bias_s);
+    const float4* beta4 = reinterpret_cast<const float4*>(beta_s);
     int it = 0;
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
       const int st = it % P.nstages;
       const int as = it & 1;
       const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
       const int y = ty * 16 + ly;
+      // residual = centre pixels of the input halo tile: pull them into registers as soon as the tile has landed and
+      // release the smem stage right away (the stage then only lives for load + MMA, not for the whole epilogue)
+      constexpr int NRES = (KW / 2) * (COUT / 8);
+      uint4 res[NRES];
+      if (use_res) {
+        bar_wait(&full_bar[st], (uint32_t)((it / P.nstages) & 1));
+        const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * C::A_BYTES);
+#pragma unroll
+        for (int jj = 0; jj < KW / 2; jj++) {
+          const int pc = (ly + 1) * C::PITCH + 8 * (2 * jj + half) + lx + 1;  // this thread's centre pixel
+#pragma unroll
+          for (int ch = 0; ch < COUT / 8; ch++) res[jj * (COUT / 8) + ch] = a_st[ch * C::CS + pc];
+        }
+        __syncwarp();
+        if (lane == 0) bar_arrive(&empty_bar[st]);
+      }
       bar_wait(&tfull_bar[as], (uint32_t)((it >> 1) & 1));
       tc_after();
-      const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * P.a_bytes);
-      for (int j = 0; j < P.KW; j++) {
-        const int x = (tx * P.KW + j) * 8 + lx;
-        const bool valid = (y < P.H) && (x < P.W);
-        const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * P.acc_stride + j * P.Cout);
-        bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * P.Cout;
-        const int pc = (ly + 1) * P.pitch + 8 * j + lx + 1;  // centre pixel of this thread in the halo tile
-        for (int c = 0; c < P.Cout; c += 16) {
-          float v[16];
-          ld16(taddr + c, v);
-          if (valid) {
 #pragma unroll
-            for (int i = 0; i < 16; i++) v[i] += bias_s[c + i];
+      for (int jj = 0; jj < KW / 2; jj++) {
+        const int j = 2 * jj + half;
+        const int x = (tx * KW + j) * 8 + lx;
+        const bool valid = (y < P.H) && (x < P.W);
+        const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE + j * COUT);
+        bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT;
+#pragma unroll
+        for (int c = 0; c < COUT; c += 16) {
+          float v[16];
+          if (!(P.ablate & 8)) ld16(taddr + c, v);
+          else { for (int i = 0; i < 16; i++) v[i] = 0.f; }
+          if (valid && !(P.ablate & 4)) {
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              const float4 b = bias4[(c >> 2) + q];
+              v[4 * q] += b.x; v[4 * q + 1] += b.y; v[4 * q + 2] += b.z; v[4 * q + 3] += b.w;
+            }
             if (use_res) {
-              const uint4 r0 = a_st[(c >> 3) * P.CS + pc], r1 = a_st[((c >> 3) + 1) * P.CS + pc];
+              const uint4 r0 = res[jj * (COUT / 8) + (c >> 3)], r1 = res[jj * (COUT / 8) + (c >> 3) + 1];
               const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
-              for (int i = 0; i < 8; i++) {
-                float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rr[i]));
-                v[2 * i] = v[2 * i] * beta_s[c + 2 * i] + f.x;
-                v[2 * i + 1] = v[2 * i + 1] * beta_s[c + 2 * i + 1] + f.y;
+              for (int q = 0; q < 4; q++) {
+                const float4 be = beta4[(c >> 2) + q];
+                const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rr[2 * q]));
+                const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rr[2 * q + 1]));
+                v[4 * q] = fmaf(v[4 * q], be.x, f0.x); v[4 * q + 1] = fmaf(v[4 * q + 1], be.y, f0.y);
+                v[4 * q + 2] = fmaf(v[4 * q + 2], be.z, f1.x); v[4 * q + 3] = fmaf(v[4 * q + 3], be.w, f1.y);
               }
             }
             if (P.act) {
@@ -266,17 +351,14 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       }
       tc_before();
       __syncwarp();
-      if (lane == 0) {
-        bar_arrive(&tempty_bar[as]);
-        if (use_res) bar_arrive(&empty_bar[st]);
-      }
+      if (lane == 0) bar_arrive(&tempty_bar[as]);
     }
   }
   tc_before();
   __syncthreads();
   if (warp == 4) {
     tc_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)P.tmem_cols)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
                  : "memory");
   }
 }
@@ -290,11 +372,10 @@ static uint16_t f2bf_v2(float f) {
   return (uint16_t)(u >> 16);
 }
 
+// instances: Head cnn1/cnn2 (16 ch), block-4 ResConv (32 ch), block-3 ResConv (64 ch)
 bool v2_supported(const Layer& L) {
-  if (L.kind != LK_CONV3 || L.stride != 1) return false;
-  if (L.cin % 16 || L.cout % 16 || L.cin != L.cin_pad) return false;
-  if (L.has_beta && L.cin != L.cout) return false;
-  return (size_t)9 * L.cin * L.cout * 2 <= 80 * 1024;  // weights must stay resident next to >= 2 A stages
+  if (L.kind != LK_CONV3 || L.stride != 1 || L.cin != L.cout || L.cin != L.cin_pad) return false;
+  return L.cin == 16 || L.cin == 32 || L.cin == 64;
 }
 
 // Packs Conv2d weights [Co][Ci][3][3] into the resident smem image [tap][Ci/8][Co][8] bf16.
@@ -314,6 +395,25 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
   return 0;
 }
 
+template <int CIN, int COUT, int KW>
+static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
+  using C = V2Cfg<CIN, COUT, KW>;
+  const size_t fixed = (size_t)C::W_BYTES + C::BB_BYTES;
+  const size_t budget = 220 * 1024 - fixed;
+  P.nstages = (int)std::min<size_t>(V2_MAX_STAGES, budget / C::A_BYTES);
+  if (P.nstages < 2) VFI_FAIL(h, VFI_E_ARG, "conv_v2: shared memory budget (Cin=%d)", CIN);
+  P.tiles_x = cdiv(P.W, 8 * KW);
+  P.tiles_y = cdiv(P.H, 16);
+  P.num_tiles = P.N * P.tiles_x * P.tiles_y;
+  const size_t smem = fixed + (size_t)P.nstages * C::A_BYTES;
+  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   224 * 1024));
+  const int grid = std::min(P.num_tiles, h->sm_count);
+  conv_v2_kernel<CIN, COUT, KW><<<grid, V2_THREADS, smem, s>>>(P);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
 int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, int H, int W, float slope,
               cudaStream_t s) {
   ProfScope _ps(h, PC_CONV_TC, s);
@@ -321,45 +421,14 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   V2Params P;
   memset(&P, 0, sizeof(P));
   P.in = in; P.out = out; P.wpack = L.wv2; P.bias = L.bias; P.beta = L.has_beta ? L.beta : nullptr;
-  P.N = N; P.H = H; P.W = W; P.Cin = L.cin; P.Cout = L.cout;
+  P.N = N; P.H = H; P.W = W;
   P.act = L.act ? 1 : 0;
   P.slope = slope;
-  P.w_bytes = 9 * L.cin * L.cout * 2;
-  const int nchunk = L.cin / 8;
-  P.chunk_shift = -1;
-  for (int b = 0; b < 6; b++) if ((1 << b) == nchunk) P.chunk_shift = b;
-  const size_t budget = 220 * 1024 - P.w_bytes - 1024;
-  int kw = 4;
-  for (; kw >= 1; kw >>= 1) {
-    if (2 * kw * L.cout > 512) continue;
-    if (kw > 1 && W <= 8 * (kw / 2)) continue;  // do not tile wider than the image needs
-    const int pitch = 8 * kw + 2, npix = 18 * pitch;
-    int cs = npix;
-    // 8 threads of a store phase cover (chunk j, pixel p) pairs: make j*CS + p distinct mod 8
-    const int want = nchunk >= 8 ? 1 : (nchunk == 4 ? 2 : (nchunk == 2 ? 4 : 0));
-    while (want && (nchunk >= 8 ? (cs % 2 == 0) : (cs % 8 != want))) cs++;
-    const size_t a_bytes = ((size_t)nchunk * cs * 16 + 127) & ~(size_t)127;
-    if (2 * a_bytes <= budget) {
-      P.KW = kw; P.pitch = pitch; P.npix = npix; P.CS = cs; P.a_bytes = (int)a_bytes;
-      P.nstages = (int)std::min<size_t>(V2_MAX_STAGES, budget / a_bytes);
-      break;
-    }
+  P.ablate = h->opt_v2_ablate;
+  switch (L.cin) {
+    case 16: return launch_v2<16, 16, 4>(h, P, s);
+    case 32: return launch_v2<32, 32, 4>(h, P, s);
+    case 64: return launch_v2<64, 64, 2>(h, P, s);
   }
-  if (!P.KW) VFI_FAIL(h, VFI_E_ARG, "conv_v2: no tile configuration fits (Cin=%d Cout=%d)", L.cin, L.cout);
-  P.acc_stride = P.KW * L.cout;
-  int cols = 2 * P.acc_stride;
-  P.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
-  P.tiles_x = cdiv(W, 8 * P.KW);
-  P.tiles_y = cdiv(H, 16);
-  P.num_tiles = N * P.tiles_x * P.tiles_y;
-  const size_t smem = (size_t)P.w_bytes + ((2 * L.cout * 4 + 127) & ~127) + (size_t)P.nstages * P.a_bytes;
-  static bool attr_set = false;
-  if (!attr_set) {
-    VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
-    attr_set = true;
-  }
-  const int grid = std::min(P.num_tiles, h->sm_count);
-  conv_v2_kernel<<<grid, V2_THREADS, smem, s>>>(P);
-  VFI_LAUNCHED(h);
-  return 0;
+  VFI_FAIL(h, VFI_E_ARG, "conv_v2: no instance for Cin=%d", L.cin);
 }
