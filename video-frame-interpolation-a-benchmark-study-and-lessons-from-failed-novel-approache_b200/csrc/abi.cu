@@ -48,8 +48,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_create(int device, vfi
 static void free_layers(vfi_handle* h) {
   for (int i = 0; i < VFI_NUM_LAYERS; i++) {
     Layer& L = h->layers[i];
-    cudaFree(L.w32); cudaFree(L.bias); cudaFree(L.beta); cudaFree(L.wtc); cudaFree(L.bias_tc); cudaFree(L.wv2);
-    L.w32 = L.bias = L.beta = L.bias_tc = nullptr;
+    cudaFree(L.w32); cudaFree(L.bias); cudaFree(L.beta); cudaFree(L.wtc); cudaFree(L.bias_tc); cudaFree(L.wv2); cudaFree(L.bias_v2);
+    L.w32 = L.bias = L.beta = L.bias_tc = L.bias_v2 = nullptr;
     L.wtc = nullptr;
     L.wv2 = nullptr;
   }
@@ -171,6 +171,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
     const bool tc = (id == 1 || id == 2 || id >= 4);
     if (tc) {
       if (int rc = tc_build_layer(h, L, w)) return rc;
+    }
+    if (tc || id == 3) {
       if (int rc = v2_build_layer(h, L, w)) return rc;
     }
   }
@@ -221,15 +223,16 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
   for (int i = 0; i < 5; i++) sl[i] = (16 >> i) * inv;
 
   // ---- workspace ----
-  size_t xin_e = 0, a0_e = 0, f_e = 0, low_e = 0;
+  size_t xin_e = 0, a0_e = 0, f_e = 0;
   for (int i = 0; i < 5; i++) {
     size_t hs = Hp / sl[i], wsz = Wp / sl[i];
     int c = BLOCK_C[i];
     xin_e = std::max(xin_e, (size_t)N * hs * wsz * (i == 0 ? 16 : 32));
     a0_e = std::max(a0_e, (size_t)N * (hs / 2) * (wsz / 2) * (c / 2));
     f_e = std::max(f_e, (size_t)N * (hs / 4) * (wsz / 4) * c);
-    low_e = std::max(low_e, (size_t)N * hs * wsz * 16);
   }
+  // the final block's lastconv output keeps only flow delta + mask (8-float texels) on the tcgen05 path
+  const int last_c = bf ? 8 : 16;
   const size_t px = (size_t)Hp * Wp;
   Carve cv{nullptr, 0};
   for (int pass = 0; pass < 2; pass++) {
@@ -241,13 +244,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     uint8_t* ht0 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
     uint8_t* ht1 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
     float* tdev = cv.take<float>(64);
-    float* state = cv.take<float>((size_t)N * px * 16);
-    float* fm = cv.take<float>((size_t)N * px * 8);
+    float* low[5];
+    for (int i = 0; i < 5; i++) low[i] = cv.take<float>((size_t)N * (Hp / sl[i]) * (Wp / sl[i]) * (i == 4 ? last_c : 16));
     uint8_t* xin = cv.take<uint8_t>(xin_e * esz);
     uint8_t* a0 = cv.take<uint8_t>(a0_e * esz);
     uint8_t* fa = cv.take<uint8_t>(f_e * esz);
     uint8_t* fb = cv.take<uint8_t>(f_e * esz);
-    float* low = cv.take<float>(low_e);
     if (pass == 0) {
       if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc;
       continue;
@@ -261,11 +263,15 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     if ((rc = k_head_cnn0(h, h->layers[0], imgs, ht0, NI, Hp, Wp, bf, s))) return rc;
     if ((rc = run_conv(h, h->layers[1], ht0, nullptr, ht1, NI, Hp / 2, Wp / 2, bf, false, s))) return rc;
     if ((rc = run_conv(h, h->layers[2], ht1, nullptr, ht0, NI, Hp / 2, Wp / 2, bf, false, s))) return rc;
-    if ((rc = k_deconv4_direct(h, h->layers[3], ht0, feats, NI, Hp / 2, Wp / 2, bf, 0, s))) return rc;
+    if (bf && h->opt_conv_v2) rc = k_conv_v2(h, h->layers[3], (const bf16*)ht0, (bf16*)feats, NI, Hp / 2, Wp / 2, h->slope, s);
+    else rc = k_deconv4_direct(h, h->layers[3], ht0, feats, NI, Hp / 2, Wp / 2, bf, 0, s);
+    if (rc) return rc;
+    LowSet lows;
+    memset(&lows, 0, sizeof(lows));
     for (int i = 0; i < 5; i++) {
       const int sc = sl[i], hs = Hp / sc, wsz = Wp / sc;
       const Layer* Lb = &h->layers[4 + 11 * i];
-      if ((rc = k_gather(h, imgs, feats, state, tdev, xin, B, T, Hp, Wp, sc, i == 0, bf, bf, s))) return rc;
+      if ((rc = k_gather(h, imgs, feats, lows, tdev, xin, B, T, Hp, Wp, sc, bf, bf, s))) return rc;
       if ((rc = run_conv(h, Lb[0], xin, nullptr, a0, N, hs, wsz, bf, bf, s))) return rc;
       if ((rc = run_conv(h, Lb[1], a0, nullptr, fa, N, hs / 2, wsz / 2, bf, false, s))) return rc;
       uint8_t *cur = fa, *nxt = fb;
@@ -273,12 +279,13 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
         if ((rc = run_conv(h, Lb[2 + j], cur, cur, nxt, N, hs / 4, wsz / 4, bf, false, s))) return rc;
         std::swap(cur, nxt);
       }
-      if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low, N, hs / 4, wsz / 4, false, h->slope, s);
-      else rc = k_deconv4_direct(h, Lb[10], cur, low, N, hs / 4, wsz / 4, false, 1, s);
+      const int lc = i == 4 ? last_c : 16;
+      if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low[i], N, hs / 4, wsz / 4, false, h->slope, s, lc);
+      else rc = k_deconv4_direct(h, Lb[10], cur, low[i], N, hs / 4, wsz / 4, false, 1, s);
       if (rc) return rc;
-      if ((rc = k_upsample(h, low, state, fm, N, Hp, Wp, sc, i == 0, i == 4, s))) return rc;
+      lows.p[i] = low[i]; lows.s[i] = sc; lows.c4[i] = lc / 4; lows.n = i + 1;
     }
-    if ((rc = k_final_blend(h, imgs, fm, hud_mask, tdev, out, out_f32, flow_out, B, T, H, W, Hp, Wp, s))) return rc;
+    if ((rc = k_final_blend(h, imgs, lows, hud_mask, tdev, out, out_f32, flow_out, B, T, H, W, Hp, Wp, s))) return rc;
   }
   return VFI_OK;
 }
@@ -303,7 +310,10 @@ extern "C" __attribute__((visibility("default"))) int vfi_warp_blend(vfi_handle*
     if ((rc = k_pad_rgbx(h, img0, imgs, N, H, W, H, W, s))) return rc;
     if ((rc = k_pad_rgbx(h, img1, imgs + (size_t)N * px * 4, N, H, W, H, W, s))) return rc;
     if ((rc = k_pack_fm(h, flow, mask, fm, N, H, W, H, W, s))) return rc;
-    if ((rc = k_final_blend(h, imgs, fm, nullptr, tdev, out, out_f32, nullptr, N, 1, H, W, H, W, s))) return rc;
+    LowSet lows;
+    memset(&lows, 0, sizeof(lows));
+    lows.p[0] = fm; lows.s[0] = 1; lows.c4[0] = 2; lows.n = 1;
+    if ((rc = k_final_blend(h, imgs, lows, nullptr, tdev, out, out_f32, nullptr, N, 1, H, W, H, W, s))) return rc;
   }
   return VFI_OK;
 }
@@ -340,7 +350,9 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
     int rc;
     if ((rc = k_f32_to_act(h, x, xb, nin, true, s))) return rc;
     if (layer == 3) {
-      if ((rc = k_deconv4_direct(h, L, xb, yb, N, Hin, Win, true, 0, s))) return rc;
+      if (h->opt_conv_v2) rc = k_conv_v2(h, L, xb, yb, N, Hin, Win, h->slope, s);
+      else rc = k_deconv4_direct(h, L, xb, yb, N, Hin, Win, true, 0, s);
+      if (rc) return rc;
       return k_act_to_f32(h, yb, y, nout, true, s);
     }
     const bf16* in = xb;

@@ -51,6 +51,7 @@ struct Layer {
   int cblk = 0, rows_total = 0, nsteps = 0, n_total = 0, b_box = 0;
   TcStep steps[VFI_MAX_STEPS];
   float* bias_tc = nullptr;  // bias laid out by accumulator column (n_total floats)
+  float* bias_v2 = nullptr;  // conv_v2.cu Head.cnn3 instance: bias per (phase, channel) column
   bf16* wv2 = nullptr;       // conv_v2.cu resident-weight image [tap][cin/8][cout][8] (null: layer not v2-capable)
 };
 
@@ -119,13 +120,20 @@ int vfi_red_reserve(vfi_handle* h, size_t bytes);
 // ---- elementwise.cu -----------------------------------------------------------------------
 int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s);
 int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, int NI, int Hp, int Wp, bool bf, cudaStream_t s);
-int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const float* state, const float* tsteps_dev,
-             void* out, int B, int T, int Hp, int Wp, int s_int, bool first, bool bf, bool phase, cudaStream_t s);
-int k_upsample(vfi_handle* h, const float* low13, float* state, float* fm, int N, int Hp, int Wp, int s_int,
-               bool first, bool last, cudaStream_t s);
-int k_final_blend(vfi_handle* h, const uint8_t* imgs, const float* fm, const uint8_t* hud, const float* tsteps_dev,
-                  uint8_t* out, float* out_f32, float* flow_out, int B, int T, int H, int W, int Hp, int Wp,
-                  cudaStream_t s);
+// The lastconv outputs of the blocks run so far.  low[k] = [N, Hp/s[k], Wp/s[k], 4*c4[k]] fp32 (flow 4, mask 1,
+// feat 8).  The reference's full-resolution flow / mask / feat tensors (IFBlock.forward's F.interpolate(scale) and
+// IFNet.forward's flow = flow + fd) are never materialised: a consumer evaluates, at the pixels it needs,
+//   flow = sum_k s[k] * bilerp(low[k][0:4]),  (mask, feat) = bilerp(low[n-1][4:13])        
+struct LowSet {
+  const float* p[5];
+  int s[5];
+  int c4[5];  // float4 per texel: 4 (16 channels) or 2 (the final block's compact flow+mask)
+  int n;
+};
+int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
+             void* out, int B, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s);
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B,
+                  int T, int H, int W, int Hp, int Wp, cudaStream_t s);
 int k_pack_fm(vfi_handle* h, const float* flow, const float* mask, float* fm, int N, int H, int W, int Hp, int Wp,
               cudaStream_t s);
 int k_f32_to_act(vfi_handle* h, const float* src, void* dst, size_t n, bool bf, cudaStream_t s);
@@ -143,9 +151,10 @@ int k_deconv4_direct(vfi_handle* h, const Layer& L, const void* in, void* out, i
 // ---- conv_tc.cu ---------------------------------------------------------------------------
 int tc_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch);  // packs wtc + step table
 // conv (mode 0/1) : in plain (stride 1) or phase planes (stride 2) bf16, out bf16 plain or phase (out_phase)
-// lastconv (deconv): in plain bf16, out = fp32 low13 [N,4Hin,4Win,16]
+// lastconv (deconv): in plain bf16, out = fp32 low [N,4Hin,4Win,low_c]: low_c = 16 (13 channels) or 8 (the final
+// block: only flow delta + mask, 5 channels, are consumed downstream)
 int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
-              int Win, bool out_phase, float slope, cudaStream_t s);
+              int Win, bool out_phase, float slope, cudaStream_t s, int low_c = 16);
 
 // ---- conv_v2.cu ---------------------------------------------------------------------------
 bool v2_supported(const Layer& L);

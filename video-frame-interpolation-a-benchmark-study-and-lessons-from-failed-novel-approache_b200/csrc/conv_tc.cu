@@ -30,6 +30,7 @@ struct TcParams {
   uint32_t sbo16, layout_type;
   int epi_mode;  // 0 conv->plain bf16, 1 conv->phase-plane bf16, 2 lastconv->pixel-shuffled fp32 low13
   int cout, act;
+  int low_c;     // epi_mode 2: floats per output texel, 16 (13 channels) or 8 (5 channels: flow delta + mask)
   float slope;
   const float* bias;
   const float* beta;
@@ -250,28 +251,48 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       } else {
-        // lastconv: 4 phases x 64 columns (52 used) -> PixelShuffle(2) -> low13 [N, 4Ho, 4Wo, 16] fp32
+        // lastconv: 4 phases x 64 columns (52 used) -> PixelShuffle(2) -> low [N, 4Ho, 4Wo, low_c] fp32
         float* ob = reinterpret_cast<float*>(P.out);
         const int H4 = 4 * P.Ho, W4 = 4 * P.Wo;
         for (int ph = 0; ph < 4; ph++) {
-          float v[64];
+          const int p = ph >> 1, q = ph & 1;
+          if (P.low_c == 16) {
+            float v[64];
 #pragma unroll
-          for (int c = 0; c < 64; c += 16) tmem_ld16(taddr + ph * 64 + c, v + c);
-          if (valid) {
-            const int p = ph >> 1, q = ph & 1;
+            for (int c = 0; c < 64; c += 16) tmem_ld16(taddr + ph * 64 + c, v + c);
+            if (valid) {
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-              const int i = k >> 1, jj = k & 1;
-              float o[16];
+              for (int k = 0; k < 4; k++) {
+                const int i = k >> 1, jj = k & 1;
+                float o[16];
 #pragma unroll
-              for (int cc = 0; cc < 13; cc++) o[cc] = v[cc * 4 + k] + __ldg(P.bias + cc * 4 + k);
-              o[13] = o[14] = o[15] = 0.f;
-              float4* dst = reinterpret_cast<float4*>(
-                  ob + (((size_t)n * H4 + 4 * y + 2 * p + i) * W4 + 4 * x + 2 * q + jj) * 16);
-              dst[0] = make_float4(o[0], o[1], o[2], o[3]);
-              dst[1] = make_float4(o[4], o[5], o[6], o[7]);
-              dst[2] = make_float4(o[8], o[9], o[10], o[11]);
-              dst[3] = make_float4(o[12], o[13], o[14], o[15]);
+                for (int cc = 0; cc < 13; cc++) o[cc] = v[cc * 4 + k] + __ldg(P.bias + cc * 4 + k);
+                o[13] = o[14] = o[15] = 0.f;
+                float4* dst = reinterpret_cast<float4*>(
+                    ob + (((size_t)n * H4 + 4 * y + 2 * p + i) * W4 + 4 * x + 2 * q + jj) * 16);
+                dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+                dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+                dst[2] = make_float4(o[8], o[9], o[10], o[11]);
+                dst[3] = make_float4(o[12], o[13], o[14], o[15]);
+              }
+            }
+          } else {
+            // final block: channels 0..4 (deconv channels 0..19) only
+            float v[32];
+            tmem_ld16(taddr + ph * 64, v);
+            tmem_ld16(taddr + ph * 64 + 16, v + 16);
+            if (valid) {
+#pragma unroll
+              for (int k = 0; k < 4; k++) {
+                const int i = k >> 1, jj = k & 1;
+                float o[5];
+#pragma unroll
+                for (int cc = 0; cc < 5; cc++) o[cc] = v[cc * 4 + k] + __ldg(P.bias + cc * 4 + k);
+                float4* dst = reinterpret_cast<float4*>(
+                    ob + (((size_t)n * H4 + 4 * y + 2 * p + i) * W4 + 4 * x + 2 * q + jj) * 8);
+                dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+                dst[1] = make_float4(o[4], 0.f, 0.f, 0.f);
+              }
             }
           }
         }
@@ -463,7 +484,7 @@ static int make_tmap_w(vfi_handle* h, CUtensorMap* out, const bf16* base, int cb
 }
 
 int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
-              int Win, bool out_phase, float slope, cudaStream_t s) {
+              int Win, bool out_phase, float slope, cudaStream_t s, int low_c) {
   ProfScope _ps(h, PC_CONV_TC, s);
   TcParams P;
   memset(&P, 0, sizeof(P));
@@ -502,6 +523,7 @@ int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residua
   P.layout_type = L.cblk == 64 ? 2 : L.cblk == 32 ? 4 : 6;
   P.epi_mode = L.kind == LK_DECONV4 ? 2 : (out_phase ? 1 : 0);
   P.cout = L.cout;
+  P.low_c = low_c;
   P.act = L.act ? 1 : 0;
   P.slope = slope;
   P.bias = L.bias;

@@ -147,7 +147,9 @@ __device__ __forceinline__ uint32_t pk_bf16(float a, float b) {
 }
 }  // namespace
 
-template <int CIN, int COUT, int KW>
+// EPI 0: conv (+ResConv) -> bf16 NHWC.  EPI 1: Head.cnn3 = ConvTranspose2d(16,4,4,2,1) run as a 3x3 conv whose 16
+// output columns are (output phase p,q) x (4 channels); the epilogue scatters them to the 2x2 output quad.
+template <int CIN, int COUT, int KW, int EPI>
 __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_constant__ V2Params P) {
   using C = V2Cfg<CIN, COUT, KW>;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   float* bias_s = reinterpret_cast<float*>(smem + C::W_BYTES);
   float* beta_s = bias_s + COUT;
   uint8_t* a_s = smem + C::W_BYTES + C::BB_BYTES;
-  const bool use_res = P.beta != nullptr;
+  const bool use_res = EPI == 0 && P.beta != nullptr;
 
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
@@ -313,6 +315,25 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
         const int x = (tx * KW + j) * 8 + lx;
         const bool valid = (y < P.H) && (x < P.W);
         const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE + j * COUT);
+        if constexpr (EPI == 1) {
+          static_assert(EPI != 1 || COUT == 16, "Head deconv instance");
+          float v[16];
+          ld16(taddr, v);
+          if (valid) {
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              const float4 b = bias4[q];
+              v[4 * q] += b.x; v[4 * q + 1] += b.y; v[4 * q + 2] += b.z; v[4 * q + 3] += b.w;
+            }
+#pragma unroll
+            for (int p = 0; p < 2; p++) {  // output row 2y+p, pixels 2x and 2x+1, 4 channels each
+              uint4 o;
+              o.x = pk_bf16(v[8 * p], v[8 * p + 1]); o.y = pk_bf16(v[8 * p + 2], v[8 * p + 3]);
+              o.z = pk_bf16(v[8 * p + 4], v[8 * p + 5]); o.w = pk_bf16(v[8 * p + 6], v[8 * p + 7]);
+              *reinterpret_cast<uint4*>(P.out + (((size_t)n * 2 * P.H + 2 * y + p) * (2 * P.W) + 2 * x) * 4) = o;
+            }
+          }
+        } else {
         bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT;
 #pragma unroll
         for (int c = 0; c < COUT; c += 16) {
@@ -348,6 +369,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
             *reinterpret_cast<uint4*>(op + c + 8) = o1;
           }
         }
+        }
       }
       tc_before();
       __syncwarp();
@@ -374,6 +396,7 @@ static uint16_t f2bf_v2(float f) {
 
 // instances: Head cnn1/cnn2 (16 ch), block-4 ResConv (32 ch), block-3 ResConv (64 ch)
 bool v2_supported(const Layer& L) {
+  if (L.kind == LK_DECONV4) return L.cin == 16 && L.cout == 4;  // Head.cnn3
   if (L.kind != LK_CONV3 || L.stride != 1 || L.cin != L.cout || L.cin != L.cin_pad) return false;
   return L.cin == 16 || L.cin == 32 || L.cin == 64;
 }
@@ -382,6 +405,31 @@ bool v2_supported(const Layer& L) {
 int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
   if (!v2_supported(L)) return 0;
   const int nch = L.cin / 8;
+  if (L.kind == LK_DECONV4) {
+    // ConvTranspose2d(16,4,4,2,1): output pixel (2y+p, 2x+q) reads input (y+dy, x+dx) through kernel element
+    // ky = p + 1 - 2*dy, kx = q + 1 - 2*dx.  Column = (2p+q)*4 + co of a 3x3 "conv" over the input grid; taps a
+    // phase does not use are zero.  w: [Ci][Co][4][4].
+    std::vector<uint16_t> pk((size_t)9 * 16 * 16, 0);
+    for (int tap = 0; tap < 9; tap++) {
+      const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+      for (int ph = 0; ph < 4; ph++) {
+        const int ky = (ph >> 1) + 1 - 2 * dy, kx = (ph & 1) + 1 - 2 * dx;
+        if (ky < 0 || ky > 3 || kx < 0 || kx > 3) continue;
+        for (int co = 0; co < 4; co++)
+          for (int ci = 0; ci < 16; ci++)
+            pk[(((size_t)tap * nch + ci / 8) * 16 + ph * 4 + co) * 8 + ci % 8] =
+                f2bf_v2(w[(((size_t)ci * 4 + co) * 4 + ky) * 4 + kx]);
+      }
+    }
+    VFI_CUDA(h, cudaMalloc(&L.wv2, pk.size() * 2));
+    VFI_CUDA(h, cudaMemcpy(L.wv2, pk.data(), pk.size() * 2, cudaMemcpyHostToDevice));
+    float b16[16], bh[4];
+    VFI_CUDA(h, cudaMemcpy(bh, L.bias, sizeof(bh), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 16; i++) b16[i] = bh[i & 3];
+    VFI_CUDA(h, cudaMalloc(&L.bias_v2, sizeof(b16)));
+    VFI_CUDA(h, cudaMemcpy(L.bias_v2, b16, sizeof(b16), cudaMemcpyHostToDevice));
+    return 0;
+  }
   std::vector<uint16_t> pk((size_t)9 * L.cin * L.cout);
   for (int tap = 0; tap < 9; tap++)
     for (int j = 0; j < nch; j++)
@@ -395,7 +443,7 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
   return 0;
 }
 
-template <int CIN, int COUT, int KW>
+template <int CIN, int COUT, int KW, int EPI>
 static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
   using C = V2Cfg<CIN, COUT, KW>;
   const size_t fixed = (size_t)C::W_BYTES + C::BB_BYTES;
@@ -406,10 +454,10 @@ static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
   P.tiles_y = cdiv(P.H, 16);
   P.num_tiles = P.N * P.tiles_x * P.tiles_y;
   const size_t smem = fixed + (size_t)P.nstages * C::A_BYTES;
-  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    224 * 1024));
   const int grid = std::min(P.num_tiles, h->sm_count);
-  conv_v2_kernel<CIN, COUT, KW><<<grid, V2_THREADS, smem, s>>>(P);
+  conv_v2_kernel<CIN, COUT, KW, EPI><<<grid, V2_THREADS, smem, s>>>(P);
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -425,10 +473,14 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   P.act = L.act ? 1 : 0;
   P.slope = slope;
   P.ablate = h->opt_v2_ablate;
+  if (L.kind == LK_DECONV4) {
+    P.bias = L.bias_v2; P.beta = nullptr; P.act = 0;
+    return launch_v2<16, 16, 4, 1>(h, P, s);
+  }
   switch (L.cin) {
-    case 16: return launch_v2<16, 16, 4>(h, P, s);
-    case 32: return launch_v2<32, 32, 4>(h, P, s);
-    case 64: return launch_v2<64, 64, 2>(h, P, s);
+    case 16: return launch_v2<16, 16, 4, 0>(h, P, s);
+    case 32: return launch_v2<32, 32, 4, 0>(h, P, s);
+    case 64: return launch_v2<64, 64, 2, 0>(h, P, s);
   }
   VFI_FAIL(h, VFI_E_ARG, "conv_v2: no instance for Cin=%d", L.cin);
 }

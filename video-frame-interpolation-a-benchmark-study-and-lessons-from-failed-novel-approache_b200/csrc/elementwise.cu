@@ -159,17 +159,80 @@ int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, i
 }
 
 // ------------------------------------------------------------------------------------------
+// F.interpolate(scale_factor=s, bilinear, align_corners=False) of a coarse tensor, evaluated at ONE full-resolution
+// pixel: area_pixel_compute_source_index(scale = 1/s) = max(0, (dst + 0.5)/s - 0.5)   
+struct Lerp {
+  int o00, o01, o10, o11;  // texel offsets (y*Wl + x) inside one image of the coarse tensor
+  float hx, lx, hy, ly;
+};
+__device__ __forceinline__ Lerp lerp_setup(int x, int y, int s, int Hl, int Wl) {
+  const float rs = 1.0f / (float)s;
+  float sy = fmaxf(rs * ((float)y + 0.5f) - 0.5f, 0.f);
+  float sx = fmaxf(rs * ((float)x + 0.5f) - 0.5f, 0.f);
+  int y0 = (int)sy, x0 = (int)sx;
+  int y1 = y0 + (y0 < Hl - 1 ? 1 : 0), x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
+  Lerp L;
+  L.ly = sy - (float)y0; L.lx = sx - (float)x0;
+  L.hy = 1.f - L.ly; L.hx = 1.f - L.lx;
+  L.o00 = y0 * Wl + x0; L.o01 = y0 * Wl + x1; L.o10 = y1 * Wl + x0; L.o11 = y1 * Wl + x1;
+  return L;
+}
+// channels 4k..4k+3 of a coarse tensor with c4 float4 per texel
+__device__ __forceinline__ float4 lerp4(const float4* img, const Lerp& L, int k, int c4) {
+  float4 a = __ldg(img + c4 * L.o00 + k), b = __ldg(img + c4 * L.o01 + k), c = __ldg(img + c4 * L.o10 + k),
+         d = __ldg(img + c4 * L.o11 + k);
+  float4 r;
+  r.x = L.hy * (L.hx * a.x + L.lx * b.x) + L.ly * (L.hx * c.x + L.lx * d.x);
+  r.y = L.hy * (L.hx * a.y + L.lx * b.y) + L.ly * (L.hx * c.y + L.lx * d.y);
+  r.z = L.hy * (L.hx * a.z + L.lx * b.z) + L.ly * (L.hx * c.z + L.lx * d.z);
+  r.w = L.hy * (L.hx * a.w + L.lx * b.w) + L.ly * (L.hx * c.w + L.lx * d.w);
+  return r;
+}
+// flow after the blocks in `lows` at full-resolution pixel (x,y) of item n: flow = flow + up(low_k)[:4] * s_k, in
+// block order.  MF = 1: also (mask, feat) = up(low_last)[4:13] in m[0..2];  MF = 2: mask only, in m[0].x.
+// A low at scale 1 (the last block at scale=1.0) is read directly: interpolate(x1) is the identity.
+template <int MF>
+__device__ __forceinline__ float4 state_at(const LowSet& lows, int n, int x, int y, int Hp, int Wp, float4* m) {
+  float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    if (k < lows.n) {
+      const int sk = lows.s[k], c4 = lows.c4[k], Hl = Hp / sk, Wl = Wp / sk;
+      const float4* img = reinterpret_cast<const float4*>(lows.p[k]) + (size_t)n * Hl * Wl * c4;
+      const bool last = k == lows.n - 1;
+      if (sk == 1) {
+        const float4* px = img + (size_t)(y * Wl + x) * c4;
+        const float4 r = __ldg(px);
+        fl.x += r.x; fl.y += r.y; fl.z += r.z; fl.w += r.w;
+        if (MF == 1 && last) { m[0] = __ldg(px + 1); m[1] = __ldg(px + 2); m[2] = __ldg(px + 3); }
+        if (MF == 2 && last) m[0] = __ldg(px + 1);
+      } else {
+        const Lerp L = lerp_setup(x, y, sk, Hl, Wl);
+        const float4 r = lerp4(img, L, 0, c4);
+        const float fs = (float)sk;
+        fl.x += r.x * fs; fl.y += r.y * fs; fl.z += r.z * fs; fl.w += r.w * fs;
+        if (MF == 1 && last) { m[0] = lerp4(img, L, 1, c4); m[1] = lerp4(img, L, 2, c4); m[2] = lerp4(img, L, 3, c4); }
+        if (MF == 2 && last) m[0] = lerp4(img, L, 1, c4);
+      }
+    }
+  }
+  return fl;
+}
+
+// ------------------------------------------------------------------------------------------
 // Block-input gather.  Produces IFBlock's conv0 input at 1/s resolution in ONE pass:
 //   block 0 : cat(img0, img1, f0, f1, t)                               -> 15 ch (+1 zero)
 //   block i : cat(warp(img0,F01), warp(img1,F10), warp(f0,F01), warp(f1,F10), t, mask, feat, flow/s)
 //                                                                       -> 28 ch (+4 zero)
 // followed by F.interpolate(1/s, bilinear, align_corners=False), which for s in {2,4,8,16,32}
 // is exactly the mean of the 2x2 full-resolution pixels at offsets s/2-1, s/2,
-// so only those pixels are ever warped.  The 28-channel full-resolution concat of the reference
-// never exists.  Output NHWC, plain or split into the 4 stride-2 phase planes the conv0a TMA reads.
+// so only those pixels are ever warped, and flow / mask / feat are evaluated only there, straight from the
+// coarse lastconv outputs of the previous blocks (state_at).  Neither the 28-channel full-resolution concat
+// nor the full-resolution flow of the reference ever exists.  Output NHWC, plain or split into the 4 stride-2
+// phase planes the conv0a TMA reads.
 template <typename T, bool FIRST>
 __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats,
-                              const float* __restrict__ state, const float* __restrict__ tsteps,
+                              const __grid_constant__ LowSet lows, const float* __restrict__ tsteps,
                               T* __restrict__ out, int B, int Tn, int Hp, int Wp, int s, int phase) {
   constexpr int C = FIRST ? 16 : 32;
   const int Hs = Hp / s, Ws = Wp / s;
@@ -204,8 +267,9 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
         Act<T>::load4(f1 + 4 * ((size_t)y * Wp + x), v);
         acc[10] += v[0]; acc[11] += v[1]; acc[12] += v[2]; acc[13] += v[3];
       } else {
-        const float4* st = reinterpret_cast<const float4*>(state + (((size_t)n * Hp + y) * Wp + x) * 16);
-        float4 fl = __ldg(st), s1 = __ldg(st + 1), s2 = __ldg(st + 2), s3 = __ldg(st + 3);
+        float4 m[3];
+        const float4 fl = state_at<1>(lows, n, x, y, Hp, Wp, m);
+        const float4 s1 = m[0], s2 = m[1], s3 = m[2];
         Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
         Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
         float rgb[3];
@@ -244,13 +308,14 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
   for (int c = 0; c < C; c += 8) Act<T>::store8(out + o + c, acc + c);
 }
 
-int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const float* state, const float* tsteps_dev,
-             void* out, int B, int T, int Hp, int Wp, int s_int, bool first, bool bf, bool phase, cudaStream_t s) {
+int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
+             void* out, int B, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s) {
   ProfScope _ps(h, PC_GATHER, s);
   size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
   int grid = cdiv(total, 128);
+  const bool first = lows.n == 0;
 #define GATHER_LAUNCH(TT, F)                                                                             \
-  gather_kernel<TT, F><<<grid, 128, 0, s>>>(imgs, (const TT*)feats, state, tsteps_dev, (TT*)out, B, T, Hp, Wp, \
+  gather_kernel<TT, F><<<grid, 128, 0, s>>>(imgs, (const TT*)feats, lows, tsteps_dev, (TT*)out, B, T, Hp, Wp, \
                                             s_int, phase ? 1 : 0)
   if (bf) { if (first) GATHER_LAUNCH(bf16, true); else GATHER_LAUNCH(bf16, false); }
   else    { if (first) GATHER_LAUNCH(float, true); else GATHER_LAUNCH(float, false); }
@@ -260,77 +325,19 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const float*
 }
 
 // ------------------------------------------------------------------------------------------
-// IFBlock tail: tmp = F.interpolate(lastconv(feat), scale_factor=s, bilinear, align_corners=False);
-// flow += tmp[:, :4] * s; mask = tmp[:, 4:5]; feat = tmp[:, 5:]          (Appendix A.2)
-// low13: [N, Hp/s, Wp/s, 16] fp32 (13 used).  state: [N,Hp,Wp,16] fp32 = flow(4) mask(1) feat(8).
-// LAST: only flow + mask are needed downstream -> compact fm [N,Hp,Wp,8].
-template <bool LAST>
-__global__ void upsample_kernel(const float* __restrict__ low, float* __restrict__ state, float* __restrict__ fm,
-                                int N, int Hp, int Wp, int s, int first) {
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  size_t total = (size_t)N * Hp * Wp;
-  if (i >= total) return;
-  int x = (int)(i % Wp), y = (int)((i / Wp) % Hp), n = (int)(i / ((size_t)Wp * Hp));
-  const int Hl = Hp / s, Wl = Wp / s;
-  // area_pixel_compute_source_index(scale = 1/s, align_corners=False): max(0, (dst+0.5)/s - 0.5)
-  const float rs = 1.0f / (float)s;
-  float sy = fmaxf(rs * ((float)y + 0.5f) - 0.5f, 0.f);
-  float sx = fmaxf(rs * ((float)x + 0.5f) - 0.5f, 0.f);
-  int y0 = (int)sy, x0 = (int)sx;
-  int y1 = y0 + (y0 < Hl - 1 ? 1 : 0), x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
-  float ly = sy - (float)y0, lx = sx - (float)x0;
-  float hy = 1.f - ly, hx = 1.f - lx;
-  const float4* p00 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y0) * Wl + x0) * 16);
-  const float4* p01 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y0) * Wl + x1) * 16);
-  const float4* p10 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y1) * Wl + x0) * 16);
-  const float4* p11 = reinterpret_cast<const float4*>(low + (((size_t)n * Hl + y1) * Wl + x1) * 16);
-  constexpr int NV = LAST ? 2 : 4;
-  float4 r[NV];
-#pragma unroll
-  for (int k = 0; k < NV; k++) {
-    float4 a = __ldg(p00 + k), b = __ldg(p01 + k), c = __ldg(p10 + k), d = __ldg(p11 + k);
-    r[k].x = hy * (hx * a.x + lx * b.x) + ly * (hx * c.x + lx * d.x);
-    r[k].y = hy * (hx * a.y + lx * b.y) + ly * (hx * c.y + lx * d.y);
-    r[k].z = hy * (hx * a.z + lx * b.z) + ly * (hx * c.z + lx * d.z);
-    r[k].w = hy * (hx * a.w + lx * b.w) + ly * (hx * c.w + lx * d.w);
-  }
-  const float fs = (float)s;
-  float4 fl = make_float4(r[0].x * fs, r[0].y * fs, r[0].z * fs, r[0].w * fs);
-  float4* st = reinterpret_cast<float4*>(state + i * 16);
-  if (!first) {
-    float4 o = st[0];
-    fl.x += o.x; fl.y += o.y; fl.z += o.z; fl.w += o.w;
-  }
-  if constexpr (LAST) {
-    float4* f = reinterpret_cast<float4*>(fm + i * 8);
-    f[0] = fl;
-    f[1] = make_float4(r[1].x, 0.f, 0.f, 0.f);
-  } else {
-    st[0] = fl; st[1] = r[1]; st[2] = r[2]; st[3] = r[3];
-  }
-}
-int k_upsample(vfi_handle* h, const float* low13, float* state, float* fm, int N, int Hp, int Wp, int s_int,
-               bool first, bool last, cudaStream_t s) {
-  ProfScope _ps(h, PC_UPSAMPLE, s);
-  size_t total = (size_t)N * Hp * Wp;
-  if (last) upsample_kernel<true><<<cdiv(total, 256), 256, 0, s>>>(low13, state, fm, N, Hp, Wp, s_int, first ? 1 : 0);
-  else upsample_kernel<false><<<cdiv(total, 256), 256, 0, s>>>(low13, state, fm, N, Hp, Wp, s_int, first ? 1 : 0);
-  VFI_LAUNCHED(h);
-  return 0;
-}
-
-// ------------------------------------------------------------------------------------------
 // IFNet tail + wrapper epilogue, fused (north_star kernel (b)):
+//   flow = sum of the five blocks' upsampled deltas, mask = the last block's   (Appendix A.2; state_at)
 //   warped0 = warp(img0, flow[:, :2]); warped1 = warp(img1, flow[:, 2:4]); m = sigmoid(mask)
-//   merged = warped0*m + warped1*(1-m)                                   (Appendix A.2)
+//   merged = warped0*m + warped1*(1-m)
 //   unpad (base.py:227-229); (x*255).clip(0,255).astype(uint8) truncation (base.py:188-201)
 //   HUD composite frame[mask] = (f0 if t<0.5 else f1)[mask]              (adaptive_pipeline.py:399-409)
-// One thread per 4 output pixels: fm is read as 2x float4 per pixel, the u8 result is written as
+// One thread per 4 output pixels: the u8 result is written as
 // three 32-bit words (12 B, 4-byte aligned when W % 4 == 0).
-__device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img1, const float* fmp, int x, int y,
-                                         int Hp, int Wp, float* o /*3*/, float4* flow_o) {
-  float4 fl = __ldg(reinterpret_cast<const float4*>(fmp));
-  float mk = __ldg(fmp + 4);
+__device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img1, const LowSet& lows, int n, int x,
+                                         int y, int Hp, int Wp, float* o /*3*/, float4* flow_o) {
+  float4 m4;
+  const float4 fl = state_at<2>(lows, n, x, y, Hp, Wp, &m4);
+  const float mk = m4.x;
   Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
   Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
   float a[3], c[3];
@@ -345,10 +352,10 @@ __device__ __forceinline__ uint8_t quant_u8(float v) {
   v = fminf(fmaxf(v * 255.0f, 0.f), 255.f);
   return (uint8_t)(int)v;  // truncation, as numpy astype(uint8)
 }
-__global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const float* __restrict__ fm,
-                                   const uint8_t* __restrict__ hud, const float* __restrict__ tsteps,
-                                   uint8_t* __restrict__ out, float* __restrict__ out_f32,
-                                   float* __restrict__ flow_out, int B, int Tn, int H, int W, int Hp, int Wp) {
+__global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const __grid_constant__ LowSet lows, const uint8_t* __restrict__ hud,
+                                   const float* __restrict__ tsteps, uint8_t* __restrict__ out,
+                                   float* __restrict__ out_f32, float* __restrict__ flow_out, int B, int Tn, int H,
+                                   int W, int Hp, int Wp) {
   const int W4 = (W + 3) / 4;
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   size_t total = (size_t)B * Tn * H * W4;
@@ -367,7 +374,7 @@ __global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const float
     int x = x0 + k;
     float o[3];
     float4 fl;
-    blend_px(img0, img1, fm + (((size_t)n * Hp + y) * Wp + x) * 8, x, y, Hp, Wp, o, &fl);
+    blend_px(img0, img1, lows, n, x, y, Hp, Wp, o, &fl);
     size_t opix = ((size_t)n * H + y) * W + x;
     if (out_f32) { out_f32[opix * 3] = o[0]; out_f32[opix * 3 + 1] = o[1]; out_f32[opix * 3 + 2] = o[2]; }
     if (flow_out) reinterpret_cast<float4*>(flow_out)[opix] = fl;
@@ -388,13 +395,12 @@ __global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const float
     for (int k = 0; k < 3 * cnt; k++) op[k] = px[k];
   }
 }
-int k_final_blend(vfi_handle* h, const uint8_t* imgs, const float* fm, const uint8_t* hud, const float* tsteps_dev,
-                  uint8_t* out, float* out_f32, float* flow_out, int B, int T, int H, int W, int Hp, int Wp,
-                  cudaStream_t s) {
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B,
+                  int T, int H, int W, int Hp, int Wp, cudaStream_t s) {
   ProfScope _ps(h, PC_BLEND, s);
   size_t total = (size_t)B * T * H * ((W + 3) / 4);
-  final_blend_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, fm, hud, tsteps_dev, out, out_f32, flow_out, B, T, H, W,
-                                                      Hp, Wp);
+  final_blend_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, lows, hud, tsteps_dev, out, out_f32, flow_out,
+                                                      B, T, H, W, Hp, Wp);
   VFI_LAUNCHED(h);
   return 0;
 }
