@@ -308,12 +308,214 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
   for (int c = 0; c < C; c += 8) Act<T>::store8(out + o + c, acc + c);
 }
 
+// ------------------------------------------------------------------------------------------
+// Tiled evaluation of the same state for kernels that visit EVERY full-resolution pixel (the gathers of the two
+// finest blocks and the final blend).  A CTA owns a 32x32 pixel tile.  Stage 1 writes, for every coarse level, the
+// x-interpolated rows that cover the tile into shared memory: T[row][x] = hx*a + lx*b -- exactly the inner terms of
+// bilinear upsampling, out = hy*(hx*a + lx*b) + ly*(hx*c + lx*d).  Stage 2 finishes a pixel with two conflict-free
+// LDS.128 per level (hy*T[y0][x] + ly*T[y1][x]): the arithmetic, and so the result, is bit-identical to state_at,
+// with ~1.2 global texel loads per pixel instead of 16 per level.
+#define TL_W 32
+#define TL_H 32
+#define TL_THREADS 256
+struct Staged {
+  int off[5];   // float4 offset of level k's patch
+  int r_lo[5];  // first staged coarse row
+  int nv[5];    // float4 per texel staged
+};
+__host__ __device__ __forceinline__ int tl_rows(int s) { return (TL_H / s > 1 ? TL_H / s : 1) + 2; }
+static size_t tl_smem_bytes(const LowSet& lows, int mf) {
+  size_t n = 0;
+  for (int k = 0; k < lows.n; k++) {
+    if (lows.s[k] == 1) continue;
+    const int nv = (k == lows.n - 1) ? (mf == 1 ? 4 : mf == 2 ? 2 : 1) : 1;
+    n += (size_t)tl_rows(lows.s[k]) * nv * TL_W;
+  }
+  return n * sizeof(float4);
+}
+template <int MF>
+__device__ __forceinline__ void stage_lows(const LowSet& lows, int n, int tx0, int ty0, int Hp, int Wp, float4* sm,
+                                           Staged& S) {
+  int off = 0;
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    if (k < lows.n && lows.s[k] > 1) {
+      const int sk = lows.s[k], c4 = lows.c4[k], Hl = Hp / sk, Wl = Wp / sk;
+      const int nv = (k == lows.n - 1) ? (MF == 1 ? 4 : MF == 2 ? 2 : 1) : 1;
+      const int rows = tl_rows(sk);
+      const float rs = 1.0f / (float)sk;
+      const int r_lo = (int)fmaxf(rs * ((float)ty0 + 0.5f) - 0.5f, 0.f);
+      S.off[k] = off; S.r_lo[k] = r_lo; S.nv[k] = nv;
+      const float4* img = reinterpret_cast<const float4*>(lows.p[k]) + (size_t)n * Hl * Wl * c4;
+      for (int idx = threadIdx.x; idx < rows * TL_W; idx += TL_THREADS) {
+        const int row = idx / TL_W, xl = idx % TL_W;
+        const int ry = min(r_lo + row, Hl - 1);
+        const float sx = fmaxf(rs * ((float)min(tx0 + xl, Wp - 1) + 0.5f) - 0.5f, 0.f);  // partial tiles: clamp
+        const int x0 = (int)sx, x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
+        const float lx = sx - (float)x0, hx = 1.f - lx;
+        const float4* pa = img + (size_t)(ry * Wl + x0) * c4;
+        const float4* pb = img + (size_t)(ry * Wl + x1) * c4;
+        for (int v = 0; v < nv; v++) {
+          const float4 a = __ldg(pa + v), b = __ldg(pb + v);
+          sm[off + (row * nv + v) * TL_W + xl] =
+              make_float4(hx * a.x + lx * b.x, hx * a.y + lx * b.y, hx * a.z + lx * b.z, hx * a.w + lx * b.w);
+        }
+      }
+      off += rows * nv * TL_W;
+    }
+  }
+}
+// state_at for pixel (x,y) = tile-local column xl, from the staged rows
+template <int MF>
+__device__ __forceinline__ float4 eval_staged(const LowSet& lows, const Staged& S, const float4* sm, int n, int x,
+                                              int y, int xl, int Hp, int Wp, float4* m) {
+  float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    if (k < lows.n) {
+      const int sk = lows.s[k], Hl = Hp / sk;
+      const bool last = k == lows.n - 1;
+      if (sk == 1) {
+        const int c4 = lows.c4[k];
+        const float4* px = reinterpret_cast<const float4*>(lows.p[k]) + ((size_t)n * Hp * Wp + (size_t)y * Wp + x) * c4;
+        const float4 r = __ldg(px);
+        fl.x += r.x; fl.y += r.y; fl.z += r.z; fl.w += r.w;
+        if (MF == 1 && last) { m[0] = __ldg(px + 1); m[1] = __ldg(px + 2); m[2] = __ldg(px + 3); }
+        if (MF == 2 && last) m[0] = __ldg(px + 1);
+      } else {
+        const float rs = 1.0f / (float)sk;
+        const float sy = fmaxf(rs * ((float)y + 0.5f) - 0.5f, 0.f);
+        const int y0 = (int)sy, y1 = y0 + (y0 < Hl - 1 ? 1 : 0);
+        const float ly = sy - (float)y0, hy = 1.f - ly;
+        const int nv = S.nv[k];
+        const float4* r0 = sm + S.off[k] + (y0 - S.r_lo[k]) * nv * TL_W + xl;
+        const float4* r1 = sm + S.off[k] + (y1 - S.r_lo[k]) * nv * TL_W + xl;
+        const float4 a = r0[0], c = r1[0];
+        const float fs = (float)sk;
+        fl.x += (hy * a.x + ly * c.x) * fs; fl.y += (hy * a.y + ly * c.y) * fs;
+        fl.z += (hy * a.z + ly * c.z) * fs; fl.w += (hy * a.w + ly * c.w) * fs;
+        if (MF != 0 && last) {
+#pragma unroll
+          for (int v = 1; v < (MF == 1 ? 4 : 2); v++) {
+            const float4 p = r0[v * TL_W], q = r1[v * TL_W];
+            m[v - 1] = make_float4(hy * p.x + ly * q.x, hy * p.y + ly * q.y, hy * p.z + ly * q.z, hy * p.w + ly * q.w);
+          }
+        }
+      }
+    }
+  }
+  return fl;
+}
+
+// one warped tap of a block input (channels as in gather_kernel), accumulated into acc[28]
+template <typename T>
+__device__ __forceinline__ void gather_tap(const uint8_t* img0, const uint8_t* img1, const T* f0, const T* f1,
+                                           const float4 fl, const float4* m, int x, int y, int Hp, int Wp,
+                                           float* acc) {
+  Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
+  Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
+  float rgb[3], v[4];
+  sample_rgbx(img0, b0, rgb);
+  acc[0] += rgb[0]; acc[1] += rgb[1]; acc[2] += rgb[2];
+  sample_rgbx(img1, b1, rgb);
+  acc[3] += rgb[0]; acc[4] += rgb[1]; acc[5] += rgb[2];
+  sample_feat<T>(f0, b0, v);
+  acc[6] += v[0]; acc[7] += v[1]; acc[8] += v[2]; acc[9] += v[3];
+  sample_feat<T>(f1, b1, v);
+  acc[10] += v[0]; acc[11] += v[1]; acc[12] += v[2]; acc[13] += v[3];
+  acc[15] += m[0].x;
+  acc[16] += m[0].y; acc[17] += m[0].z; acc[18] += m[0].w;
+  acc[19] += m[1].x; acc[20] += m[1].y; acc[21] += m[1].z; acc[22] += m[1].w;
+  acc[23] += m[2].x;
+  acc[24] += fl.x; acc[25] += fl.y; acc[26] += fl.z; acc[27] += fl.w;
+}
+
+// gather_kernel for the blocks at s = 1 and s = 2, where the taps cover every full-resolution pixel
+template <typename T, int S>
+__global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* __restrict__ imgs,
+                                                                 const T* __restrict__ feats,
+                                                                 const __grid_constant__ LowSet lows,
+                                                                 const float* __restrict__ tsteps,
+                                                                 T* __restrict__ out, int B, int Tn, int Hp, int Wp,
+                                                                 int phase) {
+  extern __shared__ float4 tl_sm[];
+  const int tiles_x = Wp / TL_W, tiles_y = Hp / TL_H;
+  const int tx = blockIdx.x % tiles_x, ty = (blockIdx.x / tiles_x) % tiles_y, n = blockIdx.x / (tiles_x * tiles_y);
+  const int tx0 = tx * TL_W, ty0 = ty * TL_H;
+  Staged St;
+  stage_lows<1>(lows, n, tx0, ty0, Hp, Wp, tl_sm, St);
+  __syncthreads();
+  const int b = n / Tn;
+  const float t = tsteps[n % Tn];
+  const size_t plane = (size_t)Hp * Wp;
+  const uint8_t* img0 = imgs + ((size_t)b) * plane * 4;
+  const uint8_t* img1 = imgs + ((size_t)(B + b)) * plane * 4;
+  const T* f0 = feats + ((size_t)b) * plane * 4;
+  const T* f1 = feats + ((size_t)(B + b)) * plane * 4;
+  const int Hs = Hp / S, Ws = Wp / S;
+  constexpr int NOUT = S == 1 ? 4 : 1;  // outputs per thread
+#pragma unroll 1
+  for (int i = 0; i < NOUT; i++) {
+    float acc[32];
+#pragma unroll
+    for (int c = 0; c < 32; c++) acc[c] = 0.f;
+    int X, Y;
+    if (S == 1) {
+      const int xl = threadIdx.x % TL_W, yl = threadIdx.x / TL_W + (TL_THREADS / TL_W) * i;
+      X = tx0 + xl; Y = ty0 + yl;
+      float4 m[3];
+      const float4 fl = eval_staged<1>(lows, St, tl_sm, n, X, Y, xl, Hp, Wp, m);
+      gather_tap<T>(img0, img1, f0, f1, fl, m, X, Y, Hp, Wp, acc);
+    } else {
+      const int Xl = threadIdx.x % (TL_W / 2), Yl = threadIdx.x / (TL_W / 2);
+      X = tx0 / 2 + Xl; Y = ty0 / 2 + Yl;
+#pragma unroll 1
+      for (int d = 0; d < 4; d++) {
+        const int xl = 2 * Xl + (d & 1), x = tx0 + xl, y = ty0 + 2 * Yl + (d >> 1);
+        float4 m[3];
+        const float4 fl = eval_staged<1>(lows, St, tl_sm, n, x, y, xl, Hp, Wp, m);
+        gather_tap<T>(img0, img1, f0, f1, fl, m, x, y, Hp, Wp, acc);
+      }
+#pragma unroll
+      for (int c = 0; c < 32; c++) acc[c] *= 0.25f;
+    }
+    acc[14] = t;
+    const float inv = 1.0f / (float)S;
+    acc[24] *= inv; acc[25] *= inv; acc[26] *= inv; acc[27] *= inv;
+    size_t o;
+    if (phase) {
+      const int H2 = Hs / 2, W2 = Ws / 2;
+      o = ((((size_t)n * 4 + (Y & 1) * 2 + (X & 1)) * H2 + (Y >> 1)) * W2 + (X >> 1)) * 32;
+    } else {
+      o = (((size_t)n * Hs + Y) * Ws + X) * 32;
+    }
+#pragma unroll
+    for (int c = 0; c < 32; c += 8) Act<T>::store8(out + o + c, acc + c);
+  }
+}
+
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
              void* out, int B, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s) {
   ProfScope _ps(h, PC_GATHER, s);
   size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
   int grid = cdiv(total, 128);
   const bool first = lows.n == 0;
+  if (!first && s_int <= 2 && Hp % TL_H == 0 && Wp % TL_W == 0) {
+    const size_t smem = tl_smem_bytes(lows, 1);
+    const int tgrid = B * T * (Hp / TL_H) * (Wp / TL_W);
+#define GT_LAUNCH(TT, SS)                                                                                          \
+  do {                                                                                                             \
+    VFI_CUDA(h, cudaFuncSetAttribute(gather_tile_kernel<TT, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                     96 * 1024));                                                                  \
+    gather_tile_kernel<TT, SS><<<tgrid, TL_THREADS, smem, s>>>(imgs, (const TT*)feats, lows, tsteps_dev, (TT*)out, \
+                                                               B, T, Hp, Wp, phase ? 1 : 0);                       \
+  } while (0)
+    if (bf) { if (s_int == 1) GT_LAUNCH(bf16, 1); else GT_LAUNCH(bf16, 2); }
+    else    { if (s_int == 1) GT_LAUNCH(float, 1); else GT_LAUNCH(float, 2); }
+#undef GT_LAUNCH
+    VFI_LAUNCHED(h);
+    return 0;
+  }
 #define GATHER_LAUNCH(TT, F)                                                                             \
   gather_kernel<TT, F><<<grid, 128, 0, s>>>(imgs, (const TT*)feats, lows, tsteps_dev, (TT*)out, B, T, Hp, Wp, \
                                             s_int, phase ? 1 : 0)
@@ -333,11 +535,8 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
 //   HUD composite frame[mask] = (f0 if t<0.5 else f1)[mask]              (adaptive_pipeline.py:399-409)
 // One thread per 4 output pixels: the u8 result is written as
 // three 32-bit words (12 B, 4-byte aligned when W % 4 == 0).
-__device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img1, const LowSet& lows, int n, int x,
-                                         int y, int Hp, int Wp, float* o /*3*/, float4* flow_o) {
-  float4 m4;
-  const float4 fl = state_at<2>(lows, n, x, y, Hp, Wp, &m4);
-  const float mk = m4.x;
+__device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img1, const float4 fl, const float mk,
+                                         int x, int y, int Hp, int Wp, float* o /*3*/) {
   Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
   Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
   float a[3], c[3];
@@ -346,21 +545,29 @@ __device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img
   float m = 1.0f / (1.0f + expf(-mk));
 #pragma unroll
   for (int k = 0; k < 3; k++) o[k] = a[k] * m + c[k] * (1.0f - m);
-  *flow_o = fl;
 }
 __device__ __forceinline__ uint8_t quant_u8(float v) {
   v = fminf(fmaxf(v * 255.0f, 0.f), 255.f);
   return (uint8_t)(int)v;  // truncation, as numpy astype(uint8)
 }
-__global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const __grid_constant__ LowSet lows, const uint8_t* __restrict__ hud,
-                                   const float* __restrict__ tsteps, uint8_t* __restrict__ out,
-                                   float* __restrict__ out_f32, float* __restrict__ flow_out, int B, int Tn, int H,
-                                   int W, int Hp, int Wp) {
-  const int W4 = (W + 3) / 4;
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  size_t total = (size_t)B * Tn * H * W4;
-  if (i >= total) return;
-  int xq = (int)(i % W4), y = (int)((i / W4) % H), n = (int)(i / ((size_t)W4 * H));
+__global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* __restrict__ imgs,
+                                                                 const __grid_constant__ LowSet lows,
+                                                                 const uint8_t* __restrict__ hud,
+                                                                 const float* __restrict__ tsteps,
+                                                                 uint8_t* __restrict__ out,
+                                                                 float* __restrict__ out_f32,
+                                                                 float* __restrict__ flow_out, int B, int Tn, int H,
+                                                                 int W, int Hp, int Wp) {
+  extern __shared__ float4 tl_sm[];
+  const int tiles_x = (W + TL_W - 1) / TL_W, tiles_y = (H + TL_H - 1) / TL_H;
+  const int tx = blockIdx.x % tiles_x, ty = (blockIdx.x / tiles_x) % tiles_y, n = blockIdx.x / (tiles_x * tiles_y);
+  const int tx0 = tx * TL_W, ty0 = ty * TL_H;
+  Staged St;
+  stage_lows<2>(lows, n, tx0, ty0, Hp, Wp, tl_sm, St);
+  __syncthreads();
+  const int xq = threadIdx.x % (TL_W / 4), y = ty0 + threadIdx.x / (TL_W / 4);
+  const int x0 = tx0 + xq * 4;
+  if (y >= H || x0 >= W) return;
   int b = n / Tn;
   float t = tsteps[n % Tn];
   const size_t plane = (size_t)Hp * Wp;
@@ -368,13 +575,13 @@ __global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const __gri
   const uint8_t* img1 = imgs + (size_t)(B + b) * plane * 4;
   const uint8_t* hsrc = t < 0.5f ? img0 : img1;
   uint8_t px[12];
-  int x0 = xq * 4;
   int cnt = min(4, W - x0);
   for (int k = 0; k < cnt; k++) {
     int x = x0 + k;
     float o[3];
-    float4 fl;
-    blend_px(img0, img1, lows, n, x, y, Hp, Wp, o, &fl);
+    float4 m4;
+    const float4 fl = eval_staged<2>(lows, St, tl_sm, n, x, y, x - tx0, Hp, Wp, &m4);
+    blend_px(img0, img1, fl, m4.x, x, y, Hp, Wp, o);
     size_t opix = ((size_t)n * H + y) * W + x;
     if (out_f32) { out_f32[opix * 3] = o[0]; out_f32[opix * 3 + 1] = o[1]; out_f32[opix * 3 + 2] = o[2]; }
     if (flow_out) reinterpret_cast<float4*>(flow_out)[opix] = fl;
@@ -395,12 +602,14 @@ __global__ void final_blend_kernel(const uint8_t* __restrict__ imgs, const __gri
     for (int k = 0; k < 3 * cnt; k++) op[k] = px[k];
   }
 }
-int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B,
-                  int T, int H, int W, int Hp, int Wp, cudaStream_t s) {
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev,
+                  uint8_t* out, float* out_f32, float* flow_out, int B, int T, int H, int W, int Hp, int Wp,
+                  cudaStream_t s) {
   ProfScope _ps(h, PC_BLEND, s);
-  size_t total = (size_t)B * T * H * ((W + 3) / 4);
-  final_blend_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, lows, hud, tsteps_dev, out, out_f32, flow_out,
-                                                      B, T, H, W, Hp, Wp);
+  const size_t smem = tl_smem_bytes(lows, 2);
+  const int grid = B * T * ((H + TL_H - 1) / TL_H) * ((W + TL_W - 1) / TL_W);
+  final_blend_kernel<<<grid, TL_THREADS, smem, s>>>(imgs, lows, hud, tsteps_dev, out, out_f32, flow_out, B, T, H, W,
+                                                    Hp, Wp);
   VFI_LAUNCHED(h);
   return 0;
 }
