@@ -283,7 +283,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low[i], N, hs / 4, wsz / 4, false, h->slope, s, lc);
       else rc = k_deconv4_direct(h, Lb[10], cur, low[i], N, hs / 4, wsz / 4, false, 1, s);
       if (rc) return rc;
-      lows.p[i] = low[i]; lows.s[i] = sc; lows.c4[i] = lc / 4; lows.n = i + 1;
+      lows.push(low[i], sc, lc, Hp, Wp);
     }
     if ((rc = k_final_blend(h, imgs, lows, hud_mask, tdev, out, out_f32, flow_out, B, T, H, W, Hp, Wp, s))) return rc;
   }
@@ -312,7 +312,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_warp_blend(vfi_handle*
     if ((rc = k_pack_fm(h, flow, mask, fm, N, H, W, H, W, s))) return rc;
     LowSet lows;
     memset(&lows, 0, sizeof(lows));
-    lows.p[0] = fm; lows.s[0] = 1; lows.c4[0] = 2; lows.n = 1;
+    lows.push(fm, 1, 8, H, W);
     if ((rc = k_final_blend(h, imgs, lows, nullptr, tdev, out, out_f32, nullptr, N, 1, H, W, H, W, s))) return rc;
   }
   return VFI_OK;

@@ -128,7 +128,14 @@ struct LowSet {
   const float* p[5];
   int s[5];
   int c4[5];  // float4 per texel: 4 (16 channels) or 2 (the final block's compact flow+mask)
+  int Hl[5], Wl[5];  // Hp / s, Wp / s
+  float rs[5], fs[5];  // 1/s and s as floats
   int n;
+  void push(const float* ptr, int scale, int ch, int Hp, int Wp) {
+    p[n] = ptr; s[n] = scale; c4[n] = ch / 4; Hl[n] = Hp / scale; Wl[n] = Wp / scale;
+    rs[n] = 1.0f / (float)scale; fs[n] = (float)scale;
+    n++;
+  }
 };
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
              void* out, int B, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s);

@@ -61,13 +61,19 @@ __device__ __forceinline__ Bil bil_setup(float fx, float fy, int W, int H) {
   b.w00 = (1.f - wx) * (1.f - wy); b.w01 = wx * (1.f - wy); b.w10 = (1.f - wx) * wy; b.w11 = wx * wy;
   return b;
 }
+// byte k of a packed RGBX word as float, exact, on the full-rate pipes (PRMT + FADD instead of the quarter-rate I2F):
+// 0x4B0000bb is the float 8388608 + bb
+template <int K>
+__device__ __forceinline__ float u8f(uint32_t v) {
+  return __uint_as_float(__byte_perm(v, 0x4B000000u, 0x7440 | K)) - 8388608.0f;
+}
 __device__ __forceinline__ void sample_rgbx(const uint8_t* img, const Bil& b, float* rgb) {
-  const uchar4* p = reinterpret_cast<const uchar4*>(img);
-  uchar4 a = __ldg(p + b.o00), c = __ldg(p + b.o01), d = __ldg(p + b.o10), e = __ldg(p + b.o11);
+  const uint32_t* p = reinterpret_cast<const uint32_t*>(img);
+  const uint32_t a = __ldg(p + b.o00), c = __ldg(p + b.o01), d = __ldg(p + b.o10), e = __ldg(p + b.o11);
   const float k = 1.0f / 255.0f;
-  rgb[0] = (b.w00 * a.x + b.w01 * c.x + b.w10 * d.x + b.w11 * e.x) * k;
-  rgb[1] = (b.w00 * a.y + b.w01 * c.y + b.w10 * d.y + b.w11 * e.y) * k;
-  rgb[2] = (b.w00 * a.z + b.w01 * c.z + b.w10 * d.z + b.w11 * e.z) * k;
+  rgb[0] = (b.w00 * u8f<0>(a) + b.w01 * u8f<0>(c) + b.w10 * u8f<0>(d) + b.w11 * u8f<0>(e)) * k;
+  rgb[1] = (b.w00 * u8f<1>(a) + b.w01 * u8f<1>(c) + b.w10 * u8f<1>(d) + b.w11 * u8f<1>(e)) * k;
+  rgb[2] = (b.w00 * u8f<2>(a) + b.w01 * u8f<2>(c) + b.w10 * u8f<2>(d) + b.w11 * u8f<2>(e)) * k;
 }
 template <typename T>
 __device__ __forceinline__ void sample_feat(const T* f, const Bil& b, float* o) {
@@ -318,87 +324,98 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
 #define TL_W 32
 #define TL_H 32
 #define TL_THREADS 256
-struct Staged {
-  int off[5];   // float4 offset of level k's patch
-  int r_lo[5];  // first staged coarse row
-  int nv[5];    // float4 per texel staged
+#define TL_TAB (5 * TL_H)  // float4 slots of the row table at the start of the tile's shared memory
+// per (level, tile row): where the two staged coarse rows of that pixel row start (float4 offsets) + the y weights
+struct __align__(16) RowTap {
+  int o0, o1;
+  float hy, ly;
 };
 __host__ __device__ __forceinline__ int tl_rows(int s) { return (TL_H / s > 1 ? TL_H / s : 1) + 2; }
+__host__ __device__ __forceinline__ int tl_nv(int mf) { return mf == 1 ? 4 : mf == 2 ? 2 : 1; }
 static size_t tl_smem_bytes(const LowSet& lows, int mf) {
-  size_t n = 0;
+  size_t n = TL_TAB;
   for (int k = 0; k < lows.n; k++) {
     if (lows.s[k] == 1) continue;
-    const int nv = (k == lows.n - 1) ? (mf == 1 ? 4 : mf == 2 ? 2 : 1) : 1;
-    n += (size_t)tl_rows(lows.s[k]) * nv * TL_W;
+    n += (size_t)tl_rows(lows.s[k]) * ((k == lows.n - 1) ? tl_nv(mf) : 1) * TL_W;
   }
   return n * sizeof(float4);
 }
+// Stage 1.  Thread t owns tile column t%32 (its x taps are computed once per level) and rows t/32, t/32+8, ...;
+// warp k also fills level k's row table.
 template <int MF>
-__device__ __forceinline__ void stage_lows(const LowSet& lows, int n, int tx0, int ty0, int Hp, int Wp, float4* sm,
-                                           Staged& S) {
-  int off = 0;
+__device__ __forceinline__ void tile_stage(const LowSet& L, int n, int tx0, int ty0, int Hp, int Wp, float4* sm) {
+  RowTap* ytab = reinterpret_cast<RowTap*>(sm);
+  const int xl = threadIdx.x & (TL_W - 1), row0 = threadIdx.x >> 5;
+  int off = TL_TAB;
 #pragma unroll
   for (int k = 0; k < 5; k++) {
-    if (k < lows.n && lows.s[k] > 1) {
-      const int sk = lows.s[k], c4 = lows.c4[k], Hl = Hp / sk, Wl = Wp / sk;
-      const int nv = (k == lows.n - 1) ? (MF == 1 ? 4 : MF == 2 ? 2 : 1) : 1;
+    if (k < L.n && L.s[k] > 1) {
+      const int sk = L.s[k], c4 = L.c4[k], Hl = L.Hl[k], Wl = L.Wl[k];
+      const int nv = (k == L.n - 1) ? tl_nv(MF) : 1;
       const int rows = tl_rows(sk);
-      const float rs = 1.0f / (float)sk;
+      const float rs = L.rs[k];
       const int r_lo = (int)fmaxf(rs * ((float)ty0 + 0.5f) - 0.5f, 0.f);
-      S.off[k] = off; S.r_lo[k] = r_lo; S.nv[k] = nv;
-      const float4* img = reinterpret_cast<const float4*>(lows.p[k]) + (size_t)n * Hl * Wl * c4;
-      for (int idx = threadIdx.x; idx < rows * TL_W; idx += TL_THREADS) {
-        const int row = idx / TL_W, xl = idx % TL_W;
+      if (row0 == k) {
+        const float sy = fmaxf(rs * ((float)min(ty0 + xl, Hp - 1) + 0.5f) - 0.5f, 0.f);
+        const int y0 = (int)sy, y1 = y0 + (y0 < Hl - 1 ? 1 : 0);
+        RowTap t;
+        t.ly = sy - (float)y0; t.hy = 1.f - t.ly;
+        t.o0 = off + (y0 - r_lo) * nv * TL_W; t.o1 = off + (y1 - r_lo) * nv * TL_W;
+        ytab[k * TL_H + xl] = t;
+      }
+      const float sx = fmaxf(rs * ((float)min(tx0 + xl, Wp - 1) + 0.5f) - 0.5f, 0.f);
+      const int x0 = (int)sx, x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
+      const float lx = sx - (float)x0, hx = 1.f - lx;
+      const float4* img = reinterpret_cast<const float4*>(L.p[k]) + (size_t)n * Hl * Wl * c4;
+      for (int row = row0; row < rows; row += TL_THREADS / TL_W) {
         const int ry = min(r_lo + row, Hl - 1);
-        const float sx = fmaxf(rs * ((float)min(tx0 + xl, Wp - 1) + 0.5f) - 0.5f, 0.f);  // partial tiles: clamp
-        const int x0 = (int)sx, x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
-        const float lx = sx - (float)x0, hx = 1.f - lx;
         const float4* pa = img + (size_t)(ry * Wl + x0) * c4;
         const float4* pb = img + (size_t)(ry * Wl + x1) * c4;
-        for (int v = 0; v < nv; v++) {
-          const float4 a = __ldg(pa + v), b = __ldg(pb + v);
-          sm[off + (row * nv + v) * TL_W + xl] =
-              make_float4(hx * a.x + lx * b.x, hx * a.y + lx * b.y, hx * a.z + lx * b.z, hx * a.w + lx * b.w);
+        float4* dst = sm + off + row * nv * TL_W + xl;
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+          if (v < nv) {
+            const float4 a = __ldg(pa + v), b = __ldg(pb + v);
+            dst[v * TL_W] =
+                make_float4(hx * a.x + lx * b.x, hx * a.y + lx * b.y, hx * a.z + lx * b.z, hx * a.w + lx * b.w);
+          }
         }
       }
       off += rows * nv * TL_W;
     }
   }
 }
-// state_at for pixel (x,y) = tile-local column xl, from the staged rows
+// Stage 2: state_at for pixel (x,y) = tile-local (xl,yl)
 template <int MF>
-__device__ __forceinline__ float4 eval_staged(const LowSet& lows, const Staged& S, const float4* sm, int n, int x,
-                                              int y, int xl, int Hp, int Wp, float4* m) {
+__device__ __forceinline__ float4 tile_eval(const LowSet& L, const float4* sm, int n, int x, int y, int xl, int yl,
+                                            float4* m) {
+  const RowTap* ytab = reinterpret_cast<const RowTap*>(sm);
   float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int k = 0; k < 5; k++) {
-    if (k < lows.n) {
-      const int sk = lows.s[k], Hl = Hp / sk;
-      const bool last = k == lows.n - 1;
-      if (sk == 1) {
-        const int c4 = lows.c4[k];
-        const float4* px = reinterpret_cast<const float4*>(lows.p[k]) + ((size_t)n * Hp * Wp + (size_t)y * Wp + x) * c4;
+    if (k < L.n) {
+      const bool last = k == L.n - 1;
+      if (L.s[k] == 1) {
+        const int c4 = L.c4[k];
+        const float4* px = reinterpret_cast<const float4*>(L.p[k]) + ((size_t)n * L.Hl[k] + y) * L.Wl[k] * c4 + x * c4;
         const float4 r = __ldg(px);
         fl.x += r.x; fl.y += r.y; fl.z += r.z; fl.w += r.w;
         if (MF == 1 && last) { m[0] = __ldg(px + 1); m[1] = __ldg(px + 2); m[2] = __ldg(px + 3); }
         if (MF == 2 && last) m[0] = __ldg(px + 1);
       } else {
-        const float rs = 1.0f / (float)sk;
-        const float sy = fmaxf(rs * ((float)y + 0.5f) - 0.5f, 0.f);
-        const int y0 = (int)sy, y1 = y0 + (y0 < Hl - 1 ? 1 : 0);
-        const float ly = sy - (float)y0, hy = 1.f - ly;
-        const int nv = S.nv[k];
-        const float4* r0 = sm + S.off[k] + (y0 - S.r_lo[k]) * nv * TL_W + xl;
-        const float4* r1 = sm + S.off[k] + (y1 - S.r_lo[k]) * nv * TL_W + xl;
+        const RowTap t = ytab[k * TL_H + yl];
+        const float4* r0 = sm + t.o0 + xl;
+        const float4* r1 = sm + t.o1 + xl;
         const float4 a = r0[0], c = r1[0];
-        const float fs = (float)sk;
-        fl.x += (hy * a.x + ly * c.x) * fs; fl.y += (hy * a.y + ly * c.y) * fs;
-        fl.z += (hy * a.z + ly * c.z) * fs; fl.w += (hy * a.w + ly * c.w) * fs;
+        const float fs = L.fs[k];
+        fl.x += (t.hy * a.x + t.ly * c.x) * fs; fl.y += (t.hy * a.y + t.ly * c.y) * fs;
+        fl.z += (t.hy * a.z + t.ly * c.z) * fs; fl.w += (t.hy * a.w + t.ly * c.w) * fs;
         if (MF != 0 && last) {
 #pragma unroll
-          for (int v = 1; v < (MF == 1 ? 4 : 2); v++) {
+          for (int v = 1; v < tl_nv(MF); v++) {
             const float4 p = r0[v * TL_W], q = r1[v * TL_W];
-            m[v - 1] = make_float4(hy * p.x + ly * q.x, hy * p.y + ly * q.y, hy * p.z + ly * q.z, hy * p.w + ly * q.w);
+            m[v - 1] = make_float4(t.hy * p.x + t.ly * q.x, t.hy * p.y + t.ly * q.y, t.hy * p.z + t.ly * q.z,
+                                   t.hy * p.w + t.ly * q.w);
           }
         }
       }
@@ -430,7 +447,8 @@ __device__ __forceinline__ void gather_tap(const uint8_t* img0, const uint8_t* i
   acc[24] += fl.x; acc[25] += fl.y; acc[26] += fl.z; acc[27] += fl.w;
 }
 
-// gather_kernel for the blocks at s = 1 and s = 2, where the taps cover every full-resolution pixel
+// gather_kernel for the blocks at s = 1 and s = 2, where the taps cover every full-resolution pixel.
+// grid = (Wp/32, Hp/32, N)
 template <typename T, int S>
 __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* __restrict__ imgs,
                                                                  const T* __restrict__ feats,
@@ -439,14 +457,11 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
                                                                  T* __restrict__ out, int B, int Tn, int Hp, int Wp,
                                                                  int phase) {
   extern __shared__ float4 tl_sm[];
-  const int tiles_x = Wp / TL_W, tiles_y = Hp / TL_H;
-  const int tx = blockIdx.x % tiles_x, ty = (blockIdx.x / tiles_x) % tiles_y, n = blockIdx.x / (tiles_x * tiles_y);
-  const int tx0 = tx * TL_W, ty0 = ty * TL_H;
-  Staged St;
-  stage_lows<1>(lows, n, tx0, ty0, Hp, Wp, tl_sm, St);
+  const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
+  tile_stage<1>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
   __syncthreads();
   const int b = n / Tn;
-  const float t = tsteps[n % Tn];
+  const float t = tsteps[n - b * Tn];
   const size_t plane = (size_t)Hp * Wp;
   const uint8_t* img0 = imgs + ((size_t)b) * plane * 4;
   const uint8_t* img1 = imgs + ((size_t)(B + b)) * plane * 4;
@@ -461,20 +476,22 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
     for (int c = 0; c < 32; c++) acc[c] = 0.f;
     int X, Y;
     if (S == 1) {
-      const int xl = threadIdx.x % TL_W, yl = threadIdx.x / TL_W + (TL_THREADS / TL_W) * i;
+      const int xl = threadIdx.x & (TL_W - 1), yl = (threadIdx.x >> 5) + (TL_THREADS / TL_W) * i;
       X = tx0 + xl; Y = ty0 + yl;
       float4 m[3];
-      const float4 fl = eval_staged<1>(lows, St, tl_sm, n, X, Y, xl, Hp, Wp, m);
+      const float4 fl = tile_eval<1>(lows, tl_sm, n, X, Y, xl, yl, m);
       gather_tap<T>(img0, img1, f0, f1, fl, m, X, Y, Hp, Wp, acc);
     } else {
-      const int Xl = threadIdx.x % (TL_W / 2), Yl = threadIdx.x / (TL_W / 2);
-      X = tx0 / 2 + Xl; Y = ty0 / 2 + Yl;
+      const int Xl = threadIdx.x & (TL_W / 2 - 1), Yl = threadIdx.x >> 4;
+      X = (tx0 >> 1) + Xl; Y = (ty0 >> 1) + Yl;
 #pragma unroll 1
       for (int d = 0; d < 4; d++) {
-        const int xl = 2 * Xl + (d & 1), x = tx0 + xl, y = ty0 + 2 * Yl + (d >> 1);
+        // odd groups of four outputs visit their right-hand tap first: the 8 lanes of an LDS.128 phase then hit 8
+        // distinct 16-byte bank groups
+        const int xl = 2 * Xl + ((d & 1) ^ ((Xl >> 2) & 1)), yl = 2 * Yl + (d >> 1);
         float4 m[3];
-        const float4 fl = eval_staged<1>(lows, St, tl_sm, n, x, y, xl, Hp, Wp, m);
-        gather_tap<T>(img0, img1, f0, f1, fl, m, x, y, Hp, Wp, acc);
+        const float4 fl = tile_eval<1>(lows, tl_sm, n, tx0 + xl, ty0 + yl, xl, yl, m);
+        gather_tap<T>(img0, img1, f0, f1, fl, m, tx0 + xl, ty0 + yl, Hp, Wp, acc);
       }
 #pragma unroll
       for (int c = 0; c < 32; c++) acc[c] *= 0.25f;
@@ -502,7 +519,7 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
   const bool first = lows.n == 0;
   if (!first && s_int <= 2 && Hp % TL_H == 0 && Wp % TL_W == 0) {
     const size_t smem = tl_smem_bytes(lows, 1);
-    const int tgrid = B * T * (Hp / TL_H) * (Wp / TL_W);
+    const dim3 tgrid(Wp / TL_W, Hp / TL_H, B * T);
 #define GT_LAUNCH(TT, SS)                                                                                          \
   do {                                                                                                             \
     VFI_CUDA(h, cudaFuncSetAttribute(gather_tile_kernel<TT, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
@@ -533,8 +550,7 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
 //   merged = warped0*m + warped1*(1-m)
 //   unpad (base.py:227-229); (x*255).clip(0,255).astype(uint8) truncation (base.py:188-201)
 //   HUD composite frame[mask] = (f0 if t<0.5 else f1)[mask]              (adaptive_pipeline.py:399-409)
-// One thread per 4 output pixels: the u8 result is written as
-// three 32-bit words (12 B, 4-byte aligned when W % 4 == 0).
+// The u8 tile is assembled in shared memory and written as aligned 32-bit words, 96 B per tile row.
 __device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img1, const float4 fl, const float mk,
                                          int x, int y, int Hp, int Wp, float* o /*3*/) {
   Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
@@ -542,7 +558,7 @@ __device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img
   float a[3], c[3];
   sample_rgbx(img0, b0, a);
   sample_rgbx(img1, b1, c);
-  float m = 1.0f / (1.0f + expf(-mk));
+  const float m = __fdividef(1.0f, 1.0f + __expf(-mk));  // sigmoid; ~2 ulp, far inside the 1e-4 parity budget
 #pragma unroll
   for (int k = 0; k < 3; k++) o[k] = a[k] * m + c[k] * (1.0f - m);
 }
@@ -559,30 +575,27 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
                                                                  float* __restrict__ flow_out, int B, int Tn, int H,
                                                                  int W, int Hp, int Wp) {
   extern __shared__ float4 tl_sm[];
-  const int tiles_x = (W + TL_W - 1) / TL_W, tiles_y = (H + TL_H - 1) / TL_H;
-  const int tx = blockIdx.x % tiles_x, ty = (blockIdx.x / tiles_x) % tiles_y, n = blockIdx.x / (tiles_x * tiles_y);
-  const int tx0 = tx * TL_W, ty0 = ty * TL_H;
-  Staged St;
-  stage_lows<2>(lows, n, tx0, ty0, Hp, Wp, tl_sm, St);
+  __shared__ __align__(16) uint8_t s_rgb[TL_H][TL_W * 3];  // the tile's u8 result, stored row-wise as 32-bit words
+  const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
+  tile_stage<2>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
   __syncthreads();
-  const int xq = threadIdx.x % (TL_W / 4), y = ty0 + threadIdx.x / (TL_W / 4);
-  const int x0 = tx0 + xq * 4;
-  if (y >= H || x0 >= W) return;
-  int b = n / Tn;
-  float t = tsteps[n % Tn];
+  const int b = n / Tn;
+  const float t = tsteps[n - b * Tn];
   const size_t plane = (size_t)Hp * Wp;
   const uint8_t* img0 = imgs + (size_t)b * plane * 4;
   const uint8_t* img1 = imgs + (size_t)(B + b) * plane * 4;
   const uint8_t* hsrc = t < 0.5f ? img0 : img1;
-  uint8_t px[12];
-  int cnt = min(4, W - x0);
-  for (int k = 0; k < cnt; k++) {
-    int x = x0 + k;
+  // a warp = one tile row (lane = column): conflict-free LDS.128 of the staged rows, broadcast row table
+  const int xl = threadIdx.x & (TL_W - 1), x = tx0 + xl;
+#pragma unroll 1
+  for (int i = 0; i < TL_H / (TL_THREADS / TL_W); i++) {
+    const int yl = (threadIdx.x >> 5) + (TL_THREADS / TL_W) * i, y = ty0 + yl;
+    if (y >= H || x >= W) continue;
     float o[3];
     float4 m4;
-    const float4 fl = eval_staged<2>(lows, St, tl_sm, n, x, y, x - tx0, Hp, Wp, &m4);
+    const float4 fl = tile_eval<2>(lows, tl_sm, n, x, y, xl, yl, &m4);
     blend_px(img0, img1, fl, m4.x, x, y, Hp, Wp, o);
-    size_t opix = ((size_t)n * H + y) * W + x;
+    const size_t opix = ((size_t)n * H + y) * W + x;
     if (out_f32) { out_f32[opix * 3] = o[0]; out_f32[opix * 3 + 1] = o[1]; out_f32[opix * 3 + 2] = o[2]; }
     if (flow_out) reinterpret_cast<float4*>(flow_out)[opix] = fl;
     uint8_t r = quant_u8(o[0]), g = quant_u8(o[1]), bl = quant_u8(o[2]);
@@ -590,16 +603,24 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
       uchar4 sp = __ldg(reinterpret_cast<const uchar4*>(hsrc) + (size_t)y * Wp + x);
       r = sp.x; g = sp.y; bl = sp.z;
     }
-    px[3 * k] = r; px[3 * k + 1] = g; px[3 * k + 2] = bl;
+    s_rgb[yl][3 * xl] = r; s_rgb[yl][3 * xl + 1] = g; s_rgb[yl][3 * xl + 2] = bl;
   }
-  uint8_t* op = out + (((size_t)n * H + y) * W + x0) * 3;
-  if (cnt == 4 && (W & 3) == 0) {
-    uint32_t* o32 = reinterpret_cast<uint32_t*>(op);
-    o32[0] = px[0] | (px[1] << 8) | (px[2] << 16) | ((uint32_t)px[3] << 24);
-    o32[1] = px[4] | (px[5] << 8) | (px[6] << 16) | ((uint32_t)px[7] << 24);
-    o32[2] = px[8] | (px[9] << 8) | (px[10] << 16) | ((uint32_t)px[11] << 24);
+  __syncthreads();
+  const int cols = min(TL_W, W - tx0), rows = min(TL_H, H - ty0);
+  if ((W & 3) == 0) {
+    // tx0*3 and W*3 are multiples of 4: each tile row is cols*3/4 aligned words
+    const int wpr = cols * 3 / 4;
+    for (int w = threadIdx.x; w < TL_H * (TL_W * 3 / 4); w += TL_THREADS) {
+      const int row = w / (TL_W * 3 / 4), col = w - row * (TL_W * 3 / 4);
+      if (row < rows && col < wpr)
+        reinterpret_cast<uint32_t*>(out + (((size_t)n * H + ty0 + row) * W + tx0) * 3)[col] =
+            reinterpret_cast<const uint32_t*>(&s_rgb[row][0])[col];
+    }
   } else {
-    for (int k = 0; k < 3 * cnt; k++) op[k] = px[k];
+    for (int w = threadIdx.x; w < TL_H * TL_W * 3; w += TL_THREADS) {
+      const int row = w / (TL_W * 3), col = w - row * (TL_W * 3);
+      if (row < rows && col < cols * 3) out[(((size_t)n * H + ty0 + row) * W + tx0) * 3 + col] = s_rgb[row][col];
+    }
   }
 }
 int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev,
@@ -607,7 +628,7 @@ int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const 
                   cudaStream_t s) {
   ProfScope _ps(h, PC_BLEND, s);
   const size_t smem = tl_smem_bytes(lows, 2);
-  const int grid = B * T * ((H + TL_H - 1) / TL_H) * ((W + TL_W - 1) / TL_W);
+  const dim3 grid((W + TL_W - 1) / TL_W, (H + TL_H - 1) / TL_H, B * T);
   final_blend_kernel<<<grid, TL_THREADS, smem, s>>>(imgs, lows, hud, tsteps_dev, out, out_f32, flow_out, B, T, H, W,
                                                     Hp, Wp);
   VFI_LAUNCHED(h);
