@@ -153,3 +153,26 @@ def test_conv_v2_halo_tile_kernel(engine, weights, layer, Hin, Win):
     scale = max(1.0, ref.abs().max().item())
     assert (y2 - ref).abs().max().item() <= 1.5e-2 * scale
     assert (y2 - y1).abs().max().item() <= 1.0e-2 * scale          # same operands, different accumulation order + bf16 store
+
+
+@pytest.mark.parametrize("layer", [15, 37, 38, 48, 49])
+@pytest.mark.parametrize("Hin,Win", [(26, 44), (64, 96), (136, 240)])
+def test_conv_s2_plane_window_kernel(engine, weights, layer, Hin, Win):
+    """csrc/conv_s2.cu (stride-2 convs: resident weights, one 17 x (8KW+1) window per phase plane per tile) against
+    torch and against the TMA-per-tap kernel on the same bf16 operands; partial tiles in both directions."""
+    torch.backends.cudnn.allow_tf32 = False
+    li = layer_info(layer)
+    g = torch.Generator().manual_seed(200 + layer)
+    x = torch.randn((2, Hin, Win, li["cin_pad"]), generator=g).cuda()
+    x[..., li["cin"]:] = 0
+    try:
+        engine.set_option("conv_v2", 1)
+        y2 = engine.debug_conv(layer, _abi.PRECISION_BF16, x, None)
+        engine.set_option("conv_v2", 0)
+        y1 = engine.debug_conv(layer, _abi.PRECISION_BF16, x, None)
+    finally:
+        engine.set_option("conv_v2", 1)
+    ref = _torch_layer(weights, layer, x, None, True)
+    scale = max(1.0, ref.abs().max().item())
+    assert (y2 - ref).abs().max().item() <= 1.5e-2 * scale
+    assert (y2 - y1).abs().max().item() <= 1.0e-2 * scale

@@ -48,10 +48,11 @@ extern "C" __attribute__((visibility("default"))) int vfi_create(int device, vfi
 static void free_layers(vfi_handle* h) {
   for (int i = 0; i < VFI_NUM_LAYERS; i++) {
     Layer& L = h->layers[i];
-    cudaFree(L.w32); cudaFree(L.bias); cudaFree(L.beta); cudaFree(L.wtc); cudaFree(L.bias_tc); cudaFree(L.wv2); cudaFree(L.bias_v2);
+    cudaFree(L.w32); cudaFree(L.bias); cudaFree(L.beta); cudaFree(L.wtc); cudaFree(L.bias_tc); cudaFree(L.wv2); cudaFree(L.bias_v2); cudaFree(L.ws2);
     L.w32 = L.bias = L.beta = L.bias_tc = L.bias_v2 = nullptr;
     L.wtc = nullptr;
     L.wv2 = nullptr;
+    L.ws2 = nullptr;
   }
 }
 
@@ -171,6 +172,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
     const bool tc = (id == 1 || id == 2 || id >= 4);
     if (tc) {
       if (int rc = tc_build_layer(h, L, w)) return rc;
+      if (int rc = s2_build_layer(h, L, w)) return rc;
     }
     if (tc || id == 3) {
       if (int rc = v2_build_layer(h, L, w)) return rc;
@@ -196,6 +198,8 @@ static int run_conv(vfi_handle* h, const Layer& L, const void* in, const void* r
                     int Win, bool bf, bool out_phase, cudaStream_t s) {
   if (bf && h->opt_conv_v2 && L.wv2 && !out_phase && (res == nullptr || res == in))
     return k_conv_v2(h, L, (const bf16*)in, (bf16*)out, N, Hin, Win, h->slope, s);
+  if (bf && h->opt_conv_v2 && L.ws2 && res == nullptr)
+    return k_conv_s2(h, L, (const bf16*)in, (bf16*)out, N, Hin, Win, out_phase, h->slope, s);
   if (bf) return k_conv_tc(h, L, (const bf16*)in, (const bf16*)res, out, N, Hin, Win, out_phase, h->slope, s);
   return k_conv3_direct(h, L, in, res, out, N, Hin, Win, false, h->slope, s);
 }
@@ -365,6 +369,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
     }
     if (h->opt_conv_v2 && L.wv2 && !s2 && (resp == nullptr || resp == xb)) {
       if ((rc = k_conv_v2(h, L, xb, yb, N, Hin, Win, h->slope, s))) return rc;
+    } else if (h->opt_conv_v2 && L.ws2 && s2) {
+      if ((rc = k_conv_s2(h, L, in, yb, N, Hin, Win, false, h->slope, s))) return rc;
     } else if ((rc = k_conv_tc(h, L, in, resp, yb, N, Hin, Win, false, h->slope, s))) return rc;
     return k_act_to_f32(h, yb, y, nout, true, s);
   }

@@ -52,6 +52,7 @@ struct Layer {
   TcStep steps[VFI_MAX_STEPS];
   float* bias_tc = nullptr;  // bias laid out by accumulator column (n_total floats)
   float* bias_v2 = nullptr;  // conv_v2.cu Head.cnn3 instance: bias per (phase, channel) column
+  bf16* ws2 = nullptr;       // conv_s2.cu resident-weight image of a stride-2 conv (null: not s2-capable)
   bf16* wv2 = nullptr;       // conv_v2.cu resident-weight image [tap][cin/8][cout][8] (null: layer not v2-capable)
 };
 
@@ -169,5 +170,12 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch);
 // stride-1 3x3 conv (+ResConv epilogue), plain NHWC bf16 in/out
 int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, int H, int W, float slope,
               cudaStream_t s);
+
+// ---- conv_s2.cu ---------------------------------------------------------------------------
+bool s2_supported(const Layer& L);
+int s2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch);
+// stride-2 3x3 conv + LeakyReLU: phase-plane bf16 in, plain or phase-plane bf16 out
+int k_conv_s2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, int Hin, int Win, bool out_phase,
+              float slope, cudaStream_t s);
 
 // ---- reduce.cu is reached only through the ABI functions -----------------------------------
