@@ -12,8 +12,9 @@
 //   D (TMEM)     : KW accumulators of Cout fp32 columns, double buffered (2*KW*Cout <= 512 columns).
 //   epilogue     : tcgen05.ld -> +bias -> (*beta + residual, taken from the SAME smem halo tile) -> LeakyReLU
 //                  -> bf16 NHWC store.
-// Warp roles (416 threads): warps 0-3 producers (cp.async 16 B, zero fill = conv padding, up to 3 tiles in flight),
-// warp 4 TMEM allocator + MMA issuer (converged warp, elected lane), warps 5-12 epilogue (two per TMEM lane group).
+// Warp roles (544 threads): warps 0-7 producers (cp.async 16 B, zero fill = conv padding, up to 3 tiles in flight; the
+// per-thread copy list is tile independent and lives in registers), warp 8 TMEM allocator + MMA issuer (converged
+// warp, elected lane), warps 9-16 epilogue (two per TMEM lane group).
 // Layer semantics: SURVEY.md Appendix A.2 (conv(), ResConv).
 #include <algorithm>
 
@@ -33,8 +34,9 @@ struct V2Params {
   float slope;
 };
 
-#define V2_THREADS 416
-#define V2_PRODUCERS 128
+#define V2_PRODUCERS 256
+#define V2_THREADS (V2_PRODUCERS + 32 + 256)
+#define V2_PW (V2_PRODUCERS / 32)  // producer warps; warp V2_PW = MMA issuer; the 8 warps after it = epilogue
 #define V2_MAX_STAGES 4
 #define V2_DEPTH 3
 
@@ -169,7 +171,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) {
+  if (warp == V2_PW) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(&tmem_base_smem)),
                  "r"((uint32_t)C::TMEM_COLS)
                  : "memory");
@@ -190,13 +192,26 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   tc_after();
   const uint32_t tmem_base = tmem_base_smem;
 
-  if (warp < 4) {
+  if (warp < V2_PW) {
     // ================= producers: halo tile -> smem [chunk][pixel][8ch] =================
     // cp.async (LDGSTS, 16 B, L2-only) straight into the UMMA layout; zero fill (src-size 0) is the conv padding.
     // Up to V2_DEPTH tiles are in flight per thread: tile i is published (wait_group -> fence.proxy.async -> arrive)
-    // while tiles i+1..i+V2_DEPTH are still streaming in.
+    // while tiles i+1..i+V2_DEPTH are still streaming in.  The copy list of a thread does not depend on the tile:
+    //   meta = smem offset (16-byte units, bits 0-13) | halo row << 14 | halo col << 19 | unused << 31
+    //   srel = source element offset relative to the halo origin
     constexpr int ROW_ITEMS = C::PITCH * C::NCHUNK;
     constexpr int PER_THREAD = (C::TOTAL_ITEMS + V2_PRODUCERS - 1) / V2_PRODUCERS;
+    uint32_t meta[PER_THREAD];
+    int srel[PER_THREAD];
+#pragma unroll
+    for (int u = 0; u < PER_THREAD; u++) {
+      const int i = (int)threadIdx.x + u * V2_PRODUCERS;
+      const int py = i / ROW_ITEMS, rem = i - py * ROW_ITEMS;
+      const int px = rem / C::NCHUNK, j = rem - px * C::NCHUNK;
+      meta[u] = (uint32_t)(j * C::CS + py * C::PITCH + px) | ((uint32_t)py << 14) | ((uint32_t)px << 19) |
+                (i >= C::TOTAL_ITEMS ? 0x80000000u : 0u);
+      srel[u] = (py * P.W + px) * CIN + j * 8;
+    }
     const int depth = P.nstages - 1 < V2_DEPTH ? P.nstages - 1 : V2_DEPTH;  // stages >= tiles in flight + the one in MMA
     int it = 0;
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
@@ -216,16 +231,16 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       bar_wait(&empty_bar[st], ph ^ 1);
       const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
       const bf16* img = P.in + (size_t)n * P.H * P.W * CIN;
+      const bf16* org = img + ((ptrdiff_t)gy0 * P.W + gx0) * CIN;  // halo origin (may lie outside the image)
+      if (!(P.ablate & 1)) {
 #pragma unroll
-      for (int u = 0; u < PER_THREAD; u++) {
-        const int i = (int)threadIdx.x + u * V2_PRODUCERS;
-        if (i < C::TOTAL_ITEMS && !(P.ablate & 1)) {
-          const int py = i / ROW_ITEMS, rem = i - py * ROW_ITEMS;
-          const int px = rem / C::NCHUNK, j = rem - px * C::NCHUNK;
-          const int gy = gy0 + py, gx = gx0 + px;
-          const bool ok = gy >= 0 && gy < P.H && gx >= 0 && gx < P.W;
-          const bf16* src = ok ? img + ((size_t)gy * P.W + gx) * CIN + j * 8 : img;
-          cp_async16(dst + (uint32_t)(j * C::CS + py * C::PITCH + px) * 16, src, ok ? 16u : 0u);
+        for (int u = 0; u < PER_THREAD; u++) {
+          const uint32_t mt = meta[u];
+          if (!(mt & 0x80000000u)) {
+            const int gy = gy0 + (int)((mt >> 14) & 31), gx = gx0 + (int)((mt >> 19) & 63);
+            const bool ok = (unsigned)gy < (unsigned)P.H && (unsigned)gx < (unsigned)P.W;
+            cp_async16(dst + ((mt & 0x3FFFu) << 4), ok ? org + srel[u] : img, ok ? 16u : 0u);
+          }
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -236,7 +251,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     __syncwarp();
     if (lane == 0)
       for (int k = (it < depth ? it : depth); k > 0; k--) bar_arrive(&full_bar[(it - k) % P.nstages]);
-  } else if (warp == 4) {
+  } else if (warp == V2_PW) {
     // ================= MMA issuer: the warp stays converged, one elected lane issues =================
     const uint32_t leader = elect_one();
     constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(COUT >> 3) << 17) | (8u << 24);
@@ -280,7 +295,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   } else {
     // ================= epilogue: 8 warps, two per TMEM lane group, each taking every other sub-tile =================
     const int lg = warp & 3;                 // TMEM lane group this warp may access
-    const int half = (warp - 5) >> 2;        // 0: even sub-tiles, 1: odd sub-tiles
+    const int half = (warp - V2_PW - 1) >> 2;  // 0: even sub-tiles, 1: odd sub-tiles
     const int m = lg * 32 + lane;
     const int ly = m >> 3, lx = m & 7;
     const float4* bias4 = reinterpret_cast<const float4*>(bias_s);
@@ -378,7 +393,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   }
   tc_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == V2_PW) {
     tc_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
                  : "memory");
