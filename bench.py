@@ -133,7 +133,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=75)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--pairs", type=int, default=4, help="frame pairs per step (batch)")
+    ap.add_argument("--pairs", type=int, default=8, help="frame pairs per step (batch)")
     ap.add_argument("--pool", type=int, default=24, help="unique synthetic pairs resident in HBM")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")

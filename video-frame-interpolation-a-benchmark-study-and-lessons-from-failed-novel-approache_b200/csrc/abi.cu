@@ -104,6 +104,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!h || !key) return VFI_E_ARG;
   if (!strcmp(key, "conv_v2")) { h->opt_conv_v2 = value; return VFI_OK; }
   if (!strcmp(key, "v2_ablate")) { h->opt_v2_ablate = value; return VFI_OK; }
+  if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }
   VFI_FAIL(h, VFI_E_ARG, "unknown option %s", key);
 }
 

@@ -51,6 +51,7 @@ struct Layer {
   int cblk = 0, rows_total = 0, nsteps = 0, n_total = 0, b_box = 0;
   TcStep steps[VFI_MAX_STEPS];
   float* bias_tc = nullptr;  // bias laid out by accumulator column (n_total floats)
+  float h_bias_v2[64] = {0}, h_beta[64] = {0};  // host copies for conv_v2's constant-bank epilogue parameters
   float* bias_v2 = nullptr;  // conv_v2.cu Head.cnn3 instance: bias per (phase, channel) column
   bf16* ws2 = nullptr;       // conv_s2.cu resident-weight image of a stride-2 conv (null: not s2-capable)
   bf16* wv2 = nullptr;       // conv_v2.cu resident-weight image [tap][cin/8][cout][8] (null: layer not v2-capable)
@@ -71,6 +72,7 @@ struct vfi_handle {
   void* red = nullptr;
   size_t red_bytes = 0;
   void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled entry point
+  int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps
   int opt_v2_ablate = 0;        // debug only: see V2Params::ablate
   int opt_conv_v2 = 1;          // vfi_set_option("conv_v2"): resident-weight halo-tile conv kernel where it applies
   // optional per-kernel-class timing (vfi_profile_enable): event pairs around every launch

@@ -30,7 +30,7 @@ struct S2Params {
 #define S2_PRODUCERS 256
 #define S2_THREADS (S2_PRODUCERS + 32 + 256)
 #define S2_PW (S2_PRODUCERS / 32)  // producer warps; warp S2_PW = MMA issuer; the 8 warps after it = epilogue
-#define S2_MAX_STAGES 4
+#define S2_MAX_STAGES 6
 
 template <int CIN, int COUT, int KW>
 struct S2Cfg {
@@ -100,7 +100,9 @@ __global__ void __launch_bounds__(S2_THREADS, 1) conv_s2_kernel(const __grid_con
       meta[u] = (uint32_t)(j * C::CS + pix) | ((uint32_t)pr << 14) | ((uint32_t)pc << 19) | (skip ? 0x80000000u : 0u);
       srel[u] = ((plane * P.Ho + pr) * P.Wo + pc) * CIN + j * 8;
     }
-    const int depth = P.nstages - 1 < 3 ? P.nstages - 1 : 3;  // tiles in flight per thread
+    // tiles in flight per thread; nstages - depth - 1 tiles of slack keep the publish hand-shake off the MMA warp's
+    // critical path (see conv_v2.cu)
+    const int depth = P.nstages - 2 < 1 ? 1 : (P.nstages - 2 > 3 ? 3 : P.nstages - 2);
     int it = 0;
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
       const int st = it % P.nstages;

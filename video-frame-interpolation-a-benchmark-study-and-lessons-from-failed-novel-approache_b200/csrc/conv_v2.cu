@@ -32,15 +32,31 @@ struct V2Params {
   int ablate;  // debug (vfi_set_option "v2_ablate"): 1 skip loads, 2 skip MMAs, 4 skip epilogue math+stores, 8 skip TMEM loads
   int act;
   float slope;
+  // bias / beta by output column, read by the epilogue through the constant bank: the shared-memory pipe is saturated
+  // by the tensor core's operand reads while MMAs are in flight
+  float bias_c[64];
+  float beta_c[64];
+  unsigned long long* trace;  // debug (vfi_set_option "v2_trace"): CTA 0 timestamps [role][tile < 64][8]
 };
 
 #define V2_PRODUCERS 256
-#define V2_THREADS (V2_PRODUCERS + 32 + 256)
-#define V2_PW (V2_PRODUCERS / 32)  // producer warps; warp V2_PW = MMA issuer; the 8 warps after it = epilogue
-#define V2_MAX_STAGES 4
+#define V2_EPI_WARPS 16
+#define V2_THREADS (V2_PRODUCERS + 32 + 32 * V2_EPI_WARPS)
+#define V2_PW (V2_PRODUCERS / 32)  // producer warps; warp V2_PW = MMA issuer; the V2_EPI_WARPS warps after it = epilogue
+#define V2_MAX_STAGES 6
 #define V2_DEPTH 3
 
 // Compile-time geometry of one (Cin, Cout, KW) instance.
+__device__ __forceinline__ unsigned long long v2_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define V2_TRACE(role, tile_i, ev)                                                              \
+  do {                                                                                          \
+    if (P.trace && blockIdx.x == 0 && (tile_i) < 64) P.trace[((role)*64 + (tile_i)) * 8 + (ev)] = v2_now(); \
+  } while (0)
+
 template <int CIN, int COUT, int KW>
 struct V2Cfg {
   static constexpr int NCHUNK = CIN / 8;
@@ -81,6 +97,21 @@ __device__ __forceinline__ void bar_wait(uint64_t* b, uint32_t parity) {
       "bra V2_WAIT;\n\t"
       "V2_DONE:\n\t}" ::"r"(s_u32(b)), "r"(parity)
       : "memory");
+}
+// polling wait with back-off, for waits that are normally long (stage release, accumulator release): a warp parked here
+// must not compete with the epilogue warps for issue slots and the shared-memory pipe
+__device__ __forceinline__ void bar_wait_relaxed(uint64_t* b, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P1;\n\t}"
+        : "=r"(done)
+        : "r"(s_u32(b)), "r"(parity)
+        : "memory");
+    if (!done) __nanosleep(200);
+  } while (!done);
 }
 __device__ __forceinline__ void bar_arrive(uint64_t* b) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s_u32(b)) : "memory");
@@ -132,6 +163,35 @@ __device__ __forceinline__ void ld16(uint32_t taddr, float* v) {
 #pragma unroll
   for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
+// tcgen05.ld of N consecutive fp32 accumulator columns of this warp's 32 lanes; NO wait (caller issues wait::ld)
+template <int N>
+__device__ __forceinline__ void ld_cols(uint32_t taddr, float* v) {
+  static_assert(N == 8 || N == 16 || N == 32, "ld_cols width");
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  if constexpr (N == 8) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr)
+                 : "memory");
+  } else if constexpr (N == 16) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+  } else {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+  }
+}
 // no-swizzle K-major descriptor: start, LBO (K-direction core-matrix stride), SBO (8-row group stride), bytes
 __device__ __forceinline__ uint64_t desc_ns(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = (uint64_t)((saddr & 0x3FFFF) >> 4);
@@ -167,8 +227,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
 
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], V2_PRODUCERS / 32); bar_init(&empty_bar[i], use_res ? 9 : 1); }
-    for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], 8); }
+    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], V2_PRODUCERS / 32); bar_init(&empty_bar[i], use_res ? 1 + V2_EPI_WARPS : 1); }
+    for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], V2_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == V2_PW) {
@@ -212,7 +272,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
                 (i >= C::TOTAL_ITEMS ? 0x80000000u : 0u);
       srel[u] = (py * P.W + px) * CIN + j * 8;
     }
-    const int depth = P.nstages - 1 < V2_DEPTH ? P.nstages - 1 : V2_DEPTH;  // stages >= tiles in flight + the one in MMA
+    // tiles in flight per thread.  A tile is published when the producer comes round `depth` iterations later, i.e.
+    // after it has been granted the stage of tile it+depth-nstages: nstages - depth - 1 tiles of slack keep that
+    // hand-shake off the MMA warp's critical path (with no slack, load / MMA / epilogue times ADD instead of overlap).
+    const int depth = P.nstages - 2 < 1 ? 1 : (P.nstages - 2 > V2_DEPTH ? V2_DEPTH : P.nstages - 2);
     int it = 0;
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
       const int st = it % P.nstages;
@@ -227,8 +290,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
         fence_async_smem();
         __syncwarp();
         if (lane == 0) bar_arrive(&full_bar[(it - depth) % P.nstages]);
+        if (threadIdx.x == 0) V2_TRACE(0, it - depth, 3);  // published
       }
-      bar_wait(&empty_bar[st], ph ^ 1);
+      if (threadIdx.x == 0) V2_TRACE(0, it, 0);  // wants stage
+      bar_wait_relaxed(&empty_bar[st], ph ^ 1);
+      if (threadIdx.x == 0) V2_TRACE(0, it, 1);  // got stage
       const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
       const bf16* img = P.in + (size_t)n * P.H * P.W * CIN;
       const bf16* org = img + ((ptrdiff_t)gy0 * P.W + gx0) * CIN;  // halo origin (may lie outside the image)
@@ -244,6 +310,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
+      if (threadIdx.x == 0) V2_TRACE(0, it, 2);  // loads issued
     }
     // drain: publish the last `depth` tiles
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -263,8 +330,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       const int st = it % P.nstages;
       const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
       const int as = it & 1;
-      bar_wait(&tempty_bar[as], (uint32_t)(((it >> 1) & 1) ^ 1));
+      if (leader) V2_TRACE(1, it, 0);
+      bar_wait_relaxed(&tempty_bar[as], (uint32_t)(((it >> 1) & 1) ^ 1));
+      if (leader) V2_TRACE(1, it, 1);  // accumulator free
       bar_wait(&full_bar[st], ph);
+      if (leader) V2_TRACE(1, it, 2);  // tile landed
       tc_after();
       const uint64_t ad0 = desc_ns(s_u32(a_s + (size_t)st * C::A_BYTES), A_LBO, A_SBO);
       if (!(P.ablate & 2)) {
@@ -289,17 +359,29 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       if (leader) {
         commit_to(&empty_bar[st]);
         commit_to(&tfull_bar[as]);
+        V2_TRACE(1, it, 3);  // MMAs issued
       }
       __syncwarp();
     }
   } else {
-    // ================= epilogue: 8 warps, two per TMEM lane group, each taking every other sub-tile =================
-    const int lg = warp & 3;                 // TMEM lane group this warp may access
-    const int half = (warp - V2_PW - 1) >> 2;  // 0: even sub-tiles, 1: odd sub-tiles
+    // ================= epilogue: 16 warps = 4 TMEM lane groups x NSJ sub-tile classes x NSC channel slices.  A warp
+    // keeps its slice's bias / beta in registers, pulls its accumulator columns with one tcgen05.wait::ld, hands the
+    // TMEM buffer back to the MMA warp, and only then does the bias / residual / activation math and the stores.
+    const int lg = warp & 3;                      // TMEM lane group this warp may access
+    const int role = (warp - V2_PW - 1) >> 2;     // 0..3
+    constexpr int NSJ = KW >= 2 ? 2 : 1;          // sub-tile classes (j mod NSJ)
+    constexpr int NSC = 4 / NSJ;                  // channel slices
+    constexpr int CH = COUT / NSC;                // channels (accumulator columns) per warp and sub-tile
+    constexpr int NJ = KW / NSJ;                  // sub-tiles per warp and tile
+    static_assert(CH == 8 || CH == 16 || CH == 32, "epilogue slice width");
+    const int jc = role % NSJ;
+    const int cb = (role / NSJ) * CH;
     const int m = lg * 32 + lane;
     const int ly = m >> 3, lx = m & 7;
-    const float4* bias4 = reinterpret_cast<const float4*>(bias_s);
-    const float4* beta4 = reinterpret_cast<const float4*>(beta_s);
+    const float* bias_r = P.bias_c + cb;  // warp-uniform constant-bank reads
+    const float* beta_r = P.beta_c + cb;
+    constexpr int NR = CH / 8;
+    const bool tr = warp == V2_PW + 1 && lane == 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
       const int st = it % P.nstages;
@@ -308,87 +390,90 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       const int y = ty * 16 + ly;
       // residual = centre pixels of the input halo tile: pull them into registers as soon as the tile has landed and
       // release the smem stage right away (the stage then only lives for load + MMA, not for the whole epilogue)
-      constexpr int NRES = (KW / 2) * (COUT / 8);
-      uint4 res[NRES];
+      uint4 res[NJ * NR];
+      if (tr) V2_TRACE(2, it, 3);  // tile begin
       if (use_res) {
         bar_wait(&full_bar[st], (uint32_t)((it / P.nstages) & 1));
+        if (tr) V2_TRACE(2, it, 4);  // input tile visible
         const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * C::A_BYTES);
 #pragma unroll
-        for (int jj = 0; jj < KW / 2; jj++) {
-          const int pc = (ly + 1) * C::PITCH + 8 * (2 * jj + half) + lx + 1;  // this thread's centre pixel
+        for (int jj = 0; jj < NJ; jj++) {
+          const int pc = (ly + 1) * C::PITCH + 8 * (jj * NSJ + jc) + lx + 1;  // this thread's centre pixel
 #pragma unroll
-          for (int ch = 0; ch < COUT / 8; ch++) res[jj * (COUT / 8) + ch] = a_st[ch * C::CS + pc];
+          for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = a_st[(cb / 8 + ch) * C::CS + pc];
         }
         __syncwarp();
         if (lane == 0) bar_arrive(&empty_bar[st]);
       }
+      if (tr) V2_TRACE(2, it, 0);  // residual read, waiting for the accumulator
       bar_wait(&tfull_bar[as], (uint32_t)((it >> 1) & 1));
+      if (tr) V2_TRACE(2, it, 1);  // accumulator complete
       tc_after();
+      float v[NJ][CH];
+      if (!(P.ablate & 8)) {
 #pragma unroll
-      for (int jj = 0; jj < KW / 2; jj++) {
-        const int j = 2 * jj + half;
+        for (int jj = 0; jj < NJ; jj++)
+          ld_cols<CH>(tmem_base + ((uint32_t)(lg * 32) << 16) +
+                          (uint32_t)(as * C::ACC_STRIDE + (jj * NSJ + jc) * COUT + cb), v[jj]);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      } else {
+#pragma unroll
+        for (int jj = 0; jj < NJ; jj++)
+#pragma unroll
+          for (int i = 0; i < CH; i++) v[jj][i] = 0.f;
+      }
+      if (tr) V2_TRACE(2, it, 5);  // accumulator in registers
+      tc_before();
+      __syncwarp();
+      if (lane == 0) bar_arrive(&tempty_bar[as]);
+      if (tr) V2_TRACE(2, it, 2);  // accumulator released
+#pragma unroll
+      for (int jj = 0; jj < NJ; jj++) {
+        const int j = jj * NSJ + jc;
         const int x = (tx * KW + j) * 8 + lx;
         const bool valid = (y < P.H) && (x < P.W);
-        const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE + j * COUT);
-        if constexpr (EPI == 1) {
-          static_assert(EPI != 1 || COUT == 16, "Head deconv instance");
-          float v[16];
-          ld16(taddr, v);
-          if (valid) {
+        if (valid && !(P.ablate & 4)) {
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-              const float4 b = bias4[q];
-              v[4 * q] += b.x; v[4 * q + 1] += b.y; v[4 * q + 2] += b.z; v[4 * q + 3] += b.w;
-            }
-#pragma unroll
-            for (int p = 0; p < 2; p++) {  // output row 2y+p, pixels 2x and 2x+1, 4 channels each
-              uint4 o;
-              o.x = pk_bf16(v[8 * p], v[8 * p + 1]); o.y = pk_bf16(v[8 * p + 2], v[8 * p + 3]);
-              o.z = pk_bf16(v[8 * p + 4], v[8 * p + 5]); o.w = pk_bf16(v[8 * p + 6], v[8 * p + 7]);
-              *reinterpret_cast<uint4*>(P.out + (((size_t)n * 2 * P.H + 2 * y + p) * (2 * P.W) + 2 * x) * 4) = o;
-            }
-          }
-        } else {
-        bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT;
-#pragma unroll
-        for (int c = 0; c < COUT; c += 16) {
-          float v[16];
-          if (!(P.ablate & 8)) ld16(taddr + c, v);
-          else { for (int i = 0; i < 16; i++) v[i] = 0.f; }
-          if (valid && !(P.ablate & 4)) {
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-              const float4 b = bias4[(c >> 2) + q];
-              v[4 * q] += b.x; v[4 * q + 1] += b.y; v[4 * q + 2] += b.z; v[4 * q + 3] += b.w;
-            }
+          for (int i = 0; i < CH; i++) v[jj][i] += bias_r[i];
+          if constexpr (EPI == 1) {
+            // Head.cnn3: column = (2p+q)*4 + co; this warp's 8 columns are output row 2y+p (p = cb/8), pixels 2x and
+            // 2x+1, 4 channels each
+            static_assert(EPI != 1 || (COUT == 16 && CH == 8), "Head deconv instance");
+            uint4 o;
+            o.x = pk_bf16(v[jj][0], v[jj][1]); o.y = pk_bf16(v[jj][2], v[jj][3]);
+            o.z = pk_bf16(v[jj][4], v[jj][5]); o.w = pk_bf16(v[jj][6], v[jj][7]);
+            *reinterpret_cast<uint4*>(P.out + (((size_t)n * 2 * P.H + 2 * y + (cb >> 3)) * (2 * P.W) + 2 * x) * 4) = o;
+          } else {
             if (use_res) {
-              const uint4 r0 = res[jj * (COUT / 8) + (c >> 3)], r1 = res[jj * (COUT / 8) + (c >> 3) + 1];
-              const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
-              for (int q = 0; q < 4; q++) {
-                const float4 be = beta4[(c >> 2) + q];
-                const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rr[2 * q]));
-                const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rr[2 * q + 1]));
-                v[4 * q] = fmaf(v[4 * q], be.x, f0.x); v[4 * q + 1] = fmaf(v[4 * q + 1], be.y, f0.y);
-                v[4 * q + 2] = fmaf(v[4 * q + 2], be.z, f1.x); v[4 * q + 3] = fmaf(v[4 * q + 3], be.w, f1.y);
+              for (int ch = 0; ch < NR; ch++) {
+                const uint4 r = res[jj * NR + ch];
+                const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                  const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rr[q]));
+                  const int i = ch * 8 + 2 * q;
+                  v[jj][i] = fmaf(v[jj][i], beta_r[i], f.x);
+                  v[jj][i + 1] = fmaf(v[jj][i + 1], beta_r[i + 1], f.y);
+                }
               }
             }
             if (P.act) {
 #pragma unroll
-              for (int i = 0; i < 16; i++) v[i] = v[i] > 0.f ? v[i] : v[i] * P.slope;
+              for (int i = 0; i < CH; i++) v[jj][i] = v[jj][i] > 0.f ? v[jj][i] : v[jj][i] * P.slope;
             }
-            uint4 o0, o1;
-            o0.x = pk_bf16(v[0], v[1]); o0.y = pk_bf16(v[2], v[3]); o0.z = pk_bf16(v[4], v[5]); o0.w = pk_bf16(v[6], v[7]);
-            o1.x = pk_bf16(v[8], v[9]); o1.y = pk_bf16(v[10], v[11]); o1.z = pk_bf16(v[12], v[13]); o1.w = pk_bf16(v[14], v[15]);
-            *reinterpret_cast<uint4*>(op + c) = o0;
-            *reinterpret_cast<uint4*>(op + c + 8) = o1;
+            bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT + cb;
+#pragma unroll
+            for (int c = 0; c < CH; c += 8) {
+              uint4 o;
+              o.x = pk_bf16(v[jj][c], v[jj][c + 1]); o.y = pk_bf16(v[jj][c + 2], v[jj][c + 3]);
+              o.z = pk_bf16(v[jj][c + 4], v[jj][c + 5]); o.w = pk_bf16(v[jj][c + 6], v[jj][c + 7]);
+              *reinterpret_cast<uint4*>(op + c) = o;
+            }
           }
         }
-        }
       }
-      tc_before();
-      __syncwarp();
-      if (lane == 0) bar_arrive(&tempty_bar[as]);
+      if (tr) V2_TRACE(2, it, 7);  // tile stored
     }
   }
   tc_before();
@@ -441,10 +526,13 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
     float b16[16], bh[4];
     VFI_CUDA(h, cudaMemcpy(bh, L.bias, sizeof(bh), cudaMemcpyDeviceToHost));
     for (int i = 0; i < 16; i++) b16[i] = bh[i & 3];
+    for (int i = 0; i < 64; i++) { L.h_bias_v2[i] = b16[i & 15]; L.h_beta[i] = 1.f; }
     VFI_CUDA(h, cudaMalloc(&L.bias_v2, sizeof(b16)));
     VFI_CUDA(h, cudaMemcpy(L.bias_v2, b16, sizeof(b16), cudaMemcpyHostToDevice));
     return 0;
   }
+  VFI_CUDA(h, cudaMemcpy(L.h_bias_v2, L.bias, L.cout * sizeof(float), cudaMemcpyDeviceToHost));
+  if (L.has_beta) VFI_CUDA(h, cudaMemcpy(L.h_beta, L.beta, L.cout * sizeof(float), cudaMemcpyDeviceToHost));
   std::vector<uint16_t> pk((size_t)9 * L.cin * L.cout);
   for (int tap = 0; tap < 9; tap++)
     for (int j = 0; j < nch; j++)
@@ -488,6 +576,29 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   P.act = L.act ? 1 : 0;
   P.slope = slope;
   P.ablate = h->opt_v2_ablate;
+  for (int i = 0; i < 64; i++) { P.bias_c[i] = L.h_bias_v2[i]; P.beta_c[i] = L.has_beta ? L.h_beta[i] : 1.f; }
+  if (h->opt_v2_trace) {
+    // debug: time-stamp CTA 0's producer / MMA / epilogue hand-shakes of this launch and dump them for tools/v2_trace.py
+    static unsigned long long* tbuf = nullptr;
+    const size_t tbytes = 3 * 64 * 8 * sizeof(unsigned long long);
+    if (!tbuf) VFI_CUDA(h, cudaMalloc(&tbuf, tbytes));
+    VFI_CUDA(h, cudaMemsetAsync(tbuf, 0, tbytes, s));
+    P.trace = tbuf;
+    int rc;
+    switch (L.cin) {
+      case 16: rc = launch_v2<16, 16, 4, 0>(h, P, s); break;
+      case 32: rc = launch_v2<32, 32, 4, 0>(h, P, s); break;
+      default: rc = launch_v2<64, 64, 1, 0>(h, P, s); break;
+    }
+    if (rc) return rc;
+    std::vector<unsigned long long> host(3 * 64 * 8);
+    VFI_CUDA(h, cudaStreamSynchronize(s));
+    VFI_CUDA(h, cudaMemcpy(host.data(), tbuf, tbytes, cudaMemcpyDeviceToHost));
+    char path[128];
+    snprintf(path, sizeof(path), "gpurun_out/v2_trace_c%d.bin", L.cin);
+    if (FILE* f = fopen(path, "wb")) { fwrite(host.data(), 1, tbytes, f); fclose(f); }
+    return 0;
+  }
   if (L.kind == LK_DECONV4) {
     P.bias = L.bias_v2; P.beta = nullptr; P.act = 0;
     return launch_v2<16, 16, 4, 1>(h, P, s);
@@ -495,7 +606,7 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   switch (L.cin) {
     case 16: return launch_v2<16, 16, 4, 0>(h, P, s);
     case 32: return launch_v2<32, 32, 4, 0>(h, P, s);
-    case 64: return launch_v2<64, 64, 2, 0>(h, P, s);
+    case 64: return launch_v2<64, 64, 1, 0>(h, P, s);  // KW = 1: 6 stages beside the 72 KB of weights
   }
   VFI_FAIL(h, VFI_E_ARG, "conv_v2: no instance for Cin=%d", L.cin);
 }
