@@ -183,3 +183,24 @@ def test_run_model_benchmark_keys(engine):
     out = run_model_benchmark(m, tr, num_intermediate=1, target_scale=1.0)
     for k in ("time_mean_ms", "time_p99_ms", "throughput_fps", "vram_peak_mb", "psnr_mean", "ssim_mean"):
         assert k in out
+
+
+def test_clip_streamer_equals_batch_api():
+    """The pipelined clip API (three streams, two slots) returns exactly what interpolate_batch returns, slot reuse
+    included."""
+    m = RIFEModel()
+    m.load()
+    ts = [0.25, 0.5, 0.75]
+    clip = gen_clip(13, 96, 160, seed=11, cut_every=0, fast=None)
+    want = [m.interpolate_batch(clip[3 * b:3 * b + 3], clip[3 * b + 1:3 * b + 4], ts) for b in range(4)]
+    torch.cuda.synchronize()           # the engine's workspace is shared: no other stream may be mid-inference
+    host = torch.from_numpy(clip).pin_memory()
+    st = m.clip_streamer(pairs=3, H=96, W=160, timestamps=ts, depth=2)
+    pending = []
+    for b in range(4):
+        pending.append((st.submit(host[3 * b:3 * b + 4]), b))
+        if len(pending) == 2:                       # collect before the slot is reused
+            slot, b0 = pending.pop(0)
+            assert np.array_equal(st.result(slot).numpy(), want[b0])
+    slot, b0 = pending.pop(0)
+    assert np.array_equal(st.result(slot).numpy(), want[b0])

@@ -117,6 +117,11 @@ class RIFEModel(BaseModel):
         out = self._engine.infer(frames0, frames1, list(timestamps), scale, prec, hud_mask=hud_masks)
         return out if device_out else out.cpu().numpy()
 
+    def clip_streamer(self, pairs: int, H: int, W: int, timestamps, depth: int = 2) -> "ClipStreamer":
+        """Extra (not in the reference): pipelined clip interpolation, see ClipStreamer."""
+        self.ensure_loaded()
+        return ClipStreamer(self, pairs, H, W, list(timestamps), depth)
+
     def upscale(self, frame: np.ndarray, scale: float = 1.333) -> np.ndarray:
         """RIFE does no SR: Lanczos on the host exactly as the reference (rife_wrapper.py:156-164)."""
         h, w = frame.shape[:2]
@@ -134,6 +139,73 @@ class RIFEModel(BaseModel):
                 nxt += [self.interpolate(a, b, num_frames=1)[0], b]
             seq = nxt
         return seq[1:-1]
+
+
+class ClipStreamer:
+    """Streams a clip through RIFE in batches of `pairs` consecutive frame pairs with the host<->device copies
+    overlapped with the kernels: three CUDA streams (upload, compute, download) and `depth` buffer slots.
+    A batch is the pairs+1 consecutive frames clip[s : s+pairs+1] (frame k and k+1 form pair k), so every frame crosses
+    PCIe once, as uint8.  The reference's hot loop (scripts/run_benchmarks.py:142) does upload, compute and
+    download serially per pair.
+
+        st = model.clip_streamer(pairs=8, H=1080, W=1920, timestamps=[0.25, 0.5, 0.75])
+        slot = st.submit(frames_pinned)      # (pairs+1, H, W, 3) uint8 pinned host tensor; returns immediately
+        out = st.result(slot)                # (pairs, T, H, W, 3) uint8 pinned host tensor (valid until the slot is reused)
+    """
+
+    def __init__(self, model: "RIFEModel", pairs: int, H: int, W: int, timestamps, depth: int = 2):
+        self.m, self.B, self.ts, self.depth = model, pairs, timestamps, depth
+        dev = model.device
+        T = len(timestamps)
+        self.prec = _abi.PRECISION_BF16 if model.precision == 'bf16' else _abi.PRECISION_FP32
+        self.scale = 0.5 if model.uhd_mode else 1.0
+        with torch.cuda.device(dev):
+            self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+            self.in_dev = [torch.empty((pairs + 1, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(depth)]
+            self.out_dev = [torch.empty((pairs, T, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(depth)]
+            self.out_host = [torch.empty((pairs, T, H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(depth)]
+            self.ev_in = [torch.cuda.Event() for _ in range(depth)]
+            self.ev_cmp = [torch.cuda.Event() for _ in range(depth)]
+            self.ev_out = [torch.cuda.Event() for _ in range(depth)]
+        self.k = 0
+        self.h2d_bytes = (pairs + 1) * H * W * 3
+        self.d2h_bytes = pairs * T * H * W * 3
+
+    def submit(self, frames_host: torch.Tensor) -> int:
+        i = self.k % self.depth
+        first = self.k < self.depth
+        cur = torch.cuda.current_stream(self.m.device)
+        if self.k == 0:
+            for s in (self.s_in, self.s_cmp, self.s_out):
+                s.wait_stream(cur)
+        with torch.cuda.stream(self.s_in):
+            if not first:
+                self.s_in.wait_event(self.ev_cmp[i])        # the kernels that read this input slot are done
+            self.in_dev[i].copy_(frames_host, non_blocking=True)
+            self.ev_in[i].record(self.s_in)
+        with torch.cuda.stream(self.s_cmp):
+            self.s_cmp.wait_event(self.ev_in[i])
+            if not first:
+                self.s_cmp.wait_event(self.ev_out[i])       # the previous result in this output slot has left
+            self.m._engine.infer(self.in_dev[i][:-1], self.in_dev[i][1:], self.ts, self.scale, self.prec,
+                                 out=self.out_dev[i])
+            self.ev_cmp[i].record(self.s_cmp)
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(self.ev_cmp[i])
+            self.out_host[i].copy_(self.out_dev[i], non_blocking=True)
+            self.ev_out[i].record(self.s_out)
+        self.k += 1
+        return i
+
+    def result(self, slot: int) -> torch.Tensor:
+        self.ev_out[slot].synchronize()
+        return self.out_host[slot]
+
+    def join(self) -> None:
+        """Make the current stream wait for everything submitted so far (for event timing / ordering)."""
+        cur = torch.cuda.current_stream(self.m.device)
+        for s in (self.s_in, self.s_cmp, self.s_out):
+            cur.wait_stream(s)
 
 
 class RIFELiteModel(RIFEModel):
