@@ -133,7 +133,7 @@ def test_single_layer_vs_torch(engine, weights, layer, prec):
     assert err <= tol, f"layer {layer} ({li['key']}): {err} > {tol}"
 
 
-@pytest.mark.parametrize("layer", [1, 2, 39, 46, 50, 57])
+@pytest.mark.parametrize("layer", [1, 2, 17, 24, 28, 35, 39, 46, 50, 57])
 @pytest.mark.parametrize("Hin,Win", [(16, 8), (23, 41), (50, 100), (136, 240)])
 def test_conv_v2_halo_tile_kernel(engine, weights, layer, Hin, Win):
     """csrc/conv_v2.cu (resident weights, one halo tile per 16 x 8KW outputs, shifted no-swizzle descriptors) against

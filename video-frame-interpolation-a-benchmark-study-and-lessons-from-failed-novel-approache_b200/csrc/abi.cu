@@ -223,7 +223,10 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
   const int mult = 64 * inv > 32 ? 64 * inv : 32;
   const int Hp = (H + mult - 1) / mult * mult, Wp = (W + mult - 1) / mult * mult;
   if (Hp - H >= H || Wp - W >= W) VFI_FAIL(h, VFI_E_ARG, "frame too small for reflect padding to %d", mult);
-  const int N = B * T, NI = 2 * B;
+  // consecutive pairs of one clip (img1 is img0 shifted by one frame): frame b+1 is both pair b's second and pair
+  // b+1's first frame -- pad it and run the Head on it once
+  const bool clipmode = B > 1 && img1 == img0 + (size_t)H * W * 3;
+  const int N = B * T, NI = clipmode ? B + 1 : 2 * B, I1 = clipmode ? 1 : B;
   int sl[5];
   for (int i = 0; i < 5; i++) sl[i] = (16 >> i) * inv;
 
@@ -263,7 +266,9 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     VFI_CUDA(h, cudaMemcpyAsync(tdev, timesteps, T * sizeof(float), cudaMemcpyHostToDevice, s));
     // to_tensor + reflect pad, both frames of every pair
     if ((rc = k_pad_rgbx(h, img0, imgs, B, H, W, Hp, Wp, s))) return rc;
-    if ((rc = k_pad_rgbx(h, img1, imgs + (size_t)B * px * 4, B, H, W, Hp, Wp, s))) return rc;
+    if (clipmode) rc = k_pad_rgbx(h, img1 + (size_t)(B - 1) * H * W * 3, imgs + (size_t)B * px * 4, 1, H, W, Hp, Wp, s);
+    else rc = k_pad_rgbx(h, img1, imgs + (size_t)B * px * 4, B, H, W, Hp, Wp, s);
+    if (rc) return rc;
     // Head (encode) once per image, shared by all T timesteps
     if ((rc = k_head_cnn0(h, h->layers[0], imgs, ht0, NI, Hp, Wp, bf, s))) return rc;
     if ((rc = run_conv(h, h->layers[1], ht0, nullptr, ht1, NI, Hp / 2, Wp / 2, bf, false, s))) return rc;
@@ -276,7 +281,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     for (int i = 0; i < 5; i++) {
       const int sc = sl[i], hs = Hp / sc, wsz = Wp / sc;
       const Layer* Lb = &h->layers[4 + 11 * i];
-      if ((rc = k_gather(h, imgs, feats, lows, tdev, xin, B, T, Hp, Wp, sc, bf, bf, s))) return rc;
+      if ((rc = k_gather(h, imgs, feats, lows, tdev, xin, B, I1, T, Hp, Wp, sc, bf, bf, s))) return rc;
       if ((rc = run_conv(h, Lb[0], xin, nullptr, a0, N, hs, wsz, bf, bf, s))) return rc;
       if ((rc = run_conv(h, Lb[1], a0, nullptr, fa, N, hs / 2, wsz / 2, bf, false, s))) return rc;
       uint8_t *cur = fa, *nxt = fb;
@@ -290,7 +295,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       if (rc) return rc;
       lows.push(low[i], sc, lc, Hp, Wp);
     }
-    if ((rc = k_final_blend(h, imgs, lows, hud_mask, tdev, out, out_f32, flow_out, B, T, H, W, Hp, Wp, s))) return rc;
+    if ((rc = k_final_blend(h, imgs, lows, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s))) return rc;
   }
   return VFI_OK;
 }
@@ -318,7 +323,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_warp_blend(vfi_handle*
     LowSet lows;
     memset(&lows, 0, sizeof(lows));
     lows.push(fm, 1, 8, H, W);
-    if ((rc = k_final_blend(h, imgs, lows, nullptr, tdev, out, out_f32, nullptr, N, 1, H, W, H, W, s))) return rc;
+    if ((rc = k_final_blend(h, imgs, lows, nullptr, tdev, out, out_f32, nullptr, N, N, 1, H, W, H, W, s))) return rc;
   }
   return VFI_OK;
 }

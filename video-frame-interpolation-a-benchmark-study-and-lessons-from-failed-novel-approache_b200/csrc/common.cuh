@@ -51,7 +51,7 @@ struct Layer {
   int cblk = 0, rows_total = 0, nsteps = 0, n_total = 0, b_box = 0;
   TcStep steps[VFI_MAX_STEPS];
   float* bias_tc = nullptr;  // bias laid out by accumulator column (n_total floats)
-  float h_bias_v2[64] = {0}, h_beta[64] = {0};  // host copies for conv_v2's constant-bank epilogue parameters
+  float h_bias_v2[128] = {0}, h_beta[128] = {0};  // host copies for conv_v2's constant-bank epilogue parameters
   float* bias_v2 = nullptr;  // conv_v2.cu Head.cnn3 instance: bias per (phase, channel) column
   bf16* ws2 = nullptr;       // conv_s2.cu resident-weight image of a stride-2 conv (null: not s2-capable)
   bf16* wv2 = nullptr;       // conv_v2.cu resident-weight image [tap][cin/8][cout][8] (null: layer not v2-capable)
@@ -141,9 +141,12 @@ struct LowSet {
   }
 };
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
-             void* out, int B, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s);
-int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B,
-                  int T, int H, int W, int Hp, int Wp, cudaStream_t s);
+             void* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s);
+// I1: index of pair 0's second frame in imgs / feats (B when the two frame sets are stored one after the other, 1 when
+// the pairs are consecutive frames of one clip)
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev,
+                  uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp, int Wp,
+                  cudaStream_t s);
 int k_pack_fm(vfi_handle* h, const float* flow, const float* mask, float* fm, int N, int H, int W, int Hp, int Wp,
               cudaStream_t s);
 int k_f32_to_act(vfi_handle* h, const float* src, void* dst, size_t n, bool bf, cudaStream_t s);

@@ -34,8 +34,8 @@ struct V2Params {
   float slope;
   // bias / beta by output column, read by the epilogue through the constant bank: the shared-memory pipe is saturated
   // by the tensor core's operand reads while MMAs are in flight
-  float bias_c[64];
-  float beta_c[64];
+  float bias_c[128];
+  float beta_c[128];
   unsigned long long* trace;  // debug (vfi_set_option "v2_trace"): CTA 0 timestamps [role][tile < 64][8]
 };
 
@@ -57,6 +57,7 @@ __device__ __forceinline__ unsigned long long v2_now() {
     if (P.trace && blockIdx.x == 0 && (tile_i) < 64) P.trace[((role)*64 + (tile_i)) * 8 + (ev)] = v2_now(); \
   } while (0)
 
+// COUT here = output channels computed by ONE CTA (the layer's Cout / NSPLIT)
 template <int CIN, int COUT, int KW>
 struct V2Cfg {
   static constexpr int NCHUNK = CIN / 8;
@@ -75,12 +76,13 @@ struct V2Cfg {
   static constexpr int A_BYTES = (NCHUNK * CS * 16 + 127) & ~127;
   static constexpr int W_BYTES = 9 * CIN * COUT * 2;
   static constexpr int BB_BYTES = (2 * COUT * 4 + 127) & ~127;
-  static constexpr int ACC_STRIDE = KW * COUT;
-  static constexpr int TMEM_COLS = 2 * ACC_STRIDE <= 32 ? 32 : 2 * ACC_STRIDE <= 64 ? 64 : 2 * ACC_STRIDE <= 128 ? 128
-                                   : 2 * ACC_STRIDE <= 256 ? 256 : 512;
+  static constexpr int ACC_COLS = KW * COUT;  // accumulator columns of one tile
+  static constexpr int TMEM_COLS = 2 * ACC_COLS <= 32 ? 32 : 2 * ACC_COLS <= 64 ? 64 : 2 * ACC_COLS <= 128 ? 128
+                                   : 2 * ACC_COLS <= 256 ? 256 : 512;
+  static constexpr int ACC_STRIDE = TMEM_COLS / 2;  // the two accumulator buffers start on power-of-two columns
   static constexpr int TOTAL_ITEMS = NPIX * NCHUNK;
   static constexpr int UNROLL = (TOTAL_ITEMS + 2 * V2_PRODUCERS - 1) / (2 * V2_PRODUCERS);  // two load batches per tile
-  static_assert(2 * ACC_STRIDE <= 512, "TMEM budget");
+  static_assert(2 * ACC_COLS <= 512, "TMEM budget");
 };
 
 namespace {
@@ -211,9 +213,16 @@ __device__ __forceinline__ uint32_t pk_bf16(float a, float b) {
 
 // EPI 0: conv (+ResConv) -> bf16 NHWC.  EPI 1: Head.cnn3 = ConvTranspose2d(16,4,4,2,1) run as a 3x3 conv whose 16
 // output columns are (output phase p,q) x (4 channels); the epilogue scatters them to the 2x2 output quad.
-template <int CIN, int COUT, int KW, int EPI>
+// NSPLIT > 1: the layer's output channels are split over NSPLIT groups of CTAs (CTA c serves group c % NSPLIT) so that
+// the group's 9 x CIN x COUT/NSPLIT weight slice stays resident where the whole matrix would not fit (c = 96, 128).
+template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1>
 __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_constant__ V2Params P) {
-  using C = V2Cfg<CIN, COUT, KW>;
+  constexpr int CN = COUT / NSPLIT;  // GEMM N of this CTA
+  static_assert(COUT % NSPLIT == 0 && CN % 16 == 0, "channel split");
+  using C = V2Cfg<CIN, CN, KW>;
+  const int split = NSPLIT > 1 ? (int)blockIdx.x % NSPLIT : 0;
+  const int co0 = split * CN;  // first output channel of this CTA
+  const int tile0 = (int)blockIdx.x / NSPLIT, tile_step = (int)gridDim.x / NSPLIT;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t full_bar[V2_MAX_STAGES], empty_bar[V2_MAX_STAGES], tfull_bar[2], tempty_bar[2];
   __shared__ uint32_t tmem_base_smem;
@@ -221,7 +230,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t* w_s = smem;
   float* bias_s = reinterpret_cast<float*>(smem + C::W_BYTES);
-  float* beta_s = bias_s + COUT;
+  float* beta_s = bias_s + CN;
   uint8_t* a_s = smem + C::W_BYTES + C::BB_BYTES;
   const bool use_res = EPI == 0 && P.beta != nullptr;
 
@@ -238,12 +247,12 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   {
-    const uint4* src = reinterpret_cast<const uint4*>(P.wpack);
+    const uint4* src = reinterpret_cast<const uint4*>(P.wpack + (size_t)split * 9 * CIN * CN);
     uint4* dst = reinterpret_cast<uint4*>(w_s);
     for (int i = threadIdx.x; i < C::W_BYTES / 16; i += V2_THREADS) dst[i] = __ldg(src + i);
-    for (int i = threadIdx.x; i < COUT; i += V2_THREADS) {
-      bias_s[i] = P.bias[i];
-      beta_s[i] = use_res ? P.beta[i] : 1.f;
+    for (int i = threadIdx.x; i < CN; i += V2_THREADS) {
+      bias_s[i] = P.bias[co0 + i];
+      beta_s[i] = use_res ? P.beta[co0 + i] : 1.f;
     }
     fence_async_smem();
   }
@@ -277,7 +286,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     // hand-shake off the MMA warp's critical path (with no slack, load / MMA / epilogue times ADD instead of overlap).
     const int depth = P.nstages - 2 < 1 ? 1 : (P.nstages - 2 > V2_DEPTH ? V2_DEPTH : P.nstages - 2);
     int it = 0;
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
       const int st = it % P.nstages;
       const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
       const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
@@ -321,12 +330,12 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   } else if (warp == V2_PW) {
     // ================= MMA issuer: the warp stays converged, one elected lane issues =================
     const uint32_t leader = elect_one();
-    constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(COUT >> 3) << 17) | (8u << 24);
-    constexpr uint32_t A_LBO = C::CS * 16, A_SBO = C::PITCH * 16, B_LBO = COUT * 16, B_SBO = 128;
+    constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(CN >> 3) << 17) | (8u << 24);
+    constexpr uint32_t A_LBO = C::CS * 16, A_SBO = C::PITCH * 16, B_LBO = CN * 16, B_SBO = 128;
     constexpr int KSTEPS = CIN / 16;
     const uint64_t bd0 = desc_ns(s_u32(w_s), B_LBO, B_SBO);
     int it = 0;
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
       const int st = it % P.nstages;
       const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
       const int as = it & 1;
@@ -350,8 +359,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
             constexpr int dummy = 0;
             (void)dummy;
             const uint32_t a_off = (uint32_t)((tap / 3) * C::PITCH + (tap % 3) + 8 * j + 2 * k * C::CS);
-            const uint32_t b_off = (uint32_t)((tap * C::NCHUNK + 2 * k) * COUT);
-            mma_bf16_elect(leader, dcol0 + (uint32_t)(j * COUT), ad0 + a_off, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
+            const uint32_t b_off = (uint32_t)((tap * C::NCHUNK + 2 * k) * CN);
+            mma_bf16_elect(leader, dcol0 + (uint32_t)(j * CN), ad0 + a_off, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
           }
         }
       }
@@ -370,20 +379,23 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     const int lg = warp & 3;                      // TMEM lane group this warp may access
     const int role = (warp - V2_PW - 1) >> 2;     // 0..3
     constexpr int NSJ = KW >= 2 ? 2 : 1;          // sub-tile classes (j mod NSJ)
-    constexpr int NSC = 4 / NSJ;                  // channel slices
-    constexpr int CH = COUT / NSC;                // channels (accumulator columns) per warp and sub-tile
+    constexpr int Q = 4 / NSJ;                    // warps available per lane group and sub-tile class
+    constexpr int CH = (CN % Q == 0 && (CN / Q == 8 || CN / Q == 16 || CN / Q == 32)) ? CN / Q : 16;  // columns per warp
+    constexpr int NSC = CN / CH;                  // channel slices in use (<= 4 / NSJ; spare warps only hand-shake)
+    static_assert(NSC <= Q && NSC * CH == CN, "epilogue slicing");
     constexpr int NJ = KW / NSJ;                  // sub-tiles per warp and tile
     static_assert(CH == 8 || CH == 16 || CH == 32, "epilogue slice width");
     const int jc = role % NSJ;
     const int cb = (role / NSJ) * CH;
+    const bool active = role / NSJ < NSC;
     const int m = lg * 32 + lane;
     const int ly = m >> 3, lx = m & 7;
-    const float* bias_r = P.bias_c + cb;  // warp-uniform constant-bank reads
-    const float* beta_r = P.beta_c + cb;
+    const float* bias_r = P.bias_c + co0 + (active ? cb : 0);  // warp-uniform constant-bank reads
+    const float* beta_r = P.beta_c + co0 + (active ? cb : 0);
     constexpr int NR = CH / 8;
     const bool tr = warp == V2_PW + 1 && lane == 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
       const int st = it % P.nstages;
       const int as = it & 1;
       const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
@@ -396,11 +408,12 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
         bar_wait(&full_bar[st], (uint32_t)((it / P.nstages) & 1));
         if (tr) V2_TRACE(2, it, 4);  // input tile visible
         const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * C::A_BYTES);
+        if (active)
 #pragma unroll
         for (int jj = 0; jj < NJ; jj++) {
           const int pc = (ly + 1) * C::PITCH + 8 * (jj * NSJ + jc) + lx + 1;  // this thread's centre pixel
 #pragma unroll
-          for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = a_st[(cb / 8 + ch) * C::CS + pc];
+          for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = a_st[((co0 + cb) / 8 + ch) * C::CS + pc];
         }
         __syncwarp();
         if (lane == 0) bar_arrive(&empty_bar[st]);
@@ -410,11 +423,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       if (tr) V2_TRACE(2, it, 1);  // accumulator complete
       tc_after();
       float v[NJ][CH];
-      if (!(P.ablate & 8)) {
+      if (!(P.ablate & 8) && active) {
 #pragma unroll
         for (int jj = 0; jj < NJ; jj++)
           ld_cols<CH>(tmem_base + ((uint32_t)(lg * 32) << 16) +
-                          (uint32_t)(as * C::ACC_STRIDE + (jj * NSJ + jc) * COUT + cb), v[jj]);
+                          (uint32_t)(as * C::ACC_STRIDE + (jj * NSJ + jc) * CN + cb), v[jj]);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       } else {
 #pragma unroll
@@ -432,7 +445,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
         const int j = jj * NSJ + jc;
         const int x = (tx * KW + j) * 8 + lx;
         const bool valid = (y < P.H) && (x < P.W);
-        if (valid && !(P.ablate & 4)) {
+        if (valid && active && !(P.ablate & 4)) {
 #pragma unroll
           for (int i = 0; i < CH; i++) v[jj][i] += bias_r[i];
           if constexpr (EPI == 1) {
@@ -462,7 +475,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
 #pragma unroll
               for (int i = 0; i < CH; i++) v[jj][i] = v[jj][i] > 0.f ? v[jj][i] : v[jj][i] * P.slope;
             }
-            bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT + cb;
+            bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT + co0 + cb;
 #pragma unroll
             for (int c = 0; c < CH; c += 8) {
               uint4 o;
@@ -498,8 +511,9 @@ static uint16_t f2bf_v2(float f) {
 bool v2_supported(const Layer& L) {
   if (L.kind == LK_DECONV4) return L.cin == 16 && L.cout == 4;  // Head.cnn3
   if (L.kind != LK_CONV3 || L.stride != 1 || L.cin != L.cout || L.cin != L.cin_pad) return false;
-  return L.cin == 16 || L.cin == 32 || L.cin == 64;
+  return L.cin == 16 || L.cin == 32 || L.cin == 64 || L.cin == 96 || L.cin == 128;
 }
+static int v2_nsplit(int c) { return c == 96 ? 2 : c == 128 ? 4 : 1; }
 
 // Packs Conv2d weights [Co][Ci][3][3] into the resident smem image [tap][Ci/8][Co][8] bf16.
 int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
@@ -526,29 +540,32 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
     float b16[16], bh[4];
     VFI_CUDA(h, cudaMemcpy(bh, L.bias, sizeof(bh), cudaMemcpyDeviceToHost));
     for (int i = 0; i < 16; i++) b16[i] = bh[i & 3];
-    for (int i = 0; i < 64; i++) { L.h_bias_v2[i] = b16[i & 15]; L.h_beta[i] = 1.f; }
+    for (int i = 0; i < 128; i++) { L.h_bias_v2[i] = b16[i & 15]; L.h_beta[i] = 1.f; }
     VFI_CUDA(h, cudaMalloc(&L.bias_v2, sizeof(b16)));
     VFI_CUDA(h, cudaMemcpy(L.bias_v2, b16, sizeof(b16), cudaMemcpyHostToDevice));
     return 0;
   }
   VFI_CUDA(h, cudaMemcpy(L.h_bias_v2, L.bias, L.cout * sizeof(float), cudaMemcpyDeviceToHost));
   if (L.has_beta) VFI_CUDA(h, cudaMemcpy(L.h_beta, L.beta, L.cout * sizeof(float), cudaMemcpyDeviceToHost));
+  // [split][tap][Ci/8][Co/nsplit][8]: each output-channel group's slice is one contiguous resident image
+  const int nsp = v2_nsplit(L.cin), cn = L.cout / nsp;
   std::vector<uint16_t> pk((size_t)9 * L.cin * L.cout);
   for (int tap = 0; tap < 9; tap++)
     for (int j = 0; j < nch; j++)
       for (int co = 0; co < L.cout; co++)
         for (int e = 0; e < 8; e++) {
           const int ci = j * 8 + e;
-          pk[(((size_t)tap * nch + j) * L.cout + co) * 8 + e] = f2bf_v2(w[((size_t)co * L.cin + ci) * 9 + tap]);
+          pk[((((size_t)(co / cn) * 9 + tap) * nch + j) * cn + co % cn) * 8 + e] =
+              f2bf_v2(w[((size_t)co * L.cin + ci) * 9 + tap]);
         }
   VFI_CUDA(h, cudaMalloc(&L.wv2, pk.size() * 2));
   VFI_CUDA(h, cudaMemcpy(L.wv2, pk.data(), pk.size() * 2, cudaMemcpyHostToDevice));
   return 0;
 }
 
-template <int CIN, int COUT, int KW, int EPI>
+template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1>
 static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
-  using C = V2Cfg<CIN, COUT, KW>;
+  using C = V2Cfg<CIN, COUT / NSPLIT, KW>;
   const size_t fixed = (size_t)C::W_BYTES + C::BB_BYTES;
   const size_t budget = 220 * 1024 - fixed;
   P.nstages = (int)std::min<size_t>(V2_MAX_STAGES, budget / C::A_BYTES);
@@ -557,10 +574,10 @@ static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
   P.tiles_y = cdiv(P.H, 16);
   P.num_tiles = P.N * P.tiles_x * P.tiles_y;
   const size_t smem = fixed + (size_t)P.nstages * C::A_BYTES;
-  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   224 * 1024));
-  const int grid = std::min(P.num_tiles, h->sm_count);
-  conv_v2_kernel<CIN, COUT, KW, EPI><<<grid, V2_THREADS, smem, s>>>(P);
+  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+  const int grid = std::min(P.num_tiles, h->sm_count / NSPLIT) * NSPLIT;
+  conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT><<<grid, V2_THREADS, smem, s>>>(P);
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -576,7 +593,7 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   P.act = L.act ? 1 : 0;
   P.slope = slope;
   P.ablate = h->opt_v2_ablate;
-  for (int i = 0; i < 64; i++) { P.bias_c[i] = L.h_bias_v2[i]; P.beta_c[i] = L.has_beta ? L.h_beta[i] : 1.f; }
+  for (int i = 0; i < 128; i++) { P.bias_c[i] = L.h_bias_v2[i]; P.beta_c[i] = L.has_beta ? L.h_beta[i] : 1.f; }
   if (h->opt_v2_trace) {
     // debug: time-stamp CTA 0's producer / MMA / epilogue hand-shakes of this launch and dump them for tools/v2_trace.py
     static unsigned long long* tbuf = nullptr;
@@ -607,6 +624,8 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
     case 16: return launch_v2<16, 16, 4, 0>(h, P, s);
     case 32: return launch_v2<32, 32, 4, 0>(h, P, s);
     case 64: return launch_v2<64, 64, 1, 0>(h, P, s);  // KW = 1: 6 stages beside the 72 KB of weights
+    case 96: return launch_v2<96, 96, 1, 0, 2>(h, P, s);    // 2 x 48 output channels: 81 KB of weights per CTA
+    case 128: return launch_v2<128, 128, 1, 0, 4>(h, P, s);  // 4 x 32 output channels: 72 KB of weights per CTA
   }
   VFI_FAIL(h, VFI_E_ARG, "conv_v2: no instance for Cin=%d", L.cin);
 }

@@ -239,7 +239,7 @@ __device__ __forceinline__ float4 state_at(const LowSet& lows, int n, int x, int
 template <typename T, bool FIRST>
 __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats,
                               const __grid_constant__ LowSet lows, const float* __restrict__ tsteps,
-                              T* __restrict__ out, int B, int Tn, int Hp, int Wp, int s, int phase) {
+                              T* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, int s, int phase) {
   constexpr int C = FIRST ? 16 : 32;
   const int Hs = Hp / s, Ws = Wp / s;
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -250,9 +250,9 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
   float t = tsteps[n % Tn];
   const size_t plane = (size_t)Hp * Wp;
   const uint8_t* img0 = imgs + ((size_t)b) * plane * 4;
-  const uint8_t* img1 = imgs + ((size_t)(B + b)) * plane * 4;
+  const uint8_t* img1 = imgs + ((size_t)(I1 + b)) * plane * 4;
   const T* f0 = feats + ((size_t)b) * plane * 4;
-  const T* f1 = feats + ((size_t)(B + b)) * plane * 4;
+  const T* f1 = feats + ((size_t)(I1 + b)) * plane * 4;
   const int ns = s == 1 ? 1 : 2;
   const int by = s == 1 ? Y : s * Y + s / 2 - 1;
   const int bx = s == 1 ? X : s * X + s / 2 - 1;
@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
                                                                  const T* __restrict__ feats,
                                                                  const __grid_constant__ LowSet lows,
                                                                  const float* __restrict__ tsteps,
-                                                                 T* __restrict__ out, int B, int Tn, int Hp, int Wp,
+                                                                 T* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp,
                                                                  int phase) {
   extern __shared__ float4 tl_sm[];
   const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
@@ -464,9 +464,9 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
   const float t = tsteps[n - b * Tn];
   const size_t plane = (size_t)Hp * Wp;
   const uint8_t* img0 = imgs + ((size_t)b) * plane * 4;
-  const uint8_t* img1 = imgs + ((size_t)(B + b)) * plane * 4;
+  const uint8_t* img1 = imgs + ((size_t)(I1 + b)) * plane * 4;
   const T* f0 = feats + ((size_t)b) * plane * 4;
-  const T* f1 = feats + ((size_t)(B + b)) * plane * 4;
+  const T* f1 = feats + ((size_t)(I1 + b)) * plane * 4;
   const int Hs = Hp / S, Ws = Wp / S;
   constexpr int NOUT = S == 1 ? 4 : 1;  // outputs per thread
 #pragma unroll 1
@@ -512,7 +512,7 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
 }
 
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
-             void* out, int B, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s) {
+             void* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s) {
   ProfScope _ps(h, PC_GATHER, s);
   size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
   int grid = cdiv(total, 128);
@@ -525,7 +525,7 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
     VFI_CUDA(h, cudaFuncSetAttribute(gather_tile_kernel<TT, SS>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
                                      96 * 1024));                                                                  \
     gather_tile_kernel<TT, SS><<<tgrid, TL_THREADS, smem, s>>>(imgs, (const TT*)feats, lows, tsteps_dev, (TT*)out, \
-                                                               B, T, Hp, Wp, phase ? 1 : 0);                       \
+                                                               B, I1, T, Hp, Wp, phase ? 1 : 0);                       \
   } while (0)
     if (bf) { if (s_int == 1) GT_LAUNCH(bf16, 1); else GT_LAUNCH(bf16, 2); }
     else    { if (s_int == 1) GT_LAUNCH(float, 1); else GT_LAUNCH(float, 2); }
@@ -534,7 +534,7 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
     return 0;
   }
 #define GATHER_LAUNCH(TT, F)                                                                             \
-  gather_kernel<TT, F><<<grid, 128, 0, s>>>(imgs, (const TT*)feats, lows, tsteps_dev, (TT*)out, B, T, Hp, Wp, \
+  gather_kernel<TT, F><<<grid, 128, 0, s>>>(imgs, (const TT*)feats, lows, tsteps_dev, (TT*)out, B, I1, T, Hp, Wp, \
                                             s_int, phase ? 1 : 0)
   if (bf) { if (first) GATHER_LAUNCH(bf16, true); else GATHER_LAUNCH(bf16, false); }
   else    { if (first) GATHER_LAUNCH(float, true); else GATHER_LAUNCH(float, false); }
@@ -572,7 +572,7 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
                                                                  const float* __restrict__ tsteps,
                                                                  uint8_t* __restrict__ out,
                                                                  float* __restrict__ out_f32,
-                                                                 float* __restrict__ flow_out, int B, int Tn, int H,
+                                                                 float* __restrict__ flow_out, int B, int I1, int Tn, int H,
                                                                  int W, int Hp, int Wp) {
   extern __shared__ float4 tl_sm[];
   __shared__ __align__(16) uint8_t s_rgb[TL_H][TL_W * 3];  // the tile's u8 result, stored row-wise as 32-bit words
@@ -583,7 +583,7 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
   const float t = tsteps[n - b * Tn];
   const size_t plane = (size_t)Hp * Wp;
   const uint8_t* img0 = imgs + (size_t)b * plane * 4;
-  const uint8_t* img1 = imgs + (size_t)(B + b) * plane * 4;
+  const uint8_t* img1 = imgs + (size_t)(I1 + b) * plane * 4;
   const uint8_t* hsrc = t < 0.5f ? img0 : img1;
   // a warp = one tile row (lane = column): conflict-free LDS.128 of the staged rows, broadcast row table
   const int xl = threadIdx.x & (TL_W - 1), x = tx0 + xl;
@@ -624,12 +624,12 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
   }
 }
 int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev,
-                  uint8_t* out, float* out_f32, float* flow_out, int B, int T, int H, int W, int Hp, int Wp,
-                  cudaStream_t s) {
+                  uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp,
+                  int Wp, cudaStream_t s) {
   ProfScope _ps(h, PC_BLEND, s);
   const size_t smem = tl_smem_bytes(lows, 2);
   const dim3 grid((W + TL_W - 1) / TL_W, (H + TL_H - 1) / TL_H, B * T);
-  final_blend_kernel<<<grid, TL_THREADS, smem, s>>>(imgs, lows, hud, tsteps_dev, out, out_f32, flow_out, B, T, H, W,
+  final_blend_kernel<<<grid, TL_THREADS, smem, s>>>(imgs, lows, hud, tsteps_dev, out, out_f32, flow_out, B, I1, T, H, W,
                                                     Hp, Wp);
   VFI_LAUNCHED(h);
   return 0;
