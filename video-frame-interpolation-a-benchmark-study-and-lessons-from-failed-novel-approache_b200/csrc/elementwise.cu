@@ -469,7 +469,7 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
   const T* f1 = feats + ((size_t)(I1 + b)) * plane * 4;
   const int Hs = Hp / S, Ws = Wp / S;
   constexpr int NOUT = S == 1 ? 4 : 1;  // outputs per thread
-#pragma unroll 1
+#pragma unroll 2
   for (int i = 0; i < NOUT; i++) {
     float acc[32];
 #pragma unroll
@@ -484,7 +484,7 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
     } else {
       const int Xl = threadIdx.x & (TL_W / 2 - 1), Yl = threadIdx.x >> 4;
       X = (tx0 >> 1) + Xl; Y = (ty0 >> 1) + Yl;
-#pragma unroll 1
+#pragma unroll 2
       for (int d = 0; d < 4; d++) {
         // odd groups of four outputs visit their right-hand tap first: the 8 lanes of an LDS.128 phase then hit 8
         // distinct 16-byte bank groups
@@ -587,7 +587,7 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
   const uint8_t* hsrc = t < 0.5f ? img0 : img1;
   // a warp = one tile row (lane = column): conflict-free LDS.128 of the staged rows, broadcast row table
   const int xl = threadIdx.x & (TL_W - 1), x = tx0 + xl;
-#pragma unroll 1
+#pragma unroll 2
   for (int i = 0; i < TL_H / (TL_THREADS / TL_W); i++) {
     const int yl = (threadIdx.x >> 5) + (TL_THREADS / TL_W) * i, y = ty0 + yl;
     if (y >= H || x >= W) continue;
