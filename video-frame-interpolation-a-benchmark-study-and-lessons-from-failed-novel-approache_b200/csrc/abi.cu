@@ -104,6 +104,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!h || !key) return VFI_E_ARG;
   if (!strcmp(key, "conv_v2")) { h->opt_conv_v2 = value; return VFI_OK; }
   if (!strcmp(key, "v2_ablate")) { h->opt_v2_ablate = value; return VFI_OK; }
+  if (!strcmp(key, "fuse_gather")) { h->opt_fuse_gather = value; return VFI_OK; }
   if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }
   VFI_FAIL(h, VFI_E_ARG, "unknown option %s", key);
 }
@@ -281,8 +282,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     for (int i = 0; i < 5; i++) {
       const int sc = sl[i], hs = Hp / sc, wsz = Wp / sc;
       const Layer* Lb = &h->layers[4 + 11 * i];
-      if ((rc = k_gather(h, imgs, feats, lows, tdev, xin, B, I1, T, Hp, Wp, sc, bf, bf, s))) return rc;
-      if ((rc = run_conv(h, Lb[0], xin, nullptr, a0, N, hs, wsz, bf, bf, s))) return rc;
+      if (bf && sc == 1 && i > 0 && h->opt_fuse_gather && h->opt_conv_v2 && Lb[0].ws2 && Lb[0].cout == 16) {
+        if ((rc = k_gather_conv0a(h, Lb[0], imgs, feats, lows, tdev, (bf16*)a0, B, I1, T, Hp, Wp, s))) return rc;
+      } else {
+        if ((rc = k_gather(h, imgs, feats, lows, tdev, xin, B, I1, T, Hp, Wp, sc, bf, bf, s))) return rc;
+        if ((rc = run_conv(h, Lb[0], xin, nullptr, a0, N, hs, wsz, bf, bf, s))) return rc;
+      }
       if ((rc = run_conv(h, Lb[1], a0, nullptr, fa, N, hs / 2, wsz / 2, bf, false, s))) return rc;
       uint8_t *cur = fa, *nxt = fb;
       for (int j = 0; j < 8; j++) {

@@ -72,6 +72,7 @@ struct vfi_handle {
   void* red = nullptr;
   size_t red_bytes = 0;
   void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled entry point
+  int opt_fuse_gather = 1;      // vfi_set_option("fuse_gather"): finest block's gather fused with conv0[0]
   int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps
   int opt_v2_ablate = 0;        // debug only: see V2Params::ablate
   int opt_conv_v2 = 1;          // vfi_set_option("conv_v2"): resident-weight halo-tile conv kernel where it applies
@@ -147,6 +148,9 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
 int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev,
                   uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp, int Wp,
                   cudaStream_t s);
+// finest block at scale 1.0: gather fused with conv0[0] (tcgen05), bf16 only
+int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
+                    const float* tsteps_dev, bf16* out, int B, int I1, int T, int Hp, int Wp, cudaStream_t s);
 int k_pack_fm(vfi_handle* h, const float* flow, const float* mask, float* fm, int N, int H, int W, int Hp, int Wp,
               cudaStream_t s);
 int k_f32_to_act(vfi_handle* h, const float* src, void* dst, size_t n, bool bf, cudaStream_t s);

@@ -3,6 +3,7 @@
 // accumulate, and the final fused backward-warp + sigmoid-blend + u8 store.
 // Reference semantics: SURVEY.md Appendix A.2 (IFNet.forward / IFBlock.forward / warp()).
 #include "common.cuh"
+#include "umma.cuh"
 
 // ------------------------------------------------------------------------------------------
 // small typed load/store helpers
@@ -342,7 +343,7 @@ static size_t tl_smem_bytes(const LowSet& lows, int mf) {
 }
 // Stage 1.  Thread t owns tile column t%32 (its x taps are computed once per level) and rows t/32, t/32+8, ...;
 // warp k also fills level k's row table.
-template <int MF>
+template <int MF, int NT = TL_THREADS>
 __device__ __forceinline__ void tile_stage(const LowSet& L, int n, int tx0, int ty0, int Hp, int Wp, float4* sm) {
   RowTap* ytab = reinterpret_cast<RowTap*>(sm);
   const int xl = threadIdx.x & (TL_W - 1), row0 = threadIdx.x >> 5;
@@ -367,7 +368,7 @@ __device__ __forceinline__ void tile_stage(const LowSet& L, int n, int tx0, int 
       const int x0 = (int)sx, x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
       const float lx = sx - (float)x0, hx = 1.f - lx;
       const float4* img = reinterpret_cast<const float4*>(L.p[k]) + (size_t)n * Hl * Wl * c4;
-      for (int row = row0; row < rows; row += TL_THREADS / TL_W) {
+      for (int row = row0; row < rows; row += NT / TL_W) {
         const int ry = min(r_lo + row, Hl - 1);
         const float4* pa = img + (size_t)(ry * Wl + x0) * c4;
         const float4* pb = img + (size_t)(ry * Wl + x1) * c4;
@@ -695,6 +696,179 @@ __global__ void plain_to_phase_kernel(const bf16* __restrict__ s, bf16* __restri
 int k_plain_to_phase(vfi_handle* h, const bf16* src, bf16* dst, int N, int H, int W, int C, cudaStream_t s) {
   size_t total = (size_t)N * H * W * C;
   plain_to_phase_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, N, H, W, C);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Finest block at scale 1.0 (s = 1): block-input gather FUSED with conv0's first stride-2 convolution.
+// The 28-channel block input (64 B/pixel in bf16, 1.6 GB per 12 frames at 1080p) never goes to HBM: a CTA gathers
+// the 33 x 33 input pixels (32 x 32 tile + the top / left halo a stride-2, pad-1 conv needs) straight into shared
+// memory, laid out as conv_s2.cu's four phase-plane windows [Cin/8][plane][17][17][8 ch], one warp issues the
+// 2 x 9 x 2 tcgen05.mma (M = 128 = 16 x 8 outputs, N = 16, K = 16) against the 9 KB of weights and four warps run the
+// bias + LeakyReLU epilogue, writing the 16 x 16 x 16 output tile as the phase planes conv0's second conv reads.
+#define GC_THREADS 512
+#define GC_PW 17
+#define GC_PLANE (17 * GC_PW)
+#define GC_NPIX (4 * GC_PLANE)
+#define GC_CS 1162  // chunk stride (16-byte units): >= GC_NPIX, == 2 mod 8 (bank spread, see umma::chunk_stride)
+#define GC_A_BYTES (4 * GC_CS * 16)
+#define GC_W_BYTES (9 * 32 * 16 * 2)
+
+struct GcPix {  // evaluated state of one input pixel
+  float4 fl;
+  float4 m[3];
+};
+
+__device__ __forceinline__ uint32_t gc_pix_index(int ly, int lx, int ty0, int tx0) {
+  // tile-local (ly, lx) in [0, 33): global pixel (ty0 - 1 + ly, tx0 - 1 + lx); ty0, tx0 are even
+  const int py = (ly + 1) & 1, px = (lx + 1) & 1;  // parity of the global coordinate
+  const int pr = (ly + 1) >> 1, pc = (lx + 1) >> 1;  // window row / col: (g >> 1) - t0/2 + 1
+  return (uint32_t)((py * 2 + px) * GC_PLANE + pr * GC_PW + pc);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(GC_THREADS, 2)
+gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
+                     const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
+                     bf16* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, float slope, int stage_bytes) {
+  using namespace umma;
+  extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
+  __shared__ uint64_t mma_bar;
+  __shared__ uint32_t tmem_slot;
+  uint8_t* a_s = reinterpret_cast<uint8_t*>(tl_sm) + stage_bytes;
+  const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* w_s = a_s + GC_A_BYTES;
+  if (threadIdx.x == 0) { bar_init(&mma_bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, 32);
+  for (int i = threadIdx.x; i < GC_W_BYTES / 16; i += GC_THREADS)
+    reinterpret_cast<uint4*>(w_s)[i] = __ldg(reinterpret_cast<const uint4*>(wpack) + i);
+  // stage only the flow rows (11 KB); mask / feat of the finest coarse level are interpolated straight from global
+  // memory (L1 / L2 resident: one 64 B texel serves four pixels), which leaves room for the A tile beside the staging
+  // area at two CTAs per SM and lets a pixel go from evaluation to its A chunks in one pass
+  tile_stage<0, GC_THREADS>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
+  tc_before();
+  __syncthreads();
+  tc_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  const int b = n / Tn;
+  const float t = tsteps[n - b * Tn];
+  const size_t plane = (size_t)Hp * Wp;
+  const uint8_t* img0 = imgs + ((size_t)b) * plane * 4;
+  const uint8_t* img1 = imgs + ((size_t)(I1 + b)) * plane * 4;
+  const T* f0 = feats + ((size_t)b) * plane * 4;
+  const T* f1 = feats + ((size_t)(I1 + b)) * plane * 4;
+  const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it
+  const float4* mf_img = reinterpret_cast<const float4*>(lows.p[kl]) + (size_t)n * lows.Hl[kl] * lows.Wl[kl] * lows.c4[kl];
+  // pixels of this thread: 2 interior (tile-local (xl, yl), (xl, yl + 16)) + for threads < 65 one halo pixel
+#pragma unroll 1
+  for (int i = 0; i < 3; i++) {
+    int ly, lx;  // 33 x 33 coordinates: global pixel (ty0 - 1 + ly, tx0 - 1 + lx)
+    if (i < 2) { lx = (threadIdx.x & 31) + 1; ly = (threadIdx.x >> 5) + 16 * i + 1; }
+    else {
+      if (threadIdx.x >= 65) break;
+      ly = threadIdx.x < 33 ? 0 : (int)threadIdx.x - 32;   // row -1 (lx 0..32), then column -1 (ly 1..32)
+      lx = threadIdx.x < 33 ? (int)threadIdx.x : 0;
+    }
+    const int gy = ty0 - 1 + ly, gx = tx0 - 1 + lx;
+    float acc[32];
+#pragma unroll
+    for (int c = 0; c < 32; c++) acc[c] = 0.f;
+    if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
+      float4 fl, m[3];
+      if (i < 2) fl = tile_eval<0>(lows, tl_sm, n, gx, gy, lx - 1, ly - 1, nullptr);
+      else fl = state_at<0>(lows, n, gx, gy, Hp, Wp, nullptr);
+      {
+        const Lerp L = lerp_setup(gx, gy, lows.s[kl], lows.Hl[kl], lows.Wl[kl]);
+        m[0] = lerp4(mf_img, L, 1, lows.c4[kl]); m[1] = lerp4(mf_img, L, 2, lows.c4[kl]); m[2] = lerp4(mf_img, L, 3, lows.c4[kl]);
+      }
+      gather_tap<T>(img0, img1, f0, f1, fl, m, gx, gy, Hp, Wp, acc);
+      acc[14] = t;
+    }
+    const uint32_t pix = gc_pix_index(ly, lx, ty0, tx0);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      uint4 u;
+      u.x = pk_bf16(acc[8 * j], acc[8 * j + 1]); u.y = pk_bf16(acc[8 * j + 2], acc[8 * j + 3]);
+      u.z = pk_bf16(acc[8 * j + 4], acc[8 * j + 5]); u.w = pk_bf16(acc[8 * j + 6], acc[8 * j + 7]);
+      *reinterpret_cast<uint4*>(a_s + ((size_t)j * GC_CS + pix) * 16) = u;
+    }
+  }
+  fence_async_smem();
+  __syncthreads();
+
+  // ---- phase 3: 2 sub-tiles (output columns 0-7, 8-15) x 9 taps x 2 k-steps of tcgen05.mma, then the epilogue ----
+  if (warp == 0) {
+    const uint32_t leader = elect_one();
+    constexpr uint32_t IDESC = idesc_bf16_m128(16);
+    const uint64_t ad0 = desc_ns(s_u32(a_s), GC_CS * 16, GC_PW * 16);
+    const uint64_t bd0 = desc_ns(s_u32(w_s), 16 * 16, 128);
+#pragma unroll
+    for (int tap = 0; tap < 9; tap++) {
+#pragma unroll
+      for (int k = 0; k < 2; k++) {
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          const int ky = tap / 3, kx = tap % 3;
+          const int pl = (ky != 1 ? 2 : 0) + (kx != 1 ? 1 : 0);
+          const uint32_t a_off = (uint32_t)(pl * GC_PLANE + (ky != 0 ? 1 : 0) * GC_PW + (kx != 0 ? 1 : 0) + 8 * j + 2 * k * GC_CS);
+          const uint32_t b_off = (uint32_t)((tap * 4 + 2 * k) * 16);
+          mma_bf16_elect(leader, tmem_base + (uint32_t)(j * 16), ad0 + a_off, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
+        }
+      }
+    }
+    if (leader) commit_to(&mma_bar);
+    __syncwarp();
+  }
+  if (warp < 4) {
+    bar_wait(&mma_bar, 0);
+    tc_after();
+    const int m = warp * 32 + lane;
+    const int Ho = Hp >> 1, Wo = Wp >> 1;
+    const int oy = (ty0 >> 1) + (m >> 3);
+    float v[2][16];
+    ld16(tmem_base + ((uint32_t)(warp * 32) << 16), v[0]);
+    ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + 16, v[1]);
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      const int ox = (tx0 >> 1) + 8 * j + (m & 7);
+#pragma unroll
+      for (int c = 0; c < 16; c++) {
+        float x = v[j][c] + __ldg(bias + c);
+        v[j][c] = x > 0.f ? x : x * slope;
+      }
+      // conv0's second conv is stride 2 too: write its four phase planes [N, 4, Ho/2, Wo/2, 16]
+      const size_t opix = ((((size_t)n * 4 + (oy & 1) * 2 + (ox & 1)) * (Ho >> 1) + (oy >> 1)) * (Wo >> 1) + (ox >> 1));
+      uint4 o0, o1;
+      o0.x = pk_bf16(v[j][0], v[j][1]); o0.y = pk_bf16(v[j][2], v[j][3]); o0.z = pk_bf16(v[j][4], v[j][5]); o0.w = pk_bf16(v[j][6], v[j][7]);
+      o1.x = pk_bf16(v[j][8], v[j][9]); o1.y = pk_bf16(v[j][10], v[j][11]); o1.z = pk_bf16(v[j][12], v[j][13]); o1.w = pk_bf16(v[j][14], v[j][15]);
+      reinterpret_cast<uint4*>(out + opix * 16)[0] = o0;
+      reinterpret_cast<uint4*>(out + opix * 16)[1] = o1;
+    }
+  }
+  tc_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_after();
+    tmem_dealloc(tmem_base, 32);
+  }
+}
+
+// Lb0 = the block's conv0[0] layer (28 -> 16, stride 2).  Output: its activation as the phase planes of [N, Hp/2, Wp/2, 16].
+int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
+                    const float* tsteps_dev, bf16* out, int B, int I1, int T, int Hp, int Wp, cudaStream_t s) {
+  ProfScope _ps(h, PC_GATHER, s);
+  if (!Lb0.ws2 || Lb0.cin_pad != 32 || Lb0.cout != 16) VFI_FAIL(h, VFI_E_STATE, "gather_conv0a: layer not packed");
+  if (Hp % TL_H || Wp % TL_W) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: padded size must be a multiple of 32");
+  const size_t un = (tl_smem_bytes(lows, 0) + 127) & ~(size_t)127;
+  const size_t smem = un + GC_A_BYTES + GC_W_BYTES;
+  VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  if (smem > 112 * 1024) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: shared memory budget");
+  const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
+  gather_conv0a_kernel<bf16><<<grid, GC_THREADS, smem, s>>>(imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out,
+                                                          B, I1, T, Hp, Wp, h->slope, (int)un);
   VFI_LAUNCHED(h);
   return 0;
 }
