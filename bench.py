@@ -37,27 +37,36 @@ def peaks():
     return 6650.0, 1590.0, 1400.0, "fallback"
 
 
-def tc_flops_per_batch(B, T, Hp, Wp):
-    """Algorithmic (dense, unpadded channels) FLOPs of every tcgen05 conv launch of one batch."""
+def tc_flops_per_batch(B, T, Hp, Wp, n_images, fused_conv0a):
+    """Algorithmic (dense, unpadded channels) FLOPs of the tcgen05 conv launches of one batch, as executed:
+    the Head runs once per distinct frame (n_images); with the finest block's conv0[0] fused into the gather
+    kernel its FLOPs are accounted to that kernel (returned separately)."""
     from vfi_b200.ifnet_layers import layer_info
     from vfi_b200.ifnet_params import BLOCK_C
     fl = 0
-    for layer in (1, 2):  # Head cnn1/cnn2 on 2B images at half resolution
+    for layer in (1, 2):  # Head cnn1/cnn2 at half resolution
         li = layer_info(layer)
-        fl += 2 * 2 * B * (Hp // 2) * (Wp // 2) * 9 * li["cin"] * li["cout"]
+        fl += 2 * n_images * (Hp // 2) * (Wp // 2) * 9 * li["cin"] * li["cout"]
+    fl += 2 * n_images * Hp * Wp * 4 * 16 * 4  # Head cnn3: ConvTranspose 4x4 s2, 4 taps per output pixel
+    fused = 0
     for b in range(5):
         s = 16 >> b
         hs, ws = Hp // s, Wp // s
         base = 4 + 11 * b
         n = B * T
         li = layer_info(base)
-        fl += 2 * n * (hs // 2) * (ws // 2) * 9 * li["cin"] * li["cout"]
+        f0 = 2 * n * (hs // 2) * (ws // 2) * 9 * li["cin"] * li["cout"]
+        if b == 4 and fused_conv0a:
+            fused = f0
+        else:
+            fl += f0
         li = layer_info(base + 1)
         fl += 2 * n * (hs // 4) * (ws // 4) * 9 * li["cin"] * li["cout"]
         c = BLOCK_C[b]
         fl += 8 * 2 * n * (hs // 4) * (ws // 4) * 9 * c * c
-        fl += 2 * n * (hs // 2) * (ws // 2) * 4 * c * 52  # ConvTranspose 4x4 s2: 4 taps per output pixel
-    return fl
+        # ConvTranspose 4x4 s2: 4 taps per output pixel; the final block computes only the 20 of 52 channels used
+        fl += 2 * n * (hs // 2) * (ws // 2) * 4 * c * 52
+    return fl, fused
 
 
 class ClockSampler(threading.Thread):
@@ -240,19 +249,36 @@ def main():
                          "share": v[0] / tot if tot else 0} for k, v in prof.items() if v[1]}
         tc_ms, tc_n = prof["conv_tcgen05"]
         if tc_n and args.precision == "bf16":
-            fl = tc_flops_per_batch(B, T, 1088, 1920) * psteps
-            ach = fl / (tc_ms / 1000.0) / 1e12
-            roof = {"kernel": "conv_tc_kernel (all tcgen05 implicit-GEMM conv launches)", "bound": "tensor",
-                    "achieved": ach, "peak": tf_sust, "unit": "TFLOP/s", "frac": ach / tf_sust, "traffic": None,
-                    "peak_source": f"{src} bf16_tflops_sustained", "launches": tc_n // psteps,
-                    "avg_launch_us": tc_ms / tc_n * 1000.0,
-                    "algorithmic_gflop_per_step": fl / psteps / 1e9}
-            wb_ms, wb_n = prof["warp_blend"]
-            if wb_n:
-                by = B * T * H * W * (6 + 20 + 3)
-                roof["warp_blend"] = {"bound": "hbm", "achieved": by * psteps / (wb_ms / 1000.0) / 1e9, "peak": hbm,
-                                      "unit": "GB/s", "frac": by * psteps / (wb_ms / 1000.0) / 1e9 / hbm,
-                                      "bytes_per_px": 29}
+            fused_on = prof["gather_conv0a"][1] > 0
+            fl, fl_fused = tc_flops_per_batch(B, T, 1088, 1920, B + 1, fused_on)
+            ach = fl * psteps / (tc_ms / 1000.0) / 1e12
+            px = B * T * 1088 * 1920   # padded full-resolution pixels of one step
+            roof = {"kernel": "tcgen05 implicit-GEMM conv kernels (conv_v2 / conv_s2 / conv_tc: every conv launch of the step "
+                              "except the one fused into the gather)",
+                    "bound": "tensor", "achieved": ach, "peak": tf_sust, "unit": "TFLOP/s", "frac": ach / tf_sust,
+                    "traffic": None, "peak_source": f"{src} bf16_tflops_sustained", "launches": tc_n // psteps,
+                    "avg_launch_us": tc_ms / tc_n * 1000.0, "algorithmic_gflop_per_step": fl / 1e9,
+                    "note": "N = 16..64 output channels per MMA: the A operand read from shared memory (4 KB per "
+                            "128x16 MMA at 128 B/clk) bounds these layers at 25-50 % of the tensor pipe; see DESIGN.md"}
+            others = {}
+
+            def hbm_entry(key, bytes_per_px, what):
+                ms_k, n_k = prof[key]
+                if n_k:
+                    by = px * bytes_per_px
+                    others[key] = {"bound": "hbm", "achieved": by * psteps / (ms_k / 1000.0) / 1e9, "peak": hbm, "unit": "GB/s",
+                                   "frac": by * psteps / (ms_k / 1000.0) / 1e9 / hbm, "algorithmic_bytes_per_px": bytes_per_px,
+                                   "ms_per_step": ms_k / psteps, "what": what}
+            # algorithmic bytes per padded full-resolution pixel of one (pair, timestep) item
+            hbm_entry("warp_blend", 8 + 32 + 5 + 3, "RGBX taps of both frames 8, last block's flow+mask 32, coarse flows 5, u8 out 3")
+            hbm_entry("gather_conv0a", 8 + 16 + 16 + 5 + 8, "RGBX taps 8, Head feature taps 16, block-3 output 16 (64 B / 4 px), "
+                                                          "coarser flows 5, conv0[0] output 8 (32 B / 4 px)")
+            hbm_entry("gather", (8 + 16 + 5 + 16) + (8 + 16 + 2 + 4) / 4.0 + 2,
+                      "blocks 0-3: taps + coarse inputs + 64 B per output pixel of the block input (s = 2: every pixel; "
+                      "s = 4, 8, 16: 1/4, 1/16, 1/64 of them)")
+            roof["other_kernels"] = others
+            if fused_on:
+                roof["fused_gather_conv0a_gflop_per_step"] = fl_fused / 1e9
 
     cpu_base = None
     if rank == 0 and not args.no_cpu_baseline:

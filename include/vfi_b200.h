@@ -125,7 +125,7 @@ int vfi_debug_conv(vfi_handle* h, int layer, int precision, const float* x, int 
 /* Per-kernel-class device timing for bench.py's roofline block.  While enabled every kernel launch is
  * bracketed by CUDA events on its stream; vfi_profile_read synchronises, returns summed milliseconds and
  * launch counts per class (0 pad, 1 head_cnn0, 2 conv_tcgen05, 3 conv_direct, 4 deconv_direct, 5 gather,
- * 6 upsample, 7 warp_blend, 8 reduce, 9 misc) and clears the log. */
+ * 6 gather_conv0a (finest block: gather fused with conv0[0]), 7 warp_blend, 8 reduce, 9 misc) and clears the log. */
 #define VFI_PROFILE_CLASSES 10
 int vfi_profile_enable(vfi_handle* h, int on);
 int vfi_profile_read(vfi_handle* h, double* ms, long long* counts, int ncat);

@@ -14,7 +14,7 @@ from vfi_b200.engine import Engine
 from vfi_b200.synth import gen_clip
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
-B = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 H, W = (int(sys.argv[3]), int(sys.argv[4])) if len(sys.argv) > 4 else (1080, 1920)
 e = Engine.get(0)
 e.load_weights(ifnet_params.random_init(1234))

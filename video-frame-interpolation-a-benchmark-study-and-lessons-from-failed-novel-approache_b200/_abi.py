@@ -11,7 +11,7 @@ PRECISION_FP32, PRECISION_BF16 = 0, 1
 ROUTE_RIFE, ROUTE_VFIMAMBA, ROUTE_SCENE_CHANGE = 0, 1, 2
 ROUTE_NAMES = ("rife", "vfimamba", "scene_change")
 IFNET_PARAMS = 5664776
-PROFILE_CLASSES = ("pad", "head_cnn0", "conv_tcgen05", "conv_direct", "deconv_direct", "gather", "upsample",
+PROFILE_CLASSES = ("pad", "head_cnn0", "conv_tcgen05", "conv_direct", "deconv_direct", "gather", "gather_conv0a",
                    "warp_blend", "reduce", "misc")
 
 _vp, _i, _f, _d, _sz, _ll = C.c_void_p, C.c_int, C.c_float, C.c_double, C.c_size_t, C.c_longlong

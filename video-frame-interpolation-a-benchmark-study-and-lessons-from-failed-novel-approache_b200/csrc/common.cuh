@@ -82,7 +82,7 @@ struct vfi_handle {
   std::vector<int> prof_cat;
 };
 
-enum ProfCat { PC_PAD = 0, PC_HEAD0, PC_CONV_TC, PC_CONV_DIRECT, PC_DECONV_DIRECT, PC_GATHER, PC_UPSAMPLE, PC_BLEND,
+enum ProfCat { PC_PAD = 0, PC_HEAD0, PC_CONV_TC, PC_CONV_DIRECT, PC_DECONV_DIRECT, PC_GATHER, PC_GATHER_CONV, PC_BLEND,
                PC_REDUCE, PC_MISC, PC_COUNT };
 void prof_begin(vfi_handle* h, int cat, cudaStream_t s);
 void prof_end(vfi_handle* h, cudaStream_t s);

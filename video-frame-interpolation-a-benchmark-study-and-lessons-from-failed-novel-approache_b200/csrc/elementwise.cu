@@ -708,6 +708,7 @@ int k_plain_to_phase(vfi_handle* h, const bf16* src, bf16* dst, int N, int H, in
 // 2 x 9 x 2 tcgen05.mma (M = 128 = 16 x 8 outputs, N = 16, K = 16) against the 9 KB of weights and four warps run the
 // bias + LeakyReLU epilogue, writing the 16 x 16 x 16 output tile as the phase planes conv0's second conv reads.
 #define GC_THREADS 512
+#define GC_NPX (1024 / GC_THREADS)  // interior pixels per thread
 #define GC_PW 17
 #define GC_PLANE (17 * GC_PW)
 #define GC_NPIX (4 * GC_PLANE)
@@ -728,7 +729,7 @@ __device__ __forceinline__ uint32_t gc_pix_index(int ly, int lx, int ty0, int tx
 }
 
 template <typename T>
-__global__ void __launch_bounds__(GC_THREADS, 2)
+__global__ void __launch_bounds__(GC_THREADS, GC_THREADS == 1024 ? 1 : 2)
 gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
                      const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
                      bf16* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, float slope, int stage_bytes) {
@@ -762,11 +763,11 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   const T* f1 = feats + ((size_t)(I1 + b)) * plane * 4;
   const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it
   const float4* mf_img = reinterpret_cast<const float4*>(lows.p[kl]) + (size_t)n * lows.Hl[kl] * lows.Wl[kl] * lows.c4[kl];
-  // pixels of this thread: 2 interior (tile-local (xl, yl), (xl, yl + 16)) + for threads < 65 one halo pixel
+  // pixels of this thread: GC_NPX interior ones + for threads < 65 one halo pixel
 #pragma unroll 1
-  for (int i = 0; i < 3; i++) {
+  for (int i = 0; i < GC_NPX + 1; i++) {
     int ly, lx;  // 33 x 33 coordinates: global pixel (ty0 - 1 + ly, tx0 - 1 + lx)
-    if (i < 2) { lx = (threadIdx.x & 31) + 1; ly = (threadIdx.x >> 5) + 16 * i + 1; }
+    if (i < GC_NPX) { lx = (threadIdx.x & 31) + 1; ly = (threadIdx.x >> 5) + (GC_THREADS / 32) * i + 1; }
     else {
       if (threadIdx.x >= 65) break;
       ly = threadIdx.x < 33 ? 0 : (int)threadIdx.x - 32;   // row -1 (lx 0..32), then column -1 (ly 1..32)
@@ -778,7 +779,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
     for (int c = 0; c < 32; c++) acc[c] = 0.f;
     if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
       float4 fl, m[3];
-      if (i < 2) fl = tile_eval<0>(lows, tl_sm, n, gx, gy, lx - 1, ly - 1, nullptr);
+      if (i < GC_NPX) fl = tile_eval<0>(lows, tl_sm, n, gx, gy, lx - 1, ly - 1, nullptr);
       else fl = state_at<0>(lows, n, gx, gy, Hp, Wp, nullptr);
       {
         const Lerp L = lerp_setup(gx, gy, lows.s[kl], lows.Hl[kl], lows.Wl[kl]);
@@ -859,7 +860,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
 // Lb0 = the block's conv0[0] layer (28 -> 16, stride 2).  Output: its activation as the phase planes of [N, Hp/2, Wp/2, 16].
 int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
                     const float* tsteps_dev, bf16* out, int B, int I1, int T, int Hp, int Wp, cudaStream_t s) {
-  ProfScope _ps(h, PC_GATHER, s);
+  ProfScope _ps(h, PC_GATHER_CONV, s);
   if (!Lb0.ws2 || Lb0.cin_pad != 32 || Lb0.cout != 16) VFI_FAIL(h, VFI_E_STATE, "gather_conv0a: layer not packed");
   if (Hp % TL_H || Wp % TL_W) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: padded size must be a multiple of 32");
   const size_t un = (tl_smem_bytes(lows, 0) + 127) & ~(size_t)127;
