@@ -707,29 +707,86 @@ int k_plain_to_phase(vfi_handle* h, const bf16* src, bf16* dst, int N, int H, in
 // memory, laid out as conv_s2.cu's four phase-plane windows [Cin/8][plane][17][17][8 ch], one warp issues the
 // 2 x 9 x 2 tcgen05.mma (M = 128 = 16 x 8 outputs, N = 16, K = 16) against the 9 KB of weights and four warps run the
 // bias + LeakyReLU epilogue, writing the 16 x 16 x 16 output tile as the phase planes conv0's second conv reads.
-#define GC_THREADS 512
-#define GC_NPX (1024 / GC_THREADS)  // interior pixels per thread
+#define GC_THREADS 384   // 3 pixels per thread cover the 33 x 33 = 1089 input pixels with every warp equally loaded
+#define GC_TW 33         // staged / gathered region: the 32 x 32 tile plus its top row and left column
 #define GC_PW 17
 #define GC_PLANE (17 * GC_PW)
 #define GC_NPIX (4 * GC_PLANE)
 #define GC_CS 1162  // chunk stride (16-byte units): >= GC_NPIX, == 2 mod 8 (bank spread, see umma::chunk_stride)
 #define GC_A_BYTES (4 * GC_CS * 16)
 #define GC_W_BYTES (9 * 32 * 16 * 2)
+#define GC_TAB (5 * GC_TW)
 
-struct GcPix {  // evaluated state of one input pixel
-  float4 fl;
-  float4 m[3];
-};
-
-__device__ __forceinline__ uint32_t gc_pix_index(int ly, int lx, int ty0, int tx0) {
-  // tile-local (ly, lx) in [0, 33): global pixel (ty0 - 1 + ly, tx0 - 1 + lx); ty0, tx0 are even
-  const int py = (ly + 1) & 1, px = (lx + 1) & 1;  // parity of the global coordinate
+__device__ __forceinline__ uint32_t gc_pix_index(int ly, int lx) {
+  // region-local (ly, lx) in [0, 33): global pixel (ty0 - 1 + ly, tx0 - 1 + lx); ty0, tx0 are even
+  const int py = (ly + 1) & 1, px = (lx + 1) & 1;    // parity of the global coordinate
   const int pr = (ly + 1) >> 1, pc = (lx + 1) >> 1;  // window row / col: (g >> 1) - t0/2 + 1
   return (uint32_t)((py * 2 + px) * GC_PLANE + pr * GC_PW + pc);
 }
+static size_t gc_stage_bytes(const LowSet& lows) {
+  size_t n = GC_TAB;
+  for (int k = 0; k < lows.n; k++) n += (size_t)tl_rows(lows.s[k]) * GC_TW;
+  return n * sizeof(float4);
+}
+// tile_stage for the 33 x 33 region whose origin is (tx0 - 1, ty0 - 1): flow rows only
+__device__ __forceinline__ void gc_stage(const LowSet& L, int n, int ox, int oy, int Hp, int Wp, float4* sm) {
+  RowTap* ytab = reinterpret_cast<RowTap*>(sm);
+  const int col = threadIdx.x % GC_TW, row0 = threadIdx.x / GC_TW;
+  constexpr int RSTEP = GC_THREADS / GC_TW;  // rows per pass; threads >= RSTEP * GC_TW only help with the row tables
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int off = GC_TAB;
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    if (k < L.n) {
+      const int sk = L.s[k], c4 = L.c4[k], Hl = L.Hl[k], Wl = L.Wl[k];
+      const int rows = tl_rows(sk);
+      const float rs = L.rs[k];
+      const int r_lo = (int)fmaxf(rs * ((float)max(oy, 0) + 0.5f) - 0.5f, 0.f);
+      if (warp == k) {
+        for (int yl = lane; yl < GC_TW; yl += 32) {
+          const float sy = fmaxf(rs * ((float)min(max(oy + yl, 0), Hp - 1) + 0.5f) - 0.5f, 0.f);
+          const int y0 = (int)sy, y1 = y0 + (y0 < Hl - 1 ? 1 : 0);
+          RowTap t;
+          t.ly = sy - (float)y0; t.hy = 1.f - t.ly;
+          t.o0 = off + (y0 - r_lo) * GC_TW; t.o1 = off + (y1 - r_lo) * GC_TW;
+          ytab[k * GC_TW + yl] = t;
+        }
+      }
+      if (row0 < RSTEP) {
+        const float sx = fmaxf(rs * ((float)min(max(ox + col, 0), Wp - 1) + 0.5f) - 0.5f, 0.f);
+        const int x0 = (int)sx, x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
+        const float lx = sx - (float)x0, hx = 1.f - lx;
+        const float4* img = reinterpret_cast<const float4*>(L.p[k]) + (size_t)n * Hl * Wl * c4;
+        for (int row = row0; row < rows; row += RSTEP) {
+          const int ry = min(r_lo + row, Hl - 1);
+          const float4 a = __ldg(img + (size_t)(ry * Wl + x0) * c4), b = __ldg(img + (size_t)(ry * Wl + x1) * c4);
+          sm[off + row * GC_TW + col] =
+              make_float4(hx * a.x + lx * b.x, hx * a.y + lx * b.y, hx * a.z + lx * b.z, hx * a.w + lx * b.w);
+        }
+      }
+      off += rows * GC_TW;
+    }
+  }
+}
+// flow at region-local pixel (lx, ly) from the staged rows (every level of a finest block's LowSet has s > 1)
+__device__ __forceinline__ float4 gc_eval(const LowSet& L, const float4* sm, int lx, int ly) {
+  const RowTap* ytab = reinterpret_cast<const RowTap*>(sm);
+  float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    if (k < L.n) {
+      const RowTap t = ytab[k * GC_TW + ly];
+      const float4 a = sm[t.o0 + lx], c = sm[t.o1 + lx];
+      const float fs = L.fs[k];
+      fl.x += (t.hy * a.x + t.ly * c.x) * fs; fl.y += (t.hy * a.y + t.ly * c.y) * fs;
+      fl.z += (t.hy * a.z + t.ly * c.z) * fs; fl.w += (t.hy * a.w + t.ly * c.w) * fs;
+    }
+  }
+  return fl;
+}
 
 template <typename T>
-__global__ void __launch_bounds__(GC_THREADS, GC_THREADS == 1024 ? 1 : 2)
+__global__ void __launch_bounds__(GC_THREADS, 2)
 gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
                      const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
                      bf16* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, float slope, int stage_bytes) {
@@ -745,10 +802,10 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   if (warp == 0) tmem_alloc(&tmem_slot, 32);
   for (int i = threadIdx.x; i < GC_W_BYTES / 16; i += GC_THREADS)
     reinterpret_cast<uint4*>(w_s)[i] = __ldg(reinterpret_cast<const uint4*>(wpack) + i);
-  // stage only the flow rows (11 KB); mask / feat of the finest coarse level are interpolated straight from global
-  // memory (L1 / L2 resident: one 64 B texel serves four pixels), which leaves room for the A tile beside the staging
-  // area at two CTAs per SM and lets a pixel go from evaluation to its A chunks in one pass
-  tile_stage<0, GC_THREADS>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
+  // stage only the flow rows (incl. the halo row / column); mask / feat of the finest coarse level are interpolated
+  // straight from global memory (L1 / L2 resident: one 64 B texel serves four pixels), which leaves room for the A tile
+  // beside the staging area at two CTAs per SM and lets a pixel go from evaluation to its A chunks in one pass
+  gc_stage(lows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
   tc_before();
   __syncthreads();
   tc_after();
@@ -763,24 +820,16 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   const T* f1 = feats + ((size_t)(I1 + b)) * plane * 4;
   const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it
   const float4* mf_img = reinterpret_cast<const float4*>(lows.p[kl]) + (size_t)n * lows.Hl[kl] * lows.Wl[kl] * lows.c4[kl];
-  // pixels of this thread: GC_NPX interior ones + for threads < 65 one halo pixel
 #pragma unroll 1
-  for (int i = 0; i < GC_NPX + 1; i++) {
-    int ly, lx;  // 33 x 33 coordinates: global pixel (ty0 - 1 + ly, tx0 - 1 + lx)
-    if (i < GC_NPX) { lx = (threadIdx.x & 31) + 1; ly = (threadIdx.x >> 5) + (GC_THREADS / 32) * i + 1; }
-    else {
-      if (threadIdx.x >= 65) break;
-      ly = threadIdx.x < 33 ? 0 : (int)threadIdx.x - 32;   // row -1 (lx 0..32), then column -1 (ly 1..32)
-      lx = threadIdx.x < 33 ? (int)threadIdx.x : 0;
-    }
+  for (int p = threadIdx.x; p < GC_TW * GC_TW; p += GC_THREADS) {
+    const int ly = p / GC_TW, lx = p - ly * GC_TW;  // global pixel (ty0 - 1 + ly, tx0 - 1 + lx)
     const int gy = ty0 - 1 + ly, gx = tx0 - 1 + lx;
     float acc[32];
 #pragma unroll
     for (int c = 0; c < 32; c++) acc[c] = 0.f;
     if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
-      float4 fl, m[3];
-      if (i < GC_NPX) fl = tile_eval<0>(lows, tl_sm, n, gx, gy, lx - 1, ly - 1, nullptr);
-      else fl = state_at<0>(lows, n, gx, gy, Hp, Wp, nullptr);
+      float4 m[3];
+      const float4 fl = gc_eval(lows, tl_sm, lx, ly);
       {
         const Lerp L = lerp_setup(gx, gy, lows.s[kl], lows.Hl[kl], lows.Wl[kl]);
         m[0] = lerp4(mf_img, L, 1, lows.c4[kl]); m[1] = lerp4(mf_img, L, 2, lows.c4[kl]); m[2] = lerp4(mf_img, L, 3, lows.c4[kl]);
@@ -788,7 +837,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
       gather_tap<T>(img0, img1, f0, f1, fl, m, gx, gy, Hp, Wp, acc);
       acc[14] = t;
     }
-    const uint32_t pix = gc_pix_index(ly, lx, ty0, tx0);
+    const uint32_t pix = gc_pix_index(ly, lx);
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       uint4 u;
@@ -863,7 +912,9 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
   ProfScope _ps(h, PC_GATHER_CONV, s);
   if (!Lb0.ws2 || Lb0.cin_pad != 32 || Lb0.cout != 16) VFI_FAIL(h, VFI_E_STATE, "gather_conv0a: layer not packed");
   if (Hp % TL_H || Wp % TL_W) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: padded size must be a multiple of 32");
-  const size_t un = (tl_smem_bytes(lows, 0) + 127) & ~(size_t)127;
+  for (int k = 0; k < lows.n; k++)
+    if (lows.s[k] < 2) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: coarse levels only");
+  const size_t un = (gc_stage_bytes(lows) + 127) & ~(size_t)127;
   const size_t smem = un + GC_A_BYTES + GC_W_BYTES;
   VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   if (smem > 112 * 1024) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: shared memory budget");
