@@ -128,7 +128,9 @@ def test_single_layer_vs_torch(engine, weights, layer, prec):
     res = torch.randn((2, Hin, Win, li["cout"]), generator=g).cuda() if li["beta"] else None
     y = engine.debug_conv(layer, prec, x, res)
     ref = _torch_layer(weights, layer, x, res, prec == _abi.PRECISION_BF16)
-    err = (y[..., :ref.shape[-1]] - ref).abs().max().item()
+    nc = 5 if (layer == 58 and prec == _abi.PRECISION_BF16) else ref.shape[-1]    # final lastconv: only flow + mask are computed
+    ref = ref[..., :nc]
+    err = (y[..., :nc] - ref).abs().max().item()
     tol = (1e-4 if prec == _abi.PRECISION_FP32 else 1.5e-2) * max(1.0, ref.abs().max().item())
     assert err <= tol, f"layer {layer} ({li['key']}): {err} > {tol}"
 

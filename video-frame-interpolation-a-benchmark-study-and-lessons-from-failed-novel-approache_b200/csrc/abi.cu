@@ -177,7 +177,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
       if (int rc = s2_build_layer(h, L, w)) return rc;
     }
     if (tc || id == 3) {
-      if (int rc = v2_build_layer(h, L, w)) return rc;
+      if (id != 58 && L.kind == LK_DECONV4 && L.cout == 52) { /* only the final block's lastconv has a conv_v2 form */ }
+      else if (int rc = v2_build_layer(h, L, w)) return rc;
     }
   }
   if (off != n_params) VFI_FAIL(h, VFI_E_ARG, "parameter blob length mismatch (%zu consumed)", off);
@@ -295,7 +296,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
         std::swap(cur, nxt);
       }
       const int lc = i == 4 ? last_c : 16;
-      if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low[i], N, hs / 4, wsz / 4, false, h->slope, s, lc);
+      if (bf && i == 4 && h->opt_conv_v2 && Lb[10].wv2) rc = k_conv_v2_last(h, Lb[10], (const bf16*)cur, low[i], lc, N, hs / 4, wsz / 4, s);
+      else if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low[i], N, hs / 4, wsz / 4, false, h->slope, s, lc);
       else rc = k_deconv4_direct(h, Lb[10], cur, low[i], N, hs / 4, wsz / 4, false, 1, s);
       if (rc) return rc;
       lows.push(low[i], sc, lc, Hp, Wp);
@@ -372,6 +374,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
     }
     const bf16* in = xb;
     if (s2) { if ((rc = k_plain_to_phase(h, xb, xp, N, Hin, Win, L.cin_pad, s))) return rc; in = xp; }
+    if (L.kind == LK_DECONV4 && layer == 58 && h->opt_conv_v2 && L.wv2)  // channels 0-4 only; 5-15 stay as the caller set them
+      return k_conv_v2_last(h, L, in, y, 16, N, Hin, Win, s);
     if (L.kind == LK_DECONV4) return k_conv_tc(h, L, in, nullptr, y, N, Hin, Win, false, h->slope, s);
     const bf16* resp = nullptr;
     if (L.has_beta) {  // ResConv: residual defaults to the layer input (x), as in the net

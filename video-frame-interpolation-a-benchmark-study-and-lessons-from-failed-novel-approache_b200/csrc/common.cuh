@@ -115,6 +115,21 @@ struct ProfScope {
       VFI_FAIL(h, VFI_E_CUDA, "%s:%d launch: %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \
   } while (0)
 
+// One 32-byte store = one full DRAM/L2 sector per lane.  Two 16-byte stores of the same 32 bytes are two half-sector
+// writes per lane (lanes sit >= 64 B apart in every NHWC epilogue here) and measured 2x slower on B200.
+#ifdef __CUDACC__
+__device__ __forceinline__ void st_v8(void* p, uint4 a, uint4 b) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z),
+               "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
+}
+__device__ __forceinline__ void st_v8f(float* p, float4 a, float4 b) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z),
+               "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w)
+               : "memory");
+}
+#endif
+
 static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 // arena helpers (abi.cu)
@@ -179,6 +194,9 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch);
 // stride-1 3x3 conv (+ResConv epilogue), plain NHWC bf16 in/out
 int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, int H, int W, float slope,
               cudaStream_t s);
+
+int k_conv_v2_last(vfi_handle* h, const Layer& L, const bf16* in, float* low, int low_c, int N, int H, int W,
+                   cudaStream_t s);
 
 // ---- conv_s2.cu ---------------------------------------------------------------------------
 bool s2_supported(const Layer& L);

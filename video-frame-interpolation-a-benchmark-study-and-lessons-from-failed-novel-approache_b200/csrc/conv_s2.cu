@@ -215,8 +215,7 @@ __global__ void __launch_bounds__(S2_THREADS, 1) conv_s2_kernel(const __grid_con
               uint4 o0, o1;
               o0.x = pk_bf16(v[0], v[1]); o0.y = pk_bf16(v[2], v[3]); o0.z = pk_bf16(v[4], v[5]); o0.w = pk_bf16(v[6], v[7]);
               o1.x = pk_bf16(v[8], v[9]); o1.y = pk_bf16(v[10], v[11]); o1.z = pk_bf16(v[12], v[13]); o1.w = pk_bf16(v[14], v[15]);
-              *reinterpret_cast<uint4*>(op + c) = o0;
-              *reinterpret_cast<uint4*>(op + c + 8) = o1;
+              st_v8(op + c, o0, o1);
             }
           }
         }

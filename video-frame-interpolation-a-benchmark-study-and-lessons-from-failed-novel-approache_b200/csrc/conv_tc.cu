@@ -246,8 +246,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             uint4 o0, o1;
             o0.x = pack_bf16(v[0], v[1]); o0.y = pack_bf16(v[2], v[3]); o0.z = pack_bf16(v[4], v[5]); o0.w = pack_bf16(v[6], v[7]);
             o1.x = pack_bf16(v[8], v[9]); o1.y = pack_bf16(v[10], v[11]); o1.z = pack_bf16(v[12], v[13]); o1.w = pack_bf16(v[14], v[15]);
-            *reinterpret_cast<uint4*>(op + c) = o0;
-            *reinterpret_cast<uint4*>(op + c + 8) = o1;
+            st_v8(op + c, o0, o1);
           }
         }
       } else {
@@ -270,10 +269,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 o[13] = o[14] = o[15] = 0.f;
                 float4* dst = reinterpret_cast<float4*>(
                     ob + (((size_t)n * H4 + 4 * y + 2 * p + i) * W4 + 4 * x + 2 * q + jj) * 16);
-                dst[0] = make_float4(o[0], o[1], o[2], o[3]);
-                dst[1] = make_float4(o[4], o[5], o[6], o[7]);
-                dst[2] = make_float4(o[8], o[9], o[10], o[11]);
-                dst[3] = make_float4(o[12], o[13], o[14], o[15]);
+                st_v8f(reinterpret_cast<float*>(dst), make_float4(o[0], o[1], o[2], o[3]), make_float4(o[4], o[5], o[6], o[7]));
+                st_v8f(reinterpret_cast<float*>(dst + 2), make_float4(o[8], o[9], o[10], o[11]),
+                       make_float4(o[12], o[13], o[14], o[15]));
               }
             }
           } else {
@@ -290,8 +288,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int cc = 0; cc < 5; cc++) o[cc] = v[cc * 4 + k] + __ldg(P.bias + cc * 4 + k);
                 float4* dst = reinterpret_cast<float4*>(
                     ob + (((size_t)n * H4 + 4 * y + 2 * p + i) * W4 + 4 * x + 2 * q + jj) * 8);
-                dst[0] = make_float4(o[0], o[1], o[2], o[3]);
-                dst[1] = make_float4(o[4], 0.f, 0.f, 0.f);
+                st_v8f(reinterpret_cast<float*>(dst), make_float4(o[0], o[1], o[2], o[3]), make_float4(o[4], 0.f, 0.f, 0.f));
               }
             }
           }

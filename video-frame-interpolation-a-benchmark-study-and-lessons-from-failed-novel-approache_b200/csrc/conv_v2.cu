@@ -36,6 +36,8 @@ struct V2Params {
   // by the tensor core's operand reads while MMAs are in flight
   float bias_c[128];
   float beta_c[128];
+  float* low_out;  // EPI 2 (final block's lastconv): [N, 4H, 4W, low_c] fp32, channels 0-4 written
+  int low_c;
   unsigned long long* trace;  // debug (vfi_set_option "v2_trace"): CTA 0 timestamps [role][tile < 64][8]
 };
 
@@ -193,6 +195,13 @@ __device__ __forceinline__ void ld_cols(uint32_t taddr, float* v) {
         : "r"(taddr)
         : "memory");
   }
+}
+// one 32-byte (full-sector) global store
+__device__ __forceinline__ void st_global_v8(float* p, float a, float b, float c, float d, float e, float f, float g,
+                                             float h) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d),
+               "f"(e), "f"(f), "f"(g), "f"(h)
+               : "memory");
 }
 // no-swizzle K-major descriptor: start, LBO (K-direction core-matrix stride), SBO (8-row group stride), bytes
 __device__ __forceinline__ uint64_t desc_ns(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
@@ -372,6 +381,50 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       }
       __syncwarp();
     }
+  } else if constexpr (EPI == 2) {
+    // ================= epilogue of the final block's lastconv: ConvTranspose2d(32, 52, 4, 2, 1) + PixelShuffle(2), of
+    // which only flow delta + mask (output channels 0-4 = deconv channels 0-19) are consumed.  Accumulator column =
+    // (2p+q)*20 + (2i+jj)*5 + c: deconv phase (p,q), pixel-shuffle sub-position (i,jj), channel c -> output pixel
+    // (4y + 2p + i, 4x + 2q + jj).  Warp role = (sub-tile j, phase row p): its 40 columns are the 2 x 4 output pixels of
+    // rows 4y+2p and 4y+2p+1, columns 4x .. 4x+3: 128 contiguous bytes per row and thread.
+    static_assert(EPI != 2 || (CN == 80 && KW == 2), "final lastconv instance");
+    const int lg = warp & 3;
+    const int role = (warp - V2_PW - 1) >> 2;  // 0..3
+    const int j = role & 1, pr = role >> 1;
+    const int m = lg * 32 + lane;
+    const int ly = m >> 3, lx = m & 7;
+    const float* bias_r = P.bias_c + pr * 40;
+    int it = 0;
+    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
+      const int as = it & 1;
+      const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+      const int y = ty * 16 + ly, x = (tx * KW + j) * 8 + lx;
+      bar_wait(&tfull_bar[as], (uint32_t)((it >> 1) & 1));
+      tc_after();
+      float v[40];
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE + j * CN + pr * 40);
+      ld_cols<32>(taddr, v);
+      ld_cols<8>(taddr + 32, v + 32);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      tc_before();
+      __syncwarp();
+      if (lane == 0) bar_arrive(&tempty_bar[as]);
+      if (y < P.H && x < P.W) {
+        const int H4 = 4 * P.H, W4 = 4 * P.W, lc = P.low_c;
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+          float* row = P.low_out + (((size_t)n * H4 + 4 * y + 2 * pr + i) * W4 + 4 * x) * lc;
+#pragma unroll
+          for (int q = 0; q < 2; q++)
+#pragma unroll
+            for (int jj = 0; jj < 2; jj++) {
+              const int c0 = q * 20 + (2 * i + jj) * 5;
+              st_global_v8(row + (2 * q + jj) * lc, v[c0] + bias_r[c0], v[c0 + 1] + bias_r[c0 + 1], v[c0 + 2] + bias_r[c0 + 2],
+                           v[c0 + 3] + bias_r[c0 + 3], v[c0 + 4] + bias_r[c0 + 4], 0.f, 0.f, 0.f);
+            }
+        }
+      }
+    }
   } else {
     // ================= epilogue: 16 warps = 4 TMEM lane groups x NSJ sub-tile classes x NSC channel slices.  A warp
     // keeps its slice's bias / beta in registers, pulls its accumulator columns with one tcgen05.wait::ld, hands the
@@ -380,7 +433,9 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     const int role = (warp - V2_PW - 1) >> 2;     // 0..3
     constexpr int NSJ = KW >= 2 ? 2 : 1;          // sub-tile classes (j mod NSJ)
     constexpr int Q = 4 / NSJ;                    // warps available per lane group and sub-tile class
-    constexpr int CH = (CN % Q == 0 && (CN / Q == 8 || CN / Q == 16 || CN / Q == 32)) ? CN / Q : 16;  // columns per warp
+    // columns per warp: CN / Q when that is 16 or 32, else 16 (32-byte stores; spare warps only hand-shake), 8 only for
+    // the Head deconv instance whose 8 columns are one output row
+    constexpr int CH = EPI == 1 ? 8 : (CN % Q == 0 && (CN / Q == 16 || CN / Q == 32)) ? CN / Q : 16;
     constexpr int NSC = CN / CH;                  // channel slices in use (<= 4 / NSJ; spare warps only hand-shake)
     static_assert(NSC <= Q && NSC * CH == CN, "epilogue slicing");
     constexpr int NJ = KW / NSJ;                  // sub-tiles per warp and tile
@@ -476,12 +531,21 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
               for (int i = 0; i < CH; i++) v[jj][i] = v[jj][i] > 0.f ? v[jj][i] : v[jj][i] * P.slope;
             }
             bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT + co0 + cb;
+            if constexpr (CH >= 16) {
 #pragma unroll
-            for (int c = 0; c < CH; c += 8) {
+              for (int c = 0; c < CH; c += 16) {
+                uint4 o0, o1;
+                o0.x = pk_bf16(v[jj][c], v[jj][c + 1]); o0.y = pk_bf16(v[jj][c + 2], v[jj][c + 3]);
+                o0.z = pk_bf16(v[jj][c + 4], v[jj][c + 5]); o0.w = pk_bf16(v[jj][c + 6], v[jj][c + 7]);
+                o1.x = pk_bf16(v[jj][c + 8], v[jj][c + 9]); o1.y = pk_bf16(v[jj][c + 10], v[jj][c + 11]);
+                o1.z = pk_bf16(v[jj][c + 12], v[jj][c + 13]); o1.w = pk_bf16(v[jj][c + 14], v[jj][c + 15]);
+                st_v8(op + c, o0, o1);  // one full 32-byte sector per lane
+              }
+            } else {
               uint4 o;
-              o.x = pk_bf16(v[jj][c], v[jj][c + 1]); o.y = pk_bf16(v[jj][c + 2], v[jj][c + 3]);
-              o.z = pk_bf16(v[jj][c + 4], v[jj][c + 5]); o.w = pk_bf16(v[jj][c + 6], v[jj][c + 7]);
-              *reinterpret_cast<uint4*>(op + c) = o;
+              o.x = pk_bf16(v[jj][0], v[jj][1]); o.y = pk_bf16(v[jj][2], v[jj][3]);
+              o.z = pk_bf16(v[jj][4], v[jj][5]); o.w = pk_bf16(v[jj][6], v[jj][7]);
+              *reinterpret_cast<uint4*>(op) = o;
             }
           }
         }
@@ -509,7 +573,7 @@ static uint16_t f2bf_v2(float f) {
 
 // instances: Head cnn1/cnn2 (16 ch), block-4 ResConv (32 ch), block-3 ResConv (64 ch)
 bool v2_supported(const Layer& L) {
-  if (L.kind == LK_DECONV4) return L.cin == 16 && L.cout == 4;  // Head.cnn3
+  if (L.kind == LK_DECONV4) return (L.cin == 16 && L.cout == 4) || (L.cin == 32 && L.cout == 52);  // Head.cnn3, final lastconv
   if (L.kind != LK_CONV3 || L.stride != 1 || L.cin != L.cout || L.cin != L.cin_pad) return false;
   return L.cin == 16 || L.cin == 32 || L.cin == 64 || L.cin == 96 || L.cin == 128;
 }
@@ -519,6 +583,31 @@ static int v2_nsplit(int c) { return c == 96 ? 2 : c == 128 ? 4 : 1; }
 int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
   if (!v2_supported(L)) return 0;
   const int nch = L.cin / 8;
+  if (L.kind == LK_DECONV4 && L.cout == 52) {
+    // final block's lastconv, channels 0-19 only: column (2p+q)*20 + (2i+jj)*5 + c <- deconv channel 4c + 2i + jj of
+    // phase (p,q); kernel element ky = p + 1 - 2*dy, kx = q + 1 - 2*dx of tap (dy,dx); w: [Ci][52][4][4]
+    std::vector<uint16_t> pk((size_t)9 * 32 * 80, 0);
+    std::vector<float> bias_h(L.cout);
+    VFI_CUDA(h, cudaMemcpy(bias_h.data(), L.bias, L.cout * sizeof(float), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 128; i++) { L.h_bias_v2[i] = 0.f; L.h_beta[i] = 1.f; }
+    for (int ph = 0; ph < 4; ph++)
+      for (int k = 0; k < 4; k++)
+        for (int c = 0; c < 5; c++) {
+          const int col = ph * 20 + k * 5 + c, dc = 4 * c + k;
+          L.h_bias_v2[col] = bias_h[dc];
+          for (int tap = 0; tap < 9; tap++) {
+            const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+            const int ky = (ph >> 1) + 1 - 2 * dy, kx = (ph & 1) + 1 - 2 * dx;
+            if (ky < 0 || ky > 3 || kx < 0 || kx > 3) continue;
+            for (int ci = 0; ci < 32; ci++)
+              pk[(((size_t)tap * nch + ci / 8) * 80 + col) * 8 + ci % 8] =
+                  f2bf_v2(w[(((size_t)ci * 52 + dc) * 4 + ky) * 4 + kx]);
+          }
+        }
+    VFI_CUDA(h, cudaMalloc(&L.wv2, pk.size() * 2));
+    VFI_CUDA(h, cudaMemcpy(L.wv2, pk.data(), pk.size() * 2, cudaMemcpyHostToDevice));
+    return 0;
+  }
   if (L.kind == LK_DECONV4) {
     // ConvTranspose2d(16,4,4,2,1): output pixel (2y+p, 2x+q) reads input (y+dy, x+dx) through kernel element
     // ky = p + 1 - 2*dy, kx = q + 1 - 2*dx.  Column = (2p+q)*4 + co of a 3x3 "conv" over the input grid; taps a
@@ -616,6 +705,7 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
     if (FILE* f = fopen(path, "wb")) { fwrite(host.data(), 1, tbytes, f); fclose(f); }
     return 0;
   }
+  if (L.kind == LK_DECONV4 && L.cout == 52) VFI_FAIL(h, VFI_E_ARG, "conv_v2: use k_conv_v2_last for the final lastconv");
   if (L.kind == LK_DECONV4) {
     P.bias = L.bias_v2; P.beta = nullptr; P.act = 0;
     return launch_v2<16, 16, 4, 1>(h, P, s);
@@ -628,4 +718,19 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
     case 128: return launch_v2<128, 128, 1, 0, 4>(h, P, s);  // 4 x 32 output channels: 72 KB of weights per CTA
   }
   VFI_FAIL(h, VFI_E_ARG, "conv_v2: no instance for Cin=%d", L.cin);
+}
+
+// Final block's lastconv (ConvTranspose 4x4 s2 + PixelShuffle(2), output channels 0-4 = flow delta + mask):
+// in [N, H, W, 32] bf16 -> low [N, 4H, 4W, low_c] fp32 (low_c = 8 in the network, 16 in the vfi_debug_conv layout)
+int k_conv_v2_last(vfi_handle* h, const Layer& L, const bf16* in, float* low, int low_c, int N, int H, int W,
+                   cudaStream_t s) {
+  ProfScope _ps(h, PC_CONV_TC, s);
+  if (!L.wv2 || L.kind != LK_DECONV4 || L.cout != 52) VFI_FAIL(h, VFI_E_STATE, "conv_v2_last: layer not packed");
+  V2Params P;
+  memset(&P, 0, sizeof(P));
+  P.in = in; P.wpack = L.wv2; P.bias = L.bias; P.beta = nullptr;
+  P.low_out = low; P.low_c = low_c;
+  P.N = N; P.H = H; P.W = W;
+  for (int i = 0; i < 128; i++) { P.bias_c[i] = L.h_bias_v2[i]; P.beta_c[i] = 1.f; }
+  return launch_v2<32, 80, 2, 2>(h, P, s);
 }

@@ -20,6 +20,10 @@ template <> struct Act<float> {
   static __device__ __forceinline__ void store4(float* p, const float* v) {
     reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
   }
+  static __device__ __forceinline__ void store16(float* p, const float* v) {  // 16 channels = two full sectors
+    st_v8f(p, make_float4(v[0], v[1], v[2], v[3]), make_float4(v[4], v[5], v[6], v[7]));
+    st_v8f(p + 8, make_float4(v[8], v[9], v[10], v[11]), make_float4(v[12], v[13], v[14], v[15]));
+  }
 };
 template <> struct Act<bf16> {
   static __device__ __forceinline__ void load4(const bf16* p, float* v) {
@@ -42,6 +46,12 @@ template <> struct Act<bf16> {
     uint2 u;
     u.x = pack(v[0], v[1]); u.y = pack(v[2], v[3]);
     *reinterpret_cast<uint2*>(p) = u;
+  }
+  static __device__ __forceinline__ void store16(bf16* p, const float* v) {  // 16 channels = one full 32-byte sector
+    uint4 a, b;
+    a.x = pack(v[0], v[1]); a.y = pack(v[2], v[3]); a.z = pack(v[4], v[5]); a.w = pack(v[6], v[7]);
+    b.x = pack(v[8], v[9]); b.y = pack(v[10], v[11]); b.z = pack(v[12], v[13]); b.w = pack(v[14], v[15]);
+    st_v8(p, a, b);
   }
 };
 
@@ -150,8 +160,7 @@ __global__ void head_cnn0_kernel(const uint8_t* __restrict__ imgs, const float* 
 #pragma unroll
   for (int c = 0; c < 16; c++) acc[c] = acc[c] > 0.f ? acc[c] : acc[c] * slope;
   T* o = out + i * 16;
-  Act<T>::store8(o, acc);
-  Act<T>::store8(o + 8, acc + 8);
+  Act<T>::store16(o, acc);
 }
 int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, int NI, int Hp, int Wp, bool bf,
                 cudaStream_t s) {
@@ -312,7 +321,7 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
     o = i * C;
   }
 #pragma unroll
-  for (int c = 0; c < C; c += 8) Act<T>::store8(out + o + c, acc + c);
+  for (int c = 0; c < C; c += 16) Act<T>::store16(out + o + c, acc + c);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -508,7 +517,7 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
       o = (((size_t)n * Hs + Y) * Ws + X) * 32;
     }
 #pragma unroll
-    for (int c = 0; c < 32; c += 8) Act<T>::store8(out + o + c, acc + c);
+    for (int c = 0; c < 32; c += 16) Act<T>::store16(out + o + c, acc + c);
   }
 }
 
@@ -894,8 +903,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
       uint4 o0, o1;
       o0.x = pk_bf16(v[j][0], v[j][1]); o0.y = pk_bf16(v[j][2], v[j][3]); o0.z = pk_bf16(v[j][4], v[j][5]); o0.w = pk_bf16(v[j][6], v[j][7]);
       o1.x = pk_bf16(v[j][8], v[j][9]); o1.y = pk_bf16(v[j][10], v[j][11]); o1.z = pk_bf16(v[j][12], v[j][13]); o1.w = pk_bf16(v[j][14], v[j][15]);
-      reinterpret_cast<uint4*>(out + opix * 16)[0] = o0;
-      reinterpret_cast<uint4*>(out + opix * 16)[1] = o1;
+      st_v8(out + opix * 16, o0, o1);
     }
   }
   tc_before();
