@@ -254,6 +254,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     uint8_t* ht0 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
     uint8_t* ht1 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
     float* tdev = cv.take<float>(64);
+    float* flow3 = cv.take<float>((size_t)N * px * 4);  // blocks 0-3 flow per pixel (written by the fused finest gather)
     float* low[5];
     for (int i = 0; i < 5; i++) low[i] = cv.take<float>((size_t)N * (Hp / sl[i]) * (Wp / sl[i]) * (i == 4 ? last_c : 16));
     uint8_t* xin = cv.take<uint8_t>(xin_e * esz);
@@ -280,11 +281,13 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     if (rc) return rc;
     LowSet lows;
     memset(&lows, 0, sizeof(lows));
+    const float* flow_pre = nullptr;
     for (int i = 0; i < 5; i++) {
       const int sc = sl[i], hs = Hp / sc, wsz = Wp / sc;
       const Layer* Lb = &h->layers[4 + 11 * i];
       if (bf && sc == 1 && i > 0 && h->opt_fuse_gather && h->opt_conv_v2 && Lb[0].ws2 && Lb[0].cout == 16) {
-        if ((rc = k_gather_conv0a(h, Lb[0], imgs, feats, lows, tdev, (bf16*)a0, B, I1, T, Hp, Wp, s))) return rc;
+        if ((rc = k_gather_conv0a(h, Lb[0], imgs, feats, lows, tdev, (bf16*)a0, flow3, B, I1, T, Hp, Wp, s))) return rc;
+        flow_pre = flow3;
       } else {
         if ((rc = k_gather(h, imgs, feats, lows, tdev, xin, B, I1, T, Hp, Wp, sc, bf, bf, s))) return rc;
         if ((rc = run_conv(h, Lb[0], xin, nullptr, a0, N, hs, wsz, bf, bf, s))) return rc;
@@ -302,7 +305,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       if (rc) return rc;
       lows.push(low[i], sc, lc, Hp, Wp);
     }
-    if ((rc = k_final_blend(h, imgs, lows, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s))) return rc;
+    if ((rc = k_final_blend(h, imgs, lows, flow_pre, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s))) return rc;
   }
   return VFI_OK;
 }
@@ -330,7 +333,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_warp_blend(vfi_handle*
     LowSet lows;
     memset(&lows, 0, sizeof(lows));
     lows.push(fm, 1, 8, H, W);
-    if ((rc = k_final_blend(h, imgs, lows, nullptr, tdev, out, out_f32, nullptr, N, N, 1, H, W, H, W, s))) return rc;
+    if ((rc = k_final_blend(h, imgs, lows, nullptr, nullptr, tdev, out, out_f32, nullptr, N, N, 1, H, W, H, W, s))) return rc;
   }
   return VFI_OK;
 }

@@ -160,12 +160,14 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
              void* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s);
 // I1: index of pair 0's second frame in imgs / feats (B when the two frame sets are stored one after the other, 1 when
 // the pairs are consecutive frames of one clip)
-int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev,
-                  uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp, int Wp,
+// flow_pre (nullable): [N,Hp,Wp,4] fp32 flow already summed over every level of `lows` but the last (full-resolution) one
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const float* flow_pre, const uint8_t* hud,
+                  const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp, int Wp,
                   cudaStream_t s);
 // finest block at scale 1.0: gather fused with conv0[0] (tcgen05), bf16 only
 int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
-                    const float* tsteps_dev, bf16* out, int B, int I1, int T, int Hp, int Wp, cudaStream_t s);
+                    const float* tsteps_dev, bf16* out, float* flow_sum, int B, int I1, int T, int Hp, int Wp,
+                    cudaStream_t s);
 int k_pack_fm(vfi_handle* h, const float* flow, const float* mask, float* fm, int N, int H, int W, int Hp, int Wp,
               cudaStream_t s);
 int k_f32_to_act(vfi_handle* h, const float* src, void* dst, size_t n, bool bf, cudaStream_t s);

@@ -576,8 +576,12 @@ __device__ __forceinline__ uint8_t quant_u8(float v) {
   v = fminf(fmaxf(v * 255.0f, 0.f), 255.f);
   return (uint8_t)(int)v;  // truncation, as numpy astype(uint8)
 }
+// PRE: the flow of all coarser blocks was already summed per pixel by the finest block's gather (flow_pre); `lows` then
+// holds only the last block's full-resolution output and nothing is staged.
+template <bool PRE>
 __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* __restrict__ imgs,
                                                                  const __grid_constant__ LowSet lows,
+                                                                 const float4* __restrict__ flow_pre,
                                                                  const uint8_t* __restrict__ hud,
                                                                  const float* __restrict__ tsteps,
                                                                  uint8_t* __restrict__ out,
@@ -587,8 +591,10 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
   extern __shared__ float4 tl_sm[];
   __shared__ __align__(16) uint8_t s_rgb[TL_H][TL_W * 3];  // the tile's u8 result, stored row-wise as 32-bit words
   const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
-  tile_stage<2>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
-  __syncthreads();
+  if (!PRE) {
+    tile_stage<2>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
+    __syncthreads();
+  }
   const int b = n / Tn;
   const float t = tsteps[n - b * Tn];
   const size_t plane = (size_t)Hp * Wp;
@@ -603,7 +609,11 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
     if (y >= H || x >= W) continue;
     float o[3];
     float4 m4;
-    const float4 fl = tile_eval<2>(lows, tl_sm, n, x, y, xl, yl, &m4);
+    float4 fl = tile_eval<2>(lows, tl_sm, n, x, y, xl, yl, &m4);
+    if (PRE) {
+      const float4 f3 = __ldg(flow_pre + ((size_t)n * Hp + y) * Wp + x);
+      fl.x += f3.x; fl.y += f3.y; fl.z += f3.z; fl.w += f3.w;
+    }
     blend_px(img0, img1, fl, m4.x, x, y, Hp, Wp, o);
     const size_t opix = ((size_t)n * H + y) * W + x;
     if (out_f32) { out_f32[opix * 3] = o[0]; out_f32[opix * 3 + 1] = o[1]; out_f32[opix * 3 + 2] = o[2]; }
@@ -633,14 +643,23 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
     }
   }
 }
-int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const uint8_t* hud, const float* tsteps_dev,
-                  uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp,
+int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const float* flow_pre, const uint8_t* hud,
+                  const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp,
                   int Wp, cudaStream_t s) {
   ProfScope _ps(h, PC_BLEND, s);
   const size_t smem = tl_smem_bytes(lows, 2);
   const dim3 grid((W + TL_W - 1) / TL_W, (H + TL_H - 1) / TL_H, B * T);
-  final_blend_kernel<<<grid, TL_THREADS, smem, s>>>(imgs, lows, hud, tsteps_dev, out, out_f32, flow_out, B, I1, T, H, W,
-                                                    Hp, Wp);
+  if (flow_pre) {
+    if (lows.n < 1 || lows.s[lows.n - 1] != 1) VFI_FAIL(h, VFI_E_ARG, "final blend: pre-summed flow needs a full-resolution last level");
+    LowSet last;
+    memset(&last, 0, sizeof(last));
+    last.push(lows.p[lows.n - 1], 1, lows.c4[lows.n - 1] * 4, Hp, Wp);
+    final_blend_kernel<true><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
+                                                         out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp);
+  } else {
+    final_blend_kernel<false><<<grid, TL_THREADS, smem, s>>>(imgs, lows, nullptr, hud, tsteps_dev, out, out_f32, flow_out, B,
+                                                             I1, T, H, W, Hp, Wp);
+  }
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -798,7 +817,8 @@ template <typename T>
 __global__ void __launch_bounds__(GC_THREADS, 2)
 gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
                      const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
-                     bf16* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, float slope, int stage_bytes) {
+                     bf16* __restrict__ out, float4* __restrict__ flow_sum, int B, int I1, int Tn, int Hp, int Wp, float slope,
+                     int stage_bytes) {
   using namespace umma;
   extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
   __shared__ uint64_t mma_bar;
@@ -839,6 +859,8 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
     if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
       float4 m[3];
       const float4 fl = gc_eval(lows, tl_sm, lx, ly);
+      // the flow of blocks 0..3 at this pixel, for the final blend (tile-interior pixels: each written exactly once)
+      if (flow_sum && ly > 0 && lx > 0) flow_sum[((size_t)n * Hp + gy) * Wp + gx] = fl;
       {
         const Lerp L = lerp_setup(gx, gy, lows.s[kl], lows.Hl[kl], lows.Wl[kl]);
         m[0] = lerp4(mf_img, L, 1, lows.c4[kl]); m[1] = lerp4(mf_img, L, 2, lows.c4[kl]); m[2] = lerp4(mf_img, L, 3, lows.c4[kl]);
@@ -916,7 +938,8 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
 
 // Lb0 = the block's conv0[0] layer (28 -> 16, stride 2).  Output: its activation as the phase planes of [N, Hp/2, Wp/2, 16].
 int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
-                    const float* tsteps_dev, bf16* out, int B, int I1, int T, int Hp, int Wp, cudaStream_t s) {
+                    const float* tsteps_dev, bf16* out, float* flow_sum, int B, int I1, int T, int Hp, int Wp,
+                    cudaStream_t s) {
   ProfScope _ps(h, PC_GATHER_CONV, s);
   if (!Lb0.ws2 || Lb0.cin_pad != 32 || Lb0.cout != 16) VFI_FAIL(h, VFI_E_STATE, "gather_conv0a: layer not packed");
   if (Hp % TL_H || Wp % TL_W) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: padded size must be a multiple of 32");
@@ -928,7 +951,7 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
   if (smem > 112 * 1024) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: shared memory budget");
   const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
   gather_conv0a_kernel<bf16><<<grid, GC_THREADS, smem, s>>>(imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out,
-                                                          B, I1, T, Hp, Wp, h->slope, (int)un);
+                                                          reinterpret_cast<float4*>(flow_sum), B, I1, T, Hp, Wp, h->slope, (int)un);
   VFI_LAUNCHED(h);
   return 0;
 }
