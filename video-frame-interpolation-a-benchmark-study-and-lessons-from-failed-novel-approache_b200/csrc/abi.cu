@@ -254,6 +254,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     uint8_t* ht0 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
     uint8_t* ht1 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
     float* tdev = cv.take<float>(64);
+    Tap* taps = cv.take<Tap>((size_t)5 * (Hp + Wp));
     float* flow3 = cv.take<float>((size_t)N * px * 4);  // blocks 0-3 flow per pixel (written by the fused finest gather)
     float* low[5];
     for (int i = 0; i < 5; i++) low[i] = cv.take<float>((size_t)N * (Hp / sl[i]) * (Wp / sl[i]) * (i == 4 ? last_c : 16));
@@ -267,6 +268,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     }
     int rc;
     VFI_CUDA(h, cudaMemcpyAsync(tdev, timesteps, T * sizeof(float), cudaMemcpyHostToDevice, s));
+    if ((rc = k_build_taps(h, taps, sl, 5, Hp, Wp, s))) return rc;
     // to_tensor + reflect pad, both frames of every pair
     if ((rc = k_pad_rgbx(h, img0, imgs, B, H, W, Hp, Wp, s))) return rc;
     if (clipmode) rc = k_pad_rgbx(h, img1 + (size_t)(B - 1) * H * W * 3, imgs + (size_t)B * px * 4, 1, H, W, Hp, Wp, s);
@@ -303,7 +305,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       else if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low[i], N, hs / 4, wsz / 4, false, h->slope, s, lc);
       else rc = k_deconv4_direct(h, Lb[10], cur, low[i], N, hs / 4, wsz / 4, false, 1, s);
       if (rc) return rc;
-      lows.push(low[i], sc, lc, Hp, Wp);
+      lows.push(low[i], sc, lc, Hp, Wp, taps + (size_t)i * (Hp + Wp));
     }
     if ((rc = k_final_blend(h, imgs, lows, flow_pre, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s))) return rc;
   }

@@ -143,19 +143,29 @@ int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, i
 // feat 8).  The reference's full-resolution flow / mask / feat tensors (IFBlock.forward's F.interpolate(scale) and
 // IFNet.forward's flow = flow + fd) are never materialised: a consumer evaluates, at the pixels it needs,
 //   flow = sum_k s[k] * bilerp(low[k][0:4]),  (mask, feat) = bilerp(low[n-1][4:13])        
+// one axis of F.interpolate(bilinear, align_corners=False) from a grid s times coarser: v = h * src[i0] + l * src[i1]
+struct __align__(16) Tap {
+  int i0, i1;
+  float h, l;
+};
 struct LowSet {
   const float* p[5];
+  const Tap* xt[5];  // per level (optional): taps of every padded-frame column [Wp] and row [Hp], see k_build_taps
+  const Tap* yt[5];
   int s[5];
   int c4[5];  // float4 per texel: 4 (16 channels) or 2 (the final block's compact flow+mask)
   int Hl[5], Wl[5];  // Hp / s, Wp / s
   float rs[5], fs[5];  // 1/s and s as floats
   int n;
-  void push(const float* ptr, int scale, int ch, int Hp, int Wp) {
+  void push(const float* ptr, int scale, int ch, int Hp, int Wp, const Tap* taps = nullptr) {
+    xt[n] = taps; yt[n] = taps ? taps + Wp : nullptr;
     p[n] = ptr; s[n] = scale; c4[n] = ch / 4; Hl[n] = Hp / scale; Wl[n] = Wp / scale;
     rs[n] = 1.0f / (float)scale; fs[n] = (float)scale;
     n++;
   }
 };
+// tap tables of `n` levels: level k at out + k * (Wp + Hp), columns first
+int k_build_taps(vfi_handle* h, Tap* out, const int* scales, int n, int Hp, int Wp, cudaStream_t s);
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
              void* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s);
 // I1: index of pair 0's second frame in imgs / feats (B when the two frame sets are stored one after the other, 1 when

@@ -97,6 +97,44 @@ __device__ __forceinline__ void sample_feat(const T* f, const Bil& b, float* o) 
   for (int i = 0; i < 4; i++) o[i] = b.w00 * a[i] + b.w01 * c[i] + b.w10 * d[i] + b.w11 * e[i];
 }
 
+// The same three helpers on 32-bit PIXEL indices into the whole image set (base = image index * Hp * Wp folded into the
+// offsets): one IMAD.WIDE per tap instead of 64-bit pointer arithmetic.  NI * Hp * Wp < 2^31 is checked by the host.
+__device__ __forceinline__ Bil bil_setup(float fx, float fy, int W, int H, int base) {
+  fx = fminf(fmaxf(fx, 0.f), (float)(W - 1));
+  fy = fminf(fmaxf(fy, 0.f), (float)(H - 1));
+  const int x0 = (int)fx, y0 = (int)fy;  // truncation == floor: both are >= 0
+  const float wx = fx - (float)x0, wy = fy - (float)y0;
+  const int dx = x0 < W - 1 ? 1 : 0, dy = y0 < H - 1 ? W : 0;
+  Bil b;
+  b.o00 = base + y0 * W + x0; b.o01 = b.o00 + dx; b.o10 = b.o00 + dy; b.o11 = b.o10 + dx;
+  const float ux = 1.f - wx, uy = 1.f - wy;
+  b.w00 = ux * uy; b.w01 = wx * uy; b.w10 = ux * wy; b.w11 = wx * wy;
+  return b;
+}
+__device__ __forceinline__ void sample_rgbx(const uint32_t* __restrict__ imgs, const Bil& b, float* rgb) {
+  const uint32_t a = __ldg(imgs + b.o00), c = __ldg(imgs + b.o01), d = __ldg(imgs + b.o10), e = __ldg(imgs + b.o11);
+  const float k = 1.0f / 255.0f;
+  rgb[0] = (b.w00 * u8f<0>(a) + b.w01 * u8f<0>(c) + b.w10 * u8f<0>(d) + b.w11 * u8f<0>(e)) * k;
+  rgb[1] = (b.w00 * u8f<1>(a) + b.w01 * u8f<1>(c) + b.w10 * u8f<1>(d) + b.w11 * u8f<1>(e)) * k;
+  rgb[2] = (b.w00 * u8f<2>(a) + b.w01 * u8f<2>(c) + b.w10 * u8f<2>(d) + b.w11 * u8f<2>(e)) * k;
+}
+__device__ __forceinline__ void feat4(const float* __restrict__ f, int pix, float* v) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(f) + pix);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+__device__ __forceinline__ void feat4(const bf16* __restrict__ f, int pix, float* v) {
+  const uint2 a = __ldg(reinterpret_cast<const uint2*>(f) + pix);
+  v[0] = __uint_as_float(a.x << 16); v[1] = __uint_as_float(a.x & 0xffff0000u);
+  v[2] = __uint_as_float(a.y << 16); v[3] = __uint_as_float(a.y & 0xffff0000u);
+}
+template <typename T>
+__device__ __forceinline__ void sample_feat_px(const T* __restrict__ feats, const Bil& b, float* o) {
+  float a[4], c[4], d[4], e[4];
+  feat4(feats, b.o00, a); feat4(feats, b.o01, c); feat4(feats, b.o10, d); feat4(feats, b.o11, e);
+#pragma unroll
+  for (int i = 0; i < 4; i++) o[i] = b.w00 * a[i] + b.w01 * c[i] + b.w10 * d[i] + b.w11 * e[i];
+}
+
 // ------------------------------------------------------------------------------------------
 // to_tensor + pad_to_multiple(reflect) (models/base.py:175-186, :203-225) kept in uint8: RGB -> RGBX
 __global__ void pad_rgbx_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int B, int H, int W,
@@ -204,6 +242,30 @@ __device__ __forceinline__ float4 lerp4(const float4* img, const Lerp& L, int k,
   r.w = L.hy * (L.hx * a.w + L.lx * b.w) + L.ly * (L.hx * c.w + L.lx * d.w);
   return r;
 }
+// The same source index / weights for every column and row of the padded frame, once per call: the tiled kernels read
+// them instead of redoing the float arithmetic per thread and level.
+struct TapScales { int s[5]; };
+__global__ void build_taps_kernel(Tap* __restrict__ out, const TapScales sc, int n, int Hp, int Wp) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+  if (i >= Wp + Hp || k >= n) return;
+  const int s = sc.s[k];
+  const int d = i < Wp ? i : i - Wp, L = (i < Wp ? Wp : Hp) / s;
+  const float rs = 1.0f / (float)s;
+  const float src = fmaxf(rs * ((float)d + 0.5f) - 0.5f, 0.f);
+  Tap t;
+  t.i0 = (int)src; t.i1 = t.i0 + (t.i0 < L - 1 ? 1 : 0);
+  t.l = src - (float)t.i0; t.h = 1.f - t.l;
+  out[(size_t)k * (Wp + Hp) + i] = t;
+}
+int k_build_taps(vfi_handle* h, Tap* out, const int* scales, int n, int Hp, int Wp, cudaStream_t s) {
+  ProfScope _ps(h, PC_MISC, s);
+  TapScales sc;
+  for (int k = 0; k < 5; k++) sc.s[k] = k < n ? scales[k] : 1;
+  build_taps_kernel<<<dim3(cdiv(Wp + Hp, 256), n), 256, 0, s>>>(out, sc, n, Hp, Wp);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
 // flow after the blocks in `lows` at full-resolution pixel (x,y) of item n: flow = flow + up(low_k)[:4] * s_k, in
 // block order.  MF = 1: also (mask, feat) = up(low_last)[4:13] in m[0..2];  MF = 2: mask only, in m[0].x.
 // A low at scale 1 (the last block at scale=1.0) is read directly: interpolate(x1) is the identity.
@@ -738,9 +800,10 @@ int k_plain_to_phase(vfi_handle* h, const bf16* src, bf16* dst, int N, int H, in
 #define GC_THREADS 384   // 3 pixels per thread cover the 33 x 33 = 1089 input pixels with every warp equally loaded
 #define GC_TW 33         // staged / gathered region: the 32 x 32 tile plus its top row and left column
 #define GC_PW 17
-#define GC_PLANE (17 * GC_PW)
+#define GC_PLANE 292  // plane stride (16-byte units): >= 17 * GC_PW and == 4 mod 8, so the two planes a row's pixels
+                      // alternate between sit 64 B apart modulo 128 and a quarter-warp's 16-byte stores never collide
 #define GC_NPIX (4 * GC_PLANE)
-#define GC_CS 1162  // chunk stride (16-byte units): >= GC_NPIX, == 2 mod 8 (bank spread, see umma::chunk_stride)
+#define GC_CS 1170  // chunk stride (16-byte units): >= GC_NPIX, == 2 mod 8 (bank spread, see umma::chunk_stride)
 #define GC_A_BYTES (4 * GC_CS * 16)
 #define GC_W_BYTES (9 * 32 * 16 * 2)
 #define GC_TAB (5 * GC_TW)
@@ -751,49 +814,55 @@ __device__ __forceinline__ uint32_t gc_pix_index(int ly, int lx) {
   const int pr = (ly + 1) >> 1, pc = (lx + 1) >> 1;  // window row / col: (g >> 1) - t0/2 + 1
   return (uint32_t)((py * 2 + px) * GC_PLANE + pr * GC_PW + pc);
 }
-static size_t gc_stage_bytes(const LowSet& lows) {
-  size_t n = GC_TAB;
-  for (int k = 0; k < lows.n; k++) n += (size_t)tl_rows(lows.s[k]) * GC_TW;
-  return n * sizeof(float4);
-}
-// tile_stage for the 33 x 33 region whose origin is (tx0 - 1, ty0 - 1): flow rows only
-__device__ __forceinline__ void gc_stage(const LowSet& L, int n, int ox, int oy, int Hp, int Wp, float4* sm) {
-  RowTap* ytab = reinterpret_cast<RowTap*>(sm);
-  const int col = threadIdx.x % GC_TW, row0 = threadIdx.x / GC_TW;
-  constexpr int RSTEP = GC_THREADS / GC_TW;  // rows per pass; threads >= RSTEP * GC_TW only help with the row tables
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int off = GC_TAB;
-#pragma unroll
+struct GcRows { int start[6]; };  // first staged row of each level; start[n] = all rows
+static size_t gc_stage_bytes(const LowSet& lows, GcRows* R) {
+  int rows = 0;
   for (int k = 0; k < 5; k++) {
-    if (k < L.n) {
-      const int sk = L.s[k], c4 = L.c4[k], Hl = L.Hl[k], Wl = L.Wl[k];
-      const int rows = tl_rows(sk);
-      const float rs = L.rs[k];
-      const int r_lo = (int)fmaxf(rs * ((float)max(oy, 0) + 0.5f) - 0.5f, 0.f);
-      if (warp == k) {
-        for (int yl = lane; yl < GC_TW; yl += 32) {
-          const float sy = fmaxf(rs * ((float)min(max(oy + yl, 0), Hp - 1) + 0.5f) - 0.5f, 0.f);
-          const int y0 = (int)sy, y1 = y0 + (y0 < Hl - 1 ? 1 : 0);
-          RowTap t;
-          t.ly = sy - (float)y0; t.hy = 1.f - t.ly;
-          t.o0 = off + (y0 - r_lo) * GC_TW; t.o1 = off + (y1 - r_lo) * GC_TW;
-          ytab[k * GC_TW + yl] = t;
-        }
-      }
-      if (row0 < RSTEP) {
-        const float sx = fmaxf(rs * ((float)min(max(ox + col, 0), Wp - 1) + 0.5f) - 0.5f, 0.f);
-        const int x0 = (int)sx, x1 = x0 + (x0 < Wl - 1 ? 1 : 0);
-        const float lx = sx - (float)x0, hx = 1.f - lx;
-        const float4* img = reinterpret_cast<const float4*>(L.p[k]) + (size_t)n * Hl * Wl * c4;
-        for (int row = row0; row < rows; row += RSTEP) {
-          const int ry = min(r_lo + row, Hl - 1);
-          const float4 a = __ldg(img + (size_t)(ry * Wl + x0) * c4), b = __ldg(img + (size_t)(ry * Wl + x1) * c4);
-          sm[off + row * GC_TW + col] =
-              make_float4(hx * a.x + lx * b.x, hx * a.y + lx * b.y, hx * a.z + lx * b.z, hx * a.w + lx * b.w);
-        }
-      }
-      off += rows * GC_TW;
-    }
+    R->start[k] = rows;
+    if (k < lows.n) rows += tl_rows(lows.s[k]);
+  }
+  R->start[5] = rows;
+  return ((size_t)GC_TAB + (size_t)rows * GC_TW) * sizeof(float4);
+}
+__device__ __forceinline__ Tap ld_tap(const Tap* p) {
+  const int4 v = __ldg(reinterpret_cast<const int4*>(p));
+  Tap t;
+  t.i0 = v.x; t.i1 = v.y; t.h = __int_as_float(v.z); t.l = __int_as_float(v.w);
+  return t;
+}
+// The flow rows of every coarse level for the 33 x 33 region whose origin is (ox, oy) = (tx0 - 1, ty0 - 1), x-interpolated
+// to the region's columns and pre-multiplied by the level's flow scale (a power of two: exact).  The staged rows of all
+// levels are one flat array of 33-float4 rows, so entry e is simply staged row e / 33, column e % 33; the x taps come
+// from the per-call tables (k_build_taps), the level of a row from the host-computed row starts.
+__device__ __forceinline__ void gc_stage(const LowSet& L, const GcRows& R, int n, int ox, int oy, int Hp, int Wp, float4* sm) {
+  RowTap* ytab = reinterpret_cast<RowTap*>(sm);
+  const float oyf = (float)max(oy, 0) + 0.5f;
+  for (int e = threadIdx.x; e < L.n * GC_TW; e += GC_THREADS) {
+    const int k = e / GC_TW, yl = e - k * GC_TW;
+    const Tap ty = ld_tap(L.yt[k] + min(max(oy + yl, 0), Hp - 1));
+    const int r_lo = (int)fmaxf(L.rs[k] * oyf - 0.5f, 0.f);
+    const int off = GC_TAB + R.start[k] * GC_TW;
+    RowTap t;
+    t.o0 = (off + (ty.i0 - r_lo) * GC_TW) * 16; t.o1 = (off + (ty.i1 - r_lo) * GC_TW) * 16;  // byte offsets
+    t.hy = ty.h; t.ly = ty.l;
+    ytab[e] = t;
+  }
+  const int total = R.start[5] * GC_TW;
+#pragma unroll 2
+  for (int e = threadIdx.x; e < total; e += GC_THREADS) {
+    const int u = e / GC_TW, col = e - u * GC_TW;
+    int k = 0;
+#pragma unroll
+    for (int j = 1; j < 5; j++) k += (j < L.n && u >= R.start[j]) ? 1 : 0;
+    const int Hl = L.Hl[k], Wl = L.Wl[k], c4 = L.c4[k];
+    const int r_lo = (int)fmaxf(L.rs[k] * oyf - 0.5f, 0.f);
+    const int ry = min(r_lo + u - R.start[k], Hl - 1);
+    const Tap tx = ld_tap(L.xt[k] + min(max(ox + col, 0), Wp - 1));
+    const float4* row = reinterpret_cast<const float4*>(L.p[k]) + ((size_t)n * Hl + ry) * Wl * c4;
+    const float4 a = __ldg(row + tx.i0 * c4), b = __ldg(row + tx.i1 * c4);
+    const float fs = L.fs[k];
+    sm[GC_TAB + e] = make_float4((tx.h * a.x + tx.l * b.x) * fs, (tx.h * a.y + tx.l * b.y) * fs,
+                                 (tx.h * a.z + tx.l * b.z) * fs, (tx.h * a.w + tx.l * b.w) * fs);
   }
 }
 // flow at region-local pixel (lx, ly) from the staged rows (every level of a finest block's LowSet has s > 1)
@@ -804,10 +873,10 @@ __device__ __forceinline__ float4 gc_eval(const LowSet& L, const float4* sm, int
   for (int k = 0; k < 5; k++) {
     if (k < L.n) {
       const RowTap t = ytab[k * GC_TW + ly];
-      const float4 a = sm[t.o0 + lx], c = sm[t.o1 + lx];
-      const float fs = L.fs[k];
-      fl.x += (t.hy * a.x + t.ly * c.x) * fs; fl.y += (t.hy * a.y + t.ly * c.y) * fs;
-      fl.z += (t.hy * a.z + t.ly * c.z) * fs; fl.w += (t.hy * a.w + t.ly * c.w) * fs;
+      const char* col = reinterpret_cast<const char*>(sm + lx);
+      const float4 a = *reinterpret_cast<const float4*>(col + t.o0), c = *reinterpret_cast<const float4*>(col + t.o1);
+      fl.x = fmaf(t.ly, c.x, fmaf(t.hy, a.x, fl.x)); fl.y = fmaf(t.ly, c.y, fmaf(t.hy, a.y, fl.y));
+      fl.z = fmaf(t.ly, c.z, fmaf(t.hy, a.z, fl.z)); fl.w = fmaf(t.ly, c.w, fmaf(t.hy, a.w, fl.w));
     }
   }
   return fl;
@@ -817,8 +886,8 @@ template <typename T>
 __global__ void __launch_bounds__(GC_THREADS, 2)
 gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
                      const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
-                     bf16* __restrict__ out, float4* __restrict__ flow_sum, int B, int I1, int Tn, int Hp, int Wp, float slope,
-                     int stage_bytes) {
+                     bf16* __restrict__ out, float4* __restrict__ flow_sum, const __grid_constant__ GcRows grows, int B, int I1, int Tn, int Hp,
+                     int Wp, float slope, int stage_bytes) {
   using namespace umma;
   extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
   __shared__ uint64_t mma_bar;
@@ -834,7 +903,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   // stage only the flow rows (incl. the halo row / column); mask / feat of the finest coarse level are interpolated
   // straight from global memory (L1 / L2 resident: one 64 B texel serves four pixels), which leaves room for the A tile
   // beside the staging area at two CTAs per SM and lets a pixel go from evaluation to its A chunks in one pass
-  gc_stage(lows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
+  gc_stage(lows, grows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
   tc_before();
   __syncthreads();
   tc_after();
@@ -842,40 +911,64 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
 
   const int b = n / Tn;
   const float t = tsteps[n - b * Tn];
-  const size_t plane = (size_t)Hp * Wp;
-  const uint8_t* img0 = imgs + ((size_t)b) * plane * 4;
-  const uint8_t* img1 = imgs + ((size_t)(I1 + b)) * plane * 4;
-  const T* f0 = feats + ((size_t)b) * plane * 4;
-  const T* f1 = feats + ((size_t)(I1 + b)) * plane * 4;
-  const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it
-  const float4* mf_img = reinterpret_cast<const float4*>(lows.p[kl]) + (size_t)n * lows.Hl[kl] * lows.Wl[kl] * lows.c4[kl];
+  const int plane = Hp * Wp;
+  const uint32_t* img32 = reinterpret_cast<const uint32_t*>(imgs);
+  const int base0 = b * plane, base1 = (I1 + b) * plane;
+  const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it (16-channel texels: c4 == 4)
+  const int mWl = lows.Wl[kl];
+  const float4* mf_img = reinterpret_cast<const float4*>(lows.p[kl]) + (size_t)n * lows.Hl[kl] * mWl * 4;
+  const Tap *mxt = lows.xt[kl], *myt = lows.yt[kl];
+  float4* fsum = flow_sum ? flow_sum + (size_t)n * plane : nullptr;
+  // Work units: region rows 0..32 with lane = column 1..32 (one image row per warp instruction: two or three cache
+  // lines per tap instead of the five a row-straddling warp touches), then the halo column (lx = 0) in two more units.
+  constexpr int GC_UNITS = GC_TW + 2;
 #pragma unroll 1
-  for (int p = threadIdx.x; p < GC_TW * GC_TW; p += GC_THREADS) {
-    const int ly = p / GC_TW, lx = p - ly * GC_TW;  // global pixel (ty0 - 1 + ly, tx0 - 1 + lx)
-    const int gy = ty0 - 1 + ly, gx = tx0 - 1 + lx;
-    float acc[32];
+  for (int unit = warp; unit < GC_UNITS; unit += GC_THREADS / 32) {
+    int ly, lx;
+    if (unit < GC_TW) { ly = unit; lx = lane + 1; }
+    else { ly = (unit - GC_TW) * 32 + lane; lx = 0; if (ly >= GC_TW) continue; }
+    const int gy = ty0 - 1 + ly, gx = tx0 - 1 + lx;  // global pixel
+    uint4 u[4];
 #pragma unroll
-    for (int c = 0; c < 32; c++) acc[c] = 0.f;
+    for (int j = 0; j < 4; j++) u[j] = make_uint4(0u, 0u, 0u, 0u);
     if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
-      float4 m[3];
       const float4 fl = gc_eval(lows, tl_sm, lx, ly);
       // the flow of blocks 0..3 at this pixel, for the final blend (tile-interior pixels: each written exactly once)
-      if (flow_sum && ly > 0 && lx > 0) flow_sum[((size_t)n * Hp + gy) * Wp + gx] = fl;
+      if (fsum && ly > 0 && lx > 0) fsum[gy * Wp + gx] = fl;
+      // mask + 8 feature channels: bilinear x2 of texel channels 4..12
+      const Tap ty = ld_tap(myt + gy), tx = ld_tap(mxt + gx);
+      const int r0 = ty.i0 * mWl, r1 = ty.i1 * mWl;
+      const float4 *p00 = mf_img + (r0 + tx.i0) * 4, *p01 = mf_img + (r0 + tx.i1) * 4, *p10 = mf_img + (r1 + tx.i0) * 4,
+                   *p11 = mf_img + (r1 + tx.i1) * 4;
+      const float w00 = ty.h * tx.h, w01 = ty.h * tx.l, w10 = ty.l * tx.h, w11 = ty.l * tx.l;
+      float mf[9];
       {
-        const Lerp L = lerp_setup(gx, gy, lows.s[kl], lows.Hl[kl], lows.Wl[kl]);
-        m[0] = lerp4(mf_img, L, 1, lows.c4[kl]); m[1] = lerp4(mf_img, L, 2, lows.c4[kl]); m[2] = lerp4(mf_img, L, 3, lows.c4[kl]);
+        const float4 a = __ldg(p00 + 1), b = __ldg(p01 + 1), c = __ldg(p10 + 1), d = __ldg(p11 + 1);
+        mf[0] = w00 * a.x + w01 * b.x + w10 * c.x + w11 * d.x; mf[1] = w00 * a.y + w01 * b.y + w10 * c.y + w11 * d.y;
+        mf[2] = w00 * a.z + w01 * b.z + w10 * c.z + w11 * d.z; mf[3] = w00 * a.w + w01 * b.w + w10 * c.w + w11 * d.w;
       }
-      gather_tap<T>(img0, img1, f0, f1, fl, m, gx, gy, Hp, Wp, acc);
-      acc[14] = t;
+      {
+        const float4 a = __ldg(p00 + 2), b = __ldg(p01 + 2), c = __ldg(p10 + 2), d = __ldg(p11 + 2);
+        mf[4] = w00 * a.x + w01 * b.x + w10 * c.x + w11 * d.x; mf[5] = w00 * a.y + w01 * b.y + w10 * c.y + w11 * d.y;
+        mf[6] = w00 * a.z + w01 * b.z + w10 * c.z + w11 * d.z; mf[7] = w00 * a.w + w01 * b.w + w10 * c.w + w11 * d.w;
+      }
+      mf[8] = w00 * __ldg(&p00[3].x) + w01 * __ldg(&p01[3].x) + w10 * __ldg(&p10[3].x) + w11 * __ldg(&p11[3].x);
+      const Bil b0 = bil_setup((float)gx + fl.x, (float)gy + fl.y, Wp, Hp, base0);
+      const Bil b1 = bil_setup((float)gx + fl.z, (float)gy + fl.w, Wp, Hp, base1);
+      float c0[3], c1[3], v0[4], v1[4];
+      sample_rgbx(img32, b0, c0);
+      sample_rgbx(img32, b1, c1);
+      sample_feat_px<T>(feats, b0, v0);
+      sample_feat_px<T>(feats, b1, v1);
+      // channel order of the block input: warped img0 (3), img1 (3), f0 (4), f1 (4), timestep, mask, feat (8), flow (4)
+      u[0] = make_uint4(pk_bf16(c0[0], c0[1]), pk_bf16(c0[2], c1[0]), pk_bf16(c1[1], c1[2]), pk_bf16(v0[0], v0[1]));
+      u[1] = make_uint4(pk_bf16(v0[2], v0[3]), pk_bf16(v1[0], v1[1]), pk_bf16(v1[2], v1[3]), pk_bf16(t, mf[0]));
+      u[2] = make_uint4(pk_bf16(mf[1], mf[2]), pk_bf16(mf[3], mf[4]), pk_bf16(mf[5], mf[6]), pk_bf16(mf[7], mf[8]));
+      u[3] = make_uint4(pk_bf16(fl.x, fl.y), pk_bf16(fl.z, fl.w), 0u, 0u);
     }
     const uint32_t pix = gc_pix_index(ly, lx);
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-      uint4 u;
-      u.x = pk_bf16(acc[8 * j], acc[8 * j + 1]); u.y = pk_bf16(acc[8 * j + 2], acc[8 * j + 3]);
-      u.z = pk_bf16(acc[8 * j + 4], acc[8 * j + 5]); u.w = pk_bf16(acc[8 * j + 6], acc[8 * j + 7]);
-      *reinterpret_cast<uint4*>(a_s + ((size_t)j * GC_CS + pix) * 16) = u;
-    }
+    for (int j = 0; j < 4; j++) *reinterpret_cast<uint4*>(a_s + ((size_t)j * GC_CS + pix) * 16) = u[j];
   }
   fence_async_smem();
   __syncthreads();
@@ -945,13 +1038,15 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
   if (Hp % TL_H || Wp % TL_W) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: padded size must be a multiple of 32");
   for (int k = 0; k < lows.n; k++)
     if (lows.s[k] < 2) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: coarse levels only");
-  const size_t un = (gc_stage_bytes(lows) + 127) & ~(size_t)127;
+  if (lows.n < 1 || lows.c4[lows.n - 1] != 4 || !lows.xt[0]) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: needs tap tables and 16-channel coarse levels");
+  GcRows grows;
+  const size_t un = (gc_stage_bytes(lows, &grows) + 127) & ~(size_t)127;
   const size_t smem = un + GC_A_BYTES + GC_W_BYTES;
   VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   if (smem > 112 * 1024) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: shared memory budget");
   const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
   gather_conv0a_kernel<bf16><<<grid, GC_THREADS, smem, s>>>(imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out,
-                                                          reinterpret_cast<float4*>(flow_sum), B, I1, T, Hp, Wp, h->slope, (int)un);
+                                                          reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, Hp, Wp, h->slope, (int)un);
   VFI_LAUNCHED(h);
   return 0;
 }
