@@ -256,8 +256,20 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     float* tdev = cv.take<float>(64);
     Tap* taps = cv.take<Tap>((size_t)5 * (Hp + Wp));
     float* flow3 = cv.take<float>((size_t)N * px * 4);  // blocks 0-3 flow per pixel (written by the fused finest gather)
+    // coarse level i = block i's lastconv output: LowPlanes (blocks 0..3, bf16 mode) or fp32 texels
     float* low[5];
-    for (int i = 0; i < 5; i++) low[i] = cv.take<float>((size_t)N * (Hp / sl[i]) * (Wp / sl[i]) * (i == 4 ? last_c : 16));
+    LowPlanes lowp[5];
+    for (int i = 0; i < 5; i++) {
+      const size_t texels = (size_t)N * (Hp / sl[i]) * (Wp / sl[i]);
+      if (bf && i < 4) {
+        lowp[i].flow = cv.take<float>(texels * 4);
+        lowp[i].mf = cv.take<bf16>(texels * 8);
+        lowp[i].f7 = cv.take<bf16>(texels);
+        low[i] = nullptr;
+      } else {
+        low[i] = cv.take<float>(texels * (i == 4 ? last_c : 16));
+      }
+    }
     uint8_t* xin = cv.take<uint8_t>(xin_e * esz);
     uint8_t* a0 = cv.take<uint8_t>(a0_e * esz);
     uint8_t* fa = cv.take<uint8_t>(f_e * esz);
@@ -302,10 +314,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       }
       const int lc = i == 4 ? last_c : 16;
       if (bf && i == 4 && h->opt_conv_v2 && Lb[10].wv2) rc = k_conv_v2_last(h, Lb[10], (const bf16*)cur, low[i], lc, N, hs / 4, wsz / 4, s);
+      else if (bf && i < 4) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, nullptr, N, hs / 4, wsz / 4, false, h->slope, s, 16, &lowp[i]);
       else if (bf) rc = k_conv_tc(h, Lb[10], (const bf16*)cur, nullptr, low[i], N, hs / 4, wsz / 4, false, h->slope, s, lc);
       else rc = k_deconv4_direct(h, Lb[10], cur, low[i], N, hs / 4, wsz / 4, false, 1, s);
       if (rc) return rc;
-      lows.push(low[i], sc, lc, Hp, Wp, taps + (size_t)i * (Hp + Wp));
+      if (bf && i < 4) lows.push_planes(lowp[i], sc, Hp, Wp, taps + (size_t)i * (Hp + Wp));
+      else lows.push(low[i], sc, lc, Hp, Wp, taps + (size_t)i * (Hp + Wp));
     }
     if ((rc = k_final_blend(h, imgs, lows, flow_pre, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s))) return rc;
   }
@@ -368,6 +382,9 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
     bf16* xp = cv.take<bf16>(nin);
     bf16* rb = cv.take<bf16>(nout);
     bf16* yb = cv.take<bf16>(nout);
+    const size_t dtex = L.kind == LK_DECONV4 ? (size_t)N * 16 * Hin * Win : 0;
+    bf16* dmf = cv.take<bf16>(dtex * 8);
+    bf16* df7 = cv.take<bf16>(dtex);
     if (pass == 0) { if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc; continue; }
     int rc;
     if ((rc = k_f32_to_act(h, x, xb, nin, true, s))) return rc;
@@ -381,7 +398,14 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
     if (s2) { if ((rc = k_plain_to_phase(h, xb, xp, N, Hin, Win, L.cin_pad, s))) return rc; in = xp; }
     if (L.kind == LK_DECONV4 && layer == 58 && h->opt_conv_v2 && L.wv2)  // channels 0-4 only; 5-15 stay as the caller set them
       return k_conv_v2_last(h, L, in, y, 16, N, Hin, Win, s);
-    if (L.kind == LK_DECONV4) return k_conv_tc(h, L, in, nullptr, y, N, Hin, Win, false, h->slope, s);
+    if (L.kind == LK_DECONV4) {  // blocks 0..3: through the production LowPlanes epilogue, then unpacked to [.,16] fp32
+      const size_t texels = (size_t)N * 4 * Hin * 4 * Win;
+      LowPlanes pl;
+      pl.flow = reinterpret_cast<float*>(yb);  // nout = texels * 52 / 4 bf16 >= 16 B per texel
+      pl.mf = dmf; pl.f7 = df7;
+      if ((rc = k_conv_tc(h, L, in, nullptr, nullptr, N, Hin, Win, false, h->slope, s, 16, &pl))) return rc;
+      return k_unpack_planes(h, pl, y, texels, s);
+    }
     const bf16* resp = nullptr;
     if (L.has_beta) {  // ResConv: residual defaults to the layer input (x), as in the net
       resp = xb;

@@ -148,8 +148,18 @@ struct __align__(16) Tap {
   int i0, i1;
   float h, l;
 };
+// bf16-mode storage of a coarse level (blocks 0..3), one array per field so a gather touches only what it needs:
+// [N,Hl,Wl] x { flow delta: 4 fp32 | mask + feat 0..6: 8 bf16 | feat 7: 1 bf16 }.  The flow stays fp32 (it is summed over
+// blocks and addresses pixels); mask / feat feed the next block's bf16 convolution input anyway.
+struct LowPlanes {
+  float* flow;
+  bf16* mf;
+  bf16* f7;
+};
 struct LowSet {
   const float* p[5];
+  const bf16* mf[5];  // non-null: the level is stored as LowPlanes (p = flow plane, c4 = 1)
+  const bf16* f7[5];
   const Tap* xt[5];  // per level (optional): taps of every padded-frame column [Wp] and row [Hp], see k_build_taps
   const Tap* yt[5];
   int s[5];
@@ -159,9 +169,14 @@ struct LowSet {
   int n;
   void push(const float* ptr, int scale, int ch, int Hp, int Wp, const Tap* taps = nullptr) {
     xt[n] = taps; yt[n] = taps ? taps + Wp : nullptr;
+    mf[n] = nullptr; f7[n] = nullptr;
     p[n] = ptr; s[n] = scale; c4[n] = ch / 4; Hl[n] = Hp / scale; Wl[n] = Wp / scale;
     rs[n] = 1.0f / (float)scale; fs[n] = (float)scale;
     n++;
+  }
+  void push_planes(const LowPlanes& pl, int scale, int Hp, int Wp, const Tap* taps = nullptr) {
+    push(pl.flow, scale, 4, Hp, Wp, taps);
+    mf[n - 1] = pl.mf; f7[n - 1] = pl.f7;
   }
 };
 // tap tables of `n` levels: level k at out + k * (Wp + Hp), columns first
@@ -197,8 +212,10 @@ int tc_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch); 
 // conv (mode 0/1) : in plain (stride 1) or phase planes (stride 2) bf16, out bf16 plain or phase (out_phase)
 // lastconv (deconv): in plain bf16, out = fp32 low [N,4Hin,4Win,low_c]: low_c = 16 (13 channels) or 8 (the final
 // block: only flow delta + mask, 5 channels, are consumed downstream)
+// planes (lastconv of blocks 0..3, bf16 mode): write the level as LowPlanes instead of fp32 texels
 int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
-              int Win, bool out_phase, float slope, cudaStream_t s, int low_c = 16);
+              int Win, bool out_phase, float slope, cudaStream_t s, int low_c = 16, const LowPlanes* planes = nullptr);
+int k_unpack_planes(vfi_handle* h, const LowPlanes& pl, float* out16, size_t texels, cudaStream_t s);
 
 // ---- conv_v2.cu ---------------------------------------------------------------------------
 bool v2_supported(const Layer& L);

@@ -30,6 +30,8 @@ struct TcParams {
   uint32_t sbo16, layout_type;
   int epi_mode;  // 0 conv->plain bf16, 1 conv->phase-plane bf16, 2 lastconv->pixel-shuffled fp32 low13
   int cout, act;
+  bf16* low_mf;  // epi_mode 2, non-null: LowPlanes output (out = flow plane)
+  bf16* low_f7;
   int low_c;     // epi_mode 2: floats per output texel, 16 (13 channels) or 8 (5 channels: flow delta + mask)
   float slope;
   const float* bias;
@@ -255,7 +257,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int H4 = 4 * P.Ho, W4 = 4 * P.Wo;
         for (int ph = 0; ph < 4; ph++) {
           const int p = ph >> 1, q = ph & 1;
-          if (P.low_c == 16) {
+          if (P.low_mf) {
+            // bf16 planes: the two texels (jj = 0, 1) of a row pair up into full 32-byte sectors of the flow and the
+            // mask/feat plane
+            float v[64];
+#pragma unroll
+            for (int c = 0; c < 64; c += 16) tmem_ld16(taddr + ph * 64 + c, v + c);
+            if (valid) {
+#pragma unroll
+              for (int i = 0; i < 2; i++) {
+                float o[2][13];
+#pragma unroll
+                for (int jj = 0; jj < 2; jj++)
+#pragma unroll
+                  for (int cc = 0; cc < 13; cc++) o[jj][cc] = v[cc * 4 + 2 * i + jj] + __ldg(P.bias + cc * 4 + 2 * i + jj);
+                const size_t t0 = ((size_t)n * H4 + 4 * y + 2 * p + i) * W4 + 4 * x + 2 * q;
+                st_v8f(ob + t0 * 4, make_float4(o[0][0], o[0][1], o[0][2], o[0][3]), make_float4(o[1][0], o[1][1], o[1][2], o[1][3]));
+                uint4 m0, m1;
+                m0.x = pack_bf16(o[0][4], o[0][5]); m0.y = pack_bf16(o[0][6], o[0][7]); m0.z = pack_bf16(o[0][8], o[0][9]); m0.w = pack_bf16(o[0][10], o[0][11]);
+                m1.x = pack_bf16(o[1][4], o[1][5]); m1.y = pack_bf16(o[1][6], o[1][7]); m1.z = pack_bf16(o[1][8], o[1][9]); m1.w = pack_bf16(o[1][10], o[1][11]);
+                st_v8(P.low_mf + t0 * 8, m0, m1);
+                *reinterpret_cast<uint32_t*>(P.low_f7 + t0) = pack_bf16(o[0][12], o[1][12]);
+              }
+            }
+          } else if (P.low_c == 16) {
             float v[64];
 #pragma unroll
             for (int c = 0; c < 64; c += 16) tmem_ld16(taddr + ph * 64 + c, v + c);
@@ -481,7 +506,7 @@ static int make_tmap_w(vfi_handle* h, CUtensorMap* out, const bf16* base, int cb
 }
 
 int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
-              int Win, bool out_phase, float slope, cudaStream_t s, int low_c) {
+              int Win, bool out_phase, float slope, cudaStream_t s, int low_c, const LowPlanes* planes) {
   ProfScope _ps(h, PC_CONV_TC, s);
   TcParams P;
   memset(&P, 0, sizeof(P));
@@ -527,7 +552,10 @@ int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residua
   P.beta = L.has_beta ? L.beta : nullptr;
   P.res = residual;
   if (P.beta && !residual) VFI_FAIL(h, VFI_E_ARG, "ResConv needs residual");
-  P.out = out;
+  P.out = planes ? (void*)planes->flow : out;
+  P.low_mf = planes ? planes->mf : nullptr;
+  P.low_f7 = planes ? planes->f7 : nullptr;
+  if (planes && (L.kind != LK_DECONV4 || low_c != 16)) VFI_FAIL(h, VFI_E_ARG, "plane output is for the 13-channel lastconv");
   memcpy(P.steps, L.steps, sizeof(TcStep) * L.nsteps);
 
   CUtensorMap tmA, tmB;

@@ -4,6 +4,7 @@
 // Reference semantics: SURVEY.md Appendix A.2 (IFNet.forward / IFBlock.forward / warp()).
 #include "common.cuh"
 #include "umma.cuh"
+#include <type_traits>
 
 // ------------------------------------------------------------------------------------------
 // small typed load/store helpers
@@ -266,10 +267,51 @@ int k_build_taps(vfi_handle* h, Tap* out, const int* scales, int n, int Hp, int 
   return 0;
 }
 
+// mask + feat 0..7 of texel `idx` of a level stored as LowPlanes (bf16 -> fp32 is a shift)
+__device__ __forceinline__ void mf9_load(const bf16* __restrict__ mf, const bf16* __restrict__ f7, int idx, float* v) {
+  const uint4 a = __ldg(reinterpret_cast<const uint4*>(mf) + idx);
+  const uint32_t h = __ldg(reinterpret_cast<const unsigned short*>(f7) + idx);
+  v[0] = __uint_as_float(a.x << 16); v[1] = __uint_as_float(a.x & 0xffff0000u);
+  v[2] = __uint_as_float(a.y << 16); v[3] = __uint_as_float(a.y & 0xffff0000u);
+  v[4] = __uint_as_float(a.z << 16); v[5] = __uint_as_float(a.z & 0xffff0000u);
+  v[6] = __uint_as_float(a.w << 16); v[7] = __uint_as_float(a.w & 0xffff0000u);
+  v[8] = __uint_as_float(h << 16);
+}
+// the MF = 1 part of state_at for a LowPlanes level: m[0] = (mask, f0, f1, f2), m[1] = (f3..f6), m[2].x = f7
+__device__ __forceinline__ void mf9_lerp(const bf16* __restrict__ mf, const bf16* __restrict__ f7, int tb, const Lerp& L,
+                                         float4* m) {
+  float a[9], b[9], c[9], d[9], r[9];
+  mf9_load(mf, f7, tb + L.o00, a); mf9_load(mf, f7, tb + L.o01, b);
+  mf9_load(mf, f7, tb + L.o10, c); mf9_load(mf, f7, tb + L.o11, d);
+#pragma unroll
+  for (int i = 0; i < 9; i++) r[i] = L.hy * (L.hx * a[i] + L.lx * b[i]) + L.ly * (L.hx * c[i] + L.lx * d[i]);
+  m[0] = make_float4(r[0], r[1], r[2], r[3]); m[1] = make_float4(r[4], r[5], r[6], r[7]);
+  m[2] = make_float4(r[8], 0.f, 0.f, 0.f);
+}
+__global__ void unpack_planes_kernel(const float4* __restrict__ flow, const bf16* __restrict__ mf, const bf16* __restrict__ f7,
+                                     float4* __restrict__ out, size_t texels) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= texels) return;
+  float v[9];
+  mf9_load(mf, f7, (int)i, v);
+  out[4 * i] = flow[i];
+  out[4 * i + 1] = make_float4(v[0], v[1], v[2], v[3]);
+  out[4 * i + 2] = make_float4(v[4], v[5], v[6], v[7]);
+  out[4 * i + 3] = make_float4(v[8], 0.f, 0.f, 0.f);
+}
+// test hook: a LowPlanes level as the fp32 [texels, 16] layout of the other precision
+int k_unpack_planes(vfi_handle* h, const LowPlanes& pl, float* out16, size_t texels, cudaStream_t s) {
+  ProfScope _ps(h, PC_MISC, s);
+  unpack_planes_kernel<<<cdiv(texels, 256), 256, 0, s>>>(reinterpret_cast<const float4*>(pl.flow), pl.mf, pl.f7,
+                                                         reinterpret_cast<float4*>(out16), texels);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
 // flow after the blocks in `lows` at full-resolution pixel (x,y) of item n: flow = flow + up(low_k)[:4] * s_k, in
 // block order.  MF = 1: also (mask, feat) = up(low_last)[4:13] in m[0..2];  MF = 2: mask only, in m[0].x.
 // A low at scale 1 (the last block at scale=1.0) is read directly: interpolate(x1) is the identity.
-template <int MF>
+template <int MF, bool PL = false>
 __device__ __forceinline__ float4 state_at(const LowSet& lows, int n, int x, int y, int Hp, int Wp, float4* m) {
   float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -289,7 +331,10 @@ __device__ __forceinline__ float4 state_at(const LowSet& lows, int n, int x, int
         const float4 r = lerp4(img, L, 0, c4);
         const float fs = (float)sk;
         fl.x += r.x * fs; fl.y += r.y * fs; fl.z += r.z * fs; fl.w += r.w * fs;
-        if (MF == 1 && last) { m[0] = lerp4(img, L, 1, c4); m[1] = lerp4(img, L, 2, c4); m[2] = lerp4(img, L, 3, c4); }
+        if (MF == 1 && last) {
+          if (PL) mf9_lerp(lows.mf[k], lows.f7[k], n * Hl * Wl, L, m);
+          else { m[0] = lerp4(img, L, 1, c4); m[1] = lerp4(img, L, 2, c4); m[2] = lerp4(img, L, 3, c4); }
+        }
         if (MF == 2 && last) m[0] = lerp4(img, L, 1, c4);
       }
     }
@@ -346,7 +391,7 @@ __global__ void gather_kernel(const uint8_t* __restrict__ imgs, const T* __restr
         acc[10] += v[0]; acc[11] += v[1]; acc[12] += v[2]; acc[13] += v[3];
       } else {
         float4 m[3];
-        const float4 fl = state_at<1>(lows, n, x, y, Hp, Wp, m);
+        const float4 fl = state_at<1, std::is_same<T, bf16>::value>(lows, n, x, y, Hp, Wp, m);
         const float4 s1 = m[0], s2 = m[1], s3 = m[2];
         Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
         Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
@@ -414,7 +459,7 @@ static size_t tl_smem_bytes(const LowSet& lows, int mf) {
 }
 // Stage 1.  Thread t owns tile column t%32 (its x taps are computed once per level) and rows t/32, t/32+8, ...;
 // warp k also fills level k's row table.
-template <int MF, int NT = TL_THREADS>
+template <int MF, int NT = TL_THREADS, bool PL = false>
 __device__ __forceinline__ void tile_stage(const LowSet& L, int n, int tx0, int ty0, int Hp, int Wp, float4* sm) {
   RowTap* ytab = reinterpret_cast<RowTap*>(sm);
   const int xl = threadIdx.x & (TL_W - 1), row0 = threadIdx.x >> 5;
@@ -444,6 +489,20 @@ __device__ __forceinline__ void tile_stage(const LowSet& L, int n, int tx0, int 
         const float4* pa = img + (size_t)(ry * Wl + x0) * c4;
         const float4* pb = img + (size_t)(ry * Wl + x1) * c4;
         float4* dst = sm + off + row * nv * TL_W + xl;
+        if (PL && MF == 1 && k == L.n - 1) {  // LowPlanes level: flow from its fp32 plane, mask / feat from the bf16 ones
+          const float4 a = __ldg(pa), b = __ldg(pb);
+          dst[0] = make_float4(hx * a.x + lx * b.x, hx * a.y + lx * b.y, hx * a.z + lx * b.z, hx * a.w + lx * b.w);
+          const int tb = (n * Hl + ry) * Wl;
+          float u[9], w[9];
+          mf9_load(L.mf[k], L.f7[k], tb + x0, u);
+          mf9_load(L.mf[k], L.f7[k], tb + x1, w);
+#pragma unroll
+          for (int i = 0; i < 9; i++) u[i] = hx * u[i] + lx * w[i];
+          dst[TL_W] = make_float4(u[0], u[1], u[2], u[3]);
+          dst[2 * TL_W] = make_float4(u[4], u[5], u[6], u[7]);
+          dst[3 * TL_W] = make_float4(u[8], 0.f, 0.f, 0.f);
+          continue;
+        }
 #pragma unroll
         for (int v = 0; v < 4; v++) {
           if (v < nv) {
@@ -530,7 +589,7 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
                                                                  int phase) {
   extern __shared__ float4 tl_sm[];
   const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
-  tile_stage<1>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
+  tile_stage<1, TL_THREADS, std::is_same<T, bf16>::value>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
   __syncthreads();
   const int b = n / Tn;
   const float t = tsteps[n - b * Tn];
@@ -916,7 +975,8 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   const int base0 = b * plane, base1 = (I1 + b) * plane;
   const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it (16-channel texels: c4 == 4)
   const int mWl = lows.Wl[kl];
-  const float4* mf_img = reinterpret_cast<const float4*>(lows.p[kl]) + (size_t)n * lows.Hl[kl] * mWl * 4;
+  const bf16 *mfp = lows.mf[kl], *f7p = lows.f7[kl];
+  const int mtb = n * lows.Hl[kl] * mWl;
   const Tap *mxt = lows.xt[kl], *myt = lows.yt[kl];
   float4* fsum = flow_sum ? flow_sum + (size_t)n * plane : nullptr;
   // Work units: region rows 0..32 with lane = column 1..32 (one image row per warp instruction: two or three cache
@@ -937,22 +997,20 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
       if (fsum && ly > 0 && lx > 0) fsum[gy * Wp + gx] = fl;
       // mask + 8 feature channels: bilinear x2 of texel channels 4..12
       const Tap ty = ld_tap(myt + gy), tx = ld_tap(mxt + gx);
-      const int r0 = ty.i0 * mWl, r1 = ty.i1 * mWl;
-      const float4 *p00 = mf_img + (r0 + tx.i0) * 4, *p01 = mf_img + (r0 + tx.i1) * 4, *p10 = mf_img + (r1 + tx.i0) * 4,
-                   *p11 = mf_img + (r1 + tx.i1) * 4;
+      const int r0 = mtb + ty.i0 * mWl, r1 = mtb + ty.i1 * mWl;
       const float w00 = ty.h * tx.h, w01 = ty.h * tx.l, w10 = ty.l * tx.h, w11 = ty.l * tx.l;
       float mf[9];
       {
-        const float4 a = __ldg(p00 + 1), b = __ldg(p01 + 1), c = __ldg(p10 + 1), d = __ldg(p11 + 1);
-        mf[0] = w00 * a.x + w01 * b.x + w10 * c.x + w11 * d.x; mf[1] = w00 * a.y + w01 * b.y + w10 * c.y + w11 * d.y;
-        mf[2] = w00 * a.z + w01 * b.z + w10 * c.z + w11 * d.z; mf[3] = w00 * a.w + w01 * b.w + w10 * c.w + w11 * d.w;
+        float a[9], c[9];
+        mf9_load(mfp, f7p, r0 + tx.i0, a);
+        mf9_load(mfp, f7p, r0 + tx.i1, c);
+#pragma unroll
+        for (int i = 0; i < 9; i++) mf[i] = w00 * a[i] + w01 * c[i];
+        mf9_load(mfp, f7p, r1 + tx.i0, a);
+        mf9_load(mfp, f7p, r1 + tx.i1, c);
+#pragma unroll
+        for (int i = 0; i < 9; i++) mf[i] += w10 * a[i] + w11 * c[i];
       }
-      {
-        const float4 a = __ldg(p00 + 2), b = __ldg(p01 + 2), c = __ldg(p10 + 2), d = __ldg(p11 + 2);
-        mf[4] = w00 * a.x + w01 * b.x + w10 * c.x + w11 * d.x; mf[5] = w00 * a.y + w01 * b.y + w10 * c.y + w11 * d.y;
-        mf[6] = w00 * a.z + w01 * b.z + w10 * c.z + w11 * d.z; mf[7] = w00 * a.w + w01 * b.w + w10 * c.w + w11 * d.w;
-      }
-      mf[8] = w00 * __ldg(&p00[3].x) + w01 * __ldg(&p01[3].x) + w10 * __ldg(&p10[3].x) + w11 * __ldg(&p11[3].x);
       const Bil b0 = bil_setup((float)gx + fl.x, (float)gy + fl.y, Wp, Hp, base0);
       const Bil b1 = bil_setup((float)gx + fl.z, (float)gy + fl.w, Wp, Hp, base1);
       float c0[3], c1[3], v0[4], v1[4];
@@ -1038,7 +1096,7 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
   if (Hp % TL_H || Wp % TL_W) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: padded size must be a multiple of 32");
   for (int k = 0; k < lows.n; k++)
     if (lows.s[k] < 2) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: coarse levels only");
-  if (lows.n < 1 || lows.c4[lows.n - 1] != 4 || !lows.xt[0]) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: needs tap tables and 16-channel coarse levels");
+  if (lows.n < 1 || !lows.mf[lows.n - 1] || !lows.xt[0]) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: needs tap tables and plane-stored coarse levels");
   GcRows grows;
   const size_t un = (gc_stage_bytes(lows, &grows) + 127) & ~(size_t)127;
   const size_t smem = un + GC_A_BYTES + GC_W_BYTES;
