@@ -242,7 +242,11 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     f_e = std::max(f_e, (size_t)N * (hs / 4) * (wsz / 4) * c);
   }
   // the final block's lastconv output keeps only flow delta + mask (8-float texels) on the tcgen05 path
-  const int last_c = bf ? 8 : 16;
+  // ... and when the finest block's gather is the fused kernel (which leaves the coarser blocks' flow summed per pixel for
+  // the blend), as fp16: 16-byte texels
+  const Layer* Lf = &h->layers[4 + 11 * 4];
+  const bool fused = bf && inv == 1 && h->opt_fuse_gather && h->opt_conv_v2 && Lf[0].ws2 && Lf[0].cout == 16;
+  const int last_c = !bf ? 16 : (fused && Lf[10].wv2) ? 4 : 8;
   const size_t px = (size_t)Hp * Wp;
   Carve cv{nullptr, 0};
   for (int pass = 0; pass < 2; pass++) {
@@ -299,7 +303,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     for (int i = 0; i < 5; i++) {
       const int sc = sl[i], hs = Hp / sc, wsz = Wp / sc;
       const Layer* Lb = &h->layers[4 + 11 * i];
-      if (bf && sc == 1 && i > 0 && h->opt_fuse_gather && h->opt_conv_v2 && Lb[0].ws2 && Lb[0].cout == 16) {
+      if (fused && i == 4) {
         if ((rc = k_gather_conv0a(h, Lb[0], imgs, feats, lows, tdev, (bf16*)a0, flow3, B, I1, T, Hp, Wp, s))) return rc;
         flow_pre = flow3;
       } else {

@@ -19,6 +19,7 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 struct V2Params {
   const bf16* in;
@@ -414,6 +415,24 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
 #pragma unroll
         for (int i = 0; i < 2; i++) {
           float* row = P.low_out + (((size_t)n * H4 + 4 * y + 2 * pr + i) * W4 + 4 * x) * lc;
+          if (lc == 4) {
+            // fp16 texels {flow delta x4, mask, 0, 0, 0} (16 B): the row's four texels are two full sectors
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+              uint4 t[2];
+#pragma unroll
+              for (int jj = 0; jj < 2; jj++) {
+                const int c0 = q * 20 + (2 * i + jj) * 5;
+                const __half2 a = __floats2half2_rn(v[c0] + bias_r[c0], v[c0 + 1] + bias_r[c0 + 1]);
+                const __half2 b = __floats2half2_rn(v[c0 + 2] + bias_r[c0 + 2], v[c0 + 3] + bias_r[c0 + 3]);
+                const __half2 c = __floats2half2_rn(v[c0 + 4] + bias_r[c0 + 4], 0.f);
+                t[jj] = make_uint4(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b),
+                                   *reinterpret_cast<const uint32_t*>(&c), 0u);
+              }
+              st_v8(row + q * 8, t[0], t[1]);
+            }
+            continue;
+          }
 #pragma unroll
           for (int q = 0; q < 2; q++)
 #pragma unroll

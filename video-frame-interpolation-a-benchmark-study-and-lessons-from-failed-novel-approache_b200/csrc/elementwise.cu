@@ -4,6 +4,7 @@
 // Reference semantics: SURVEY.md Appendix A.2 (IFNet.forward / IFBlock.forward / warp()).
 #include "common.cuh"
 #include "umma.cuh"
+#include <cuda_fp16.h>
 #include <type_traits>
 
 // ------------------------------------------------------------------------------------------
@@ -698,8 +699,9 @@ __device__ __forceinline__ uint8_t quant_u8(float v) {
   return (uint8_t)(int)v;  // truncation, as numpy astype(uint8)
 }
 // PRE: the flow of all coarser blocks was already summed per pixel by the finest block's gather (flow_pre); `lows` then
-// holds only the last block's full-resolution output and nothing is staged.
-template <bool PRE>
+// holds only the last block's full-resolution output and nothing is staged.  PRE = 1: that output is fp32 texels
+// {flow delta x4, mask, -, -, -}; PRE = 2: the same five values as fp16 (16-byte texels).
+template <int PRE>
 __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* __restrict__ imgs,
                                                                  const __grid_constant__ LowSet lows,
                                                                  const float4* __restrict__ flow_pre,
@@ -730,10 +732,24 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
     if (y >= H || x >= W) continue;
     float o[3];
     float4 m4;
-    float4 fl = tile_eval<2>(lows, tl_sm, n, x, y, xl, yl, &m4);
+    float4 fl;
     if (PRE) {
-      const float4 f3 = __ldg(flow_pre + ((size_t)n * Hp + y) * Wp + x);
+      const size_t pix = ((size_t)n * Hp + y) * Wp + x;
+      const float4 f3 = __ldg(flow_pre + pix);
+      if (PRE == 2) {
+        const uint4 tq = __ldg(reinterpret_cast<const uint4*>(lows.p[0]) + pix);
+        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&tq.x));
+        const float2 c = __half22float2(*reinterpret_cast<const __half2*>(&tq.y));
+        fl = make_float4(a.x, a.y, c.x, c.y);
+        m4.x = __low2float(*reinterpret_cast<const __half2*>(&tq.z));
+      } else {
+        const float4* px = reinterpret_cast<const float4*>(lows.p[0]) + 2 * pix;
+        fl = __ldg(px);
+        m4.x = __ldg(&px[1].x);
+      }
       fl.x += f3.x; fl.y += f3.y; fl.z += f3.z; fl.w += f3.w;
+    } else {
+      fl = tile_eval<2>(lows, tl_sm, n, x, y, xl, yl, &m4);
     }
     blend_px(img0, img1, fl, m4.x, x, y, Hp, Wp, o);
     const size_t opix = ((size_t)n * H + y) * W + x;
@@ -775,10 +791,15 @@ int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const 
     LowSet last;
     memset(&last, 0, sizeof(last));
     last.push(lows.p[lows.n - 1], 1, lows.c4[lows.n - 1] * 4, Hp, Wp);
-    final_blend_kernel<true><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
-                                                         out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp);
+    if (lows.c4[lows.n - 1] == 1)  // fp16 texels
+      final_blend_kernel<2><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
+                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp);
+    else if (lows.c4[lows.n - 1] == 2)
+      final_blend_kernel<1><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
+                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp);
+    else VFI_FAIL(h, VFI_E_ARG, "final blend: pre-summed flow needs the compact last level");
   } else {
-    final_blend_kernel<false><<<grid, TL_THREADS, smem, s>>>(imgs, lows, nullptr, hud, tsteps_dev, out, out_f32, flow_out, B,
+    final_blend_kernel<0><<<grid, TL_THREADS, smem, s>>>(imgs, lows, nullptr, hud, tsteps_dev, out, out_f32, flow_out, B,
                                                              I1, T, H, W, Hp, Wp);
   }
   VFI_LAUNCHED(h);
