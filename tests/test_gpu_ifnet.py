@@ -157,7 +157,7 @@ def test_conv_v2_halo_tile_kernel(engine, weights, layer, Hin, Win):
     assert (y2 - y1).abs().max().item() <= 1.0e-2 * scale          # same operands, different accumulation order + bf16 store
 
 
-@pytest.mark.parametrize("layer", [15, 37, 38, 48, 49])
+@pytest.mark.parametrize("layer", [15, 26, 27, 37, 38, 48, 49])
 @pytest.mark.parametrize("Hin,Win", [(26, 44), (64, 96), (136, 240)])
 def test_conv_s2_plane_window_kernel(engine, weights, layer, Hin, Win):
     """csrc/conv_s2.cu (stride-2 convs: resident weights, one 17 x (8KW+1) window per phase plane per tile) against

@@ -236,8 +236,8 @@ __global__ void __launch_bounds__(S2_THREADS, 1) conv_s2_kernel(const __grid_con
 // =============================================================================================
 bool s2_supported(const Layer& L) {
   if (L.kind != LK_CONV3 || L.stride != 2 || L.cin_pad < 16) return false;
-  return (L.cin_pad == 32 && (L.cout == 16 || L.cout == 32)) || (L.cin_pad == 16 && L.cout == 32) ||
-         (L.cin_pad == 32 && L.cout == 64);
+  return (L.cin_pad == 32 && (L.cout == 16 || L.cout == 32 || L.cout == 48 || L.cout == 64)) ||
+         (L.cin_pad == 16 && L.cout == 32) || (L.cin_pad == 48 && L.cout == 96);
 }
 
 // Conv2d weights [Co][Ci][3][3] -> resident smem image [tap][Cin_pad/8][Co][8] bf16 (padded input channels are zero)
@@ -290,7 +290,9 @@ int k_conv_s2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   // KW chosen so that 4 stages (3 tiles of cp.async in flight per producer thread) fit: these layers are HBM-bound
   if (L.cin_pad == 32 && L.cout == 16) return launch_s2<32, 16, 1>(h, P, s);
   if (L.cin_pad == 32 && L.cout == 32) return launch_s2<32, 32, 1>(h, P, s);
+  if (L.cin_pad == 32 && L.cout == 48) return launch_s2<32, 48, 1>(h, P, s);
   if (L.cin_pad == 32 && L.cout == 64) return launch_s2<32, 64, 1>(h, P, s);
+  if (L.cin_pad == 48 && L.cout == 96) return launch_s2<48, 96, 1>(h, P, s);
   if (L.cin_pad == 16 && L.cout == 32) return launch_s2<16, 32, 2>(h, P, s);
   VFI_FAIL(h, VFI_E_ARG, "conv_s2: no instance for Cin=%d Cout=%d", L.cin_pad, L.cout);
 }

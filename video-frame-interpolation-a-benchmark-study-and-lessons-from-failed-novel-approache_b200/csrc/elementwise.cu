@@ -643,12 +643,20 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
   }
 }
 
+static int launch_gather_s2(vfi_handle* h, const uint8_t* imgs, const bf16* feats, const LowSet& lows, const float* tsteps_dev,
+                            bf16* out, int B, int I1, int T, int Hp, int Wp, bool phase, cudaStream_t s);
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
              void* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s) {
   ProfScope _ps(h, PC_GATHER, s);
   size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
   int grid = cdiv(total, 128);
   const bool first = lows.n == 0;
+  if (!first && bf && s_int == 2 && Hp % TL_H == 0 && Wp % TL_W == 0 && lows.mf[lows.n - 1] && lows.xt[0] &&
+      lows.s[lows.n - 1] >= 4) {
+    bool coarse = true;  // flat staging pre-supposes every level is coarser than the frame
+    for (int k = 0; k < lows.n; k++) coarse = coarse && lows.s[k] > 1;
+    if (coarse) return launch_gather_s2(h, imgs, (const bf16*)feats, lows, tsteps_dev, (bf16*)out, B, I1, T, Hp, Wp, phase, s);
+  }
   if (!first && s_int <= 2 && Hp % TL_H == 0 && Wp % TL_W == 0) {
     const size_t smem = tl_smem_bytes(lows, 1);
     const dim3 tgrid(Wp / TL_W, Hp / TL_H, B * T);
@@ -895,14 +903,14 @@ __device__ __forceinline__ uint32_t gc_pix_index(int ly, int lx) {
   return (uint32_t)((py * 2 + px) * GC_PLANE + pr * GC_PW + pc);
 }
 struct GcRows { int start[6]; };  // first staged row of each level; start[n] = all rows
-static size_t gc_stage_bytes(const LowSet& lows, GcRows* R) {
+static size_t gc_stage_bytes(const LowSet& lows, GcRows* R, int tw = GC_TW) {
   int rows = 0;
   for (int k = 0; k < 5; k++) {
     R->start[k] = rows;
     if (k < lows.n) rows += tl_rows(lows.s[k]);
   }
   R->start[5] = rows;
-  return ((size_t)GC_TAB + (size_t)rows * GC_TW) * sizeof(float4);
+  return ((size_t)5 * tw + (size_t)rows * tw) * sizeof(float4);
 }
 __device__ __forceinline__ Tap ld_tap(const Tap* p) {
   const int4 v = __ldg(reinterpret_cast<const int4*>(p));
@@ -914,23 +922,25 @@ __device__ __forceinline__ Tap ld_tap(const Tap* p) {
 // to the region's columns and pre-multiplied by the level's flow scale (a power of two: exact).  The staged rows of all
 // levels are one flat array of 33-float4 rows, so entry e is simply staged row e / 33, column e % 33; the x taps come
 // from the per-call tables (k_build_taps), the level of a row from the host-computed row starts.
-__device__ __forceinline__ void gc_stage(const LowSet& L, const GcRows& R, int n, int ox, int oy, int Hp, int Wp, float4* sm) {
+template <int TW, int NT>
+__device__ __forceinline__ void flat_stage(const LowSet& L, const GcRows& R, int n, int ox, int oy, int Hp, int Wp, float4* sm) {
+  constexpr int GC_TW_ = TW, GC_TAB_ = 5 * TW, GC_THREADS_ = NT;
   RowTap* ytab = reinterpret_cast<RowTap*>(sm);
   const float oyf = (float)max(oy, 0) + 0.5f;
-  for (int e = threadIdx.x; e < L.n * GC_TW; e += GC_THREADS) {
-    const int k = e / GC_TW, yl = e - k * GC_TW;
+  for (int e = threadIdx.x; e < L.n * GC_TW_; e += GC_THREADS_) {
+    const int k = e / GC_TW_, yl = e - k * GC_TW_;
     const Tap ty = ld_tap(L.yt[k] + min(max(oy + yl, 0), Hp - 1));
     const int r_lo = (int)fmaxf(L.rs[k] * oyf - 0.5f, 0.f);
-    const int off = GC_TAB + R.start[k] * GC_TW;
+    const int off = GC_TAB_ + R.start[k] * GC_TW_;
     RowTap t;
-    t.o0 = (off + (ty.i0 - r_lo) * GC_TW) * 16; t.o1 = (off + (ty.i1 - r_lo) * GC_TW) * 16;  // byte offsets
+    t.o0 = (off + (ty.i0 - r_lo) * GC_TW_) * 16; t.o1 = (off + (ty.i1 - r_lo) * GC_TW_) * 16;  // byte offsets
     t.hy = ty.h; t.ly = ty.l;
     ytab[e] = t;
   }
-  const int total = R.start[5] * GC_TW;
+  const int total = R.start[5] * GC_TW_;
 #pragma unroll 2
-  for (int e = threadIdx.x; e < total; e += GC_THREADS) {
-    const int u = e / GC_TW, col = e - u * GC_TW;
+  for (int e = threadIdx.x; e < total; e += GC_THREADS_) {
+    const int u = e / GC_TW_, col = e - u * GC_TW_;
     int k = 0;
 #pragma unroll
     for (int j = 1; j < 5; j++) k += (j < L.n && u >= R.start[j]) ? 1 : 0;
@@ -941,18 +951,19 @@ __device__ __forceinline__ void gc_stage(const LowSet& L, const GcRows& R, int n
     const float4* row = reinterpret_cast<const float4*>(L.p[k]) + ((size_t)n * Hl + ry) * Wl * c4;
     const float4 a = __ldg(row + tx.i0 * c4), b = __ldg(row + tx.i1 * c4);
     const float fs = L.fs[k];
-    sm[GC_TAB + e] = make_float4((tx.h * a.x + tx.l * b.x) * fs, (tx.h * a.y + tx.l * b.y) * fs,
+    sm[GC_TAB_ + e] = make_float4((tx.h * a.x + tx.l * b.x) * fs, (tx.h * a.y + tx.l * b.y) * fs,
                                  (tx.h * a.z + tx.l * b.z) * fs, (tx.h * a.w + tx.l * b.w) * fs);
   }
 }
 // flow at region-local pixel (lx, ly) from the staged rows (every level of a finest block's LowSet has s > 1)
-__device__ __forceinline__ float4 gc_eval(const LowSet& L, const float4* sm, int lx, int ly) {
+template <int TW>
+__device__ __forceinline__ float4 flat_eval(const LowSet& L, const float4* sm, int lx, int ly) {
   const RowTap* ytab = reinterpret_cast<const RowTap*>(sm);
   float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int k = 0; k < 5; k++) {
     if (k < L.n) {
-      const RowTap t = ytab[k * GC_TW + ly];
+      const RowTap t = ytab[k * TW + ly];
       const char* col = reinterpret_cast<const char*>(sm + lx);
       const float4 a = *reinterpret_cast<const float4*>(col + t.o0), c = *reinterpret_cast<const float4*>(col + t.o1);
       fl.x = fmaf(t.ly, c.x, fmaf(t.hy, a.x, fl.x)); fl.y = fmaf(t.ly, c.y, fmaf(t.hy, a.y, fl.y));
@@ -983,7 +994,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   // stage only the flow rows (incl. the halo row / column); mask / feat of the finest coarse level are interpolated
   // straight from global memory (L1 / L2 resident: one 64 B texel serves four pixels), which leaves room for the A tile
   // beside the staging area at two CTAs per SM and lets a pixel go from evaluation to its A chunks in one pass
-  gc_stage(lows, grows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
+  flat_stage<GC_TW, GC_THREADS>(lows, grows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
   tc_before();
   __syncthreads();
   tc_after();
@@ -1013,7 +1024,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
 #pragma unroll
     for (int j = 0; j < 4; j++) u[j] = make_uint4(0u, 0u, 0u, 0u);
     if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
-      const float4 fl = gc_eval(lows, tl_sm, lx, ly);
+      const float4 fl = flat_eval<GC_TW>(lows, tl_sm, lx, ly);
       // the flow of blocks 0..3 at this pixel, for the final blend (tile-interior pixels: each written exactly once)
       if (fsum && ly > 0 && lx > 0) fsum[gy * Wp + gx] = fl;
       // mask + 8 feature channels: bilinear x2 of texel channels 4..12
@@ -1126,6 +1137,95 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
   const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
   gather_conv0a_kernel<bf16><<<grid, GC_THREADS, smem, s>>>(imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out,
                                                           reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, Hp, Wp, h->slope, (int)un);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Block-input gather at s = 2 (bf16 mode: the coarse levels are LowPlanes).  Same result as gather_tile_kernel<bf16, 2>,
+// restructured around the L1 / issue limits its profile showed:
+//   * the flow rows are staged by flat_stage (per-call tap tables, levels in one flat array, pre-scaled);
+//   * mask / feat are linear in the coarse texels, so the mean over the 2 x 2 full-resolution positions is ONE bilinear
+//     fetch with the mean weights (both positions of a pair share their source cell for every level scale >= 4) taken
+//     straight from the bf16 planes -- they are neither staged nor evaluated four times;
+//   * 32-bit pixel indexing (one IMAD.WIDE per tap), 80 registers: three CTAs per SM.
+#define G2_THREADS 256
+__global__ void __launch_bounds__(G2_THREADS, 3)
+gather_s2_kernel(const uint8_t* __restrict__ imgs, const bf16* __restrict__ feats, const __grid_constant__ LowSet lows,
+                 const __grid_constant__ GcRows grows, const float* __restrict__ tsteps, bf16* __restrict__ out, int B, int I1,
+                 int Tn, int Hp, int Wp, int phase) {
+  extern __shared__ float4 tl_sm[];
+  const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
+  flat_stage<TL_W, G2_THREADS>(lows, grows, n, tx0, ty0, Hp, Wp, tl_sm);
+  __syncthreads();
+  const int b = n / Tn;
+  const float t = tsteps[n - b * Tn];
+  const int plane = Hp * Wp;
+  const uint32_t* img32 = reinterpret_cast<const uint32_t*>(imgs);
+  const int base0 = b * plane, base1 = (I1 + b) * plane;
+  const int Xl = threadIdx.x & (TL_W / 2 - 1), Yl = threadIdx.x >> 4;
+  const int X = (tx0 >> 1) + Xl, Y = (ty0 >> 1) + Yl;
+  const int gx = tx0 + 2 * Xl, gy = ty0 + 2 * Yl;
+  float mf[9];
+  {
+    const int kl = lows.n - 1, Wl = lows.Wl[kl];
+    const Tap xa = ld_tap(lows.xt[kl] + gx), xb = ld_tap(lows.xt[kl] + gx + 1);
+    const Tap ya = ld_tap(lows.yt[kl] + gy), yb = ld_tap(lows.yt[kl] + gy + 1);
+    const float hx = 0.5f * (xa.h + xb.h), lx = 0.5f * (xa.l + xb.l), hy = 0.5f * (ya.h + yb.h), ly = 0.5f * (ya.l + yb.l);
+    const int r0 = (n * lows.Hl[kl] + ya.i0) * Wl, r1 = (n * lows.Hl[kl] + ya.i1) * Wl;
+    const float w00 = hy * hx, w01 = hy * lx, w10 = ly * hx, w11 = ly * lx;
+    float a[9], c[9];
+    mf9_load(lows.mf[kl], lows.f7[kl], r0 + xa.i0, a);
+    mf9_load(lows.mf[kl], lows.f7[kl], r0 + xa.i1, c);
+#pragma unroll
+    for (int i = 0; i < 9; i++) mf[i] = w00 * a[i] + w01 * c[i];
+    mf9_load(lows.mf[kl], lows.f7[kl], r1 + xa.i0, a);
+    mf9_load(lows.mf[kl], lows.f7[kl], r1 + xa.i1, c);
+#pragma unroll
+    for (int i = 0; i < 9; i++) mf[i] += w10 * a[i] + w11 * c[i];
+  }
+  float c0[3] = {0.f, 0.f, 0.f}, c1[3] = {0.f, 0.f, 0.f}, v0[4] = {0.f, 0.f, 0.f, 0.f}, v1[4] = {0.f, 0.f, 0.f, 0.f};
+  float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+  for (int d = 0; d < 4; d++) {
+    // odd groups of four outputs visit their right-hand tap first: the 8 lanes of an LDS.128 phase then hit 8 distinct
+    // 16-byte bank groups
+    const int xl = 2 * Xl + ((d & 1) ^ ((Xl >> 2) & 1)), yl = 2 * Yl + (d >> 1);
+    const float4 fl = flat_eval<TL_W>(lows, tl_sm, xl, yl);
+    const Bil b0 = bil_setup((float)(tx0 + xl) + fl.x, (float)(ty0 + yl) + fl.y, Wp, Hp, base0);
+    const Bil b1 = bil_setup((float)(tx0 + xl) + fl.z, (float)(ty0 + yl) + fl.w, Wp, Hp, base1);
+    float r[4];
+    sample_rgbx(img32, b0, r);
+    c0[0] += r[0]; c0[1] += r[1]; c0[2] += r[2];
+    sample_rgbx(img32, b1, r);
+    c1[0] += r[0]; c1[1] += r[1]; c1[2] += r[2];
+    sample_feat_px<bf16>(feats, b0, r);
+    v0[0] += r[0]; v0[1] += r[1]; v0[2] += r[2]; v0[3] += r[3];
+    sample_feat_px<bf16>(feats, b1, r);
+    v1[0] += r[0]; v1[1] += r[1]; v1[2] += r[2]; v1[3] += r[3];
+    fs.x += fl.x; fs.y += fl.y; fs.z += fl.z; fs.w += fl.w;
+  }
+  const float q = 0.25f, qf = 0.125f;  // mean of the four positions; the flow also scales by 1/s = 1/2
+  uint4 u[4];
+  u[0] = make_uint4(umma::pk_bf16(c0[0] * q, c0[1] * q), umma::pk_bf16(c0[2] * q, c1[0] * q), umma::pk_bf16(c1[1] * q, c1[2] * q),
+                    umma::pk_bf16(v0[0] * q, v0[1] * q));
+  u[1] = make_uint4(umma::pk_bf16(v0[2] * q, v0[3] * q), umma::pk_bf16(v1[0] * q, v1[1] * q), umma::pk_bf16(v1[2] * q, v1[3] * q),
+                    umma::pk_bf16(t, mf[0]));
+  u[2] = make_uint4(umma::pk_bf16(mf[1], mf[2]), umma::pk_bf16(mf[3], mf[4]), umma::pk_bf16(mf[5], mf[6]), umma::pk_bf16(mf[7], mf[8]));
+  u[3] = make_uint4(umma::pk_bf16(fs.x * qf, fs.y * qf), umma::pk_bf16(fs.z * qf, fs.w * qf), 0u, 0u);
+  const int Hs = Hp >> 1, Ws = Wp >> 1;
+  size_t o;
+  if (phase) o = ((((size_t)n * 4 + (Y & 1) * 2 + (X & 1)) * (Hs >> 1) + (Y >> 1)) * (Ws >> 1) + (X >> 1)) * 32;
+  else o = (((size_t)n * Hs + Y) * Ws + X) * 32;
+  st_v8(out + o, u[0], u[1]);
+  st_v8(out + o + 16, u[2], u[3]);
+}
+static int launch_gather_s2(vfi_handle* h, const uint8_t* imgs, const bf16* feats, const LowSet& lows, const float* tsteps_dev,
+                            bf16* out, int B, int I1, int T, int Hp, int Wp, bool phase, cudaStream_t s) {
+  GcRows grows;
+  const size_t smem = gc_stage_bytes(lows, &grows, TL_W);
+  const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
+  gather_s2_kernel<<<grid, G2_THREADS, smem, s>>>(imgs, feats, lows, grows, tsteps_dev, out, B, I1, T, Hp, Wp, phase ? 1 : 0);
   VFI_LAUNCHED(h);
   return 0;
 }

@@ -95,7 +95,7 @@ static inline uint16_t f2bf_host(float f) {
 // chunk stride (16-byte units) >= npix such that the 8 lanes of a 16-byte store phase hit 8 distinct bank groups
 constexpr int chunk_stride(int npix, int nchunk) {
   int c = npix;
-  if (nchunk >= 8) { while (c % 2 == 0) c++; }
+  if (nchunk >= 6) { while (c % 2 == 0) c++; }
   else if (nchunk == 4) { while (c % 8 != 2) c++; }
   else if (nchunk == 2) { while (c % 8 != 4) c++; }
   return c;
