@@ -161,6 +161,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
           float v = L.kind == LK_CONV3 ? w[((size_t)co * L.cin + ci) * 9 + t] : w[((size_t)ci * L.cout + co) * 16 + t];
           w32[((size_t)t * L.cin_pad + ci) * L.cout_pad + co] = v;
         }
+    if (id == 0) {
+      for (int t = 0; t < 9; t++)
+        for (int ci = 0; ci < 3; ci++)
+          for (int co = 0; co < 16; co++) h->head0_w[(t * 3 + ci) * 16 + co] = w[((size_t)co * 3 + ci) * 9 + t] / 255.0f;
+      for (int co = 0; co < 16; co++) h->head0_b[co] = bias[co];
+    }
     VFI_CUDA(h, cudaMalloc(&L.w32, w32.size() * 4));
     VFI_CUDA(h, cudaMemcpy(L.w32, w32.data(), w32.size() * 4, cudaMemcpyHostToDevice));
     std::vector<float> bpad(64 > L.cout_pad ? 64 : L.cout_pad, 0.f);

@@ -65,6 +65,7 @@ struct vfi_handle {
   bool weights_loaded = false;
   float slope = 0.2f;
   Layer layers[VFI_NUM_LAYERS];
+  float head0_w[27 * 16] = {0}, head0_b[16] = {0};  // Head.cnn0 weights [tap][ci][co] / 255 and bias: kernel-parameter operands
   // grow-only workspace arena
   void* ws = nullptr;
   size_t ws_bytes = 0;

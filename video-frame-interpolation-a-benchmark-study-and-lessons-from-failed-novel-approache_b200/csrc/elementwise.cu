@@ -152,49 +152,81 @@ __global__ void pad_rgbx_kernel(const uint8_t* __restrict__ src, uint8_t* __rest
   const uint8_t* p = src + (((size_t)b * H + sy) * W + sx) * 3;
   reinterpret_cast<uchar4*>(dst)[i] = make_uchar4(p[0], p[1], p[2], 0);
 }
+// the same for W % 4 == 0 and a 4-byte aligned source: a thread turns 12 source bytes (three aligned words) into four
+// RGBX pixels (one 16-byte store); only the reflected border falls back to byte loads
+__global__ void pad_rgbx4_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int B, int H, int W, int Hp,
+                                 int Wp) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const int Wq = Wp >> 2;
+  if (i >= (size_t)B * Hp * Wq) return;
+  const int x = (int)(i % Wq) * 4, y = (int)((i / Wq) % Hp), b = (int)(i / ((size_t)Wq * Hp));
+  const int sy = y < H ? y : 2 * (H - 1) - y;
+  const uint8_t* row = src + ((size_t)b * H + sy) * W * 3;
+  uint4 o;
+  if (x + 3 < W) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(row + (size_t)x * 3);
+    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+    o.x = w0 & 0x00ffffffu;
+    o.y = (w0 >> 24) | ((w1 & 0xffffu) << 8);
+    o.z = (w1 >> 16) | ((w2 & 0xffu) << 16);
+    o.w = w2 >> 8;
+  } else {
+    uint32_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int xx = x + k, sx = xx < W ? xx : 2 * (W - 1) - xx;
+      const uint8_t* p = row + (size_t)sx * 3;
+      v[k] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+    }
+    o = make_uint4(v[0], v[1], v[2], v[3]);
+  }
+  reinterpret_cast<uint4*>(dst)[i] = o;
+}
 int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s) {
   ProfScope _ps(h, PC_PAD, s);
   size_t total = (size_t)B * Hp * Wp;
-  pad_rgbx_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp);
+  if ((W & 3) == 0 && (Wp & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0)
+    pad_rgbx4_kernel<<<cdiv(total / 4, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp);
+  else
+    pad_rgbx_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp);
   VFI_LAUNCHED(h);
   return 0;
 }
 
 // ------------------------------------------------------------------------------------------
-// Head.cnn0: Conv2d(3,16,3,2,1) + LeakyReLU straight from the uint8 image (K = 27: CUDA cores).
+// Head.cnn0: Conv2d(3,16,3,2,1) + LeakyReLU straight from the uint8 image (K = 27: CUDA cores).  The 432 weights
+// (pre-divided by 255) and the bias travel as a kernel parameter, so every FFMA takes its weight as a constant-bank
+// operand: no weight loads at all, the kernel is bound by its 432 FMAs per output pixel.
+struct Head0W {
+  float w[27 * 16];
+  float b[16];
+};
 template <typename T>
-__global__ void head_cnn0_kernel(const uint8_t* __restrict__ imgs, const float* __restrict__ w /*[9][4][16]*/,
-                                 const float* __restrict__ bias, T* __restrict__ out, int NI, int Hp, int Wp,
-                                 float slope) {
-  __shared__ float sw[9 * 4 * 16];
-  __shared__ float sb[16];
-  for (int i = threadIdx.x; i < 9 * 4 * 16; i += blockDim.x) sw[i] = w[i];
-  if (threadIdx.x < 16) sb[threadIdx.x] = bias[threadIdx.x];
-  __syncthreads();
+__global__ void __launch_bounds__(128) head_cnn0_kernel(const uint8_t* __restrict__ imgs, const __grid_constant__ Head0W Wt,
+                                                        T* __restrict__ out, int NI, int Hp, int Wp, float slope) {
   int Ho = Hp / 2, Wo = Wp / 2;
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   size_t total = (size_t)NI * Ho * Wo;
   if (i >= total) return;
   int x = (int)(i % Wo), y = (int)((i / Wo) % Ho), n = (int)(i / ((size_t)Wo * Ho));
-  const uchar4* img = reinterpret_cast<const uchar4*>(imgs) + (size_t)n * Hp * Wp;
+  const uint32_t* img = reinterpret_cast<const uint32_t*>(imgs) + (size_t)n * Hp * Wp;
   float acc[16];
 #pragma unroll
-  for (int c = 0; c < 16; c++) acc[c] = sb[c];
+  for (int c = 0; c < 16; c++) acc[c] = Wt.b[c];
 #pragma unroll
   for (int r = 0; r < 3; r++) {
-    int iy = 2 * y + r - 1;
-    if (iy < 0 || iy >= Hp) continue;
+    const int iy = 2 * y + r - 1;
 #pragma unroll
     for (int q = 0; q < 3; q++) {
-      int ix = 2 * x + q - 1;
-      if (ix < 0 || ix >= Wp) continue;
-      uchar4 p = __ldg(img + (size_t)iy * Wp + ix);
-      float v[3] = {p.x / 255.0f, p.y / 255.0f, p.z / 255.0f};
-      const float* ww = sw + (r * 3 + q) * 64;
+      const int ix = 2 * x + q - 1;
+      // zero padding: only the top row / left column can fall outside (Hp, Wp are even)
+      const bool in = (r > 0 || iy >= 0) && (q > 0 || ix >= 0);
+      const uint32_t p = in ? __ldg(img + (size_t)iy * Wp + ix) : 0u;
+      const float v[3] = {u8f<0>(p), u8f<1>(p), u8f<2>(p)};
 #pragma unroll
       for (int ci = 0; ci < 3; ci++)
 #pragma unroll
-        for (int c = 0; c < 16; c++) acc[c] = fmaf(v[ci], ww[ci * 16 + c], acc[c]);
+        for (int c = 0; c < 16; c++) acc[c] = fmaf(v[ci], Wt.w[((r * 3 + q) * 3 + ci) * 16 + c], acc[c]);
     }
   }
 #pragma unroll
@@ -205,11 +237,13 @@ __global__ void head_cnn0_kernel(const uint8_t* __restrict__ imgs, const float* 
 int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, int NI, int Hp, int Wp, bool bf,
                 cudaStream_t s) {
   ProfScope _ps(h, PC_HEAD0, s);
+  (void)L;
   size_t total = (size_t)NI * (Hp / 2) * (Wp / 2);
-  if (bf)
-    head_cnn0_kernel<bf16><<<cdiv(total, 128), 128, 0, s>>>(imgs, L.w32, L.bias, (bf16*)out, NI, Hp, Wp, h->slope);
-  else
-    head_cnn0_kernel<float><<<cdiv(total, 128), 128, 0, s>>>(imgs, L.w32, L.bias, (float*)out, NI, Hp, Wp, h->slope);
+  Head0W Wt;
+  memcpy(Wt.w, h->head0_w, sizeof(Wt.w));
+  memcpy(Wt.b, h->head0_b, sizeof(Wt.b));
+  if (bf) head_cnn0_kernel<bf16><<<cdiv(total, 128), 128, 0, s>>>(imgs, Wt, (bf16*)out, NI, Hp, Wp, h->slope);
+  else head_cnn0_kernel<float><<<cdiv(total, 128), 128, 0, s>>>(imgs, Wt, (float*)out, NI, Hp, Wp, h->slope);
   VFI_LAUNCHED(h);
   return 0;
 }
