@@ -679,6 +679,8 @@ __global__ void __launch_bounds__(TL_THREADS) gather_tile_kernel(const uint8_t* 
 
 static int launch_gather_s2(vfi_handle* h, const uint8_t* imgs, const bf16* feats, const LowSet& lows, const float* tsteps_dev,
                             bf16* out, int B, int I1, int T, int Hp, int Wp, bool phase, cudaStream_t s);
+static int launch_gather_lo(vfi_handle* h, const uint8_t* imgs, const bf16* feats, const LowSet& lows, const float* tsteps_dev,
+                            bf16* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool phase, cudaStream_t s);
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,
              void* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool bf, bool phase, cudaStream_t s) {
   ProfScope _ps(h, PC_GATHER, s);
@@ -690,6 +692,11 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
     bool coarse = true;  // flat staging pre-supposes every level is coarser than the frame
     for (int k = 0; k < lows.n; k++) coarse = coarse && lows.s[k] > 1;
     if (coarse) return launch_gather_s2(h, imgs, (const bf16*)feats, lows, tsteps_dev, (bf16*)out, B, I1, T, Hp, Wp, phase, s);
+  }
+  if (!first && bf && s_int >= 4 && lows.xt[0] && lows.s[lows.n - 1] >= 2 * s_int) {
+    bool planes = true;
+    for (int k = 0; k < lows.n; k++) planes = planes && lows.mf[k] != nullptr;
+    if (planes) return launch_gather_lo(h, imgs, (const bf16*)feats, lows, tsteps_dev, (bf16*)out, B, I1, T, Hp, Wp, s_int, phase, s);
   }
   if (!first && s_int <= 2 && Hp % TL_H == 0 && Wp % TL_W == 0) {
     const size_t smem = tl_smem_bytes(lows, 1);
@@ -1260,6 +1267,97 @@ static int launch_gather_s2(vfi_handle* h, const uint8_t* imgs, const bf16* feat
   const size_t smem = gc_stage_bytes(lows, &grows, TL_W);
   const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
   gather_s2_kernel<<<grid, G2_THREADS, smem, s>>>(imgs, feats, lows, grows, tsteps_dev, out, B, I1, T, Hp, Wp, phase ? 1 : 0);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Block-input gather at s >= 4 (bf16 mode, LowPlanes levels): gather_kernel<bf16, false> with the per-call tap tables
+// instead of per-thread source-index arithmetic, 32-bit indexing, and mask / feat fetched once per output with the
+// mean weights of the 2 x 2 sampled positions (which share their source cell: the last level is at least 2s coarse).
+__global__ void __launch_bounds__(128) gather_lo_kernel(const uint8_t* __restrict__ imgs, const bf16* __restrict__ feats,
+                                                        const __grid_constant__ LowSet lows, const float* __restrict__ tsteps,
+                                                        bf16* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, int s,
+                                                        int phase) {
+  const int Hs = Hp / s, Ws = Wp / s;
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= (size_t)B * Tn * Hs * Ws) return;
+  const int X = (int)(i % Ws), Y = (int)((i / Ws) % Hs), n = (int)(i / ((size_t)Ws * Hs));
+  const int b = n / Tn;
+  const float t = tsteps[n - b * Tn];
+  const int plane = Hp * Wp;
+  const uint32_t* img32 = reinterpret_cast<const uint32_t*>(imgs);
+  const int base0 = b * plane, base1 = (I1 + b) * plane;
+  const int bx = s * X + s / 2 - 1, by = s * Y + s / 2 - 1;
+  float mf[9];
+  {
+    const int kl = lows.n - 1, Wl = lows.Wl[kl];
+    const Tap xa = ld_tap(lows.xt[kl] + bx), xb = ld_tap(lows.xt[kl] + bx + 1);
+    const Tap ya = ld_tap(lows.yt[kl] + by), yb = ld_tap(lows.yt[kl] + by + 1);
+    const float hx = 0.5f * (xa.h + xb.h), lx = 0.5f * (xa.l + xb.l), hy = 0.5f * (ya.h + yb.h), ly = 0.5f * (ya.l + yb.l);
+    const int r0 = (n * lows.Hl[kl] + ya.i0) * Wl, r1 = (n * lows.Hl[kl] + ya.i1) * Wl;
+    const float w00 = hy * hx, w01 = hy * lx, w10 = ly * hx, w11 = ly * lx;
+    float a[9], c[9];
+    mf9_load(lows.mf[kl], lows.f7[kl], r0 + xa.i0, a);
+    mf9_load(lows.mf[kl], lows.f7[kl], r0 + xa.i1, c);
+#pragma unroll
+    for (int j = 0; j < 9; j++) mf[j] = w00 * a[j] + w01 * c[j];
+    mf9_load(lows.mf[kl], lows.f7[kl], r1 + xa.i0, a);
+    mf9_load(lows.mf[kl], lows.f7[kl], r1 + xa.i1, c);
+#pragma unroll
+    for (int j = 0; j < 9; j++) mf[j] += w10 * a[j] + w11 * c[j];
+  }
+  float c0[3] = {0.f, 0.f, 0.f}, c1[3] = {0.f, 0.f, 0.f}, v0[4] = {0.f, 0.f, 0.f, 0.f}, v1[4] = {0.f, 0.f, 0.f, 0.f};
+  float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+  for (int d = 0; d < 4; d++) {
+    const int x = bx + (d & 1), y = by + (d >> 1);
+    float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+      if (k < lows.n) {
+        const Tap tx = ld_tap(lows.xt[k] + x), ty = ld_tap(lows.yt[k] + y);
+        const float4* fp = reinterpret_cast<const float4*>(lows.p[k]);
+        const int r0 = (n * lows.Hl[k] + ty.i0) * lows.Wl[k], r1 = (n * lows.Hl[k] + ty.i1) * lows.Wl[k];
+        const float4 a = __ldg(fp + r0 + tx.i0), bq = __ldg(fp + r0 + tx.i1), c = __ldg(fp + r1 + tx.i0), dq = __ldg(fp + r1 + tx.i1);
+        const float f = lows.fs[k];
+        fl.x += (ty.h * (tx.h * a.x + tx.l * bq.x) + ty.l * (tx.h * c.x + tx.l * dq.x)) * f;
+        fl.y += (ty.h * (tx.h * a.y + tx.l * bq.y) + ty.l * (tx.h * c.y + tx.l * dq.y)) * f;
+        fl.z += (ty.h * (tx.h * a.z + tx.l * bq.z) + ty.l * (tx.h * c.z + tx.l * dq.z)) * f;
+        fl.w += (ty.h * (tx.h * a.w + tx.l * bq.w) + ty.l * (tx.h * c.w + tx.l * dq.w)) * f;
+      }
+    }
+    const Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp, base0);
+    const Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp, base1);
+    float r[4];
+    sample_rgbx(img32, b0, r);
+    c0[0] += r[0]; c0[1] += r[1]; c0[2] += r[2];
+    sample_rgbx(img32, b1, r);
+    c1[0] += r[0]; c1[1] += r[1]; c1[2] += r[2];
+    sample_feat_px<bf16>(feats, b0, r);
+    v0[0] += r[0]; v0[1] += r[1]; v0[2] += r[2]; v0[3] += r[3];
+    sample_feat_px<bf16>(feats, b1, r);
+    v1[0] += r[0]; v1[1] += r[1]; v1[2] += r[2]; v1[3] += r[3];
+    fs.x += fl.x; fs.y += fl.y; fs.z += fl.z; fs.w += fl.w;
+  }
+  const float q = 0.25f, qf = 0.25f / (float)s;  // mean of the four positions; the flow also scales by 1/s
+  uint4 u[4];
+  u[0] = make_uint4(umma::pk_bf16(c0[0] * q, c0[1] * q), umma::pk_bf16(c0[2] * q, c1[0] * q), umma::pk_bf16(c1[1] * q, c1[2] * q),
+                    umma::pk_bf16(v0[0] * q, v0[1] * q));
+  u[1] = make_uint4(umma::pk_bf16(v0[2] * q, v0[3] * q), umma::pk_bf16(v1[0] * q, v1[1] * q), umma::pk_bf16(v1[2] * q, v1[3] * q),
+                    umma::pk_bf16(t, mf[0]));
+  u[2] = make_uint4(umma::pk_bf16(mf[1], mf[2]), umma::pk_bf16(mf[3], mf[4]), umma::pk_bf16(mf[5], mf[6]), umma::pk_bf16(mf[7], mf[8]));
+  u[3] = make_uint4(umma::pk_bf16(fs.x * qf, fs.y * qf), umma::pk_bf16(fs.z * qf, fs.w * qf), 0u, 0u);
+  size_t o;
+  if (phase) o = ((((size_t)n * 4 + (Y & 1) * 2 + (X & 1)) * (Hs >> 1) + (Y >> 1)) * (Ws >> 1) + (X >> 1)) * 32;
+  else o = i * 32;
+  st_v8(out + o, u[0], u[1]);
+  st_v8(out + o + 16, u[2], u[3]);
+}
+static int launch_gather_lo(vfi_handle* h, const uint8_t* imgs, const bf16* feats, const LowSet& lows, const float* tsteps_dev,
+                            bf16* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool phase, cudaStream_t s) {
+  const size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
+  gather_lo_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, feats, lows, tsteps_dev, out, B, I1, T, Hp, Wp, s_int, phase ? 1 : 0);
   VFI_LAUNCHED(h);
   return 0;
 }
