@@ -235,6 +235,9 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
   // b+1's first frame -- pad it and run the Head on it once
   const bool clipmode = B > 1 && img1 == img0 + (size_t)H * W * 3;
   const int N = B * T, NI = clipmode ? B + 1 : 2 * B, I1 = clipmode ? 1 : B;
+  // the gather / blend kernels index pixels of the whole image set with 32-bit integers
+  if ((size_t)std::max(NI, N) * Hp * Wp >= ((size_t)1 << 31))
+    VFI_FAIL(h, VFI_E_ARG, "batch too large: %d images of %dx%d exceed 2^31 pixels, split the call", std::max(NI, N), Hp, Wp);
   int sl[5];
   for (int i = 0; i < 5; i++) sl[i] = (16 >> i) * inv;
 

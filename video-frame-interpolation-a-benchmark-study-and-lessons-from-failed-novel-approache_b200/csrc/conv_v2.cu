@@ -713,7 +713,7 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
     switch (L.cin) {
       case 16: rc = launch_v2<16, 16, 4, 0>(h, P, s); break;
       case 32: rc = launch_v2<32, 32, 4, 0>(h, P, s); break;
-      default: rc = launch_v2<64, 64, 1, 0>(h, P, s); break;
+      default: rc = launch_v2<64, 64, 2, 0>(h, P, s); break;
     }
     if (rc) return rc;
     std::vector<unsigned long long> host(3 * 64 * 8);
@@ -732,7 +732,7 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   switch (L.cin) {
     case 16: return launch_v2<16, 16, 4, 0>(h, P, s);
     case 32: return launch_v2<32, 32, 4, 0>(h, P, s);
-    case 64: return launch_v2<64, 64, 1, 0>(h, P, s);  // KW = 1: 6 stages beside the 72 KB of weights
+    case 64: return launch_v2<64, 64, 2, 0>(h, P, s);  // KW = 2: 3 stages beside the 72 KB of weights
     case 96: return launch_v2<96, 96, 1, 0, 2>(h, P, s);    // 2 x 48 output channels: 81 KB of weights per CTA
     case 128: return launch_v2<128, 128, 1, 0, 4>(h, P, s);  // 4 x 32 output channels: 72 KB of weights per CTA
   }

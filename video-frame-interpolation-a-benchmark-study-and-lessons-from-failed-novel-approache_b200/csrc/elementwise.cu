@@ -732,13 +732,14 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
 //   unpad (base.py:227-229); (x*255).clip(0,255).astype(uint8) truncation (base.py:188-201)
 //   HUD composite frame[mask] = (f0 if t<0.5 else f1)[mask]              (adaptive_pipeline.py:399-409)
 // The u8 tile is assembled in shared memory and written as aligned 32-bit words, 96 B per tile row.
-__device__ __forceinline__ void blend_px(const uint8_t* img0, const uint8_t* img1, const float4 fl, const float mk,
-                                         int x, int y, int Hp, int Wp, float* o /*3*/) {
-  Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp);
-  Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp);
+// base0 / base1: pixel index of the pair's two frames in the RGBX image set
+__device__ __forceinline__ void blend_px(const uint32_t* __restrict__ img32, int base0, int base1, const float4 fl,
+                                         const float mk, int x, int y, int Hp, int Wp, float* o /*3*/) {
+  const Bil b0 = bil_setup((float)x + fl.x, (float)y + fl.y, Wp, Hp, base0);
+  const Bil b1 = bil_setup((float)x + fl.z, (float)y + fl.w, Wp, Hp, base1);
   float a[3], c[3];
-  sample_rgbx(img0, b0, a);
-  sample_rgbx(img1, b1, c);
+  sample_rgbx(img32, b0, a);
+  sample_rgbx(img32, b1, c);
   const float m = __fdividef(1.0f, 1.0f + __expf(-mk));  // sigmoid; ~2 ulp, far inside the 1e-4 parity budget
 #pragma unroll
   for (int k = 0; k < 3; k++) o[k] = a[k] * m + c[k] * (1.0f - m);
@@ -800,7 +801,7 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
     } else {
       fl = tile_eval<2>(lows, tl_sm, n, x, y, xl, yl, &m4);
     }
-    blend_px(img0, img1, fl, m4.x, x, y, Hp, Wp, o);
+    blend_px(reinterpret_cast<const uint32_t*>(imgs), b * (int)plane, (I1 + b) * (int)plane, fl, m4.x, x, y, Hp, Wp, o);
     const size_t opix = ((size_t)n * H + y) * W + x;
     if (out_f32) { out_f32[opix * 3] = o[0]; out_f32[opix * 3 + 1] = o[1]; out_f32[opix * 3 + 2] = o[2]; }
     if (flow_out) reinterpret_cast<float4*>(flow_out)[opix] = fl;
