@@ -1025,6 +1025,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
   __shared__ uint64_t mma_bar;
   __shared__ uint32_t tmem_slot;
+  __shared__ Tap mtab[2][GC_TW];  // x / y taps of the mask / feat level for the region's columns / rows
   uint8_t* a_s = reinterpret_cast<uint8_t*>(tl_sm) + stage_bytes;
   const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1037,6 +1038,12 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   // straight from global memory (L1 / L2 resident: one 64 B texel serves four pixels), which leaves room for the A tile
   // beside the staging area at two CTAs per SM and lets a pixel go from evaluation to its A chunks in one pass
   flat_stage<GC_TW, GC_THREADS>(lows, grows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
+  if (threadIdx.x >= GC_THREADS - 2 * GC_TW) {  // the last warps: they have the fewest staging entries
+    const int e = threadIdx.x - (GC_THREADS - 2 * GC_TW), ax = e / GC_TW, j = e - ax * GC_TW;
+    const int kl = lows.n - 1;
+    const Tap* src = ax ? lows.yt[kl] + max(ty0 - 1 + j, 0) : lows.xt[kl] + max(tx0 - 1 + j, 0);
+    reinterpret_cast<int4*>(&mtab[ax][j])[0] = __ldg(reinterpret_cast<const int4*>(src));
+  }
   tc_before();
   __syncthreads();
   tc_after();
@@ -1051,7 +1058,6 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   const int mWl = lows.Wl[kl];
   const bf16 *mfp = lows.mf[kl], *f7p = lows.f7[kl];
   const int mtb = n * lows.Hl[kl] * mWl;
-  const Tap *mxt = lows.xt[kl], *myt = lows.yt[kl];
   float4* fsum = flow_sum ? flow_sum + (size_t)n * plane : nullptr;
   // Work units: region rows 0..32 with lane = column 1..32 (one image row per warp instruction: two or three cache
   // lines per tap instead of the five a row-straddling warp touches), then the halo column (lx = 0) in two more units.
@@ -1070,7 +1076,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
       // the flow of blocks 0..3 at this pixel, for the final blend (tile-interior pixels: each written exactly once)
       if (fsum && ly > 0 && lx > 0) fsum[gy * Wp + gx] = fl;
       // mask + 8 feature channels: bilinear x2 of texel channels 4..12
-      const Tap ty = ld_tap(myt + gy), tx = ld_tap(mxt + gx);
+      const Tap ty = mtab[1][ly], tx = mtab[0][lx];
       const int r0 = mtb + ty.i0 * mWl, r1 = mtb + ty.i1 * mWl;
       const float w00 = ty.h * tx.h, w01 = ty.h * tx.l, w10 = ty.l * tx.h, w11 = ty.l * tx.l;
       float mf[9];
