@@ -98,6 +98,48 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
+def measure_aux(eng, clip_dev, H, W, hbm):
+    """The path's other kernels (metrics + routing statistics): CUDA-event time per
+    1080p frame on inputs larger than L2, against the HBM roofline with their algorithmic bytes."""
+    from vfi_b200.engine import HudState
+    n = min(24, clip_dev.shape[0] - 1)
+    a, b = clip_dev[:n], clip_dev[1:n + 1]
+    px = H * W
+    flow = torch.randn((8, H, W, 2), device=clip_dev.device, dtype=torch.float32) * 4.0
+    hud = HudState(eng)
+    frames = [clip_dev[i] for i in range(n)]
+    state = {"i": 0}
+
+    def hud_step():
+        hud.update(frames[state["i"] % n])
+        state["i"] += 1
+    cases = {
+        "psnr_sse (A13)": (lambda: eng.psnr_sse(a, b), n, 6 * px, "both u8 RGB frames"),
+        "ssim_full (A14)": (lambda: eng.ssim(a, b, 1), n, 6 * px, "both u8 RGB frames; gray + 7x7 windows on chip"),
+        "ssim_quarter (A6 scene cut)": (lambda: eng.ssim(a, b, 4), n, 6 * px, "both u8 RGB frames"),
+        "flow_stats (A7)": (lambda: eng.flow_stats(flow), 8, 8 * px, "fp32 flow field (u, v)"),
+        "laplacian_var (A8)": (lambda: eng.laplacian_var(a), n, 3 * px, "one u8 RGB frame"),
+        "hud_update (A9)": (hud_step, 1, 3 * px + 2 * px, "u8 RGB frame in, full-resolution mask out (+ 180x320 ring)"),
+    }
+    out = {}
+    for name, (fn, per_call, bytes_per_frame, what) in cases.items():
+        for _ in range(6):
+            fn()
+        torch.cuda.synchronize()
+        reps = 10
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / (reps * per_call)
+        gbps = bytes_per_frame / (ms / 1000.0) / 1e9
+        out[name] = {"ms_per_frame": ms, "bound": "hbm", "achieved": gbps, "peak": hbm, "unit": "GB/s", "frac": gbps / hbm,
+                     "algorithmic_bytes_per_frame": bytes_per_frame, "what": what}
+    return out
+
+
 def run_reference(args, rank, world):
     """The reference's own CPU path for this hot path = the oracle restatement (the reference's IFNet lives in a
     missing submodule; nothing of it can be installed).  One step = one Model.inference (1 pair, 1 timestep)."""
@@ -146,6 +188,7 @@ def main():
     ap.add_argument("--pool", type=int, default=24, help="unique synthetic pairs resident in HBM")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-aux", action="store_true", help="skip timing the metric / routing-statistics kernels")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     args = ap.parse_args()
 
@@ -270,15 +313,20 @@ def main():
                                    "frac": by * psteps / (ms_k / 1000.0) / 1e9 / hbm, "algorithmic_bytes_per_px": bytes_per_px,
                                    "ms_per_step": ms_k / psteps, "what": what}
             # algorithmic bytes per padded full-resolution pixel of one (pair, timestep) item
-            hbm_entry("warp_blend", 8 + 32 + 5 + 3, "RGBX taps of both frames 8, last block's flow+mask 32, coarse flows 5, u8 out 3")
-            hbm_entry("gather_conv0a", 8 + 16 + 16 + 5 + 8, "RGBX taps 8, Head feature taps 16, block-3 output 16 (64 B / 4 px), "
-                                                          "coarser flows 5, conv0[0] output 8 (32 B / 4 px)")
-            hbm_entry("gather", (8 + 16 + 5 + 16) + (8 + 16 + 2 + 4) / 4.0 + 2,
-                      "blocks 0-3: taps + coarse inputs + 64 B per output pixel of the block input (s = 2: every pixel; "
-                      "s = 4, 8, 16: 1/4, 1/16, 1/64 of them)")
+            hbm_entry("warp_blend", 8 + 16 + 16 + 3, "RGBX taps of both frames 8, blocks 0-3 flow (fp32) 16, last block's "
+                                                     "flow delta + mask (fp16 texel) 16, u8 out 3")
+            hbm_entry("gather_conv0a", 8 + 16 + 8.5 + 1.5 + 16 + 8, "RGBX taps 8, Head feature taps 16, block-3 planes 8.5 "
+                      "(34 B / 4 px), coarser flows 1.5, summed flow out 16, conv0[0] output 8 (32 B / 4 px)")
+            hbm_entry("gather", (8 + 16 + 3 + 16) + (8 + 16 + 2 + 16) / 4.0 + (8 + 16 + 2 + 16) / 16.0 + 1,
+                      "blocks 0-3: taps + coarse inputs + 64 B per output pixel of the block input (s = 2: every pixel "
+                      "sampled; s = 4, 8, 16: 1/4, 1/16, 1/64 of them)")
             roof["other_kernels"] = others
             if fused_on:
                 roof["fused_gather_conv0a_gflop_per_step"] = fl_fused / 1e9
+
+    aux = None
+    if rank == 0 and not args.no_aux:
+        aux = measure_aux(eng, clip_dev, H, W, peaks()[0])
 
     cpu_base = None
     if rank == 0 and not args.no_cpu_baseline:
@@ -316,7 +364,7 @@ def main():
                     "api": "RIFEModel.clip_streamer().submit (B+1 pinned host uint8 frames in, B x T pinned host uint8 frames out per step; upload / kernels / download on three streams, 2 slots)"},
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),
-            "roofline": roof, "kernel_breakdown": breakdown, "cpu_baseline": cpu_base,
+            "roofline": roof, "kernel_breakdown": breakdown, "aux_kernels": aux, "cpu_baseline": cpu_base,
         }
         print(json.dumps(line))
     if world > 1:

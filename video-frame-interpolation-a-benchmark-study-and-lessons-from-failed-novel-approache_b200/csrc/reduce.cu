@@ -365,35 +365,101 @@ __global__ void hud_var_kernel(const uint8_t* __restrict__ ring, HudSlots sl, do
   double var = __ddiv_rn(acc, 5.0);
   small[i] = var < thr ? 1 : 0;
 }
-__global__ void hud_upsample_kernel(const uint8_t* __restrict__ small, uint8_t* __restrict__ dst, int H, int W,
-                                    double ify, double ifx) {
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= (size_t)H * W) return;
-  int x = (int)(i % W), y = (int)(i / W);
-  int sx = min((int)floor(__dmul_rn((double)x, ifx)), HUD_W - 1);
-  int sy = min((int)floor(__dmul_rn((double)y, ify)), HUD_H - 1);
-  dst[i] = small[sy * HUD_W + sx];
-}
-// 1-D min/max filter of radius r along x (horiz = 1) or y; out-of-image samples are ignored.
-__global__ void morph1d_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int H, int W, int r,
-                               int dilate, int horiz) {
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= (size_t)H * W) return;
-  int x = (int)(i % W), y = (int)(i / W);
-  int v = dilate ? 0 : 1;
-  for (int k = -r; k <= r; k++) {
-    int xx = horiz ? x + k : x, yy = horiz ? y : y + k;
-    if (xx < 0 || xx >= W || yy < 0 || yy >= H) continue;
-    int t = src[(size_t)yy * W + xx];
-    v = dilate ? max(v, t) : min(v, t);
+// var flag -> NEAREST upsample -> close -> open -> count, in one kernel.  A CTA owns a 32 x 32 tile of the mask and works on
+// the 48 x 48 region around it (the three morphology steps reach 2 + 4 + 2 pixels) as 48 row bit-words: a horizontal
+// step is shifts and ORs of one word, a vertical step ORs neighbouring rows, erosion is dilation of the complement, and
+// "out-of-image samples are ignored" is a mask on each step's input.
+#define HM_T 32
+#define HM_R 8
+#define HM_N (HM_T + 2 * HM_R)
+#define HM_CELLS 26  // small-mask cells a 48-pixel span can touch at the smallest ratio (2)
+__device__ __forceinline__ void hm_dilate(unsigned long long* a, unsigned long long* tmp, const bool rowin, unsigned long long inx,
+                                          int r, bool complement) {
+  const int t = threadIdx.x;
+  if (t < HM_N) {
+    unsigned long long w = a[t];
+    if (complement) w = ~w;
+    w = rowin ? (w & inx) : 0ull;
+    unsigned long long hz = w;
+    for (int k = 1; k <= r; k++) hz |= (w << k) | (w >> k);
+    tmp[t] = hz;
   }
-  dst[i] = (uint8_t)v;
+  __syncthreads();
+  if (t < HM_N) {
+    unsigned long long v = 0ull;
+    for (int k = -r; k <= r; k++)
+      if (t + k >= 0 && t + k < HM_N) v |= tmp[t + k];
+    a[t] = complement ? ~v : v;
+  }
+  __syncthreads();
 }
-__global__ void mask_count_kernel(const uint8_t* __restrict__ m, size_t n, unsigned long long* __restrict__ cnt) {
+__global__ void __launch_bounds__(256) hud_mask_kernel(const uint8_t* __restrict__ ring, HudSlots sl, double thr,
+                                                       uint8_t* __restrict__ dst, int H, int W, double ify, double ifx,
+                                                       unsigned long long* __restrict__ cnt) {
+  __shared__ unsigned long long rows[HM_N], tmp[HM_N];
+  __shared__ uint8_t flag[HM_CELLS][HM_CELLS];
+  const int tx0 = blockIdx.x * HM_T, ty0 = blockIdx.y * HM_T;
+  const int ox = tx0 - HM_R, oy = ty0 - HM_R;
+  const int x_lo = max(ox, 0), x_hi = min(ox + HM_N - 1, W - 1), y_lo = max(oy, 0), y_hi = min(oy + HM_N - 1, H - 1);
+  const int cx0 = min((int)floor(__dmul_rn((double)x_lo, ifx)), HUD_W - 1), cx1 = min((int)floor(__dmul_rn((double)x_hi, ifx)), HUD_W - 1);
+  const int cy0 = min((int)floor(__dmul_rn((double)y_lo, ify)), HUD_H - 1), cy1 = min((int)floor(__dmul_rn((double)y_hi, ify)), HUD_H - 1);
+  const int ncx = cx1 - cx0 + 1, ncy = cy1 - cy0 + 1;
+  for (int e = threadIdx.x; e < ncx * ncy; e += blockDim.x) {
+    const int cy = e / ncx, cx = e - cy * ncx;
+    const int i = (cy0 + cy) * HUD_W + cx0 + cx;
+    double x[5];
+    double sum = 0.0;
+#pragma unroll
+    for (int k = 0; k < 5; k++) { x[k] = (double)ring[(size_t)sl.idx[k] * HUD_W * HUD_H + i]; sum = __dadd_rn(sum, x[k]); }
+    const double mean = __ddiv_rn(sum, 5.0);
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < 5; k++) { const double d = __dsub_rn(x[k], mean); acc = __dadd_rn(acc, __dmul_rn(d, d)); }
+    flag[cy][cx] = __ddiv_rn(acc, 5.0) < thr ? 1 : 0;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int t = warp; t < HM_N; t += 8) {
+    const int gy = oy + t;
+    const bool yin = gy >= 0 && gy < H;
+    const int cy = yin ? min((int)floor(__dmul_rn((double)gy, ify)), HUD_H - 1) - cy0 : 0;
+    unsigned int half[2];
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+      const int c = lane + 32 * hh, gx = ox + c;
+      bool bit = false;
+      if (yin && c < HM_N && gx >= 0 && gx < W) bit = flag[cy][min((int)floor(__dmul_rn((double)gx, ifx)), HUD_W - 1) - cx0] != 0;
+      half[hh] = __ballot_sync(0xffffffffu, bit);
+    }
+    if (lane == 0) rows[t] = (unsigned long long)half[0] | ((unsigned long long)half[1] << 32);
+  }
+  __syncthreads();
+  // in-image columns of the region as a bit mask; this thread's row
+  unsigned long long inx = 0ull;
+  {
+    const int c_lo = x_lo - ox, c_hi = x_hi - ox;  // 0 <= c_lo <= c_hi < 48
+    inx = ((c_hi == 63 ? 0ull : (1ull << (c_hi + 1))) - 1ull) & ~((1ull << c_lo) - 1ull);
+  }
+  const int gy_t = oy + (int)threadIdx.x;
+  const bool rowin = threadIdx.x < HM_N && gy_t >= 0 && gy_t < H;
+  hm_dilate(rows, tmp, rowin, inx, 2, false);  // MORPH_CLOSE: dilate 5x5 ...
+  hm_dilate(rows, tmp, rowin, inx, 4, true);   // ... erode 5x5, then MORPH_OPEN's erode 5x5: together erode 9x9
+  hm_dilate(rows, tmp, rowin, inx, 2, false);  // ... dilate 5x5
+  // store the tile (4 pixels per thread) and count it
+  const int yl = threadIdx.x >> 3, xq = (threadIdx.x & 7) * 4;
+  const int y = ty0 + yl, x = tx0 + xq;
+  unsigned int c4 = 0;
+  if (y < H && x < W) {
+    const unsigned long long w = rows[HM_R + yl] >> (HM_R + xq);
+    uint8_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) { v[k] = (x + k < W) ? (uint8_t)((w >> k) & 1ull) : 0; c4 += v[k]; }
+    uint8_t* o = dst + (size_t)y * W + x;
+    if (x + 3 < W && ((W & 3) == 0)) *reinterpret_cast<uchar4*>(o) = make_uchar4(v[0], v[1], v[2], v[3]);
+    else for (int k = 0; k < 4 && x + k < W; k++) o[k] = v[k];
+  }
   __shared__ unsigned long long sh[32];
-  unsigned long long c = 0;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) c += m[i];
-  c = block_sum(c, sh);
+  const unsigned long long c = block_sum((unsigned long long)c4, sh);
   if (threadIdx.x == 0 && c) atomicAdd(cnt, c);
 }
 __global__ void coverage_finish_kernel(const unsigned long long* cnt, double n, double* out) { *out = (double)(*cnt) / n; }
@@ -419,27 +485,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
     VFI_CUDA(h, cudaMemsetAsync(coverage_out, 0, sizeof(double), s));
     return VFI_OK;
   }
-  uint8_t* scratch = (uint8_t*)h->red;
-  unsigned long long* cnt = (unsigned long long*)scratch;
-  uint8_t* small = scratch + 1024;
-  uint8_t* tmp = scratch + 1024 + ((HUD_W * HUD_H + 1023) & ~1023);
+  unsigned long long* cnt = (unsigned long long*)h->red;
   HudSlots sl;
   for (int k = 0; k < 5; k++) sl.idx[k] = (int)((c - 4 + k) % hist_len);  // oldest -> newest of the last five
-  hud_var_kernel<<<cdiv(HUD_W * HUD_H, 256), 256, 0, s>>>(hist_ring, sl, var_threshold, small);
-  VFI_LAUNCHED(h);
   const double ifx = 1.0 / ((double)W / (double)HUD_W), ify = 1.0 / ((double)H / (double)HUD_H);
-  const int g = cdiv(npix, 256);
-  hud_upsample_kernel<<<g, 256, 0, s>>>(small, mask_out, H, W, ify, ifx);
-  VFI_LAUNCHED(h);
-  const int seq[3][2] = {{2, 1}, {4, 0}, {2, 1}};  // dilate5, erode9 (= erode5 twice), dilate5
-  for (int k = 0; k < 3; k++) {
-    morph1d_kernel<<<g, 256, 0, s>>>(mask_out, tmp, H, W, seq[k][0], seq[k][1], 1);
-    VFI_LAUNCHED(h);
-    morph1d_kernel<<<g, 256, 0, s>>>(tmp, mask_out, H, W, seq[k][0], seq[k][1], 0);
-    VFI_LAUNCHED(h);
-  }
   VFI_CUDA(h, cudaMemsetAsync(cnt, 0, 8, s));
-  mask_count_kernel<<<296, 256, 0, s>>>(mask_out, npix, cnt);
+  hud_mask_kernel<<<dim3(cdiv(W, HM_T), cdiv(H, HM_T)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx, cnt);
   VFI_LAUNCHED(h);
   coverage_finish_kernel<<<1, 1, 0, s>>>(cnt, (double)npix, coverage_out);
   VFI_LAUNCHED(h);
