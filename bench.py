@@ -217,6 +217,9 @@ def main():
     with contextlib.redirect_stdout(sys.stderr):   # the wrapper prints "Loading RIFE ..." like the reference; stdout is the JSON line only
         model.load()
     eng = model._engine
+    for opt in ("l2_chunk_mb", "fuse_gather", "conv_v2", "v2_tma"):  # tuning knobs of the library (defaults are the shipped ones)
+        if os.environ.get("VFI_" + opt.upper()) is not None:
+            eng.set_option(opt, int(os.environ["VFI_" + opt.upper()]))
     B, T = args.pairs, len(TIMESTEPS)
     # each rank works on its own shard of the clip (frame-pair sharding, no data-path collective)
     clip = gen_clip(args.pool, H, W, seed=1 + rank, cut_every=0, fast=None)

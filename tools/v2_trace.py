@@ -33,7 +33,8 @@ else:
     from vfi_b200.ifnet_layers import layer_info
     e = Engine.get(0)
     e.load_weights(ifnet_params.random_init(1234))
-    for layer, N, H, W in [(50, 12, 272, 480), (39, 12, 136, 240)]:
+    NN = int(os.environ.get("V2_TRACE_N", "12"))
+    for layer, N, H, W in [(50, NN, 272, 480), (39, NN, 136, 240)]:
         li = layer_info(layer)
         x = torch.randn((N, H, W, li["cin_pad"]), device="cuda")
         for _ in range(2):

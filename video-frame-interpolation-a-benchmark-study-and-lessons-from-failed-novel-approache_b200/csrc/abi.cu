@@ -105,6 +105,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!strcmp(key, "conv_v2")) { h->opt_conv_v2 = value; return VFI_OK; }
   if (!strcmp(key, "v2_ablate")) { h->opt_v2_ablate = value; return VFI_OK; }
   if (!strcmp(key, "fuse_gather")) { h->opt_fuse_gather = value; return VFI_OK; }
+  if (!strcmp(key, "v2_tma")) { h->opt_v2_tma = value; return VFI_OK; }
+  if (!strcmp(key, "l2_chunk_mb")) { h->opt_l2_chunk_mb = value; return VFI_OK; }
   if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }
   VFI_FAIL(h, VFI_E_ARG, "unknown option %s", key);
 }
@@ -321,9 +323,21 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       }
       if ((rc = run_conv(h, Lb[1], a0, nullptr, fa, N, hs / 2, wsz / 2, bf, false, s))) return rc;
       uint8_t *cur = fa, *nxt = fb;
-      for (int j = 0; j < 8; j++) {
-        if ((rc = run_conv(h, Lb[2 + j], cur, cur, nxt, N, hs / 4, wsz / 4, bf, false, s))) return rc;
-        std::swap(cur, nxt);
+      {
+        // ResConv chain, depth-first over groups of items: a group's activations (input + output of one layer) stay
+        // under opt_l2_chunk_mb, so layer j+1 reads from L2 what layer j just wrote instead of going to HBM
+        const size_t item_bytes = (size_t)(hs / 4) * (wsz / 4) * BLOCK_C[i] * esz;
+        int grp = N;
+        if (bf && h->opt_l2_chunk_mb > 0) grp = (int)std::max<size_t>(1, std::min<size_t>(N, ((size_t)h->opt_l2_chunk_mb << 20) / (2 * item_bytes)));
+        for (int n0 = 0; n0 < N; n0 += grp) {
+          const int nn = std::min(grp, N - n0);
+          uint8_t *c0 = cur + (size_t)n0 * item_bytes, *c1 = nxt + (size_t)n0 * item_bytes;
+          for (int j = 0; j < 8; j++) {
+            if ((rc = run_conv(h, Lb[2 + j], c0, c0, c1, nn, hs / 4, wsz / 4, bf, false, s))) return rc;
+            std::swap(c0, c1);
+          }
+        }
+        // eight swaps: the chain's result is back in `cur`
       }
       const int lc = i == 4 ? last_c : 16;
       if (bf && i == 4 && h->opt_conv_v2 && Lb[10].wv2) rc = k_conv_v2_last(h, Lb[10], (const bf16*)cur, low[i], lc, N, hs / 4, wsz / 4, s);

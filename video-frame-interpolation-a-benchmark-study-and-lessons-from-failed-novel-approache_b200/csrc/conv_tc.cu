@@ -485,6 +485,26 @@ static int make_tmap_act(vfi_handle* h, CUtensorMap* out, const bf16* base, int 
   tmap_cache()[key] = *out;
   return 0;
 }
+int tc_make_tmap_plain(vfi_handle* h, void* out_tmap, const bf16* base, int C, int W, int H, int N, int bc, int bw, int bh) {
+  CUtensorMap* out = reinterpret_cast<CUtensorMap*>(out_tmap);
+  TmapKey key;
+  memset(&key, 0, sizeof(key));
+  key.p = base; key.d0 = C; key.d1 = W; key.d2 = H; key.d3 = N; key.b0 = bc; key.b1 = bw; key.b2 = bh; key.rank = 14;  // 14: plain
+  auto it = tmap_cache().find(key);
+  if (it != tmap_cache().end()) { *out = it->second; return 0; }
+  PFN_encodeTiled enc;
+  if (int rc = get_encode(h, &enc)) return rc;
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {(cuuint32_t)bc, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, (void*)base, dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) VFI_FAIL(h, VFI_E_CUDA, "cuTensorMapEncodeTiled(plain C=%d W=%d H=%d N=%d box %dx%dx%d) failed: %d", C, W, H, N, bc, bw, bh, (int)r);
+  tmap_cache()[key] = *out;
+  return 0;
+}
 static int make_tmap_w(vfi_handle* h, CUtensorMap* out, const bf16* base, int cblk, int rows, int box_rows) {
   TmapKey key;
   memset(&key, 0, sizeof(key));

@@ -18,6 +18,7 @@
 // Layer semantics: SURVEY.md Appendix A.2 (conv(), ResConv).
 #include <algorithm>
 
+#include <cuda.h>
 #include "common.cuh"
 #include <cuda_fp16.h>
 
@@ -61,15 +62,17 @@ __device__ __forceinline__ unsigned long long v2_now() {
   } while (0)
 
 // COUT here = output channels computed by ONE CTA (the layer's Cout / NSPLIT)
-template <int CIN, int COUT, int KW>
+template <int CIN, int COUT, int KW, bool TMA = false>
 struct V2Cfg {
   static constexpr int NCHUNK = CIN / 8;
   static constexpr int PITCH = 8 * KW + 2;    // halo row pitch in pixels
   static constexpr int NPIX = 18 * PITCH;
   // chunk stride in 16-byte units: >= NPIX, padded so the 8 lanes of a 16-byte store phase (chunk j, pixel p) hit
   // 8 distinct bank groups: (j*CS + p) mod 8 distinct
+  // (TMA loads: every chunk is one tensor box whose destination must be 128-byte aligned -> a multiple of 8)
   static constexpr int cs() {
     int c = NPIX;
+    if (TMA) { while (c % 8) c++; return c; }
     if (NCHUNK >= 8) { while (c % 2 == 0) c++; }
     else if (NCHUNK == 4) { while (c % 8 != 2) c++; }
     else if (NCHUNK == 2) { while (c % 8 != 4) c++; }
@@ -225,11 +228,15 @@ __device__ __forceinline__ uint32_t pk_bf16(float a, float b) {
 // output columns are (output phase p,q) x (4 channels); the epilogue scatters them to the 2x2 output quad.
 // NSPLIT > 1: the layer's output channels are split over NSPLIT groups of CTAs (CTA c serves group c % NSPLIT) so that
 // the group's 9 x CIN x COUT/NSPLIT weight slice stays resident where the whole matrix would not fit (c = 96, 128).
-template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1>
-__global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_constant__ V2Params P) {
+// TMA: the halo tile arrives as NCHUNK tensor boxes {8 ch, PITCH, 18 rows} issued by ONE thread (zero fill outside the image
+// = the padding) instead of ~10 cp.async per producer thread: the tile's 16-byte requests no longer queue in the LSU in
+// front of the epilogue's loads and stores (tools/v2_trace.py: issuing them took 0.8-2.2 us of a 3 us tile period).
+template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1, bool TMA = false>
+__global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_constant__ V2Params P,
+                                                                const __grid_constant__ CUtensorMap tmA) {
   constexpr int CN = COUT / NSPLIT;  // GEMM N of this CTA
   static_assert(COUT % NSPLIT == 0 && CN % 16 == 0, "channel split");
-  using C = V2Cfg<CIN, CN, KW>;
+  using C = V2Cfg<CIN, CN, KW, TMA>;
   const int split = NSPLIT > 1 ? (int)blockIdx.x % NSPLIT : 0;
   const int co0 = split * CN;  // first output channel of this CTA
   const int tile0 = (int)blockIdx.x / NSPLIT, tile_step = (int)gridDim.x / NSPLIT;
@@ -246,7 +253,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
 
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], V2_PRODUCERS / 32); bar_init(&empty_bar[i], use_res ? 1 + V2_EPI_WARPS : 1); }
+    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], TMA ? 1 : V2_PRODUCERS / 32); bar_init(&empty_bar[i], use_res ? 1 + V2_EPI_WARPS : 1); }
     for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], V2_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -271,7 +278,32 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   tc_after();
   const uint32_t tmem_base = tmem_base_smem;
 
-  if (warp < V2_PW) {
+  if (TMA && warp < V2_PW) {
+    // ================= producer (TMA): one thread, NCHUNK tensor boxes per tile =================
+    if (threadIdx.x == 0) {
+      int it = 0;
+      for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
+        const int st = it % P.nstages;
+        const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
+        const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+        V2_TRACE(0, it, 0);  // wants stage
+        bar_wait_relaxed(&empty_bar[st], ph ^ 1);
+        V2_TRACE(0, it, 1);  // got stage
+        const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
+        const uint32_t bar = s_u32(&full_bar[st]);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(C::NCHUNK * C::NPIX * 16))
+                     : "memory");
+#pragma unroll
+        for (int j = 0; j < C::NCHUNK; j++)
+          asm volatile(
+              "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+                  dst + (uint32_t)(j * C::CS * 16)),
+              "l"((uint64_t)&tmA), "r"(bar), "r"(j * 8), "r"(tx * 8 * KW - 1), "r"(ty * 16 - 1), "r"(n)
+              : "memory");
+        V2_TRACE(0, it, 2);  // loads issued
+      }
+    }
+  } else if (warp < V2_PW) {
     // ================= producers: halo tile -> smem [chunk][pixel][8ch] =================
     // cp.async (LDGSTS, 16 B, L2-only) straight into the UMMA layout; zero fill (src-size 0) is the conv padding.
     // Up to V2_DEPTH tiles are in flight per thread: tile i is published (wait_group -> fence.proxy.async -> arrive)
@@ -671,9 +703,14 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
   return 0;
 }
 
-template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1>
+template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1, bool TMA = false>
 static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
-  using C = V2Cfg<CIN, COUT / NSPLIT, KW>;
+  using C = V2Cfg<CIN, COUT / NSPLIT, KW, TMA>;
+  CUtensorMap tmA;
+  memset(&tmA, 0, sizeof(tmA));
+  if (TMA) {
+    if (int rc = tc_make_tmap_plain(h, &tmA, P.in, CIN, P.W, P.H, P.N, 8, C::PITCH, 18)) return rc;
+  }
   const size_t fixed = (size_t)C::W_BYTES + C::BB_BYTES;
   const size_t budget = 220 * 1024 - fixed;
   P.nstages = (int)std::min<size_t>(V2_MAX_STAGES, budget / C::A_BYTES);
@@ -682,10 +719,10 @@ static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
   P.tiles_y = cdiv(P.H, 16);
   P.num_tiles = P.N * P.tiles_x * P.tiles_y;
   const size_t smem = fixed + (size_t)P.nstages * C::A_BYTES;
-  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT>,
+  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
   const int grid = std::min(P.num_tiles, h->sm_count / NSPLIT) * NSPLIT;
-  conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT><<<grid, V2_THREADS, smem, s>>>(P);
+  conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA><<<grid, V2_THREADS, smem, s>>>(P, tmA);
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -712,8 +749,8 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
     int rc;
     switch (L.cin) {
       case 16: rc = launch_v2<16, 16, 4, 0>(h, P, s); break;
-      case 32: rc = launch_v2<32, 32, 4, 0>(h, P, s); break;
-      default: rc = launch_v2<64, 64, 2, 0>(h, P, s); break;
+      case 32: rc = h->opt_v2_tma ? launch_v2<32, 32, 4, 0, 1, true>(h, P, s) : launch_v2<32, 32, 4, 0>(h, P, s); break;
+      default: rc = h->opt_v2_tma ? launch_v2<64, 64, 2, 0, 1, true>(h, P, s) : launch_v2<64, 64, 2, 0>(h, P, s); break;
     }
     if (rc) return rc;
     std::vector<unsigned long long> host(3 * 64 * 8);
@@ -730,11 +767,14 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
     return launch_v2<16, 16, 4, 1>(h, P, s);
   }
   switch (L.cin) {
-    case 16: return launch_v2<16, 16, 4, 0>(h, P, s);
-    case 32: return launch_v2<32, 32, 4, 0>(h, P, s);
-    case 64: return launch_v2<64, 64, 2, 0>(h, P, s);  // KW = 2: 3 stages beside the 72 KB of weights
-    case 96: return launch_v2<96, 96, 1, 0, 2>(h, P, s);    // 2 x 48 output channels: 81 KB of weights per CTA
-    case 128: return launch_v2<128, 128, 1, 0, 4>(h, P, s);  // 4 x 32 output channels: 72 KB of weights per CTA
+    case 16: return h->opt_v2_tma ? launch_v2<16, 16, 4, 0, 1, true>(h, P, s) : launch_v2<16, 16, 4, 0>(h, P, s);
+    case 32: return h->opt_v2_tma ? launch_v2<32, 32, 4, 0, 1, true>(h, P, s) : launch_v2<32, 32, 4, 0>(h, P, s);
+    // KW = 2: 3 stages beside the 72 KB of weights
+    case 64: return h->opt_v2_tma ? launch_v2<64, 64, 2, 0, 1, true>(h, P, s) : launch_v2<64, 64, 2, 0>(h, P, s);
+    // 2 x 48 output channels: 81 KB of weights per CTA
+    case 96: return h->opt_v2_tma ? launch_v2<96, 96, 1, 0, 2, true>(h, P, s) : launch_v2<96, 96, 1, 0, 2>(h, P, s);
+    // 4 x 32 output channels: 72 KB of weights per CTA
+    case 128: return h->opt_v2_tma ? launch_v2<128, 128, 1, 0, 4, true>(h, P, s) : launch_v2<128, 128, 1, 0, 4>(h, P, s);
   }
   VFI_FAIL(h, VFI_E_ARG, "conv_v2: no instance for Cin=%d", L.cin);
 }
