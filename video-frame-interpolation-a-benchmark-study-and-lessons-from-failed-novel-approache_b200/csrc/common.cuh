@@ -76,6 +76,7 @@ struct vfi_handle {
   int opt_l2_chunk_mb = 0;      // vfi_set_option("l2_chunk_mb"): the ResConv chain of a block runs over groups of items whose
                                 // activations (in + out) fit this many MB, so a layer reads what the previous one left in L2; 0 = off
                                 // (measured slower at every size: +15 us of fill / drain per extra launch outweighs the L2 hits)
+  int opt_v2_res_global = 0;    // vfi_set_option("v2_res_global"): ResConv residual read from global memory, not the smem tile (slower)
   int opt_v2_tma = 1;           // vfi_set_option("v2_tma"): conv_v2 halo tiles by TMA (one thread) instead of cp.async producers
   int opt_fuse_gather = 1;      // vfi_set_option("fuse_gather"): finest block's gather fused with conv0[0]
   int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps

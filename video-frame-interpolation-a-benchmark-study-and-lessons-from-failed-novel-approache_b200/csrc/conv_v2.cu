@@ -31,6 +31,7 @@ struct V2Params {
   int N, H, W;
   int tiles_x, tiles_y, num_tiles;
   int nstages;
+  int res_global;  // ResConv residual from global memory (L2) instead of the smem halo tile (measured 2.5 % slower)
   int ablate;  // debug (vfi_set_option "v2_ablate"): 1 skip loads, 2 skip MMAs, 4 skip epilogue math+stores, 8 skip TMEM loads
   int act;
   float slope;
@@ -49,6 +50,9 @@ struct V2Params {
 #define V2_PW (V2_PRODUCERS / 32)  // producer warps; warp V2_PW = MMA issuer; the V2_EPI_WARPS warps after it = epilogue
 #define V2_MAX_STAGES 6
 #define V2_DEPTH 3
+#ifndef V2_TMA_SLIM
+#define V2_TMA_SLIM 0  // 1: TMA instances run 576 threads (one producer warp) with bias / beta in registers (measured 2 % slower)
+#endif
 
 // Compile-time geometry of one (Cin, Cout, KW) instance.
 __device__ __forceinline__ unsigned long long v2_now() {
@@ -231,9 +235,13 @@ __device__ __forceinline__ uint32_t pk_bf16(float a, float b) {
 // TMA: the halo tile arrives as NCHUNK tensor boxes {8 ch, PITCH, 18 rows} issued by ONE thread (zero fill outside the image
 // = the padding) instead of ~10 cp.async per producer thread: the tile's 16-byte requests no longer queue in the LSU in
 // front of the epilogue's loads and stores (tools/v2_trace.py: issuing them took 0.8-2.2 us of a 3 us tile period).
+// TMA instances run one producer warp instead of eight: 576 threads, so the epilogue warps may use up to 112 registers and
+// keep their bias / beta slice in registers (an indexed constant-bank load per use cost ~0.5 us per tile, v2_trace).
 template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1, bool TMA = false>
-__global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_constant__ V2Params P,
-                                                                const __grid_constant__ CUtensorMap tmA) {
+__global__ void __launch_bounds__((TMA && V2_TMA_SLIM) ? 32 + 32 + 32 * V2_EPI_WARPS : V2_THREADS, 1)
+conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUtensorMap tmA) {
+  constexpr int PW_ = (TMA && V2_TMA_SLIM) ? 1 : V2_PW;                              // producer warps; warp PW_ issues the MMAs
+  constexpr int NTHREADS = (TMA && V2_TMA_SLIM) ? 32 + 32 + 32 * V2_EPI_WARPS : V2_THREADS;
   constexpr int CN = COUT / NSPLIT;  // GEMM N of this CTA
   static_assert(COUT % NSPLIT == 0 && CN % 16 == 0, "channel split");
   using C = V2Cfg<CIN, CN, KW, TMA>;
@@ -253,11 +261,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
 
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], TMA ? 1 : V2_PRODUCERS / 32); bar_init(&empty_bar[i], use_res ? 1 + V2_EPI_WARPS : 1); }
+    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], TMA ? 1 : V2_PRODUCERS / 32); bar_init(&empty_bar[i], (use_res && !P.res_global) ? 1 + V2_EPI_WARPS : 1); }
     for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], V2_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == V2_PW) {
+  if (warp == PW_) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(&tmem_base_smem)),
                  "r"((uint32_t)C::TMEM_COLS)
                  : "memory");
@@ -266,8 +274,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   {
     const uint4* src = reinterpret_cast<const uint4*>(P.wpack + (size_t)split * 9 * CIN * CN);
     uint4* dst = reinterpret_cast<uint4*>(w_s);
-    for (int i = threadIdx.x; i < C::W_BYTES / 16; i += V2_THREADS) dst[i] = __ldg(src + i);
-    for (int i = threadIdx.x; i < CN; i += V2_THREADS) {
+    for (int i = threadIdx.x; i < C::W_BYTES / 16; i += NTHREADS) dst[i] = __ldg(src + i);
+    for (int i = threadIdx.x; i < CN; i += NTHREADS) {
       bias_s[i] = P.bias[co0 + i];
       beta_s[i] = use_res ? P.beta[co0 + i] : 1.f;
     }
@@ -278,7 +286,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   tc_after();
   const uint32_t tmem_base = tmem_base_smem;
 
-  if (TMA && warp < V2_PW) {
+  if (TMA && warp < PW_) {
     // ================= producer (TMA): one thread, NCHUNK tensor boxes per tile =================
     if (threadIdx.x == 0) {
       int it = 0;
@@ -303,7 +311,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
         V2_TRACE(0, it, 2);  // loads issued
       }
     }
-  } else if (warp < V2_PW) {
+  } else if (warp < PW_) {
     // ================= producers: halo tile -> smem [chunk][pixel][8ch] =================
     // cp.async (LDGSTS, 16 B, L2-only) straight into the UMMA layout; zero fill (src-size 0) is the conv padding.
     // Up to V2_DEPTH tiles are in flight per thread: tile i is published (wait_group -> fence.proxy.async -> arrive)
@@ -369,7 +377,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     __syncwarp();
     if (lane == 0)
       for (int k = (it < depth ? it : depth); k > 0; k--) bar_arrive(&full_bar[(it - k) % P.nstages]);
-  } else if (warp == V2_PW) {
+  } else if (warp == PW_) {
     // ================= MMA issuer: the warp stays converged, one elected lane issues =================
     const uint32_t leader = elect_one();
     constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(CN >> 3) << 17) | (8u << 24);
@@ -422,7 +430,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     // rows 4y+2p and 4y+2p+1, columns 4x .. 4x+3: 128 contiguous bytes per row and thread.
     static_assert(EPI != 2 || (CN == 80 && KW == 2), "final lastconv instance");
     const int lg = warp & 3;
-    const int role = (warp - V2_PW - 1) >> 2;  // 0..3
+    const int role = (warp - PW_ - 1) >> 2;  // 0..3
     const int j = role & 1, pr = role >> 1;
     const int m = lg * 32 + lane;
     const int ly = m >> 3, lx = m & 7;
@@ -481,7 +489,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     // keeps its slice's bias / beta in registers, pulls its accumulator columns with one tcgen05.wait::ld, hands the
     // TMEM buffer back to the MMA warp, and only then does the bias / residual / activation math and the stores.
     const int lg = warp & 3;                      // TMEM lane group this warp may access
-    const int role = (warp - V2_PW - 1) >> 2;     // 0..3
+    const int role = (warp - PW_ - 1) >> 2;     // 0..3
     constexpr int NSJ = KW >= 2 ? 2 : 1;          // sub-tile classes (j mod NSJ)
     constexpr int Q = 4 / NSJ;                    // warps available per lane group and sub-tile class
     // columns per warp: CN / Q when that is 16 or 32, else 16 (32-byte stores; spare warps only hand-shake), 8 only for
@@ -496,10 +504,18 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
     const bool active = role / NSJ < NSC;
     const int m = lg * 32 + lane;
     const int ly = m >> 3, lx = m & 7;
-    const float* bias_r = P.bias_c + co0 + (active ? cb : 0);  // warp-uniform constant-bank reads
-    const float* beta_r = P.beta_c + co0 + (active ? cb : 0);
+    const float* bias_c = P.bias_c + co0 + (active ? cb : 0);  // warp-uniform constant-bank reads
+    const float* beta_c = P.beta_c + co0 + (active ? cb : 0);
+    constexpr bool REGB = TMA && V2_TMA_SLIM;
+    float bias_v[REGB ? CH : 1], beta_v[REGB ? CH : 1];
+    if constexpr (REGB) {
+#pragma unroll
+      for (int i = 0; i < CH; i++) { bias_v[i] = bias_c[i]; beta_v[i] = beta_c[i]; }
+    }
+    const float* bias_r = REGB ? bias_v : bias_c;
+    const float* beta_r = REGB ? beta_v : beta_c;
     constexpr int NR = CH / 8;
-    const bool tr = warp == V2_PW + 1 && lane == 0;
+    const bool tr = warp == PW_ + 1 && lane == 0;
     int it = 0;
     for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
       const int st = it % P.nstages;
@@ -510,7 +526,17 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
       // release the smem stage right away (the stage then only lives for load + MMA, not for the whole epilogue)
       uint4 res[NJ * NR];
       if (tr) V2_TRACE(2, it, 3);  // tile begin
-      if (use_res) {
+      if (use_res && P.res_global) {
+        if (active)
+#pragma unroll
+        for (int jj = 0; jj < NJ; jj++) {
+          const int x = (tx * KW + jj * NSJ + jc) * 8 + lx;
+          const uint4* rp = reinterpret_cast<const uint4*>(P.in + (((size_t)n * P.H + y) * P.W + x) * CIN + co0 + cb);
+          const bool ok = (y < P.H) && (x < P.W);
+#pragma unroll
+          for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = ok ? __ldg(rp + ch) : make_uint4(0u, 0u, 0u, 0u);
+        }
+      } else if (use_res) {
         bar_wait(&full_bar[st], (uint32_t)((it / P.nstages) & 1));
         if (tr) V2_TRACE(2, it, 4);  // input tile visible
         const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * C::A_BYTES);
@@ -606,7 +632,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) conv_v2_kernel(const __grid_con
   }
   tc_before();
   __syncthreads();
-  if (warp == V2_PW) {
+  if (warp == PW_) {
     tc_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
                  : "memory");
@@ -722,7 +748,7 @@ static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
   VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
   const int grid = std::min(P.num_tiles, h->sm_count / NSPLIT) * NSPLIT;
-  conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA><<<grid, V2_THREADS, smem, s>>>(P, tmA);
+  conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA><<<grid, (TMA && V2_TMA_SLIM) ? 32 + 32 + 32 * V2_EPI_WARPS : V2_THREADS, smem, s>>>(P, tmA);
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -738,6 +764,7 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   P.act = L.act ? 1 : 0;
   P.slope = slope;
   P.ablate = h->opt_v2_ablate;
+  P.res_global = h->opt_v2_res_global;
   for (int i = 0; i < 128; i++) { P.bias_c[i] = L.h_bias_v2[i]; P.beta_c[i] = L.has_beta ? L.h_beta[i] : 1.f; }
   if (h->opt_v2_trace) {
     // debug: time-stamp CTA 0's producer / MMA / epilogue hand-shakes of this launch and dump them for tools/v2_trace.py
