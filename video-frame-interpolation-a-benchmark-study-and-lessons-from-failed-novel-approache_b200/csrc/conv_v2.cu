@@ -791,7 +791,7 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
   if (L.kind == LK_DECONV4 && L.cout == 52) VFI_FAIL(h, VFI_E_ARG, "conv_v2: use k_conv_v2_last for the final lastconv");
   if (L.kind == LK_DECONV4) {
     P.bias = L.bias_v2; P.beta = nullptr; P.act = 0;
-    return launch_v2<16, 16, 4, 1>(h, P, s);
+    return h->opt_v2_tma ? launch_v2<16, 16, 4, 1, 1, true>(h, P, s) : launch_v2<16, 16, 4, 1>(h, P, s);
   }
   switch (L.cin) {
     case 16: return h->opt_v2_tma ? launch_v2<16, 16, 4, 0, 1, true>(h, P, s) : launch_v2<16, 16, 4, 0>(h, P, s);
@@ -818,5 +818,5 @@ int k_conv_v2_last(vfi_handle* h, const Layer& L, const bf16* in, float* low, in
   P.low_out = low; P.low_c = low_c;
   P.N = N; P.H = H; P.W = W;
   for (int i = 0; i < 128; i++) { P.bias_c[i] = L.h_bias_v2[i]; P.beta_c[i] = 1.f; }
-  return launch_v2<32, 80, 2, 2>(h, P, s);
+  return h->opt_v2_tma ? launch_v2<32, 80, 2, 2, 1, true>(h, P, s) : launch_v2<32, 80, 2, 2>(h, P, s);
 }
