@@ -43,8 +43,14 @@ const char* vfi_last_error(vfi_handle* h);
 /* number of kernels this handle has launched since creation (bench.py "gpu_launches") */
 long long vfi_launch_count(vfi_handle* h);
 
-/* Tuning / test knob.  key "conv_v2": 1 (default) routes the stride-1 3x3 convs whose weights fit in shared
- * memory through the resident-weight halo-tile kernel (csrc/conv_v2.cu), 0 keeps them on the TMA-per-tap kernel. */
+/* Tuning / test knobs (defaults are the fastest measured setting; every setting computes the same result):
+ *   "conv_v2"       1: stride-1 3x3 convs whose weights fit in shared memory run on the resident-weight halo-tile
+ *                      kernel (csrc/conv_v2.cu) and the stride-2 ones on csrc/conv_s2.cu; 0: TMA-per-tap kernel.
+ *   "v2_tma"        1: conv_v2 halo tiles arrive by TMA tensor boxes; 0: by cp.async producer warps.
+ *   "fuse_gather"   1: the finest block's input gather is fused with conv0[0] (and hands the summed flow to the blend).
+ *   "v2_res_global" 0: ResConv residual from the shared-memory tile; 1: from global memory.
+ *   "l2_chunk_mb"   0: off; n: run each ResConv chain depth-first over item groups of n MB of activations.
+ *   "v2_ablate", "v2_trace": debug only (tools/bench_conv.py, tools/v2_trace.py). */
 int vfi_set_option(vfi_handle* h, const char* key, int value);
 
 /* IFNet weights.  Replaces Model.load_model(dir, -1) (models/sota/rife_wrapper.py:102-103,

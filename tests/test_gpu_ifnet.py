@@ -58,6 +58,26 @@ def test_parity_uhd_scales(engine, oracle_model, prec, scale, H, W):
     _check(engine, oracle_model, fr[0], fr[1], [0.5], scale, prec)
 
 
+@pytest.mark.parametrize("opts", [{"v2_tma": 0}, {"fuse_gather": 0}, {"conv_v2": 0}, {"v2_res_global": 1}, {"l2_chunk_mb": 1}],
+                         ids=lambda o: ",".join(f"{k}={v}" for k, v in o.items()))
+def test_parity_of_every_kernel_variant(engine, oracle_model, opts):
+    """vfi_set_option only chooses between kernels that compute the same thing: each non-default path (cp.async
+    producers, unfused finest gather + tiled blend, TMA-per-tap convs, residual from global memory, depth-first
+    ResConv chain) meets the bf16 tolerance against the oracle on its own."""
+    defaults = {"v2_tma": 1, "fuse_gather": 1, "conv_v2": 1, "v2_res_global": 0, "l2_chunk_mb": 0}
+    fr = gen_clip(2, 160, 224, seed=11, cut_every=0, fast=None)
+    try:
+        for k, v in opts.items():
+            engine.set_option(k, v)
+        _check(engine, oracle_model, fr[0], fr[1], TS, 1.0, _abi.PRECISION_BF16)
+        two = engine.infer(fr[:2], fr[1:3], TS, 1.0, _abi.PRECISION_BF16).cpu().numpy()       # batch of 2: item groups
+        one = engine.infer(fr[1][None], fr[2][None], TS, 1.0, _abi.PRECISION_BF16).cpu().numpy()
+        assert np.array_equal(two[1], one[0])
+    finally:
+        for k, v in defaults.items():
+            engine.set_option(k, v)
+
+
 def test_timestep_edge_values(engine, oracle_model):
     fr = gen_clip(1, 128, 192, seed=3, cut_every=0, fast=None)
     _check(engine, oracle_model, fr[0], fr[1], [0.0, 1.0, 0.125], 1.0, _abi.PRECISION_FP32)
