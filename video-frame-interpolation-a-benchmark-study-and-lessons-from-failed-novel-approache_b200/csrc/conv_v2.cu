@@ -50,6 +50,11 @@ struct V2Params {
 #define V2_PW (V2_PRODUCERS / 32)  // producer warps; warp V2_PW = MMA issuer; the V2_EPI_WARPS warps after it = epilogue
 #define V2_MAX_STAGES 6
 #define V2_DEPTH 3
+#ifndef V2_TMA_CHUNKS
+// chunks (of NCHUNK = Cin/8) a TMA instance loads by TMA; the rest would come through the cp.async producers.  All of
+// them: splitting the tile half / half between the two paths measured 8-12 % SLOWER than TMA alone on every instance.
+#define V2_TMA_CHUNKS(n) (n)
+#endif
 #ifndef V2_TMA_SLIM
 #define V2_TMA_SLIM 0  // 1: TMA instances run 576 threads (one producer warp) with bias / beta in registers (measured 2 % slower)
 #endif
@@ -245,6 +250,9 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
   constexpr int CN = COUT / NSPLIT;  // GEMM N of this CTA
   static_assert(COUT % NSPLIT == 0 && CN % 16 == 0, "channel split");
   using C = V2Cfg<CIN, CN, KW, TMA>;
+  constexpr int TJ = TMA ? V2_TMA_CHUNKS(C::NCHUNK) : 0;  // chunks loaded by TMA
+  constexpr bool ALL_TMA = TMA && TJ == C::NCHUNK;
+  static_assert(!(V2_TMA_SLIM && TMA) || ALL_TMA, "the slim variant has no cp.async producers");
   const int split = NSPLIT > 1 ? (int)blockIdx.x % NSPLIT : 0;
   const int co0 = split * CN;  // first output channel of this CTA
   const int tile0 = (int)blockIdx.x / NSPLIT, tile_step = (int)gridDim.x / NSPLIT;
@@ -261,7 +269,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
 
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], TMA ? 1 : V2_PRODUCERS / 32); bar_init(&empty_bar[i], (use_res && !P.res_global) ? 1 + V2_EPI_WARPS : 1); }
+    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], ALL_TMA ? 1 : V2_PRODUCERS / 32 + (TJ > 0 ? 1 : 0)); bar_init(&empty_bar[i], (use_res && !P.res_global) ? 1 + V2_EPI_WARPS : 1); }
     for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], V2_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -286,7 +294,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
   tc_after();
   const uint32_t tmem_base = tmem_base_smem;
 
-  if (TMA && warp < PW_) {
+  if (ALL_TMA && warp < PW_) {
     // ================= producer (TMA): one thread, NCHUNK tensor boxes per tile =================
     if (threadIdx.x == 0) {
       int it = 0;
@@ -318,17 +326,20 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     // while tiles i+1..i+V2_DEPTH are still streaming in.  The copy list of a thread does not depend on the tile:
     //   meta = smem offset (16-byte units, bits 0-13) | halo row << 14 | halo col << 19 | unused << 31
     //   srel = source element offset relative to the halo origin
-    constexpr int ROW_ITEMS = C::PITCH * C::NCHUNK;
-    constexpr int PER_THREAD = (C::TOTAL_ITEMS + V2_PRODUCERS - 1) / V2_PRODUCERS;
+    // chunks TJ .. NCHUNK-1 come through cp.async (all of them without TMA; the branch is dead for an all-TMA instance)
+    constexpr int NC = C::NCHUNK - TJ > 0 ? C::NCHUNK - TJ : 1;
+    constexpr int ROW_ITEMS = C::PITCH * NC;
+    constexpr int TOTAL_ITEMS = C::NPIX * NC;
+    constexpr int PER_THREAD = (TOTAL_ITEMS + V2_PRODUCERS - 1) / V2_PRODUCERS;
     uint32_t meta[PER_THREAD];
     int srel[PER_THREAD];
 #pragma unroll
     for (int u = 0; u < PER_THREAD; u++) {
       const int i = (int)threadIdx.x + u * V2_PRODUCERS;
       const int py = i / ROW_ITEMS, rem = i - py * ROW_ITEMS;
-      const int px = rem / C::NCHUNK, j = rem - px * C::NCHUNK;
+      const int px = rem / NC, j = TJ + rem - px * NC;
       meta[u] = (uint32_t)(j * C::CS + py * C::PITCH + px) | ((uint32_t)py << 14) | ((uint32_t)px << 19) |
-                (i >= C::TOTAL_ITEMS ? 0x80000000u : 0u);
+                (i >= TOTAL_ITEMS ? 0x80000000u : 0u);
       srel[u] = (py * P.W + px) * CIN + j * 8;
     }
     // tiles in flight per thread.  A tile is published when the producer comes round `depth` iterations later, i.e.
@@ -355,6 +366,17 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
       bar_wait_relaxed(&empty_bar[st], ph ^ 1);
       if (threadIdx.x == 0) V2_TRACE(0, it, 1);  // got stage
       const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
+      if (TJ > 0 && threadIdx.x == 0) {  // the tile's first TJ chunks: tensor boxes, counted on the same full barrier
+        const uint32_t bar = s_u32(&full_bar[st]);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(TJ * C::NPIX * 16)) : "memory");
+#pragma unroll
+        for (int j = 0; j < TJ; j++)
+          asm volatile(
+              "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+                  dst + (uint32_t)(j * C::CS * 16)),
+              "l"((uint64_t)&tmA), "r"(bar), "r"(j * 8), "r"(gx0), "r"(gy0), "r"(n)
+              : "memory");
+      }
       const bf16* img = P.in + (size_t)n * P.H * P.W * CIN;
       const bf16* org = img + ((ptrdiff_t)gy0 * P.W + gx0) * CIN;  // halo origin (may lie outside the image)
       if (!(P.ablate & 1)) {
