@@ -569,6 +569,8 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
 #pragma unroll
           for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = a_st[((co0 + cb) / 8 + ch) * C::CS + pc];
         }
+        // the stage is refilled by TMA (async proxy): these generic-proxy reads must be ordered before that write
+        if (TMA) fence_async_smem();
         __syncwarp();
         if (lane == 0) bar_arrive(&empty_bar[st]);
       }
