@@ -38,8 +38,9 @@ def test_bf16_tracks_fp32_mode_1080p(engine, clip1080):
 
 def test_determinism_and_batch_invariance_1080p(engine, clip1080):
     x = engine.infer(clip1080[:2], clip1080[1:3], TS, 1.0, _abi.PRECISION_BF16).clone()
-    y = engine.infer(clip1080[:2], clip1080[1:3], TS, 1.0, _abi.PRECISION_BF16)
-    assert torch.equal(x, y)
+    for _ in range(4):      # a pipeline race shows as a run-to-run difference (persistent CTAs, many tiles per CTA at this size)
+        y = engine.infer(clip1080[:2], clip1080[1:3], TS, 1.0, _abi.PRECISION_BF16)
+        assert torch.equal(x, y)
     z = engine.infer(clip1080[1][None], clip1080[2][None], [0.75], 1.0, _abi.PRECISION_BF16)
     assert torch.equal(z[0, 0], x[1, 2])
 
