@@ -48,6 +48,7 @@ long long vfi_launch_count(vfi_handle* h);
  *                      kernel (csrc/conv_v2.cu) and the stride-2 ones on csrc/conv_s2.cu; 0: TMA-per-tap kernel.
  *   "v2_tma"        1: conv_v2 halo tiles arrive by TMA tensor boxes; 0: by cp.async producer warps.
  *   "fuse_gather"   1: the finest block's input gather is fused with conv0[0] (and hands the summed flow to the blend).
+ *   "v2_pm"         0: chunk-major halo tile (16-byte TMA box rows); 1: c = 64 layers use a pixel-major SWIZZLE_128B tile.
  *   "v2_res_global" 0: ResConv residual from the shared-memory tile; 1: from global memory.
  *   "l2_chunk_mb"   0: off; n: run each ResConv chain depth-first over item groups of n MB of activations.
  *   "v2_ablate", "v2_trace": debug only (tools/bench_conv.py, tools/v2_trace.py). */

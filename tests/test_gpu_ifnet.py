@@ -58,13 +58,13 @@ def test_parity_uhd_scales(engine, oracle_model, prec, scale, H, W):
     _check(engine, oracle_model, fr[0], fr[1], [0.5], scale, prec)
 
 
-@pytest.mark.parametrize("opts", [{"v2_tma": 0}, {"fuse_gather": 0}, {"conv_v2": 0}, {"v2_res_global": 1}, {"l2_chunk_mb": 1}],
+@pytest.mark.parametrize("opts", [{"v2_tma": 0}, {"fuse_gather": 0}, {"conv_v2": 0}, {"v2_res_global": 1}, {"l2_chunk_mb": 1}, {"v2_pm": 1}],
                          ids=lambda o: ",".join(f"{k}={v}" for k, v in o.items()))
 def test_parity_of_every_kernel_variant(engine, oracle_model, opts):
     """vfi_set_option only chooses between kernels that compute the same thing: each non-default path (cp.async
     producers, unfused finest gather + tiled blend, TMA-per-tap convs, residual from global memory, depth-first
-    ResConv chain) meets the bf16 tolerance against the oracle on its own."""
-    defaults = {"v2_tma": 1, "fuse_gather": 1, "conv_v2": 1, "v2_res_global": 0, "l2_chunk_mb": 0}
+    ResConv chain, pixel-major swizzled c = 64 tiles) meets the bf16 tolerance against the oracle on its own."""
+    defaults = {"v2_tma": 1, "fuse_gather": 1, "conv_v2": 1, "v2_res_global": 0, "l2_chunk_mb": 0, "v2_pm": 0}
     fr = gen_clip(2, 160, 224, seed=11, cut_every=0, fast=None)
     try:
         for k, v in opts.items():
@@ -175,6 +175,14 @@ def test_conv_v2_halo_tile_kernel(engine, weights, layer, Hin, Win):
     scale = max(1.0, ref.abs().max().item())
     assert (y2 - ref).abs().max().item() <= 1.5e-2 * scale
     assert (y2 - y1).abs().max().item() <= 1.0e-2 * scale          # same operands, different accumulation order + bf16 store
+    if li["cin"] == 64:     # the pixel-major (SWIZZLE_128B, tap-shifted descriptors) and cp.async-fed variants: same MMAs, same bits
+        for opt in ("v2_pm", "v2_tma"):
+            try:
+                engine.set_option(opt, 1 if opt == "v2_pm" else 0)
+                y3 = engine.debug_conv(layer, _abi.PRECISION_BF16, x, None)
+            finally:
+                engine.set_option(opt, 0 if opt == "v2_pm" else 1)
+            assert torch.equal(y3, y2), opt
 
 
 @pytest.mark.parametrize("layer", [15, 26, 27, 37, 38, 48, 49])

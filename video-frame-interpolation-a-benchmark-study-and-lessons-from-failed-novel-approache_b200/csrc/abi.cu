@@ -106,6 +106,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!strcmp(key, "v2_ablate")) { h->opt_v2_ablate = value; return VFI_OK; }
   if (!strcmp(key, "fuse_gather")) { h->opt_fuse_gather = value; return VFI_OK; }
   if (!strcmp(key, "v2_res_global")) { h->opt_v2_res_global = value; return VFI_OK; }
+  if (!strcmp(key, "v2_pm")) { h->opt_v2_pm = value; return VFI_OK; }
   if (!strcmp(key, "v2_tma")) { h->opt_v2_tma = value; return VFI_OK; }
   if (!strcmp(key, "l2_chunk_mb")) { h->opt_l2_chunk_mb = value; return VFI_OK; }
   if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }

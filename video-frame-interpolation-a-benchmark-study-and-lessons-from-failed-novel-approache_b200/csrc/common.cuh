@@ -77,6 +77,8 @@ struct vfi_handle {
                                 // activations (in + out) fit this many MB, so a layer reads what the previous one left in L2; 0 = off
                                 // (measured slower at every size: +15 us of fill / drain per extra launch outweighs the L2 hits)
   int opt_v2_res_global = 0;    // vfi_set_option("v2_res_global"): ResConv residual read from global memory, not the smem tile (slower)
+  int opt_v2_pm = 0;            // vfi_set_option("v2_pm"): pixel-major 128-byte-swizzled halo tiles for c = 64 (one wide TMA box per
+                                // tile, tap-shifted SWIZZLE_128B descriptors); same speed as the chunk-major tile, kept as a variant
   int opt_v2_tma = 1;           // vfi_set_option("v2_tma"): conv_v2 halo tiles by TMA (one thread) instead of cp.async producers
   int opt_fuse_gather = 1;      // vfi_set_option("fuse_gather"): finest block's gather fused with conv0[0]
   int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps
@@ -222,6 +224,8 @@ int tc_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch); 
 int k_conv_tc(vfi_handle* h, const Layer& L, const bf16* in, const bf16* residual, void* out, int N, int Hin,
               int Win, bool out_phase, float slope, cudaStream_t s, int low_c = 16, const LowPlanes* planes = nullptr);
 // plain (no swizzle) 4-D tensor map over a bf16 NHWC tensor, box {bc, bw, bh, 1}, zero fill outside
+// 128-byte-swizzled map, box {64 ch, bw, bh, 1}
+int tc_make_tmap_sw128(vfi_handle* h, void* out_tmap, const bf16* base, int C, int W, int H, int N, int bw, int bh);
 int tc_make_tmap_plain(vfi_handle* h, void* out_tmap, const bf16* base, int C, int W, int H, int N, int bc, int bw, int bh);
 int k_unpack_planes(vfi_handle* h, const LowPlanes& pl, float* out16, size_t texels, cudaStream_t s);
 

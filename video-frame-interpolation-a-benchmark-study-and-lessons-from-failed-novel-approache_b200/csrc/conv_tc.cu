@@ -485,6 +485,9 @@ static int make_tmap_act(vfi_handle* h, CUtensorMap* out, const bf16* base, int 
   tmap_cache()[key] = *out;
   return 0;
 }
+int tc_make_tmap_sw128(vfi_handle* h, void* out_tmap, const bf16* base, int C, int W, int H, int N, int bw, int bh) {
+  return make_tmap_act(h, reinterpret_cast<CUtensorMap*>(out_tmap), base, C, W, H, N, 64, bw, bh);
+}
 int tc_make_tmap_plain(vfi_handle* h, void* out_tmap, const bf16* base, int C, int W, int H, int N, int bc, int bw, int bh) {
   CUtensorMap* out = reinterpret_cast<CUtensorMap*>(out_tmap);
   TmapKey key;

@@ -55,6 +55,9 @@ struct V2Params {
 // them: splitting the tile half / half between the two paths measured 8-12 % SLOWER than TMA alone on every instance.
 #define V2_TMA_CHUNKS(n) (n)
 #endif
+#ifndef V2_PM_BASEOFF
+#define V2_PM_BASEOFF 0
+#endif
 #ifndef V2_TMA_SLIM
 #define V2_TMA_SLIM 0  // 1: TMA instances run 576 threads (one producer warp) with bias / beta in registers (measured 2 % slower)
 #endif
@@ -71,8 +74,12 @@ __device__ __forceinline__ unsigned long long v2_now() {
   } while (0)
 
 // COUT here = output channels computed by ONE CTA (the layer's Cout / NSPLIT)
-template <int CIN, int COUT, int KW, bool TMA = false>
+template <int CIN, int COUT, int KW, bool TMA = false, bool PM = false>
 struct V2Cfg {
+  // PM (pixel-major): the halo tile is [Cin/64][pixel][64 ch], one 128-byte row per pixel and 64-channel block, written by
+  // ONE TMA box per block with the 128-byte swizzle (128-byte box rows instead of 16-byte ones), read by K-major SWIZZLE_128B
+  // descriptors whose start address is shifted per tap (base_offset keeps the swizzle phase)
+  static constexpr int NKB = CIN / 64;
   static constexpr int NCHUNK = CIN / 8;
   static constexpr int PITCH = 8 * KW + 2;    // halo row pitch in pixels
   static constexpr int NPIX = 18 * PITCH;
@@ -88,9 +95,10 @@ struct V2Cfg {
     return c;
   }
   static constexpr int CS = cs();
-  static constexpr int A_BYTES = (NCHUNK * CS * 16 + 127) & ~127;
+  static constexpr int A_BYTES = PM ? ((NKB * NPIX * 128 + 1023) & ~1023) : ((NCHUNK * CS * 16 + 127) & ~127);
   static constexpr int W_BYTES = 9 * CIN * COUT * 2;
-  static constexpr int BB_BYTES = (2 * COUT * 4 + 127) & ~127;
+  static constexpr int BB_BYTES = PM ? 1024 : ((2 * COUT * 4 + 127) & ~127);
+  static_assert(!PM || (TMA && CIN % 64 == 0 && W_BYTES % 1024 == 0), "pixel-major tiles: 64-channel blocks, 1024-byte aligned stages");
   static constexpr int ACC_COLS = KW * COUT;  // accumulator columns of one tile
   static constexpr int TMEM_COLS = 2 * ACC_COLS <= 32 ? 32 : 2 * ACC_COLS <= 64 ? 64 : 2 * ACC_COLS <= 128 ? 128
                                    : 2 * ACC_COLS <= 256 ? 256 : 512;
@@ -242,21 +250,21 @@ __device__ __forceinline__ uint32_t pk_bf16(float a, float b) {
 // front of the epilogue's loads and stores (tools/v2_trace.py: issuing them took 0.8-2.2 us of a 3 us tile period).
 // TMA instances run one producer warp instead of eight: 576 threads, so the epilogue warps may use up to 112 registers and
 // keep their bias / beta slice in registers (an indexed constant-bank load per use cost ~0.5 us per tile, v2_trace).
-template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1, bool TMA = false>
+template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1, bool TMA = false, bool PM = false>
 __global__ void __launch_bounds__((TMA && V2_TMA_SLIM) ? 32 + 32 + 32 * V2_EPI_WARPS : V2_THREADS, 1)
 conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUtensorMap tmA) {
   constexpr int PW_ = (TMA && V2_TMA_SLIM) ? 1 : V2_PW;                              // producer warps; warp PW_ issues the MMAs
   constexpr int NTHREADS = (TMA && V2_TMA_SLIM) ? 32 + 32 + 32 * V2_EPI_WARPS : V2_THREADS;
   constexpr int CN = COUT / NSPLIT;  // GEMM N of this CTA
   static_assert(COUT % NSPLIT == 0 && CN % 16 == 0, "channel split");
-  using C = V2Cfg<CIN, CN, KW, TMA>;
+  using C = V2Cfg<CIN, CN, KW, TMA, PM>;
   constexpr int TJ = TMA ? V2_TMA_CHUNKS(C::NCHUNK) : 0;  // chunks loaded by TMA
   constexpr bool ALL_TMA = TMA && TJ == C::NCHUNK;
   static_assert(!(V2_TMA_SLIM && TMA) || ALL_TMA, "the slim variant has no cp.async producers");
   const int split = NSPLIT > 1 ? (int)blockIdx.x % NSPLIT : 0;
   const int co0 = split * CN;  // first output channel of this CTA
   const int tile0 = (int)blockIdx.x / NSPLIT, tile_step = (int)gridDim.x / NSPLIT;
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t full_bar[V2_MAX_STAGES], empty_bar[V2_MAX_STAGES], tfull_bar[2], tempty_bar[2];
   __shared__ uint32_t tmem_base_smem;
 
@@ -307,6 +315,17 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
         V2_TRACE(0, it, 1);  // got stage
         const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
         const uint32_t bar = s_u32(&full_bar[st]);
+        if constexpr (PM) {
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(C::NKB * C::NPIX * 128))
+                       : "memory");
+#pragma unroll
+          for (int kb = 0; kb < C::NKB; kb++)
+            asm volatile(
+                "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+                    dst + (uint32_t)(kb * C::NPIX * 128)),
+                "l"((uint64_t)&tmA), "r"(bar), "r"(kb * 64), "r"(tx * 8 * KW - 1), "r"(ty * 16 - 1), "r"(n)
+                : "memory");
+        } else {
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(C::NCHUNK * C::NPIX * 16))
                      : "memory");
 #pragma unroll
@@ -316,6 +335,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
                   dst + (uint32_t)(j * C::CS * 16)),
               "l"((uint64_t)&tmA), "r"(bar), "r"(j * 8), "r"(tx * 8 * KW - 1), "r"(ty * 16 - 1), "r"(n)
               : "memory");
+        }
         V2_TRACE(0, it, 2);  // loads issued
       }
     }
@@ -417,7 +437,8 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
       bar_wait(&full_bar[st], ph);
       if (leader) V2_TRACE(1, it, 2);  // tile landed
       tc_after();
-      const uint64_t ad0 = desc_ns(s_u32(a_s + (size_t)st * C::A_BYTES), A_LBO, A_SBO);
+      const uint32_t a_base = s_u32(a_s + (size_t)st * C::A_BYTES);
+      const uint64_t ad0 = desc_ns(a_base, A_LBO, A_SBO);
       if (!(P.ablate & 2)) {
       const uint32_t dcol0 = tmem_base + (uint32_t)(as * C::ACC_STRIDE);
       // consecutive MMAs target different accumulators (j innermost) so they pipeline; all descriptor offsets are
@@ -430,9 +451,19 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
           for (int j = 0; j < KW; j++) {
             constexpr int dummy = 0;
             (void)dummy;
-            const uint32_t a_off = (uint32_t)((tap / 3) * C::PITCH + (tap % 3) + 8 * j + 2 * k * C::CS);
             const uint32_t b_off = (uint32_t)((tap * C::NCHUNK + 2 * k) * CN);
+            if constexpr (PM) {
+              // K-major SWIZZLE_128B: rows = pixels (128 B apart), 8-row group = 8 consecutive x, next group = next y;
+              // k-step = 32 B inside the row; base_offset = the row phase of the (unaligned) start inside the 1024 B pattern
+              const uint32_t addr = a_base + (uint32_t)((k / 4) * C::NPIX * 128 + ((tap / 3) * C::PITCH + (tap % 3) + 8 * j) * 128 +
+                                                         (k % 4) * 32);
+              uint64_t d = (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(C::PITCH * 8) << 32) |
+                           ((uint64_t)1 << 46) | ((uint64_t)(V2_PM_BASEOFF ? ((addr >> 7) & 7) : 0) << 49) | ((uint64_t)2 << 61);
+              mma_bf16_elect(leader, dcol0 + (uint32_t)(j * CN), d, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
+            } else {
+            const uint32_t a_off = (uint32_t)((tap / 3) * C::PITCH + (tap % 3) + 8 * j + 2 * k * C::CS);
             mma_bf16_elect(leader, dcol0 + (uint32_t)(j * CN), ad0 + a_off, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
+            }
           }
         }
       }
@@ -567,7 +598,18 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
         for (int jj = 0; jj < NJ; jj++) {
           const int pc = (ly + 1) * C::PITCH + 8 * (jj * NSJ + jc) + lx + 1;  // this thread's centre pixel
 #pragma unroll
-          for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = a_st[((co0 + cb) / 8 + ch) * C::CS + pc];
+          for (int ch = 0; ch < NR; ch++) {
+            if constexpr (PM) {
+              const int c8 = (co0 + cb) / 8 + ch;  // 16-byte unit of the pixel's channels
+              const uint32_t row = s_u32(a_s + (size_t)st * C::A_BYTES) + (uint32_t)((c8 >> 3) * C::NPIX * 128 + pc * 128);
+              const uint32_t ad = row + (uint32_t)(((c8 & 7) ^ ((row >> 7) & 7)) << 4);
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(res[jj * NR + ch].x), "=r"(res[jj * NR + ch].y), "=r"(res[jj * NR + ch].z), "=r"(res[jj * NR + ch].w)
+                           : "r"(ad));
+            } else {
+              res[jj * NR + ch] = a_st[((co0 + cb) / 8 + ch) * C::CS + pc];
+            }
+          }
         }
         // the stage is refilled by TMA (async proxy): these generic-proxy reads must be ordered before that write
         if (TMA) fence_async_smem();
@@ -753,13 +795,14 @@ int v2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w) {
   return 0;
 }
 
-template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1, bool TMA = false>
+template <int CIN, int COUT, int KW, int EPI, int NSPLIT = 1, bool TMA = false, bool PM = false>
 static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
-  using C = V2Cfg<CIN, COUT / NSPLIT, KW, TMA>;
+  using C = V2Cfg<CIN, COUT / NSPLIT, KW, TMA, PM>;
   CUtensorMap tmA;
   memset(&tmA, 0, sizeof(tmA));
   if (TMA) {
-    if (int rc = tc_make_tmap_plain(h, &tmA, P.in, CIN, P.W, P.H, P.N, 8, C::PITCH, 18)) return rc;
+    if (PM) { if (int rc = tc_make_tmap_sw128(h, &tmA, P.in, CIN, P.W, P.H, P.N, C::PITCH, 18)) return rc; }
+    else if (int rc = tc_make_tmap_plain(h, &tmA, P.in, CIN, P.W, P.H, P.N, 8, C::PITCH, 18)) return rc;
   }
   const size_t fixed = (size_t)C::W_BYTES + C::BB_BYTES;
   const size_t budget = 220 * 1024 - fixed;
@@ -769,10 +812,10 @@ static int launch_v2(vfi_handle* h, V2Params& P, cudaStream_t s) {
   P.tiles_y = cdiv(P.H, 16);
   P.num_tiles = P.N * P.tiles_x * P.tiles_y;
   const size_t smem = fixed + (size_t)P.nstages * C::A_BYTES;
-  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA>,
+  VFI_CUDA(h, cudaFuncSetAttribute(conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA, PM>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
   const int grid = std::min(P.num_tiles, h->sm_count / NSPLIT) * NSPLIT;
-  conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA><<<grid, (TMA && V2_TMA_SLIM) ? 32 + 32 + 32 * V2_EPI_WARPS : V2_THREADS, smem, s>>>(P, tmA);
+  conv_v2_kernel<CIN, COUT, KW, EPI, NSPLIT, TMA, PM><<<grid, (TMA && V2_TMA_SLIM) ? 32 + 32 + 32 * V2_EPI_WARPS : V2_THREADS, smem, s>>>(P, tmA);
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -821,7 +864,8 @@ int k_conv_v2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, i
     case 16: return h->opt_v2_tma ? launch_v2<16, 16, 4, 0, 1, true>(h, P, s) : launch_v2<16, 16, 4, 0>(h, P, s);
     case 32: return h->opt_v2_tma ? launch_v2<32, 32, 4, 0, 1, true>(h, P, s) : launch_v2<32, 32, 4, 0>(h, P, s);
     // KW = 2: 3 stages beside the 72 KB of weights
-    case 64: return h->opt_v2_tma ? launch_v2<64, 64, 2, 0, 1, true>(h, P, s) : launch_v2<64, 64, 2, 0>(h, P, s);
+    case 64: return (h->opt_v2_tma && h->opt_v2_pm) ? launch_v2<64, 64, 2, 0, 1, true, true>(h, P, s)
+           : h->opt_v2_tma ? launch_v2<64, 64, 2, 0, 1, true>(h, P, s) : launch_v2<64, 64, 2, 0>(h, P, s);
     // 2 x 48 output channels: 81 KB of weights per CTA
     case 96: return h->opt_v2_tma ? launch_v2<96, 96, 1, 0, 2, true>(h, P, s) : launch_v2<96, 96, 1, 0, 2>(h, P, s);
     // 4 x 32 output channels: 72 KB of weights per CTA
