@@ -37,6 +37,24 @@ def peaks():
     return 6650.0, 1590.0, 1400.0, "fallback"
 
 
+def ncu_conv_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per tcgen05 conv launch (bytes, average over the step's conv launches) from
+    the committed ncu launch list of this workload, profiles/r01_launches_final.txt; None if that file is absent."""
+    import re
+    path = os.path.join(ROOT, "profiles", "r01_launches_final.txt")
+    if not os.path.exists(path):
+        return None
+    tot, n = 0.0, 0
+    for ln in open(path):
+        if ln.startswith("#") or not re.search(r"conv_(v2|s2|tc)_kernel", ln):
+            continue
+        m = re.search(r"rd\s+([\d.]+) MB\s+wr\s+([\d.]+) MB", ln)
+        if m:
+            tot += (float(m.group(1)) + float(m.group(2))) * 1e6
+            n += 1
+    return tot / n if n else None
+
+
 def tc_flops_per_batch(B, T, Hp, Wp, n_images, fused_conv0a):
     """Algorithmic (dense, unpadded channels) FLOPs of the tcgen05 conv launches of one batch, as executed:
     the Head runs once per distinct frame (n_images); with the finest block's conv0[0] fused into the gather
@@ -314,7 +332,7 @@ def main():
             roof = {"kernel": "tcgen05 implicit-GEMM conv kernels (conv_v2 / conv_s2 / conv_tc: every conv launch of the step "
                               "except the one fused into the gather)",
                     "bound": "tensor", "achieved": ach, "peak": tf_sust, "unit": "TFLOP/s", "frac": ach / tf_sust,
-                    "traffic": None, "peak_source": f"{src} bf16_tflops_sustained", "launches": tc_n // psteps,
+                    "traffic": ncu_conv_traffic(), "peak_source": f"{src} bf16_tflops_sustained", "launches": tc_n // psteps,
                     "avg_launch_us": tc_ms / tc_n * 1000.0, "algorithmic_gflop_per_step": fl / 1e9,
                     "note": "N = 16..64 output channels per MMA: the A operand read from shared memory (4 KB per "
                             "128x16 MMA at 128 B/clk) bounds these layers at 25-50 % of the tensor pipe; see DESIGN.md"}
