@@ -20,7 +20,9 @@ if args and args[0] == "--layer":
     CASES = [c for c in CASES if c[0] == int(args[1])]
     args = args[2:]
 masks = [int(a) for a in args] or [0]
+NSCALE = float(os.environ.get("BC_NSCALE", "1"))   # scales the item count: slope = per-tile cost, intercept = launch cost
 for layer, N, H, W in CASES:
+    N = max(1, int(N * NSCALE))
     li = layer_info(layer)
     x = torch.randn((N, H, W, li["cin_pad"]), device="cuda")
     for m in masks:

@@ -15,7 +15,7 @@ def show(path, ntiles=24):
     t0 = t[t > 0].min()
     r = np.where(t > 0, t - t0, -1)
     print(path)
-    print("tile | prod: want  got  issued  published | mma: start accfree landed issued | epi: begin visible res-read accdone ld0 ld1 released stored  (ns)")
+    print("tile | prod: want  got  issued  published | mma: start accfree landed issued | epi: begin visible res-read accdone ld0 ld1 released stored  (SM cycles)")
     for k in range(ntiles):
         if r[0, k, 0] < 0 and r[1, k, 0] < 0:
             break
@@ -39,7 +39,9 @@ else:
         x = torch.randn((N, H, W, li["cin_pad"]), device="cuda")
         for _ in range(2):
             e.debug_conv(layer, _abi.PRECISION_BF16, x, None)
+        e.set_option("v2_ablate", int(os.environ.get("V2_TRACE_ABLATE", "0")))
         e.set_option("v2_trace", 1)
         e.debug_conv(layer, _abi.PRECISION_BF16, x, None)
         e.set_option("v2_trace", 0)
+        e.set_option("v2_ablate", 0)
         show(f"gpurun_out/v2_trace_c{li['cin']}.bin")

@@ -50,6 +50,9 @@ struct V2Params {
 #define V2_PW (V2_PRODUCERS / 32)  // producer warps; warp V2_PW = MMA issuer; the V2_EPI_WARPS warps after it = epilogue
 #define V2_MAX_STAGES 6
 #define V2_DEPTH 3
+#ifndef V2_NACC_MAX
+#define V2_NACC_MAX 4
+#endif
 #ifndef V2_TMA_CHUNKS
 // chunks (of NCHUNK = Cin/8) a TMA instance loads by TMA; the rest would come through the cp.async producers.  All of
 // them: splitting the tile half / half between the two paths measured 8-12 % SLOWER than TMA alone on every instance.
@@ -65,7 +68,7 @@ struct V2Params {
 // Compile-time geometry of one (Cin, Cout, KW) instance.
 __device__ __forceinline__ unsigned long long v2_now() {
   unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));  // SM cycle counter: ~20 cycles a stamp (%globaltimer cost 0.3-0.5 us)
   return t;
 }
 #define V2_TRACE(role, tile_i, ev)                                                              \
@@ -100,9 +103,12 @@ struct V2Cfg {
   static constexpr int BB_BYTES = PM ? 1024 : ((2 * COUT * 4 + 127) & ~127);
   static_assert(!PM || (TMA && CIN % 64 == 0 && W_BYTES % 1024 == 0), "pixel-major tiles: 64-channel blocks, 1024-byte aligned stages");
   static constexpr int ACC_COLS = KW * COUT;  // accumulator columns of one tile
-  static constexpr int TMEM_COLS = 2 * ACC_COLS <= 32 ? 32 : 2 * ACC_COLS <= 64 ? 64 : 2 * ACC_COLS <= 128 ? 128
-                                   : 2 * ACC_COLS <= 256 ? 256 : 512;
-  static constexpr int ACC_STRIDE = TMEM_COLS / 2;  // the two accumulator buffers start on power-of-two columns
+  // TMEM accumulator ring: up to four buffers, each on a power-of-two column stride.  Two were not enough: handing a
+  // buffer from the MMA warp to the epilogue and back (commit -> mbarrier -> tcgen05.ld -> arrive -> poll) takes ~2.9 us
+  // with no work at all (v2_ablate = 7: 1.45 us per tile), longer than the tile's 1.7 us of MMAs
+  static constexpr int ACC_STRIDE = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128 : 256;
+  static constexpr int NACC = 512 / ACC_STRIDE < V2_NACC_MAX ? 512 / ACC_STRIDE : V2_NACC_MAX;
+  static constexpr int TMEM_COLS = NACC * ACC_STRIDE < 32 ? 32 : NACC * ACC_STRIDE;
   static constexpr int TOTAL_ITEMS = NPIX * NCHUNK;
   static constexpr int UNROLL = (TOTAL_ITEMS + 2 * V2_PRODUCERS - 1) / (2 * V2_PRODUCERS);  // two load batches per tile
   static_assert(2 * ACC_COLS <= 512, "TMEM budget");
@@ -265,7 +271,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
   const int co0 = split * CN;  // first output channel of this CTA
   const int tile0 = (int)blockIdx.x / NSPLIT, tile_step = (int)gridDim.x / NSPLIT;
   extern __shared__ __align__(1024) uint8_t smem[];
-  __shared__ uint64_t full_bar[V2_MAX_STAGES], empty_bar[V2_MAX_STAGES], tfull_bar[2], tempty_bar[2];
+  __shared__ uint64_t full_bar[V2_MAX_STAGES], empty_bar[V2_MAX_STAGES], tfull_bar[4], tempty_bar[4];
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -278,7 +284,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
     for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], ALL_TMA ? 1 : V2_PRODUCERS / 32 + (TJ > 0 ? 1 : 0)); bar_init(&empty_bar[i], (use_res && !P.res_global) ? 1 + V2_EPI_WARPS : 1); }
-    for (int i = 0; i < 2; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], V2_EPI_WARPS); }
+    for (int i = 0; i < C::NACC; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], V2_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == PW_) {
@@ -311,10 +317,14 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
         const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
         const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
         V2_TRACE(0, it, 0);  // wants stage
-        bar_wait_relaxed(&empty_bar[st], ph ^ 1);
+        if (P.ablate & 256) bar_wait(&empty_bar[st], ph ^ 1); else bar_wait_relaxed(&empty_bar[st], ph ^ 1);
         V2_TRACE(0, it, 1);  // got stage
         const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
         const uint32_t bar = s_u32(&full_bar[st]);
+        if (P.ablate & 1) {  // debug: no loads, the stage keeps whatever it held
+          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+          continue;
+        }
         if constexpr (PM) {
           asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(C::NKB * C::NPIX * 128))
                        : "memory");
@@ -430,9 +440,9 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
       const int st = it % P.nstages;
       const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
-      const int as = it & 1;
+      const int as = it % C::NACC;
       if (leader) V2_TRACE(1, it, 0);
-      bar_wait_relaxed(&tempty_bar[as], (uint32_t)(((it >> 1) & 1) ^ 1));
+      if (P.ablate & 512) bar_wait(&tempty_bar[as], (uint32_t)(((it / C::NACC) & 1) ^ 1)); else bar_wait_relaxed(&tempty_bar[as], (uint32_t)(((it / C::NACC) & 1) ^ 1));
       if (leader) V2_TRACE(1, it, 1);  // accumulator free
       bar_wait(&full_bar[st], ph);
       if (leader) V2_TRACE(1, it, 2);  // tile landed
@@ -469,8 +479,8 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
       }
       }
       if (leader) {
-        commit_to(&empty_bar[st]);
-        commit_to(&tfull_bar[as]);
+        if (P.ablate & 64) bar_arrive(&empty_bar[st]); else commit_to(&empty_bar[st]);
+        if (P.ablate & 128) bar_arrive(&tfull_bar[as]); else commit_to(&tfull_bar[as]);
         V2_TRACE(1, it, 3);  // MMAs issued
       }
       __syncwarp();
@@ -490,10 +500,10 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     const float* bias_r = P.bias_c + pr * 40;
     int it = 0;
     for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
-      const int as = it & 1;
+      const int as = it % C::NACC;
       const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
       const int y = ty * 16 + ly, x = (tx * KW + j) * 8 + lx;
-      bar_wait(&tfull_bar[as], (uint32_t)((it >> 1) & 1));
+      bar_wait(&tfull_bar[as], (uint32_t)((it / C::NACC) & 1));
       tc_after();
       float v[40];
       const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE + j * CN + pr * 40);
@@ -572,7 +582,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     int it = 0;
     for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
       const int st = it % P.nstages;
-      const int as = it & 1;
+      const int as = it % C::NACC;
       const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
       const int y = ty * 16 + ly;
       // residual = centre pixels of the input halo tile: pull them into registers as soon as the tile has landed and
@@ -590,10 +600,10 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
           for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = ok ? __ldg(rp + ch) : make_uint4(0u, 0u, 0u, 0u);
         }
       } else if (use_res) {
-        bar_wait(&full_bar[st], (uint32_t)((it / P.nstages) & 1));
+        if (!(P.ablate & 32)) bar_wait(&full_bar[st], (uint32_t)((it / P.nstages) & 1));
         if (tr) V2_TRACE(2, it, 4);  // input tile visible
         const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * C::A_BYTES);
-        if (active)
+        if (active && !(P.ablate & 32))
 #pragma unroll
         for (int jj = 0; jj < NJ; jj++) {
           const int pc = (ly + 1) * C::PITCH + 8 * (jj * NSJ + jc) + lx + 1;  // this thread's centre pixel
@@ -612,12 +622,22 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
           }
         }
         // the stage is refilled by TMA (async proxy): these generic-proxy reads must be ordered before that write
-        if (TMA) fence_async_smem();
+        if (TMA && !(P.ablate & 16)) fence_async_smem();
         __syncwarp();
         if (lane == 0) bar_arrive(&empty_bar[st]);
       }
       if (tr) V2_TRACE(2, it, 0);  // residual read, waiting for the accumulator
-      bar_wait(&tfull_bar[as], (uint32_t)((it >> 1) & 1));
+      if (P.ablate & 1024) {
+        if (lane == 0) bar_wait(&tfull_bar[as], (uint32_t)((it / C::NACC) & 1));
+        __syncwarp();
+      } else if (P.ablate & 2048) {
+        uint32_t done;
+        do {
+          asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.u32 %0, 1, 0, P1;\n\t}"
+                       : "=r"(done) : "r"(s_u32(&tfull_bar[as])), "r"((uint32_t)((it / C::NACC) & 1)) : "memory");
+        } while (!done);
+      } else
+      bar_wait(&tfull_bar[as], (uint32_t)((it / C::NACC) & 1));
       if (tr) V2_TRACE(2, it, 1);  // accumulator complete
       tc_after();
       float v[NJ][CH];
@@ -655,7 +675,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
             o.z = pk_bf16(v[jj][4], v[jj][5]); o.w = pk_bf16(v[jj][6], v[jj][7]);
             *reinterpret_cast<uint4*>(P.out + (((size_t)n * 2 * P.H + 2 * y + (cb >> 3)) * (2 * P.W) + 2 * x) * 4) = o;
           } else {
-            if (use_res) {
+            if (use_res && !(P.ablate & 8192)) {
 #pragma unroll
               for (int ch = 0; ch < NR; ch++) {
                 const uint4 r = res[jj * NR + ch];
@@ -669,12 +689,14 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
                 }
               }
             }
-            if (P.act) {
+            if (P.act && !(P.ablate & 16384)) {
 #pragma unroll
               for (int i = 0; i < CH; i++) v[jj][i] = v[jj][i] > 0.f ? v[jj][i] : v[jj][i] * P.slope;
             }
             bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT + co0 + cb;
-            if constexpr (CH >= 16) {
+            if ((P.ablate & 4096) && v[jj][0] != 123456.789f) {
+              // debug: math kept alive, no stores
+            } else if constexpr (CH >= 16) {
 #pragma unroll
               for (int c = 0; c < CH; c += 16) {
                 uint4 o0, o1;
@@ -692,6 +714,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
             }
           }
         }
+        if (tr && jj == 0) V2_TRACE(2, it, 6);  // first sub-tile stored
       }
       if (tr) V2_TRACE(2, it, 7);  // tile stored
     }
