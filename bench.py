@@ -264,7 +264,8 @@ def main():
         eng.infer(clip_dev[sl.start:sl.stop], clip_dev[sl.start + 1:sl.stop + 1], TIMESTEPS, 1.0, prec, out=out_dev)
 
     clip_host = torch.from_numpy(clip).pin_memory()
-    streamer = model.clip_streamer(B, H, W, TIMESTEPS, depth=2)
+    e2e_depth = int(os.environ.get("VFI_E2E_DEPTH", "2"))   # buffer slots of the pipelined public API
+    streamer = model.clip_streamer(B, H, W, TIMESTEPS, depth=e2e_depth)
 
     def step_e2e(k):
         # public pipelined API: B+1 consecutive pinned host frames in (uint8), B x T pinned host frames out, every step
@@ -394,7 +395,7 @@ def main():
                        "l2_policy": "inputs+activations per step (>1 GB) exceed the 126 MB L2; batches rotate through the pool"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(streamer.h2d_bytes),
                     "d2h_bytes_per_step": int(B * T * H * W * 3), "steps": e2e_steps,
-                    "api": "RIFEModel.clip_streamer().submit (B+1 pinned host uint8 frames in, B x T pinned host uint8 frames out per step; upload / kernels / download on three streams, 2 slots)"},
+                    "api": "RIFEModel.clip_streamer().submit (B+1 pinned host uint8 frames in, B x T pinned host uint8 frames out per step; upload / kernels / download on three streams, %d slots)" % e2e_depth},
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),
             "roofline": roof, "kernel_breakdown": breakdown, "aux_kernels": aux, "cpu_baseline": cpu_base,
