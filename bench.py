@@ -240,7 +240,7 @@ def main():
             os.close(saved_fd)
     dev = torch.device("cuda", local)
 
-    model = RIFEModel(device=f"cuda:{local}", precision=args.precision)
+    model = RIFEModel(device=f"cuda:{local}", precision=args.precision, allow_random_weights=True)
     import contextlib
     with contextlib.redirect_stdout(sys.stderr):   # the wrapper prints "Loading RIFE ..." like the reference; stdout is the JSON line only
         model.load()

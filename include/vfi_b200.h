@@ -7,7 +7,11 @@
  * pointers owned by the caller; the library owns only the handle's weights + workspace.
  * `stream` is a cudaStream_t passed as void* (0 = legacy default stream).  A handle is
  * not thread-safe; different handles are independent (the reference is single-threaded:
- * scripts/run_benchmarks.py:142 hot loop).
+ * scripts/run_benchmarks.py:142 hot loop).  All calls on one handle share its workspace, so the
+ * library ORDERS them: a call issued on a different stream than the previous call first waits
+ * (on the device, cudaStreamWaitEvent) for that previous call to finish.  Calls from several
+ * streams are therefore safe but run one after the other; use one handle per stream to overlap.
+ * Every entry point leaves the calling thread's current CUDA device as it found it.
  * There is no CPU fallback: every call fails with VFI_E_CUDA when no sm_100 device exists.
  */
 #ifndef VFI_B200_H
@@ -42,6 +46,10 @@ void vfi_destroy(vfi_handle* h);
 const char* vfi_last_error(vfi_handle* h);
 /* number of kernels this handle has launched since creation (bench.py "gpu_launches") */
 long long vfi_launch_count(vfi_handle* h);
+
+/* device memory the handle owns right now: workspace arena + reduction scratch + packed weights (bytes).  PyTorch's
+ * allocator statistics do not see these; the host wrappers add it to InferenceResult.vram_peak_mb (models/base.py:140-158) */
+size_t vfi_device_bytes(vfi_handle* h);
 
 /* Tuning / test knobs (defaults are the fastest measured setting; every setting computes the same result):
  *   "conv_v2"       1: stride-1 3x3 convs whose weights fit in shared memory run on the resident-weight halo-tile
@@ -103,6 +111,19 @@ int vfi_ssim_gray_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, i
  * field n x H x W x 2 float: out[3*i+0..2] = mean, max, std (population) of |flow|.        */
 int vfi_flow_stats(vfi_handle* h, const float* flow, int n, int H, int W, double* out, void* stream);
 
+/* Dense Farneback optical flow on the device -- replaces cv2.calcOpticalFlowFarneback(prev, next, None, pyr_scale,
+ * levels, winsize, iterations, poly_n, poly_sigma, flags=0) at models/novel/adaptive_pipeline.py:119-128
+ * (0.5, 3, 15, 3, 5, 1.2; same call at evaluation/metrics.py:379-381) and scripts/run_experiments.py:359-362,460
+ * (0.5, 1, 15, 1, 5, 1.1).  OpenCV's algorithm (optflowgf.cpp), restated in oracle/farneback_ref.py.
+ *   img0,img1 : n x H x W x channels uint8; channels 3 = RGB (converted with cv2's RGB2GRAY integers), 1 = gray
+ *   flow_out  : nullable, n x H x W x 2 float (u, v)
+ *   stats_out : nullable, n x 3 double = mean, max, std of |flow| (compute_motion, adaptive_pipeline.py:130-138);
+ *               the flow never leaves the device.  At least one of the two outputs must be given.
+ * Limits: 0 < pyr_scale < 1, poly_n 5 or 7, winsize <= 31, flags 0 (box window, no initial flow).                */
+int vfi_farneback(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int n, int H, int W, int channels,
+                  double pyr_scale, int levels, int winsize, int iterations, int poly_n, double poly_sigma,
+                  float* flow_out, double* stats_out, void* stream);
+
 /* detect_particles' frequency term (adaptive_pipeline.py:180-183): variance of the 3x3
  * Laplacian (reflect-101) of the gray image.  rgb: n x H x W x 3; out: n x double.        */
 int vfi_laplacian_var(vfi_handle* h, const uint8_t* rgb, int n, int H, int W, double* out, void* stream);
@@ -123,7 +144,7 @@ int vfi_route_decide(double ssim_score, double motion_mean, double motion_max, d
                      double* particle_score);
 
 /* Unit-test hook: run ONE conv layer of the loaded IFNet on caller data in both precisions'
- * layouts.  layer ids are listed in csrc/ifnet.h.  x: N x Hin x Win x Cin_pad (fp32 NHWC),
+ * layouts.  layer ids: csrc/common.cuh (VFI_NUM_LAYERS table) / ifnet_layers.py.  x: N x Hin x Win x Cin_pad (fp32 NHWC),
  * y: N x Hout x Wout x Cout_pad fp32 NHWC out (for lastconv: N x 4Hin x 4Win x 16).
  * residual (ResConv layers only): NULL => the layer input itself, as in the net.          */
 int vfi_debug_conv(vfi_handle* h, int layer, int precision, const float* x, int N, int Hin, int Win,

@@ -23,9 +23,11 @@ def main():
     ap.add_argument('--output', default=None, help='directory for interpolated PNGs')
     ap.add_argument('--pairs', type=int, default=4)
     ap.add_argument('--num-frames', type=int, default=3)
+    ap.add_argument('--random-weights', action='store_true',
+                    help='run without train_log/flownet.pkl on seeded random-init IFNet weights (synthetic runs only)')
     a = ap.parse_args()
     name = a.method or a.vfi_model
-    model = get_available_models()[name]()
+    model = get_available_models()[name](**({'allow_random_weights': True} if a.random_weights else {}))
     model.load()
     if a.input:
         frames = [cv2.cvtColor(cv2.imread(f), cv2.COLOR_BGR2RGB) for f in sorted(glob.glob(os.path.join(a.input, '*.png')))]

@@ -10,6 +10,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 GOLDEN = os.path.join(ROOT, "tests", "golden")
+# the v4.25 release weights cannot be fetched here: the tests opt into the seeded random-init IFNet (rife_wrapper.py
+# raises FileNotFoundError without this, as the reference does; test_host_logic.py checks that default)
+os.environ.setdefault("VFI_B200_RANDOM_WEIGHTS", "1")
 
 
 def pytest_configure(config):
@@ -66,6 +69,18 @@ def engine(lib_built, weights):
     e = Engine.get(0)
     e.load_weights(weights)
     return e
+
+
+@pytest.fixture(scope="session")
+def farneback_cv2():
+    """cv2.calcOpticalFlowFarneback on RGB frames with the reference's parameters (adaptive_pipeline.py:119-128)."""
+    import cv2
+
+    def run(f0, f1, levels=3, iterations=3, poly_sigma=1.2):
+        g0 = cv2.cvtColor(f0, cv2.COLOR_RGB2GRAY) if f0.ndim == 3 else f0
+        g1 = cv2.cvtColor(f1, cv2.COLOR_RGB2GRAY) if f1.ndim == 3 else f1
+        return cv2.calcOpticalFlowFarneback(g0, g1, None, 0.5, levels, 15, iterations, 5, poly_sigma, 0)
+    return run
 
 
 # the reference's own fixtures (tests/conftest.py:15-36), seeded

@@ -51,11 +51,34 @@ def test_hud_all_ones_returns_inputs_1080p(engine, clip1080):
     assert np.array_equal(o[0], clip1080[0]) and np.array_equal(o[1], clip1080[1]) and np.array_equal(o[2], clip1080[1])
 
 
-@pytest.mark.parametrize("H,W", [(1440, 2560)])
-def test_1440p_pads_to_64(engine, H, W):
-    """1440 is a multiple of 32 but not 64; the pass must pad to 1472 and still return HxW."""
-    fr = gen_clip(1, H, W, seed=3, cut_every=0, fast=None)
-    a = engine.infer(fr[0][None], fr[1][None], [0.5], 1.0, _abi.PRECISION_BF16, want_float=True)
-    b = engine.infer(fr[0][None], fr[1][None], [0.5], 1.0, _abi.PRECISION_FP32, want_float=True)
-    assert a[0].shape == (1, 1, H, W, 3)
-    assert float((a[1] - b[1]).abs().max()) <= 2e-2
+@pytest.mark.parametrize("H,W,seed", [(1440, 2560, 3), (2160, 3840, 4)])
+def test_config4_sizes_vs_oracle(engine, oracle_model, H, W, seed):
+    """BASELINE.json configs[3] resolutions against the CPU oracle (not against the library's own fp32 mode): 1440p pads to
+    1472 (1440 is a multiple of 32 but not of 64), 4K to 2176; fp32 mode 1e-4, bf16 mode 2e-2 and >= 45 dB."""
+    fr = gen_clip(1, H, W, seed=seed, cut_every=0, fast=None)
+    ref_u8, ref_f = ifnet_ref.interpolate_ref(oracle_model, fr[0], fr[1], [0.5], return_float=True)
+    for prec, tol in ((_abi.PRECISION_FP32, 1e-4), (_abi.PRECISION_BF16, 2e-2)):
+        out, of = engine.infer(fr[0][None], fr[1][None], [0.5], 1.0, prec, want_float=True)
+        assert out.shape == (1, 1, H, W, 3)
+        d = of[0, 0].cpu().numpy() - ref_f[0]
+        assert float(np.abs(d).max()) <= tol, (H, W, prec, float(np.abs(d).max()))
+        if prec == _abi.PRECISION_BF16:
+            assert 10 * np.log10(1.0 / float((d ** 2).mean())) >= 45.0
+        assert np.abs(out[0, 0].cpu().numpy().astype(int) - ref_u8[0].astype(int)).max() <= int(tol * 255) + 1
+
+
+def test_config4_4k_batch8_equals_singles(engine):
+    """configs[3]'s real launch shape: 8 pairs x 3 timesteps of 4K frames in one call (2.0e8 padded pixels, the largest set the
+    32-bit-indexed gather / blend kernels are allowed to see) is bit-identical to the pairs run one at a time."""
+    clip = gen_clip(8, 2160, 3840, seed=4, cut_every=0, fast=None)
+    dev = torch.from_numpy(clip).cuda()
+    batch = engine.infer(dev[:-1], dev[1:], TS, 1.0, _abi.PRECISION_BF16)            # clip mode: 9 frames through the Head
+    assert batch.shape == (8, 3, 2160, 3840, 3)
+    for b in (0, 3, 7):
+        one = engine.infer(dev[b][None], dev[b + 1][None], TS, 1.0, _abi.PRECISION_BF16)
+        assert torch.equal(one[0], batch[b]), f"pair {b}"
+    two_sets = engine.infer(dev[:-1].clone(), dev[1:].clone(), TS, 1.0, _abi.PRECISION_BF16)   # separate frame sets: 16 Head images
+    assert torch.equal(two_sets, batch)
+    from vfi_b200 import _abi as A
+    with pytest.raises(A.VFIError, match="batch too large"):                          # the guard itself (csrc/abi.cu)
+        engine.infer(dev[:5], dev[1:6], [0.5] * 64, 1.0, _abi.PRECISION_BF16)         # 320 items x 8.4e6 px > 2^31

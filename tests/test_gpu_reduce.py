@@ -51,7 +51,7 @@ def test_ssim_full_res(engine, H, W):
     assert abs(float(engine.ssim(fr[:1], fr[:1], 1)[0]) - 1.0) < 1e-12
 
 
-@pytest.mark.parametrize("H,W", [(1080, 1920), (360, 640), (28, 28)])
+@pytest.mark.parametrize("H,W", [(1080, 1920), (360, 640), (28, 28), (480, 640), (1000, 1777), (486, 482), (30, 31)])
 def test_scene_cut_ssim_quarter_res(engine, H, W):
     fr = gen_clip(7, H, W, seed=3, cut_every=4, fast=None, hud=H > 100)
     got = engine.ssim(fr[:-1], fr[1:], 4).cpu().numpy()
@@ -97,8 +97,11 @@ def test_laplacian_var(engine, H, W):
     assert np.allclose(got, want, rtol=1e-12, atol=1e-9)
 
 
-@pytest.mark.parametrize("H,W", [(360, 640), (1080, 1920), (1440, 2560)])
+@pytest.mark.parametrize("H,W", [(360, 640), (1080, 1920), (1440, 2560), (480, 640), (720, 1280), (1000, 1777), (540, 960),
+                                 (480, 854), (100, 100)])
 def test_hud_mask_bit_exact(engine, H, W):
+    """Any frame size the reference's cv2.resize calls accept (adaptive_pipeline.py:203-204), incl. the reference's own
+    480x640 fixture (tests/conftest.py:15-18), non-integer ratios and frames smaller than the 320x180 thumbnail."""
     clip = gen_clip(11 if H <= 360 else 6, H, W, seed=4, cut_every=0, fast=None)
     ref, hs = router_ref.RouterRef(), HudState(engine)
     seen_mask = False
@@ -110,10 +113,15 @@ def test_hud_mask_bit_exact(engine, H, W):
     assert seen_mask and len(hs) == min(len(clip), 10)
 
 
-def test_hud_rejects_unsupported_geometry(engine):
-    from vfi_b200 import _abi
-    with pytest.raises(_abi.VFIError, match="HUD thumbnail"):
-        HudState(engine).update(np.zeros((100, 100, 3), np.uint8))
+def test_hud_thumbnail_ring_matches_cv2(engine):
+    """The ring holds cv2.resize(gray, (320, 180)) bit for bit at a non-integer ratio (general INTER_LINEAR taps)."""
+    fr = np.random.default_rng(3).integers(0, 256, (3, 500, 888, 3), dtype=np.uint8)
+    hs = HudState(engine)
+    for f in fr:
+        hs.update(f)
+    ring = hs.ring.cpu().numpy()
+    for i, f in enumerate(fr):
+        assert np.array_equal(ring[i], cv2.resize(cv2.cvtColor(f, cv2.COLOR_RGB2GRAY), (320, 180)))
 
 
 @pytest.mark.parametrize("H,W", [(128, 192), (1080, 1920), (33, 47)])

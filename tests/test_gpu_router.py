@@ -7,7 +7,7 @@ import torch
 import vfi_b200  # noqa: F401
 from oracle import ifnet_ref, metrics_ref, router_ref
 from vfi_b200.evaluation.metrics import QualityEvaluator, compute_psnr_simple, compute_ssim_simple, psnr_batch
-from vfi_b200.models.novel.adaptive_pipeline import AdaptivePipeline, AdaptiveRouter
+from vfi_b200.models.novel.adaptive_pipeline import AdaptivePipeline, AdaptiveRouter, cv2_farneback_flow
 from vfi_b200.models.sota.rife_wrapper import RIFEModel
 from vfi_b200.scripts.run_benchmarks import get_available_models, run_model_benchmark
 from vfi_b200.synth import gen_clip, noisy_copy
@@ -35,21 +35,28 @@ def _run(router, clip):
     return np.array(rows), np.stack(masks)
 
 
+@pytest.mark.parametrize("flow", ["device", "cv2"])
 @pytest.mark.parametrize("tight", [False, True])
-def test_router_vs_reference_golden(engine, clip_and_gold, tight):
+def test_router_vs_reference_golden(engine, clip_and_gold, tight, flow):
+    """flow="device": the product path (CUDA Farneback, row N1) -- every decision bit-exact, the flow statistics within the
+    flow tolerance.  flow="cv2": OpenCV's own flow uploaded, isolating the reduction kernels (max exact, mean/std 1e-5)."""
     clip, g = clip_and_gold
     kw = {}
     if tight:
         lo, hi, pt = g["tight"].tolist()
         kw = dict(motion_threshold_low=lo, motion_threshold_high=hi, particle_threshold=pt)
-    rows, masks = _run(AdaptiveRouter(**kw), clip)
+    rows, masks = _run(AdaptiveRouter(flow_fn=cv2_farneback_flow if flow == "cv2" else None, **kw), clip)
     gold = g["rows_tight" if tight else "rows"]
     for col in (3, 4, 6):                      # has_particles, is_scene_change, route: BIT-EXACT
         assert np.array_equal(rows[:, col], gold[:, col])
-    assert np.array_equal(rows[:, 1], gold[:, 1])                       # max |flow|: exact in any order
     assert np.array_equal(rows[:, 5], gold[:, 5])                       # HUD coverage: integer count / pixels
-    assert np.allclose(rows[:, [0, 2]], gold[:, [0, 2]], rtol=1e-5, atol=1e-12)
-    assert np.allclose(rows[:, 7], gold[:, 7], rtol=1e-5, atol=1e-9)
+    if flow == "cv2":
+        assert np.array_equal(rows[:, 1], gold[:, 1])                   # max |flow|: exact in any order
+        assert np.allclose(rows[:, [0, 2]], gold[:, [0, 2]], rtol=1e-5, atol=1e-12)
+        assert np.allclose(rows[:, 7], gold[:, 7], rtol=1e-5, atol=1e-9)
+    else:
+        assert np.allclose(rows[:, [0, 1, 2]], gold[:, [0, 1, 2]], rtol=2e-3, atol=2e-3)
+        assert np.allclose(rows[:, 7], gold[:, 7], rtol=2e-3, atol=2e-3)
     if not tight:
         assert np.array_equal(masks, g["masks"])
 
@@ -59,8 +66,10 @@ def test_router_public_methods(engine, clip_and_gold):
     r, ref = AdaptiveRouter(), router_ref.RouterRef()
     cut, score = r.detect_scene_change(clip[5], clip[6])
     assert cut and abs(score - router_ref.scene_ssim(clip[5], clip[6])) < 1e-9
-    mean, mx, sd, mag = r.compute_motion(clip[0], clip[1])
-    assert mx == g["motion"][0][1] and abs(mean - g["motion"][0][0]) < 1e-5 and mag.shape == clip[0].shape[:2]
+    mean, mx, sd, mag = r.compute_motion(clip[0], clip[1])             # CUDA Farneback: flow tolerance, not bit-exact
+    assert abs(mx - g["motion"][0][1]) < 2e-3 and abs(mean - g["motion"][0][0]) < 1e-4 and mag.shape == clip[0].shape[:2]
+    mean_c, mx_c, _, _ = AdaptiveRouter(flow_fn=cv2_farneback_flow).compute_motion(clip[0], clip[1])
+    assert mx_c == g["motion"][0][1] and abs(mean_c - g["motion"][0][0]) < 1e-5
     hp, ps = r.detect_particles(clip[0], mag, sd)
     want = float(np.sqrt(min(sd / 20.0, 1.0) * min(g["laplacian_var"][0] / 500.0, 1.0)))
     assert hp == (want > 0.4) and abs(ps - want) < 1e-12

@@ -63,6 +63,18 @@ def test_rife_ctor_and_info(tmp_path, monkeypatch):
     assert m.upscale(np.zeros((30, 40, 3), np.uint8), 1.333).shape == (39, 53, 3)
 
 
+def test_missing_weights_raise_unless_opted_in(monkeypatch, capsys):
+    """external/Practical-RIFE/train_log holds no flownet.pkl: like the reference (rife_wrapper.py:56-72, :94-105) the
+    default is an error, never silent random weights; the synthetic configs opt in explicitly."""
+    monkeypatch.delenv("VFI_B200_RANDOM_WEIGHTS", raising=False)
+    with pytest.raises(FileNotFoundError, match="flownet.pkl"):
+        RIFEModel().state_dict()
+    sd = RIFEModel(allow_random_weights=True).state_dict()
+    assert "RANDOM-INIT" in capsys.readouterr().err and len(sd) == len(RIFEModel(allow_random_weights=True).state_dict())
+    monkeypatch.setenv("VFI_B200_RANDOM_WEIGHTS", "1")
+    assert RIFEModel().allow_random_weights
+
+
 @pytest.mark.skipif(torch.cuda.is_available(), reason="CPU-only behaviour")
 def test_no_cpu_fallback():
     with pytest.raises(RuntimeError, match="no CPU fallback"):

@@ -61,3 +61,15 @@ def test_hud_composite():
     m[0, :2] = True
     outs = router_ref.hud_composite([np.full((4, 4, 3), 5, np.uint8) for _ in range(3)], [0.25, 0.5, 0.75], f0, f1, m)
     assert outs[0][0, 0, 0] == 0 and outs[1][0, 0, 0] == 9 and outs[2][0, 1, 2] == 9 and outs[0][1, 1, 1] == 5
+
+
+@pytest.mark.parametrize("H,W", [(480, 640), (720, 1280), (1000, 1777), (1080, 1920), (360, 640), (480, 854), (333, 517),
+                                 (90, 160), (100, 100), (486, 482), (29, 31)])
+def test_resize_restatement_matches_cv2(H, W):
+    """oracle/resize_ref.py (what csrc/reduce.cu implements) == cv2.resize INTER_LINEAR on uint8, bit for bit, for the
+    router's two call sites (adaptive_pipeline.py:149-155 fx=fy=0.25, :203-204 dsize=(320,180))."""
+    import cv2
+    from oracle.resize_ref import resize_linear_u8
+    g = np.random.default_rng(H * 7 + W).integers(0, 256, (H, W), dtype=np.uint8)
+    assert np.array_equal(resize_linear_u8(g, (320, 180)), cv2.resize(g, (320, 180)))
+    assert np.array_equal(resize_linear_u8(g, fx=0.25, fy=0.25), cv2.resize(g, None, fx=0.25, fy=0.25))

@@ -20,6 +20,7 @@ SIGNATURES = {
     "vfi_destroy": (None, [_vp]),
     "vfi_last_error": (C.c_char_p, [_vp]),
     "vfi_launch_count": (_ll, [_vp]),
+    "vfi_device_bytes": (_sz, [_vp]),
     "vfi_set_option": (_i, [_vp, C.c_char_p, _i]),
     "vfi_ifnet_load_weights": (_i, [_vp, _vp, _sz, _vp]),
     "vfi_ifnet_infer": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _f, _i, _vp, _vp, _vp, _vp, _vp]),
@@ -28,6 +29,7 @@ SIGNATURES = {
     "vfi_ssim_gray_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "vfi_flow_stats": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "vfi_laplacian_var": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
+    "vfi_farneback": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _d, _i, _i, _i, _i, _d, _vp, _vp, _vp]),
     "vfi_hud_update": (_i, [_vp, _vp, _i, _i, _vp, _i, C.POINTER(_ll), _d, _vp, _vp, _vp]),
     "vfi_route_decide": (_i, [_d, _d, _d, _d, _d, _d, _d, _d, _d, C.POINTER(_i), C.POINTER(_d),
                               C.POINTER(_i), C.POINTER(_d)]),

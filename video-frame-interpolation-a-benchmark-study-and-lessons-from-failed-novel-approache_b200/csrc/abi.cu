@@ -36,11 +36,17 @@ extern "C" __attribute__((visibility("default"))) int vfi_create(int device, vfi
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return VFI_E_CUDA;
   if (prop.major != 10) return VFI_E_CUDA;  // sm_100a only: no fallback path exists
+  int prev = -1;
+  cudaGetDevice(&prev);
   if (cudaSetDevice(device) != cudaSuccess) return VFI_E_CUDA;
   vfi_handle* h = new vfi_handle();
   h->device = device;
   h->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < VFI_NUM_LAYERS; i++) h->layers[i] = Layer();
+  const bool ok = cudaEventCreateWithFlags(&h->scratch_ev, cudaEventDisableTiming) == cudaSuccess &&
+                  cudaMalloc(&h->tdev, 64 * sizeof(float)) == cudaSuccess;
+  if (prev >= 0 && prev != device) cudaSetDevice(prev);  // leave the caller's current device as it was
+  if (!ok) { cudaGetLastError(); delete h; return VFI_E_CUDA; }
   *out = h;
   return VFI_OK;
 }
@@ -58,11 +64,16 @@ static void free_layers(vfi_handle* h) {
 
 extern "C" __attribute__((visibility("default"))) void vfi_destroy(vfi_handle* h) {
   if (!h) return;
+  int prev = -1;
+  cudaGetDevice(&prev);
   cudaSetDevice(h->device);
   cudaDeviceSynchronize();
   free_layers(h);
   cudaFree(h->ws);
   cudaFree(h->red);
+  cudaFree(h->tdev);
+  if (h->scratch_ev) cudaEventDestroy(h->scratch_ev);
+  if (prev >= 0 && prev != h->device) cudaSetDevice(prev);
   delete h;
 }
 
@@ -115,6 +126,9 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
 
 extern "C" __attribute__((visibility("default"))) const char* vfi_last_error(vfi_handle* h) { return h ? h->err.c_str() : "null handle"; }
 extern "C" __attribute__((visibility("default"))) long long vfi_launch_count(vfi_handle* h) { return h ? h->launches : 0; }
+extern "C" __attribute__((visibility("default"))) size_t vfi_device_bytes(vfi_handle* h) {
+  return h ? h->ws_bytes + h->red_bytes + h->weight_bytes + 64 * sizeof(float) : 0;
+}
 
 static void layer_shape(int id, Layer& L) {
   L = Layer();
@@ -140,9 +154,11 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
   if (!h) return VFI_E_ARG;
   if (!params || n_params != (size_t)VFI_IFNET_PARAMS)
     VFI_FAIL(h, VFI_E_ARG, "expected %d parameters, got %zu", VFI_IFNET_PARAMS, n_params);
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  VFI_ENTER(h, 0);
   free_layers(h);
   h->weights_loaded = false;
+  size_t free0 = 0, free1 = 0, total = 0;
+  cudaMemGetInfo(&free0, &total);
   h->slope = lrelu_slope ? *lrelu_slope : 0.2f;
   size_t off = 0;
   for (int id = 0; id < VFI_NUM_LAYERS; id++) {
@@ -192,6 +208,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
     }
   }
   if (off != n_params) VFI_FAIL(h, VFI_E_ARG, "parameter blob length mismatch (%zu consumed)", off);
+  cudaMemGetInfo(&free1, &total);
+  h->weight_bytes = free0 > free1 ? free0 - free1 : 0;  // what the packed weight images actually took from the device
   h->weights_loaded = true;
   return VFI_OK;
 }
@@ -228,7 +246,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
   int inv;
   if (scale == 1.0f) inv = 1; else if (scale == 0.5f) inv = 2; else if (scale == 0.25f) inv = 4;
   else VFI_FAIL(h, VFI_E_ARG, "scale must be 1.0, 0.5 or 0.25");
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   const bool bf = precision == VFI_PRECISION_BF16;
   const size_t esz = bf ? 2 : 4;
@@ -270,7 +288,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     uint8_t* feats = cv.take<uint8_t>(NI * px * 4 * esz);
     uint8_t* ht0 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
     uint8_t* ht1 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
-    float* tdev = cv.take<float>(64);
+    float* tdev = h->tdev;
     Tap* taps = cv.take<Tap>((size_t)5 * (Hp + Wp));
     float* flow3 = cv.take<float>((size_t)N * px * 4);  // blocks 0-3 flow per pixel (written by the fused finest gather)
     // coarse level i = block i's lastconv output: LowPlanes (blocks 0..3, bf16 mode) or fp32 texels
@@ -296,7 +314,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       continue;
     }
     int rc;
-    VFI_CUDA(h, cudaMemcpyAsync(tdev, timesteps, T * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (T != h->t_n || memcmp(h->t_host, timesteps, T * sizeof(float))) {  // steady state (same timesteps every call): no copy
+      memcpy(h->t_host, timesteps, T * sizeof(float));
+      h->t_n = 0;  // invalid until the copy is enqueued
+      VFI_CUDA(h, cudaMemcpyAsync(tdev, timesteps, T * sizeof(float), cudaMemcpyHostToDevice, s));
+      h->t_n = T;
+    }
     if ((rc = k_build_taps(h, taps, sl, 5, Hp, Wp, s))) return rc;
     // to_tensor + reflect pad, both frames of every pair
     if ((rc = k_pad_rgbx(h, img0, imgs, B, H, W, Hp, Wp, s))) return rc;
@@ -359,7 +382,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_warp_blend(vfi_handle*
                               const float* mask, int N, int H, int W, uint8_t* out, float* out_f32, void* stream) {
   if (!h) return VFI_E_ARG;
   if (!img0 || !img1 || !flow || !mask || !out || N < 1 || H < 1 || W < 1) VFI_FAIL(h, VFI_E_ARG, "bad argument");
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   const size_t px = (size_t)H * W;
   Carve cv{nullptr, 0};
@@ -389,7 +412,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_debug_conv(vfi_handle*
   if (!h) return VFI_E_ARG;
   if (!h->weights_loaded) VFI_FAIL(h, VFI_E_STATE, "IFNet weights not loaded");
   if (layer < 1 || layer >= VFI_NUM_LAYERS || !x || !y) VFI_FAIL(h, VFI_E_ARG, "bad layer/argument");
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   const Layer& L = h->layers[layer];
   const bool bf = precision == VFI_PRECISION_BF16;

@@ -72,6 +72,16 @@ struct vfi_handle {
   // small scratch for reductions
   void* red = nullptr;
   size_t red_bytes = 0;
+  // One stream at a time may use the handle's scratch (ws, red, tdev).  Every entry point waits, on ITS stream, for the
+  // event the previous entry point recorded when that one ran on a different stream, so calls from several streams
+  // (ClipStreamer's compute stream next to a router call on the current stream) serialise instead of racing.
+  cudaEvent_t scratch_ev = nullptr;
+  cudaStream_t scratch_stream = nullptr;
+  bool scratch_used = false;
+  size_t weight_bytes = 0;      // device bytes held by the packed weights (vfi_device_bytes)
+  float* tdev = nullptr;        // the call's timesteps on the device (64 floats); re-uploaded only when they change
+  float t_host[64] = {0};
+  int t_n = 0;
   void* tmap_encode = nullptr;  // cuTensorMapEncodeTiled entry point
   int opt_l2_chunk_mb = 0;      // vfi_set_option("l2_chunk_mb"): the ResConv chain of a block runs over groups of items whose
                                 // activations (in + out) fit this many MB, so a layer reads what the previous one left in L2; 0 = off
@@ -99,6 +109,25 @@ struct ProfScope {
   ProfScope(vfi_handle* h_, int cat, cudaStream_t s_) : h(h_), s(s_) { if (h->profile) prof_begin(h, cat, s); }
   ~ProfScope() { if (h->profile) prof_end(h, s); }
 };
+
+// Entry-point scope: makes h->device current for the call and restores the caller's device afterwards (the library must
+// not move the thread's CUDA device behind PyTorch's back), and orders this call after the handle's previous call when
+// that one ran on another stream.
+struct CallScope {
+  vfi_handle* h; cudaStream_t s; int prev_dev = -1; bool ok = true;
+  CallScope(vfi_handle* h_, cudaStream_t s_) : h(h_), s(s_) {
+    if (cudaGetDevice(&prev_dev) != cudaSuccess) prev_dev = -1;
+    if (prev_dev != h->device && cudaSetDevice(h->device) != cudaSuccess) { ok = false; return; }
+    if (h->scratch_used && h->scratch_stream != s) cudaStreamWaitEvent(s, h->scratch_ev, 0);
+  }
+  ~CallScope() {
+    if (ok) { cudaEventRecord(h->scratch_ev, s); h->scratch_stream = s; h->scratch_used = true; }
+    if (prev_dev >= 0 && prev_dev != h->device) cudaSetDevice(prev_dev);
+  }
+};
+#define VFI_ENTER(h, stream)                                                  \
+  CallScope _scope((h), (cudaStream_t)(stream));                              \
+  if (!_scope.ok) VFI_FAIL(h, VFI_E_CUDA, "cudaSetDevice(%d) failed", (h)->device)
 
 #define VFI_FAIL(h, code, ...)                               \
   do {                                                       \
@@ -246,4 +275,5 @@ int s2_build_layer(vfi_handle* h, Layer& L, const std::vector<float>& w_torch);
 int k_conv_s2(vfi_handle* h, const Layer& L, const bf16* in, bf16* out, int N, int Hin, int Win, bool out_phase,
               float slope, cudaStream_t s);
 
-// ---- reduce.cu is reached only through the ABI functions -----------------------------------
+// ---- reduce.cu is reached through the ABI functions; farneback.cu chains the flow statistics --------------------
+int vfi_flow_stats_impl(vfi_handle* h, const float* flow, int n, int H, int W, double* out, cudaStream_t s);

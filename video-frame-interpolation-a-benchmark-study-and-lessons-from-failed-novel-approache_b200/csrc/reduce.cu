@@ -10,6 +10,37 @@ __device__ __forceinline__ int gray_u8(int r, int g, int b) {
   // cv2.cvtColor(RGB2GRAY) integer identity
   return (r * 9798 + g * 19235 + b * 3735 + 16384) >> 15;
 }
+// cv2.resize(uint8, INTER_LINEAR) restated bit-exactly (OpenCV imgproc resize.cpp: resizeGeneric_ with
+// HResizeLinear<uchar,int,short,2048> / VResizeLinear<uchar,int,short,FixedPtCast<int,uchar,22>>; pinned against cv2 4.13 by
+// tests/test_oracle_router.py through oracle/resize_ref.py).  Destination index d reads source indices s0, s1 with 11-bit
+// coefficients a0 + a1 = 2048.  Along x the fraction is zeroed where the tap pair leaves the row; along y OpenCV keeps the
+// fraction and only clips the row indices.  For even integer ratios this is the 2x2 centre average of SURVEY App. B.1.
+struct LinTap { int s0, s1, a0, a1; };
+__device__ __forceinline__ LinTap lin_tap(int d, double scale, int src, bool clamp_frac) {
+  float f = (float)__dsub_rn(__dmul_rn((double)d + 0.5, scale), 0.5);
+  int s = (int)floorf(f);
+  f = __fsub_rn(f, (float)s);
+  if (clamp_frac) {
+    if (s < 0) { s = 0; f = 0.f; }
+    if (s >= src - 1) { s = src - 1; f = 0.f; }
+  }
+  LinTap t;
+  t.a0 = __float2int_rn(__fmul_rn(__fsub_rn(1.f, f), 2048.f));
+  t.a1 = __float2int_rn(__fmul_rn(f, 2048.f));
+  t.s0 = min(max(s, 0), src - 1);
+  t.s1 = min(max(s + 1, 0), src - 1);
+  return t;
+}
+__device__ __forceinline__ int gray_at(const uint8_t* __restrict__ rgb, int W, int y, int x) {
+  const uint8_t* q = rgb + ((size_t)y * W + x) * 3;
+  return gray_u8(q[0], q[1], q[2]);
+}
+// one pixel of cv2.resize(cv2.cvtColor(rgb, RGB2GRAY), ...)
+__device__ __forceinline__ int resized_gray(const uint8_t* __restrict__ rgb, int W, const LinTap tx, const LinTap ty) {
+  const int h0 = gray_at(rgb, W, ty.s0, tx.s0) * tx.a0 + gray_at(rgb, W, ty.s0, tx.s1) * tx.a1;
+  const int h1 = gray_at(rgb, W, ty.s1, tx.s0) * tx.a0 + gray_at(rgb, W, ty.s1, tx.s1) * tx.a1;
+  return (((ty.a0 * (h0 >> 4)) >> 16) + ((ty.a1 * (h1 >> 4)) >> 16) + 2) >> 2;
+}
 template <typename T>
 __device__ __forceinline__ T warp_sum(T v) {
 #pragma unroll
@@ -81,7 +112,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_psnr_u8(vfi_handle* h,
                            unsigned long long* sse_out, double* psnr_out, void* stream) {
   if (!h) return VFI_E_ARG;
   if (!a || !b || n < 1 || elems < 1 || n > 65535) VFI_FAIL(h, VFI_E_ARG, "bad argument");
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   if (int rc = vfi_red_reserve(h, (size_t)65536 * 8)) return rc;
   unsigned long long* acc = (unsigned long long*)h->red;
@@ -123,17 +154,10 @@ __global__ void ssim_kernel(const uint8_t* __restrict__ a, const uint8_t* __rest
         va = gray_u8(q[0], q[1], q[2]);
         q = pb + ((size_t)gy * W + gx) * 3;
         vb = gray_u8(q[0], q[1], q[2]);
-      } else {
-        int sa = 2, sb = 2;
-#pragma unroll
-        for (int dy = 0; dy < 2; dy++)
-#pragma unroll
-          for (int dx = 0; dx < 2; dx++) {
-            size_t o = ((size_t)(DS * gy + DS / 2 - 1 + dy) * W + (DS * gx + DS / 2 - 1 + dx)) * 3;
-            sa += gray_u8(pa[o], pa[o + 1], pa[o + 2]);
-            sb += gray_u8(pb[o], pb[o + 1], pb[o + 2]);
-          }
-        va = sa >> 2; vb = sb >> 2;
+      } else {  // cv2.resize(gray, None, fx=0.25, fy=0.25): scale = 1 / 0.25
+        const LinTap tx = lin_tap(gx, (double)DS, W, true), ty = lin_tap(gy, (double)DS, H, false);
+        va = resized_gray(pa, W, tx, ty);
+        vb = resized_gray(pb, W, tx, ty);
       }
     }
     ga[ly][lx] = (uint8_t)va; gb[ly][lx] = (uint8_t)vb;
@@ -184,10 +208,10 @@ extern "C" __attribute__((visibility("default"))) int vfi_ssim_gray_u8(vfi_handl
   if (!h) return VFI_E_ARG;
   if (!a || !b || !out || n < 1 || n > 65535) VFI_FAIL(h, VFI_E_ARG, "bad argument");
   if (downscale != 1 && downscale != 4) VFI_FAIL(h, VFI_E_ARG, "downscale must be 1 or 4");
-  if (downscale == 4 && ((H % 4) || (W % 4))) VFI_FAIL(h, VFI_E_ARG, "x0.25 path needs H,W multiples of 4");
-  const int hh = H / downscale, ww = W / downscale;
+  // cv2.resize(fx=fy=0.25): dsize = cvRound(size * 0.25), round-half-to-even
+  const int hh = downscale == 1 ? H : (int)nearbyint(H * 0.25), ww = downscale == 1 ? W : (int)nearbyint(W * 0.25);
   if (hh < 7 || ww < 7) VFI_FAIL(h, VFI_E_ARG, "image smaller than the 7x7 SSIM window");
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   dim3 grid(cdiv(ww - 6, SS_T), cdiv(hh - 6, SS_T), n);
   const int per = grid.x * grid.y;
@@ -255,8 +279,10 @@ __global__ void flow_stats_finish_kernel(const double* __restrict__ partial, int
 extern "C" __attribute__((visibility("default"))) int vfi_flow_stats(vfi_handle* h, const float* flow, int n, int H, int W, double* out, void* stream) {
   if (!h) return VFI_E_ARG;
   if (!flow || !out || n < 1 || n > 4096 || H < 1 || W < 1) VFI_FAIL(h, VFI_E_ARG, "bad argument");
-  VFI_CUDA(h, cudaSetDevice(h->device));
-  cudaStream_t s = (cudaStream_t)stream;
+  VFI_ENTER(h, stream);
+  return vfi_flow_stats_impl(h, flow, n, H, W, out, (cudaStream_t)stream);
+}
+int vfi_flow_stats_impl(vfi_handle* h, const float* flow, int n, int H, int W, double* out, cudaStream_t s) {
   const size_t npix = (size_t)H * W;
   int bx = (int)std::min<size_t>(FS_BLOCKS, (npix + 255) / 256);
   if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * bx * 24))) return rc;
@@ -315,7 +341,7 @@ __global__ void laplacian_finish_kernel(const long long* acc, int n, double npix
 extern "C" __attribute__((visibility("default"))) int vfi_laplacian_var(vfi_handle* h, const uint8_t* rgb, int n, int H, int W, double* out, void* stream) {
   if (!h) return VFI_E_ARG;
   if (!rgb || !out || n < 1 || n > 4096 || H < 2 || W < 2) VFI_FAIL(h, VFI_E_ARG, "bad argument");
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   if (int rc = vfi_red_reserve(h, (size_t)65536 * 8)) return rc;
   long long* acc = (long long*)h->red;
@@ -336,19 +362,11 @@ extern "C" __attribute__((visibility("default"))) int vfi_laplacian_var(vfi_hand
 //   morph  : MORPH_CLOSE then MORPH_OPEN with 5x5 ones = dilate5, erode9, dilate5 (borders ignored)
 #define HUD_W 320
 #define HUD_H 180
-__global__ void hud_thumb_kernel(const uint8_t* __restrict__ rgb, int H, int W, int ry, int rx, uint8_t* __restrict__ slot) {
+__global__ void hud_thumb_kernel(const uint8_t* __restrict__ rgb, int H, int W, double sy, double sx, uint8_t* __restrict__ slot) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= HUD_W * HUD_H) return;
   int x = i % HUD_W, y = i / HUD_W;
-  int s = 2;
-#pragma unroll
-  for (int dy = 0; dy < 2; dy++)
-#pragma unroll
-    for (int dx = 0; dx < 2; dx++) {
-      const uint8_t* q = rgb + ((size_t)(ry * y + ry / 2 - 1 + dy) * W + (rx * x + rx / 2 - 1 + dx)) * 3;
-      s += gray_u8(q[0], q[1], q[2]);
-    }
-  slot[i] = (uint8_t)(s >> 2);
+  slot[i] = (uint8_t)resized_gray(rgb, W, lin_tap(x, sx, W, true), lin_tap(y, sy, H, false));
 }
 struct HudSlots { int idx[5]; };
 __global__ void hud_var_kernel(const uint8_t* __restrict__ ring, HudSlots sl, double thr, uint8_t* __restrict__ small) {
@@ -372,7 +390,19 @@ __global__ void hud_var_kernel(const uint8_t* __restrict__ ring, HudSlots sl, do
 #define HM_T 32
 #define HM_R 8
 #define HM_N (HM_T + 2 * HM_R)
-#define HM_CELLS 26  // small-mask cells a 48-pixel span can touch at the smallest ratio (2)
+#define HM_CELLS 50  // small-mask cells a 48-pixel span can touch when the frame is at least 320 x 180 (ratio >= 1);
+                     // smaller frames (nearest UPsampling of the thumbnail grid) take the unstaged path
+__device__ __forceinline__ bool hud_flag_at(const uint8_t* __restrict__ ring, const int* idx, double thr, int i) {
+  double x[5];
+  double sum = 0.0;
+#pragma unroll
+  for (int k = 0; k < 5; k++) { x[k] = (double)ring[(size_t)idx[k] * HUD_W * HUD_H + i]; sum = __dadd_rn(sum, x[k]); }
+  const double mean = __ddiv_rn(sum, 5.0);
+  double acc = 0.0;
+#pragma unroll
+  for (int k = 0; k < 5; k++) { const double d = __dsub_rn(x[k], mean); acc = __dadd_rn(acc, __dmul_rn(d, d)); }
+  return __ddiv_rn(acc, 5.0) < thr;
+}
 __device__ __forceinline__ void hm_dilate(unsigned long long* a, unsigned long long* tmp, const bool rowin, unsigned long long inx,
                                           int r, bool complement) {
   const int t = threadIdx.x;
@@ -404,31 +434,27 @@ __global__ void __launch_bounds__(256) hud_mask_kernel(const uint8_t* __restrict
   const int cx0 = min((int)floor(__dmul_rn((double)x_lo, ifx)), HUD_W - 1), cx1 = min((int)floor(__dmul_rn((double)x_hi, ifx)), HUD_W - 1);
   const int cy0 = min((int)floor(__dmul_rn((double)y_lo, ify)), HUD_H - 1), cy1 = min((int)floor(__dmul_rn((double)y_hi, ify)), HUD_H - 1);
   const int ncx = cx1 - cx0 + 1, ncy = cy1 - cy0 + 1;
-  for (int e = threadIdx.x; e < ncx * ncy; e += blockDim.x) {
-    const int cy = e / ncx, cx = e - cy * ncx;
-    const int i = (cy0 + cy) * HUD_W + cx0 + cx;
-    double x[5];
-    double sum = 0.0;
-#pragma unroll
-    for (int k = 0; k < 5; k++) { x[k] = (double)ring[(size_t)sl.idx[k] * HUD_W * HUD_H + i]; sum = __dadd_rn(sum, x[k]); }
-    const double mean = __ddiv_rn(sum, 5.0);
-    double acc = 0.0;
-#pragma unroll
-    for (int k = 0; k < 5; k++) { const double d = __dsub_rn(x[k], mean); acc = __dadd_rn(acc, __dmul_rn(d, d)); }
-    flag[cy][cx] = __ddiv_rn(acc, 5.0) < thr ? 1 : 0;
-  }
+  const bool staged = ncx <= HM_CELLS && ncy <= HM_CELLS;
+  if (staged)
+    for (int e = threadIdx.x; e < ncx * ncy; e += blockDim.x) {
+      const int cy = e / ncx, cx = e - cy * ncx;
+      flag[cy][cx] = hud_flag_at(ring, sl.idx, thr, (cy0 + cy) * HUD_W + cx0 + cx) ? 1 : 0;
+    }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int t = warp; t < HM_N; t += 8) {
     const int gy = oy + t;
     const bool yin = gy >= 0 && gy < H;
-    const int cy = yin ? min((int)floor(__dmul_rn((double)gy, ify)), HUD_H - 1) - cy0 : 0;
+    const int cya = yin ? min((int)floor(__dmul_rn((double)gy, ify)), HUD_H - 1) : 0, cy = cya - cy0;
     unsigned int half[2];
 #pragma unroll
     for (int hh = 0; hh < 2; hh++) {
       const int c = lane + 32 * hh, gx = ox + c;
       bool bit = false;
-      if (yin && c < HM_N && gx >= 0 && gx < W) bit = flag[cy][min((int)floor(__dmul_rn((double)gx, ifx)), HUD_W - 1) - cx0] != 0;
+      if (yin && c < HM_N && gx >= 0 && gx < W) {
+        const int cxa = min((int)floor(__dmul_rn((double)gx, ifx)), HUD_W - 1);
+        bit = staged ? flag[cy][cxa - cx0] != 0 : hud_flag_at(ring, sl.idx, thr, cya * HUD_W + cxa);
+      }
       half[hh] = __ballot_sync(0xffffffffu, bit);
     }
     if (lane == 0) rows[t] = (unsigned long long)half[0] | ((unsigned long long)half[1] << 32);
@@ -469,14 +495,15 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
                               void* stream) {
   if (!h) return VFI_E_ARG;
   if (!rgb || !hist_ring || !count || !mask_out || !coverage_out || hist_len < 5) VFI_FAIL(h, VFI_E_ARG, "bad argument");
-  if (H % HUD_H || W % HUD_W || ((H / HUD_H) & 1) || ((W / HUD_W) & 1))
-    VFI_FAIL(h, VFI_E_ARG, "HUD thumbnail needs H = 180*r, W = 320*r' with even r, r' (got %dx%d)", H, W);
-  VFI_CUDA(h, cudaSetDevice(h->device));
+  if (H < 1 || W < 1) VFI_FAIL(h, VFI_E_ARG, "bad frame size %dx%d", H, W);
+  VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   const size_t npix = (size_t)H * W;
   if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, npix + HUD_W * HUD_H + 4096))) return rc;
   const long long c = *count;
-  hud_thumb_kernel<<<cdiv(HUD_W * HUD_H, 256), 256, 0, s>>>(rgb, H, W, H / HUD_H, W / HUD_W,
+  // cv2.resize(gray, (320, 180)): inv_scale = dsize / ssize, scale = 1 / inv_scale (doubles, as OpenCV computes them)
+  const double rsx = 1.0 / ((double)HUD_W / (double)W), rsy = 1.0 / ((double)HUD_H / (double)H);
+  hud_thumb_kernel<<<cdiv(HUD_W * HUD_H, 256), 256, 0, s>>>(rgb, H, W, rsy, rsx,
                                                             hist_ring + (size_t)(c % hist_len) * HUD_W * HUD_H);
   VFI_LAUNCHED(h);
   *count = c + 1;

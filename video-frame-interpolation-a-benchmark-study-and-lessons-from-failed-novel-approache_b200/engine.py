@@ -19,6 +19,11 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def library_device_bytes():
+    """Device memory held by every live library handle of this process (workspaces + packed weights)."""
+    return sum(e.device_bytes() for e in _ENGINES.values())
+
+
 class Engine:
     def __init__(self, device=0):
         if not torch.cuda.is_available():
@@ -33,9 +38,16 @@ class Engine:
         self.weights_loaded = False
 
     @staticmethod
-    def get(device=0):
+    def get(device=None):
+        """The per-device engine singleton; None / 'cuda' = the CURRENT CUDA device (the rank's GPU under torchrun)."""
+        if isinstance(device, str):
+            device = torch.device(device)
         if isinstance(device, torch.device):
-            device = device.index if device.index is not None else torch.cuda.current_device()
+            device = device.index
+        if device is None:
+            if not torch.cuda.is_available():
+                raise RuntimeError("vfi_b200 needs an sm_100 CUDA device; there is no CPU fallback")
+            device = torch.cuda.current_device()
         if device not in _ENGINES:
             _ENGINES[device] = Engine(device)
         return _ENGINES[device]
@@ -51,6 +63,10 @@ class Engine:
     @property
     def launches(self):
         return int(self._lib.vfi_launch_count(self._h))
+
+    def device_bytes(self):
+        """Device memory owned by the library handle (workspace + scratch + packed weights): invisible to torch's stats."""
+        return int(self._lib.vfi_device_bytes(self._h))
 
     def set_option(self, key, value):
         self._check(self._lib.vfi_set_option(self._h, key.encode(), int(value)), "vfi_set_option")
@@ -172,6 +188,24 @@ class Engine:
             rc = self._lib.vfi_flow_stats(self._h, _ptr(flow), n, H, W, _ptr(out), _stream())
         self._check(rc, "vfi_flow_stats")
         return out
+
+    def farneback(self, img0, img1, pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2,
+                  want_flow=True, want_stats=False):
+        """Dense Farneback flow of n frame pairs on the device (defaults = adaptive_pipeline.py:119-128).
+        img0/img1: (n,H,W,3) RGB or (n,H,W) gray uint8.  Returns flow (n,H,W,2) f32 and/or stats (n,3) f64."""
+        img0, img1 = self._u8(img0), self._u8(img1)
+        ch = 3 if img0.dim() == 4 else 1
+        n, H, W = img0.shape[:3]
+        with torch.cuda.device(self.device):
+            flow = torch.empty((n, H, W, 2), dtype=torch.float32, device=self.device) if want_flow else None
+            st = torch.empty((n, 3), dtype=torch.float64, device=self.device) if want_stats else None
+            rc = self._lib.vfi_farneback(self._h, _ptr(img0), _ptr(img1), n, H, W, ch, float(pyr_scale), int(levels),
+                                         int(winsize), int(iterations), int(poly_n), float(poly_sigma), _ptr(flow),
+                                         _ptr(st), _stream())
+        self._check(rc, "vfi_farneback")
+        if want_flow and want_stats:
+            return flow, st
+        return flow if want_flow else st
 
     def laplacian_var(self, rgb):
         rgb = self._u8(rgb)

@@ -43,14 +43,14 @@ def compute_ssim_simple(pred: np.ndarray, gt: np.ndarray) -> float:
     return float(Engine.get().ssim(pred[None], gt[None], downscale=1)[0])
 
 
-def psnr_batch(pred, gt, device=0) -> np.ndarray:
+def psnr_batch(pred, gt, device=None) -> np.ndarray:
     """(n,H,W,3) uint8 numpy / CUDA tensors -> n PSNR values (float64, inf for identical frames)."""
     sse, _ = Engine.get(device).psnr_sse(pred, gt)
     n = int(np.prod(pred.shape[1:]))
     return np.array([_psnr_from_sse(int(s), n) for s in sse.tolist()], dtype=np.float64)
 
 
-def ssim_batch(pred, gt, device=0) -> np.ndarray:
+def ssim_batch(pred, gt, device=None) -> np.ndarray:
     return Engine.get(device).ssim(pred, gt, downscale=1).cpu().numpy()
 
 

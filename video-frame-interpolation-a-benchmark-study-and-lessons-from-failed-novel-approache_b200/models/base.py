@@ -46,7 +46,10 @@ def _timed(fn):
     t0 = time.perf_counter()
     frames = fn()
     ms = (time.perf_counter() - t0) * 1000.0
-    peak = torch.cuda.max_memory_allocated() / 1e6 if cuda else 0
+    peak = 0
+    if cuda:  # torch's allocator statistics + what the library handle cudaMalloc'ed itself (workspace, packed weights)
+        from ..engine import library_device_bytes
+        peak = (torch.cuda.max_memory_allocated() + library_device_bytes()) / 1e6
     return frames, ms, peak
 
 

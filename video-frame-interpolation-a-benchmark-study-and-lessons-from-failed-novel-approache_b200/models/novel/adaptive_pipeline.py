@@ -3,10 +3,11 @@
 Drop-in for the reference's models/novel/adaptive_pipeline.py: ContentAnalysis :30-40, RoutingStats
 :43-71, AdaptiveRouter :74-286 (same six constructor thresholds :81-96, same public methods and
 state), AdaptivePipeline :289-483.  The per-pair statistics run as reduction kernels through the
-C ABI: scene-cut SSIM (vfi_ssim_gray_u8, downscale 4), |flow| mean/max/std (vfi_flow_stats),
-Laplacian variance (vfi_laplacian_var), HUD temporal-variance mask (vfi_hud_update); the decision
-tree is vfi_route_decide.  The dense flow field itself still comes from OpenCV's Farneback, called
-with the reference's parameters (:119-128) and uploaded -- SURVEY.md §8(f) row N1.
+C ABI: scene-cut SSIM (vfi_ssim_gray_u8, downscale 4), dense Farneback flow with the reference's
+parameters (:119-128) and its |flow| mean/max/std (vfi_farneback -> vfi_flow_stats, the flow field never
+leaves the GPU), Laplacian variance (vfi_laplacian_var), HUD temporal-variance mask (vfi_hud_update);
+the decision tree is vfi_route_decide.  `flow_fn=cv2_farneback_flow` swaps OpenCV's own flow back in
+(host, uploaded) -- used by the tests that compare every float64 field bit for bit with the reference.
 Fixes kept minimal: the RIFE / VFIMamba imports point at models/sota.
 """
 import dataclasses
@@ -57,8 +58,11 @@ class RoutingStats:
                 'scene_change': self.scene_change_count, 'scene_change_pct': pct(self.scene_change_count)}
 
 
-def farneback_flow(frame0: np.ndarray, frame1: np.ndarray) -> np.ndarray:
-    """Dense flow source (third-party OpenCV, reference parameters adaptive_pipeline.py:119-128)."""
+FARNEBACK = dict(pyr_scale=0.5, levels=3, winsize=15, iterations=3, poly_n=5, poly_sigma=1.2)   # reference :119-128
+
+
+def cv2_farneback_flow(frame0: np.ndarray, frame1: np.ndarray) -> np.ndarray:
+    """OpenCV's own Farneback on the host (reference parameters adaptive_pipeline.py:119-128): optional flow_fn."""
     g0 = cv2.cvtColor(frame0, cv2.COLOR_RGB2GRAY)
     g1 = cv2.cvtColor(frame1, cv2.COLOR_RGB2GRAY)
     return cv2.calcOpticalFlowFarneback(g0, g1, None, pyr_scale=0.5, levels=3, winsize=15, iterations=3,
@@ -79,7 +83,7 @@ class AdaptiveRouter:
         self.hud_history_frames = hud_history_frames
         self.hud_mask: Optional[np.ndarray] = None
         self._device = device
-        self._flow_fn = flow_fn or farneback_flow
+        self._flow_fn = flow_fn          # None: Farneback on the GPU (vfi_farneback); callable(f0, f1) -> host flow (H,W,2)
         self._engine = None
         self._hud = None
         self._hud_mask_dev = None
@@ -89,7 +93,7 @@ class AdaptiveRouter:
     @property
     def engine(self) -> Engine:
         if self._engine is None:
-            self._engine = Engine.get(self._device if self._device is not None else 0)
+            self._engine = Engine.get(self._device)      # None -> the current CUDA device
         return self._engine
 
     def _hud_state(self) -> HudState:
@@ -114,8 +118,14 @@ class AdaptiveRouter:
     # -- the reference's public methods ----------------------------------------------------
     def compute_motion(self, frame0: np.ndarray, frame1: np.ndarray) -> Tuple[float, float, float, np.ndarray]:
         """(mean, max, std, |flow| map) -- reference :108-138."""
-        flow = torch.from_numpy(self._flow_fn(frame0, frame1)).to(self.engine.device)
-        st = self.engine.flow_stats(flow[None])[0].tolist()
+        if self._flow_fn is None:
+            flow, st = self.engine.farneback(self._dev(frame0)[None], self._dev(frame1)[None], want_stats=True, **FARNEBACK)
+            flow = flow[0]
+        else:
+            flow = torch.from_numpy(self._flow_fn(frame0, frame1)).to(self.engine.device)
+            st = self.engine.flow_stats(flow[None])
+        st = st[0].tolist()
+        # the reference hands the |flow| map back (:131,138); callers on the hot path (analyze) never ask for it
         mag = torch.sqrt(flow[..., 0] ** 2 + flow[..., 1] ** 2).cpu().numpy()
         return st[0], st[1], st[2], mag
 
@@ -149,8 +159,10 @@ class AdaptiveRouter:
         score = float(e.ssim(d0[None], d1[None], downscale=4)[0])
         if score < self.scene_change_threshold:
             return ContentAnalysis(0, 0, 0, False, True, 0, 'scene_change', 1.0 - score)
-        flow = self._flow_fn(frame0, frame1)
-        st = e.flow_stats(torch.from_numpy(flow)[None])
+        if self._flow_fn is None:
+            st = e.farneback(d0[None], d1[None], want_flow=False, want_stats=True, **FARNEBACK)
+        else:
+            st = e.flow_stats(torch.from_numpy(self._flow_fn(frame0, frame1))[None])
         lv = e.laplacian_var(d0[None])
         mean, mx, std = st[0].tolist()
         lv = float(lv[0])
@@ -181,13 +193,15 @@ class AdaptivePipeline(BaseModel):
     """Routes pairs by content; RIFE fast path on the B200 kernels; HUD pixels copied from the nearer input."""
 
     def __init__(self, device: str = 'cuda', motion_threshold_low: float = 5.0, motion_threshold_high: float = 25.0,
-                 enable_vfimamba: bool = True, sr_model_name: str = 'lanczos'):
+                 enable_vfimamba: bool = True, sr_model_name: str = 'lanczos', *, allow_random_weights: bool = False,
+                 flow_fn=None):
         super().__init__(device)
+        self._allow_random_weights = allow_random_weights
         self.enable_vfimamba = enable_vfimamba
         self.sr_model_name = sr_model_name
         self.router = AdaptiveRouter(motion_threshold_low=motion_threshold_low,
                                      motion_threshold_high=motion_threshold_high,
-                                     device=self.device if self.device.type == 'cuda' else None)
+                                     device=self.device if self.device.type == 'cuda' else None, flow_fn=flow_fn)
         self.stats = RoutingStats()
         self._rife = None
         self._vfimamba = None
@@ -202,7 +216,7 @@ class AdaptivePipeline(BaseModel):
     def load(self) -> None:
         print("Loading Adaptive Pipeline...")
         from ..sota.rife_wrapper import RIFEModel
-        self._rife = RIFEModel(device=str(self.device))
+        self._rife = RIFEModel(device=str(self.device), allow_random_weights=self._allow_random_weights)
         self._rife.load()
         if self.enable_vfimamba:
             try:
@@ -259,8 +273,7 @@ class AdaptivePipeline(BaseModel):
         mids = self.interpolate(frame0, frame1, num_intermediate)
         frames = [self.upscale(f, target_scale) for f in [frame0, *mids, frame1]]
         ms = (time.perf_counter() - t0) * 1000
-        peak = torch.cuda.max_memory_allocated() / 1e6 if torch.cuda.is_available() else 0
-        return InferenceResult(frames=frames, inference_time_ms=ms, vram_peak_mb=peak, model_used=self.info.name,
+        return InferenceResult(frames=frames, inference_time_ms=ms, vram_peak_mb=self._vram_mb(), model_used=self.info.name,
                                extra_info={'analysis': {'motion_mean': analysis.motion_mean,
                                                         'motion_max': analysis.motion_max,
                                                         'has_particles': analysis.has_particles,
@@ -268,6 +281,22 @@ class AdaptivePipeline(BaseModel):
                                                         'hud_coverage': analysis.hud_coverage,
                                                         'recommended_model': analysis.recommended_model},
                                            'routing_stats': self.stats.to_dict()})
+
+    def process_pair_fast(self, frame0: np.ndarray, frame1: np.ndarray, num_intermediate: int = 3,
+                          target_scale: float = 1.333) -> InferenceResult:
+        """Extra: process_pair with ONE analysis per pair (the reference analyses twice, :443 + :382,
+        pushing the HUD history twice).  Same outputs for a clip whose HUD history is pushed once per pair."""
+        self.ensure_loaded()
+        t0 = time.perf_counter()
+        mids, analysis = self._interpolate_routed(frame0, frame1, num_intermediate)
+        frames = [self.upscale(f, target_scale) for f in [frame0, *mids, frame1]]
+        ms = (time.perf_counter() - t0) * 1000
+        return InferenceResult(frames=frames, inference_time_ms=ms, vram_peak_mb=self._vram_mb(), model_used=self.info.name,
+                               extra_info={'analysis': dataclasses.asdict(analysis), 'routing_stats': self.stats.to_dict()})
+
+    def _vram_mb(self) -> float:
+        from ...engine import library_device_bytes
+        return (torch.cuda.max_memory_allocated() + library_device_bytes()) / 1e6
 
     def process_clip(self, frames, num_frames: int = 3, rank: int = 0, world: int = 1, group=None,
                      on_pair=None) -> dict:

@@ -6,9 +6,13 @@ search and FileNotFoundError behaviour (:44-72), `info` (:74-85), `load` (:87-10
 (:206-224) and `get_rife_model` (:227-245).  What changed underneath: to_tensor, reflect padding, the
 IFNet pass for ALL timesteps (Head features computed once per pair), unpad and the *255/clip/uint8
 conversion run as one C-ABI call (vfi_ifnet_infer) on the GPU; only uint8 frames cross PCIe.
-Deviations: pad multiple is max(32, 64/scale) so 1440p works; a train_log
-directory without flownet.pkl means seeded random-init weights (there is no network to fetch them).
+Deviations: pad multiple is max(32, 64/scale) so 1440p works.  A train_log directory
+without flownet.pkl raises FileNotFoundError at load() like the reference does when its weights are missing --
+unless the caller opts into seeded random-init weights (allow_random_weights=True or VFI_B200_RANDOM_WEIGHTS=1:
+the synthetic benchmark configs, tests and smoke; there is no network to fetch the release weights).
 """
+import os
+import sys
 from pathlib import Path
 from typing import List, Optional
 
@@ -27,7 +31,8 @@ class RIFEModel(BaseModel):
     """RIFE v4.25/4.26 - Real-time Intermediate Flow Estimation (arbitrary timesteps)."""
 
     def __init__(self, model_dir: Optional[str] = None, version: str = 'v4.25', device: str = 'cuda',
-                 uhd_mode: bool = False, *, precision: str = 'bf16', weight_seed: int = 1234):
+                 uhd_mode: bool = False, *, precision: str = 'bf16', weight_seed: int = 1234,
+                 allow_random_weights: bool = False):
         super().__init__(device)
         if model_dir is None:
             for cand in (Path('external/Practical-RIFE'), Path('../external/Practical-RIFE'),
@@ -50,6 +55,7 @@ class RIFEModel(BaseModel):
             raise ValueError("precision must be 'bf16' or 'fp32'")
         self.precision = precision
         self.weight_seed = weight_seed
+        self.allow_random_weights = allow_random_weights or os.environ.get('VFI_B200_RANDOM_WEIGHTS') == '1'
         self._engine = None
         self._state_dict = None
         self._pinned = {}
@@ -65,8 +71,15 @@ class RIFEModel(BaseModel):
         if self._state_dict is None:
             if (self.weights_dir / 'flownet.pkl').exists():
                 self._state_dict = ifnet_params.load_pkl(self.weights_dir)
-            else:
+            elif self.allow_random_weights:
+                print(f"WARNING: {self.weights_dir / 'flownet.pkl'} not found -- using RANDOM-INIT IFNet weights (seed "
+                      f"{self.weight_seed}); the interpolated frames are meaningless outside the synthetic benchmarks",
+                      file=sys.stderr)
                 self._state_dict = ifnet_params.random_init(self.weight_seed)
+            else:
+                raise FileNotFoundError(f"RIFE weights not found at {self.weights_dir / 'flownet.pkl'}. "
+                                        "Download from: https://github.com/hzwer/Practical-RIFE/releases "
+                                        "(or pass allow_random_weights=True for the synthetic benchmark configs)")
         return self._state_dict
 
     def load(self) -> None:
