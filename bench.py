@@ -138,6 +138,11 @@ def measure_aux(eng, clip_dev, H, W, hbm):
         "flow_stats (A7)": (lambda: eng.flow_stats(flow), 8, 8 * px, "fp32 flow field (u, v)"),
         "laplacian_var (A8)": (lambda: eng.laplacian_var(a), n, 3 * px, "one u8 RGB frame"),
         "hud_update (A9)": (hud_step, 1, 3 * px + 2 * px, "u8 RGB frame in, full-resolution mask out (+ 180x320 ring)"),
+        "psnr_ssim_fused (A13+A14)": (lambda: eng.psnr_ssim(a, b), n, 6 * px, "both u8 RGB frames, read once for both metrics"),
+        "farneback_flow_stats (N1+A7, 8 pairs/call)": (lambda: eng.farneback(a[:8], b[:8], want_flow=False, want_stats=True), 8, 6 * px,
+                                                        "both u8 RGB frames (algorithmic input; the pyramid planes are the kernel's own traffic)"),
+        "farneback_flow_stats (N1+A7, 1 pair/call)": (lambda: eng.farneback(a[:1], b[:1], want_flow=False, want_stats=True), 1, 6 * px,
+                                                       "both u8 RGB frames"),
     }
     out = {}
     for name, (fn, per_call, bytes_per_frame, what) in cases.items():

@@ -107,6 +107,12 @@ int vfi_psnr_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t
 int vfi_ssim_gray_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, int H, int W,
                      int downscale, double* out, void* stream);
 
+/* compute_psnr_simple + compute_ssim_simple of the same n frame pairs from ONE read of the frames (the evaluation loop of
+ * scripts/run_benchmarks.py:174-178 calls both per frame; evaluation/metrics.py:299-335).  a,b: n x H x W x 3 uint8 RGB.
+ * sse_out (n x uint64, exact) and psnr_out (n x double) may be NULL; ssim_out: n x double.                              */
+int vfi_psnr_ssim_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, int H, int W,
+                     unsigned long long* sse_out, double* psnr_out, double* ssim_out, void* stream);
+
 /* AdaptiveRouter.compute_motion's reductions (adaptive_pipeline.py:130-138) over a dense flow
  * field n x H x W x 2 float: out[3*i+0..2] = mean, max, std (population) of |flow|.        */
 int vfi_flow_stats(vfi_handle* h, const float* flow, int n, int H, int W, double* out, void* stream);

@@ -41,7 +41,7 @@ def test_psnr_extremes_and_unaligned(engine):
     assert sse.tolist() == [_sse(ua[i].cpu().numpy(), ub[i].cpu().numpy()) for i in range(2)]
 
 
-@pytest.mark.parametrize("H,W", [(1080, 1920), (360, 640), (45, 71), (7, 7)])
+@pytest.mark.parametrize("H,W", [(1080, 1920), (360, 640), (45, 71), (7, 7), (129, 250), (1440, 2560), (600, 129)])
 def test_ssim_full_res(engine, H, W):
     fr = gen_clip(2, H, W, seed=3, cut_every=0, fast=None, hud=H > 100)
     pred = noisy_copy(fr, seed=6)
@@ -60,6 +60,23 @@ def test_scene_cut_ssim_quarter_res(engine, H, W):
     assert np.array_equal(got < 0.65, want < 0.65)
     if H >= 360:
         assert (want < 0.65).any() and (want >= 0.65).any()
+
+
+@pytest.mark.parametrize("shape", [(3, 1080, 1920, 3), (2, 360, 640, 3), (4, 45, 71, 3), (1, 7, 7, 3), (2, 130, 123, 3), (1, 2160, 3840, 3)])
+def test_fused_psnr_ssim_equals_separate_kernels(engine, shape):
+    """vfi_psnr_ssim_u8 (one read of the frames): SSE identical to vfi_psnr_u8 and to numpy, SSIM <= 1e-9 from the oracle."""
+    n, H, W, _ = shape
+    fr = gen_clip(n - 1, H, W, seed=13, cut_every=0, fast=None, hud=H > 100) if H >= 16 else \
+        np.random.default_rng(1).integers(0, 256, shape, dtype=np.uint8)
+    pred = noisy_copy(fr, seed=7, amp=5)
+    pred[0] = fr[0]
+    sse, ps, ss = engine.psnr_ssim(pred, fr)
+    assert sse.tolist() == [_sse(pred[i], fr[i]) for i in range(n)] == engine.psnr_sse(pred, fr)[0].tolist()
+    assert float(ps[0]) == np.inf and abs(float(ss[0]) - 1.0) < 1e-12
+    want = np.array([metrics_ref.ssim_simple(pred[i], fr[i]) for i in range(n)])
+    assert np.abs(ss.cpu().numpy() - want).max() <= 1e-9
+    for i in range(1, n):
+        assert abs(float(ps[i]) - metrics_ref.psnr_simple(pred[i], fr[i])) <= 1e-12 * abs(float(ps[i]))
 
 
 def test_ssim_random_noise_range(engine):                          # reference test_metrics.py:78-85
@@ -88,7 +105,7 @@ def test_flow_stats_synthetic_extremes(engine):
     assert g[1] == 50.0 and abs(g[0] - 50.0 / (64 * 96)) < 1e-12
 
 
-@pytest.mark.parametrize("H,W", [(1080, 1920), (360, 640), (33, 65), (2, 2)])
+@pytest.mark.parametrize("H,W", [(1080, 1920), (360, 640), (33, 65), (2, 2), (2160, 3840), (700, 121), (5, 300)])
 def test_laplacian_var(engine, H, W):
     rng = np.random.default_rng(9)
     fr = rng.integers(0, 256, (3, H, W, 3), dtype=np.uint8)

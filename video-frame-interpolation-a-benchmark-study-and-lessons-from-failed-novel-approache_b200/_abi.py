@@ -27,6 +27,7 @@ SIGNATURES = {
     "vfi_warp_blend": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "vfi_psnr_u8": (_i, [_vp, _vp, _vp, _i, _sz, _vp, _vp, _vp]),
     "vfi_ssim_gray_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "vfi_psnr_ssim_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "vfi_flow_stats": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "vfi_laplacian_var": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),
     "vfi_farneback": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _d, _i, _i, _i, _i, _d, _vp, _vp, _vp]),

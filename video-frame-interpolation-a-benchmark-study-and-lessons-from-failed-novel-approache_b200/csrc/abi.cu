@@ -44,7 +44,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_create(int device, vfi
   h->sm_count = prop.multiProcessorCount;
   for (int i = 0; i < VFI_NUM_LAYERS; i++) h->layers[i] = Layer();
   const bool ok = cudaEventCreateWithFlags(&h->scratch_ev, cudaEventDisableTiming) == cudaSuccess &&
-                  cudaMalloc(&h->tdev, 64 * sizeof(float)) == cudaSuccess;
+                  cudaMalloc(&h->tdev, 64 * sizeof(float)) == cudaSuccess && cudaMalloc(&h->hud_cnt, 16) == cudaSuccess &&
+                  cudaMemset(h->hud_cnt, 0, 16) == cudaSuccess;
   if (prev >= 0 && prev != device) cudaSetDevice(prev);  // leave the caller's current device as it was
   if (!ok) { cudaGetLastError(); delete h; return VFI_E_CUDA; }
   *out = h;
@@ -72,6 +73,7 @@ extern "C" __attribute__((visibility("default"))) void vfi_destroy(vfi_handle* h
   cudaFree(h->ws);
   cudaFree(h->red);
   cudaFree(h->tdev);
+  cudaFree(h->hud_cnt);
   if (h->scratch_ev) cudaEventDestroy(h->scratch_ev);
   if (prev >= 0 && prev != h->device) cudaSetDevice(prev);
   delete h;

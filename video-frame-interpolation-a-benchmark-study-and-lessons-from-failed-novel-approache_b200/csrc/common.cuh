@@ -79,6 +79,7 @@ struct vfi_handle {
   cudaStream_t scratch_stream = nullptr;
   bool scratch_used = false;
   size_t weight_bytes = 0;      // device bytes held by the packed weights (vfi_device_bytes)
+  unsigned long long* hud_cnt = nullptr;  // {mask pixel count, CTA tickets} of the fused HUD kernel; zero between launches
   float* tdev = nullptr;        // the call's timesteps on the device (64 floats); re-uploaded only when they change
   float t_host[64] = {0};
   int t_n = 0;

@@ -203,6 +203,171 @@ __global__ void sum_partials_kernel(const double* __restrict__ partial, int per,
   s = block_sum(s, shd);
   if (threadIdx.x == 0) out[f] = s / denom;
 }
+// ---------------------------------------------------------------------------------------------
+// Full-resolution SSIM (+ the PSNR sum of squared errors of the same frame pair from the same read): the config-5 kernel.
+// A CTA owns a strip of 128 input columns (122 output windows) and a segment of rows and walks DOWN it:
+//   V phase  thread = column: gray of both images for the new row (cv2 integers), vertical 7-row running sums of
+//            (a | b << 16), a^2 + b^2, a*b -- the old row's pixel comes back from a 7-deep shared-memory ring -- written
+//            to a 16-row shared-memory tile;
+//   H phase  thread = (row, 16-column run): horizontal 7-column running sums over that tile, the SSIM rational from the
+//            five exact integer window sums, in fp64 (one multiply by a correctly rounded reciprocal per window).
+// Each input byte is read once (+ 6/128 column and 6/rows halo), 16 tile rows per pair of block barriers.
+// SSIM only needs sum(a), sum(b), sum(a^2) + sum(b^2) and sum(ab):
+//   S = (2AB/n^2 + C1)(2 cov + C2) / ((A^2 + B^2)/n^2 + C1)(var_a + var_b + C2), n = 49, cov_norm = n/(n-1)
+//     = (2AB + C1 n^2)(2(n sum(ab) - AB) + C2 n(n-1)) / (A^2 + B^2 + C1 n^2)(n(sum(a^2) + sum(b^2)) - A^2 - B^2 + C2 n(n-1))
+#define SF_COLS 128
+#define SF_OUT (SF_COLS - 6)
+#define SF_ROWS 16
+#define SF_STRIDE (SF_COLS + SF_COLS / 16)  // 16-column runs skewed by one word: the H phase reads conflict-free
+__device__ __forceinline__ double ssim_window(int pk, int q, int ab) {
+  const int A = pk & 0xffff, B = (unsigned)pk >> 16;
+  const int AB = A * B, t3 = A * A + B * B;
+  const double c1 = 6.5025 * 2401.0, c2 = 58.5225 * 2352.0;
+  const double num = ((double)(2 * AB) + c1) * ((double)(2 * (49 * ab - AB)) + c2);
+  const double den = ((double)t3 + c1) * ((double)(49 * q - t3) + c2);
+  return num * __drcp_rn(den);
+}
+template <bool SSE>
+__global__ void __launch_bounds__(SF_COLS) ssim_full_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int H, int W,
+                                                            int rows_per_seg, double* __restrict__ part_ssim,
+                                                            unsigned long long* __restrict__ part_sse) {
+  __shared__ int vt[3][SF_ROWS][SF_STRIDE];
+  __shared__ uint8_t ring[2][7][SF_COLS];
+  __shared__ double shd[32];
+  __shared__ unsigned long long shl[32];
+  const int t = threadIdx.x, f = blockIdx.z;
+  const int x = blockIdx.x * SF_OUT + t;
+  const bool xin = x < W;
+  const int oh = H - 6;                                           // output rows
+  const int y0 = blockIdx.y * rows_per_seg, y1 = min(oh, y0 + rows_per_seg);   // this CTA's output rows
+  const bool last_seg = y1 == oh, last_strip = blockIdx.x == gridDim.x - 1;
+  const uint8_t* pa = a + ((size_t)f * H * W + x) * 3;
+  const uint8_t* pb = b + ((size_t)f * H * W + x) * 3;
+  const bool own_col = xin && (t < SF_OUT || last_strip);
+  int pk = 0, q = 0, ab = 0;
+  unsigned int sse = 0;
+  double acc = 0.0;
+  const int tpos = t + (t >> 4);
+  const int hrow = t >> 3, hseg = t & 7;                          // H-phase role
+  const int ow = W - 6;
+  int slot = 0;
+  for (int r0 = y0; r0 < y1 + 6; r0 += 4) {
+    // four rows of loads in flight before any of them is consumed
+    int ga[4], gb[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int r = r0 + j;
+      ga[j] = gb[j] = 0;
+      if (xin && r < y1 + 6) {
+        const uint8_t* qa = pa + (size_t)r * W * 3;
+        const uint8_t* qb = pb + (size_t)r * W * 3;
+        const int ar = qa[0], ag = qa[1], abl = qa[2], br = qb[0], bg = qb[1], bb = qb[2];
+        ga[j] = gray_u8(ar, ag, abl);
+        gb[j] = gray_u8(br, bg, bb);
+        if (SSE && own_col && (r < y0 + rows_per_seg || last_seg)) {
+          const int d0 = ar - br, d1 = ag - bg, d2 = abl - bb;
+          sse += (unsigned)(d0 * d0 + d1 * d1 + d2 * d2);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int r = r0 + j;
+      if (r >= y1 + 6) break;                                      // uniform over the CTA
+      const int k = (r - y0) % 7;
+      if (r - y0 >= 7) {                                           // the row leaving the 7-row window
+        const int oa = ring[0][k][t], ob = ring[1][k][t];
+        pk -= oa | (ob << 16); q -= oa * oa + ob * ob; ab -= oa * ob;
+      }
+      ring[0][k][t] = (uint8_t)ga[j]; ring[1][k][t] = (uint8_t)gb[j];
+      pk += ga[j] | (gb[j] << 16); q += ga[j] * ga[j] + gb[j] * gb[j]; ab += ga[j] * gb[j];
+      if (r - y0 >= 6) {                                           // window complete: output row r - 6
+        vt[0][slot][tpos] = pk; vt[1][slot][tpos] = q; vt[2][slot][tpos] = ab;
+        slot++;
+      }
+      if (slot == SF_ROWS || (r == y1 + 5 && slot > 0)) {
+        __syncthreads();
+        if (hrow < slot) {
+          const int xl0 = hseg * 16, base = hseg * 17;
+          const int nout = min(16, min(SF_OUT - xl0, ow - (blockIdx.x * SF_OUT + xl0)));
+          if (nout > 0) {
+            const int* v0 = &vt[0][hrow][base];
+            const int* v1 = &vt[1][hrow][base];
+            const int* v2 = &vt[2][hrow][base];
+            int hp = 0, hq = 0, hab = 0;
+#pragma unroll
+            for (int c = 0; c < 7; c++) { hp += v0[c]; hq += v1[c]; hab += v2[c]; }
+#pragma unroll 4
+            for (int i = 0; i < nout; i++) {
+              acc += ssim_window(hp, hq, hab);
+              const int cn = i + 7 + ((i + 7) >> 4), co = i;      // entering / leaving column (skewed position)
+              hp += v0[cn] - v0[co]; hq += v1[cn] - v1[co]; hab += v2[cn] - v2[co];
+            }
+          }
+        }
+        __syncthreads();
+        slot = 0;
+      }
+    }
+  }
+  acc = block_sum(acc, shd);
+  const size_t pi = ((size_t)f * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  if (t == 0) part_ssim[pi] = acc;
+  if (SSE) {
+    const unsigned long long s = block_sum((unsigned long long)sse, shl);
+    if (t == 0) part_sse[pi] = s;
+  }
+}
+__global__ void ssim_full_finish_kernel(const double* __restrict__ part_ssim, const unsigned long long* __restrict__ part_sse, int per,
+                                        double denom, size_t elems, double* __restrict__ ssim_out,
+                                        unsigned long long* __restrict__ sse_out, double* __restrict__ psnr_out) {
+  __shared__ double shd[32];
+  __shared__ unsigned long long shl[32];
+  const int f = blockIdx.x;
+  double s = 0.0;
+  unsigned long long e = 0;
+  for (int i = threadIdx.x; i < per; i += blockDim.x) {
+    s += part_ssim[(size_t)f * per + i];
+    if (part_sse) e += part_sse[(size_t)f * per + i];
+  }
+  s = block_sum(s, shd);
+  if (part_sse) e = block_sum(e, shl);
+  if (threadIdx.x == 0) {
+    if (ssim_out) ssim_out[f] = s / denom;
+    if (sse_out) sse_out[f] = e;
+    if (psnr_out) psnr_out[f] = e == 0 ? INFINITY : 10.0 * log10(255.0 * 255.0 / ((double)e / (double)elems));
+  }
+}
+static int ssim_full_launch(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, int H, int W, bool want_sse,
+                            double* ssim_out, unsigned long long* sse_out, double* psnr_out, cudaStream_t s) {
+  const int oh = H - 6, ow = W - 6;
+  const int strips = cdiv(ow, SF_OUT);
+  // enough CTAs for ~6 per SM when the batch is small; at least 32 output rows per CTA so the 6-row halo stays cheap
+  int segs = std::max(1, std::min(cdiv(oh, 32), cdiv(6 * h->sm_count, strips * n)));
+  const int rps = cdiv(oh, segs);
+  segs = cdiv(oh, rps);
+  const int per = strips * segs;
+  if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * per * 16 + 64))) return rc;
+  double* part = (double*)h->red;
+  unsigned long long* parte = (unsigned long long*)(part + (size_t)n * per);
+  dim3 grid(strips, segs, n);
+  if (want_sse) ssim_full_kernel<true><<<grid, SF_COLS, 0, s>>>(a, b, H, W, rps, part, parte);
+  else ssim_full_kernel<false><<<grid, SF_COLS, 0, s>>>(a, b, H, W, rps, part, nullptr);
+  VFI_LAUNCHED(h);
+  ssim_full_finish_kernel<<<n, 256, 0, s>>>(part, want_sse ? parte : nullptr, per, (double)oh * (double)ow, (size_t)H * W * 3, ssim_out,
+                                            sse_out, psnr_out);
+  VFI_LAUNCHED(h);
+  return VFI_OK;
+}
+extern "C" __attribute__((visibility("default"))) int vfi_psnr_ssim_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, int H, int W,
+                                                                         unsigned long long* sse_out, double* psnr_out, double* ssim_out,
+                                                                         void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!a || !b || !ssim_out || n < 1 || n > 65535) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  if (H < 7 || W < 7) VFI_FAIL(h, VFI_E_ARG, "image smaller than the 7x7 SSIM window");
+  VFI_ENTER(h, stream);
+  return ssim_full_launch(h, a, b, n, H, W, true, ssim_out, sse_out, psnr_out, (cudaStream_t)stream);
+}
 extern "C" __attribute__((visibility("default"))) int vfi_ssim_gray_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, int H, int W, int downscale,
                                 double* out, void* stream) {
   if (!h) return VFI_E_ARG;
@@ -213,6 +378,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ssim_gray_u8(vfi_handl
   if (hh < 7 || ww < 7) VFI_FAIL(h, VFI_E_ARG, "image smaller than the 7x7 SSIM window");
   VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
+  if (downscale == 1) return ssim_full_launch(h, a, b, n, H, W, false, out, nullptr, nullptr, s);
   dim3 grid(cdiv(ww - 6, SS_T), cdiv(hh - 6, SS_T), n);
   const int per = grid.x * grid.y;
   if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * per * 8))) return rc;
@@ -298,57 +464,80 @@ int vfi_flow_stats_impl(vfi_handle* h, const float* flow, int n, int H, int W, d
 // Laplacian variance (adaptive_pipeline.py:180-183): cv2.Laplacian(gray, CV_64F), ksize 1 =
 // [0 1 0; 1 -4 1; 0 1 0] with BORDER_REFLECT_101, then .var().  The stencil is integer, so
 // sum(x) and sum(x^2) are exact int64; only the final variance is fp64.
-#define LP_T 32
-__global__ void laplacian_kernel(const uint8_t* __restrict__ rgb, int H, int W, long long* __restrict__ acc) {
-  __shared__ int g[LP_T + 2][LP_T + 2];
+// A warp owns 30 output columns (lanes 0 and 31 carry the left / right halo column) and walks down its row segment with the
+// previous / current / next gray rows in registers: horizontal neighbours come by shuffle, each byte is read once, no
+// shared memory and no block barrier in the loop.  Per-lane partial sums stay 32-bit (segments are at most 512 rows).
+#define LP_WARPS 4
+#define LP_COLS 30
+#define LP_MAX_ROWS 512
+__device__ __forceinline__ int lp_gray_row(const uint8_t* __restrict__ p, int W, int H, int y, int x, bool xin) {
+  if (!xin) return 0;
+  y = y < 0 ? -y : (y >= H ? 2 * (H - 1) - y : y);               // reflect-101 (cv2 BORDER_DEFAULT)
+  y = max(0, min(y, H - 1));
+  const uint8_t* q = p + ((size_t)y * W + x) * 3;
+  return gray_u8(q[0], q[1], q[2]);
+}
+__global__ void __launch_bounds__(LP_WARPS * 32) laplacian_kernel(const uint8_t* __restrict__ rgb, int H, int W, int rows_per_seg,
+                                                                 long long* __restrict__ partial) {
   __shared__ long long shl[32];
-  const int f = blockIdx.z;
+  const int f = blockIdx.z, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint8_t* p = rgb + (size_t)f * H * W * 3;
-  const int ox = blockIdx.x * LP_T, oy = blockIdx.y * LP_T;
-  for (int i = threadIdx.x; i < (LP_T + 2) * (LP_T + 2); i += blockDim.x) {
-    int ly = i / (LP_T + 2), lx = i % (LP_T + 2);
-    int gy = oy + ly - 1, gx = ox + lx - 1;
-    if (gy < 0) gy = -gy;                   // reflect-101
-    if (gx < 0) gx = -gx;
-    if (gy >= H) gy = 2 * (H - 1) - gy;
-    if (gx >= W) gx = 2 * (W - 1) - gx;
-    gy = max(0, min(gy, H - 1)); gx = max(0, min(gx, W - 1));
-    const uint8_t* q = p + ((size_t)gy * W + gx) * 3;
-    g[ly][lx] = gray_u8(q[0], q[1], q[2]);
-  }
-  __syncthreads();
-  long long s = 0, s2 = 0;
-  for (int i = threadIdx.x; i < LP_T * LP_T; i += blockDim.x) {
-    int ly = i / LP_T, lx = i % LP_T;
-    if (oy + ly < H && ox + lx < W) {
-      int v = g[ly][lx + 1] + g[ly + 2][lx + 1] + g[ly + 1][lx] + g[ly + 1][lx + 2] - 4 * g[ly + 1][lx + 1];
-      s += v; s2 += (long long)v * v;
+  const int xo = (blockIdx.x * LP_WARPS + warp) * LP_COLS + lane - 1;   // lane's own column (halo lanes: one outside the run)
+  int xs = xo < 0 ? -xo : (xo >= W ? 2 * (W - 1) - xo : xo);           // reflect-101
+  const bool xin = xo <= W && xs >= 0 && xs < W;                        // xo == W is the right halo of the last column
+  xs = max(0, min(xs, W - 1));
+  const bool owns = lane >= 1 && lane <= LP_COLS && xo < W;
+  const int y0 = blockIdx.y * rows_per_seg, y1 = min(H, y0 + rows_per_seg);
+  int s = 0;
+  unsigned int s2 = 0;
+  int gp = lp_gray_row(p, W, H, y0 - 1, xs, xin), gc = lp_gray_row(p, W, H, y0, xs, xin);
+  for (int y = y0; y < y1; y += 4) {
+    int gn[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) gn[j] = lp_gray_row(p, W, H, y + 1 + j, xs, xin && y + j < y1);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      if (y + j >= y1) break;
+      const int l = __shfl_up_sync(0xffffffffu, gc, 1), r = __shfl_down_sync(0xffffffffu, gc, 1);
+      const int v = gp + gn[j] + l + r - 4 * gc;
+      if (owns) { s += v; s2 += (unsigned)(v * v); }
+      gp = gc; gc = gn[j];
     }
   }
+  const long long bs = block_sum((long long)s, shl);
+  const long long bs2 = block_sum((long long)s2, shl);
+  if (threadIdx.x == 0) {
+    long long* o = partial + 2 * (((size_t)f * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x);
+    o[0] = bs; o[1] = bs2;
+  }
+}
+__global__ void laplacian_finish_kernel(const long long* __restrict__ partial, int per, double npix, double* __restrict__ out) {
+  __shared__ long long shl[32];
+  const int f = blockIdx.x;
+  long long s = 0, s2 = 0;
+  for (int i = threadIdx.x; i < per; i += blockDim.x) { s += partial[2 * ((size_t)f * per + i)]; s2 += partial[2 * ((size_t)f * per + i) + 1]; }
   s = block_sum(s, shl);
   s2 = block_sum(s2, shl);
   if (threadIdx.x == 0) {
-    atomicAdd((unsigned long long*)(acc + 2 * f), (unsigned long long)s);
-    atomicAdd((unsigned long long*)(acc + 2 * f + 1), (unsigned long long)s2);
+    const double mean = (double)s / npix;
+    out[f] = (double)s2 / npix - mean * mean;
   }
-}
-__global__ void laplacian_finish_kernel(const long long* acc, int n, double npix, double* out) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  double mean = (double)acc[2 * i] / npix;
-  out[i] = (double)acc[2 * i + 1] / npix - mean * mean;
 }
 extern "C" __attribute__((visibility("default"))) int vfi_laplacian_var(vfi_handle* h, const uint8_t* rgb, int n, int H, int W, double* out, void* stream) {
   if (!h) return VFI_E_ARG;
   if (!rgb || !out || n < 1 || n > 4096 || H < 2 || W < 2) VFI_FAIL(h, VFI_E_ARG, "bad argument");
   VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
-  if (int rc = vfi_red_reserve(h, (size_t)65536 * 8)) return rc;
-  long long* acc = (long long*)h->red;
-  VFI_CUDA(h, cudaMemsetAsync(acc, 0, (size_t)n * 16, s));
-  laplacian_kernel<<<dim3(cdiv(W, LP_T), cdiv(H, LP_T), n), 256, 0, s>>>(rgb, H, W, acc);
+  const int strips = cdiv(W, LP_WARPS * LP_COLS);
+  int segs = std::max(cdiv(H, LP_MAX_ROWS), std::min(cdiv(H, 16), cdiv(8 * h->sm_count, strips * n)));
+  const int rps = cdiv(H, segs);
+  segs = cdiv(H, rps);
+  const int per = strips * segs;
+  if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * per * 16))) return rc;
+  long long* partial = (long long*)h->red;
+  laplacian_kernel<<<dim3(strips, segs, n), LP_WARPS * 32, 0, s>>>(rgb, H, W, rps, partial);
   VFI_LAUNCHED(h);
-  laplacian_finish_kernel<<<cdiv(n, 128), 128, 0, s>>>(acc, n, (double)H * W, out);
+  laplacian_finish_kernel<<<n, 256, 0, s>>>(partial, per, (double)H * W, out);
   VFI_LAUNCHED(h);
   return VFI_OK;
 }
@@ -392,11 +581,16 @@ __global__ void hud_var_kernel(const uint8_t* __restrict__ ring, HudSlots sl, do
 #define HM_N (HM_T + 2 * HM_R)
 #define HM_CELLS 50  // small-mask cells a 48-pixel span can touch when the frame is at least 320 x 180 (ratio >= 1);
                      // smaller frames (nearest UPsampling of the thumbnail grid) take the unstaged path
-__device__ __forceinline__ bool hud_flag_at(const uint8_t* __restrict__ ring, const int* idx, double thr, int i) {
+// np.var(last five thumbnails) < thr with numpy's operation order; `newest` >= 0 replaces the ring read of the fifth
+// (newest) thumbnail: the fused kernel computes that value itself while another CTA may still be writing it to the ring
+__device__ __forceinline__ bool hud_flag_at(const uint8_t* __restrict__ ring, const int* idx, double thr, int i, int newest = -1) {
   double x[5];
   double sum = 0.0;
 #pragma unroll
-  for (int k = 0; k < 5; k++) { x[k] = (double)ring[(size_t)idx[k] * HUD_W * HUD_H + i]; sum = __dadd_rn(sum, x[k]); }
+  for (int k = 0; k < 5; k++) {
+    x[k] = (k == 4 && newest >= 0) ? (double)newest : (double)ring[(size_t)idx[k] * HUD_W * HUD_H + i];
+    sum = __dadd_rn(sum, x[k]);
+  }
   const double mean = __ddiv_rn(sum, 5.0);
   double acc = 0.0;
 #pragma unroll
@@ -423,9 +617,21 @@ __device__ __forceinline__ void hm_dilate(unsigned long long* a, unsigned long l
   }
   __syncthreads();
 }
-__global__ void __launch_bounds__(256) hud_mask_kernel(const uint8_t* __restrict__ ring, HudSlots sl, double thr,
+// FUSED (frames of at least 320 x 180): the launch also IS detect_hud's thumbnail step.  Every CTA computes the new frame's
+// thumbnail values for the cells it needs straight from the RGB frame (never reading the ring slot being written), the CTA
+// whose 32 x 32 tile holds a cell's first pixel stores it into the ring, and the last CTA to finish turns the count into the
+// coverage and re-arms the two counters: one launch per frame instead of thumbnail + memset + mask + coverage.
+__device__ __forceinline__ int hud_first_px(int c, double ratio, double inv, int n) {  // smallest g with min(floor(g * inv), last) == c
+  int g = max(0, min(n - 1, (int)ceil((double)c * ratio)));
+  while (g > 0 && (int)floor(__dmul_rn((double)(g - 1), inv)) >= c) g--;
+  while (g < n - 1 && (int)floor(__dmul_rn((double)g, inv)) < c) g++;
+  return g;
+}
+template <bool FUSED>
+__global__ void __launch_bounds__(256) hud_mask_kernel(uint8_t* __restrict__ ring, HudSlots sl, double thr,
                                                        uint8_t* __restrict__ dst, int H, int W, double ify, double ifx,
-                                                       unsigned long long* __restrict__ cnt) {
+                                                       unsigned long long* __restrict__ cnt, const uint8_t* __restrict__ rgb,
+                                                       double rsy, double rsx, double* __restrict__ coverage_out) {
   __shared__ unsigned long long rows[HM_N], tmp[HM_N];
   __shared__ uint8_t flag[HM_CELLS][HM_CELLS];
   const int tx0 = blockIdx.x * HM_T, ty0 = blockIdx.y * HM_T;
@@ -437,8 +643,15 @@ __global__ void __launch_bounds__(256) hud_mask_kernel(const uint8_t* __restrict
   const bool staged = ncx <= HM_CELLS && ncy <= HM_CELLS;
   if (staged)
     for (int e = threadIdx.x; e < ncx * ncy; e += blockDim.x) {
-      const int cy = e / ncx, cx = e - cy * ncx;
-      flag[cy][cx] = hud_flag_at(ring, sl.idx, thr, (cy0 + cy) * HUD_W + cx0 + cx) ? 1 : 0;
+      const int cy = e / ncx, cx = e - cy * ncx, ax = cx0 + cx, ay = cy0 + cy;
+      int newest = -1;
+      if (FUSED) {
+        newest = resized_gray(rgb, W, lin_tap(ax, rsx, W, true), lin_tap(ay, rsy, H, false));
+        const int fx = hud_first_px(ax, rsx, ifx, W), fy = hud_first_px(ay, rsy, ify, H);
+        if (fx >= tx0 && fx < tx0 + HM_T && fy >= ty0 && fy < ty0 + HM_T)
+          ring[(size_t)sl.idx[4] * HUD_W * HUD_H + ay * HUD_W + ax] = (uint8_t)newest;
+      }
+      flag[cy][cx] = hud_flag_at(ring, sl.idx, thr, ay * HUD_W + ax, newest) ? 1 : 0;
     }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -486,7 +699,18 @@ __global__ void __launch_bounds__(256) hud_mask_kernel(const uint8_t* __restrict
   }
   __shared__ unsigned long long sh[32];
   const unsigned long long c = block_sum((unsigned long long)c4, sh);
-  if (threadIdx.x == 0 && c) atomicAdd(cnt, c);
+  if (threadIdx.x == 0) {
+    if (c) atomicAdd(cnt, c);
+    if (FUSED) {
+      __threadfence();
+      const unsigned long long ticket = atomicAdd(cnt + 1, 1ull);
+      if (ticket == (unsigned long long)gridDim.x * gridDim.y - 1) {   // last CTA: every count is in
+        __threadfence();
+        *coverage_out = (double)atomicAdd(cnt, 0ull) / ((double)H * (double)W);
+        cnt[0] = 0; cnt[1] = 0;                                          // re-armed for the next frame
+      }
+    }
+  }
 }
 __global__ void coverage_finish_kernel(const unsigned long long* cnt, double n, double* out) { *out = (double)(*cnt) / n; }
 
@@ -503,6 +727,16 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
   const long long c = *count;
   // cv2.resize(gray, (320, 180)): inv_scale = dsize / ssize, scale = 1 / inv_scale (doubles, as OpenCV computes them)
   const double rsx = 1.0 / ((double)HUD_W / (double)W), rsy = 1.0 / ((double)HUD_H / (double)H);
+  HudSlots sl;
+  for (int k = 0; k < 5; k++) sl.idx[k] = (int)(((c - 4 + k) % hist_len + hist_len) % hist_len);  // oldest -> newest of the last five
+  const double ifx = 1.0 / ((double)W / (double)HUD_W), ify = 1.0 / ((double)H / (double)HUD_H);
+  if (c + 1 >= 5 && W >= HUD_W && H >= HUD_H) {  // steady state: one launch (thumbnail + mask + coverage)
+    hud_mask_kernel<true><<<dim3(cdiv(W, HM_T), cdiv(H, HM_T)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx,
+                                                                             h->hud_cnt, rgb, rsy, rsx, coverage_out);
+    VFI_LAUNCHED(h);
+    *count = c + 1;
+    return VFI_OK;
+  }
   hud_thumb_kernel<<<cdiv(HUD_W * HUD_H, 256), 256, 0, s>>>(rgb, H, W, rsy, rsx,
                                                             hist_ring + (size_t)(c % hist_len) * HUD_W * HUD_H);
   VFI_LAUNCHED(h);
@@ -513,11 +747,9 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
     return VFI_OK;
   }
   unsigned long long* cnt = (unsigned long long*)h->red;
-  HudSlots sl;
-  for (int k = 0; k < 5; k++) sl.idx[k] = (int)((c - 4 + k) % hist_len);  // oldest -> newest of the last five
-  const double ifx = 1.0 / ((double)W / (double)HUD_W), ify = 1.0 / ((double)H / (double)HUD_H);
   VFI_CUDA(h, cudaMemsetAsync(cnt, 0, 8, s));
-  hud_mask_kernel<<<dim3(cdiv(W, HM_T), cdiv(H, HM_T)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx, cnt);
+  hud_mask_kernel<false><<<dim3(cdiv(W, HM_T), cdiv(H, HM_T)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx, cnt,
+                                                                            nullptr, 0.0, 0.0, nullptr);
   VFI_LAUNCHED(h);
   coverage_finish_kernel<<<1, 1, 0, s>>>(cnt, (double)npix, coverage_out);
   VFI_LAUNCHED(h);

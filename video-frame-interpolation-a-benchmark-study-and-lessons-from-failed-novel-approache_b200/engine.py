@@ -177,6 +177,19 @@ class Engine:
         self._check(rc, "vfi_ssim_gray_u8")
         return out
 
+    def psnr_ssim(self, a, b):
+        """PSNR (exact integer SSE) and full-resolution SSIM of n frame pairs from one pass over the frames.
+        a, b: (n,H,W,3) uint8.  Returns (sse int64, psnr float64, ssim float64), each (n,), on the device."""
+        a, b = self._u8(a), self._u8(b)
+        n, H, W, _ = a.shape
+        with torch.cuda.device(self.device):
+            sse = torch.empty(n, dtype=torch.int64, device=self.device)
+            ps = torch.empty(n, dtype=torch.float64, device=self.device)
+            ss = torch.empty(n, dtype=torch.float64, device=self.device)
+            rc = self._lib.vfi_psnr_ssim_u8(self._h, _ptr(a), _ptr(b), n, H, W, _ptr(sse), _ptr(ps), _ptr(ss), _stream())
+        self._check(rc, "vfi_psnr_ssim_u8")
+        return sse, ps, ss
+
     def flow_stats(self, flow):
         """flow: (n,H,W,2) float32 -> (n,3) float64 [mean, max, std]."""
         if isinstance(flow, np.ndarray):

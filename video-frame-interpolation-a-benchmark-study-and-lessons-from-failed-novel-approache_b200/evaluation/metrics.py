@@ -54,6 +54,15 @@ def ssim_batch(pred, gt, device=None) -> np.ndarray:
     return Engine.get(device).ssim(pred, gt, downscale=1).cpu().numpy()
 
 
+def psnr_ssim_batch(pred, gt, device=None):
+    """Both metrics of (n,H,W,3) uint8 frame pairs from one pass over the frames (vfi_psnr_ssim_u8): the values of
+    psnr_batch and ssim_batch.  Returns (psnr float64 (n,), ssim float64 (n,), sse int64 (n,)) as numpy arrays."""
+    sse, _, ss = Engine.get(device).psnr_ssim(pred, gt)
+    n = int(np.prod(pred.shape[1:]))
+    sse = sse.cpu().numpy()
+    return np.array([_psnr_from_sse(int(s), n) for s in sse.tolist()], dtype=np.float64), ss.cpu().numpy(), sse
+
+
 @dataclasses.dataclass
 class QualityResults:
     psnr: float
@@ -96,7 +105,8 @@ class QualityEvaluator:
         same = len({f.shape for f in pred_frames} | {f.shape for f in gt_frames}) == 1
         if same and pred_frames:
             p, g = np.stack(pred_frames), np.stack(gt_frames)
-            ps, ss = psnr_batch(p, g).tolist(), ssim_batch(p, g).tolist()
+            ps, ss, _ = psnr_ssim_batch(p, g)
+            ps, ss = ps.tolist(), ss.tolist()
         else:
             ps = [compute_psnr_simple(a, b) for a, b in zip(pred_frames, gt_frames)]
             ss = [compute_ssim_simple(a, b) for a, b in zip(pred_frames, gt_frames)]
