@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(SF_COLS) ssim_full_kernel(const uint8_t* __res
         __syncthreads();
         if (hrow < slot) {
           const int xl0 = hseg * 16, base = hseg * 17;
-          const int nout = min(16, min(SF_OUT - xl0, ow - (blockIdx.x * SF_OUT + xl0)));
+          const int nout = min(16, min(SF_OUT - xl0, ow - ((int)blockIdx.x * SF_OUT + xl0)));   // signed: negative = no window
           if (nout > 0) {
             const int* v0 = &vt[0][hrow][base];
             const int* v1 = &vt[1][hrow][base];

@@ -245,12 +245,14 @@ class HudState:
     def __len__(self):
         return min(int(self.count.value), self.hist_len)
 
-    def update(self, rgb):
+    def update(self, rgb, mask_out=None, cov_out=None):
+        """Push one frame.  mask_out (H,W) uint8 / cov_out (1,) float64 device tensors receive the results when given
+        (the batched clip path keeps one mask per pair of a batch)."""
         rgb = self.e._u8(rgb)
         H, W, _ = rgb.shape
         with torch.cuda.device(self.e.device):
-            mask = torch.empty((H, W), dtype=torch.uint8, device=self.e.device)
-            cov = torch.empty(1, dtype=torch.float64, device=self.e.device)
+            mask = mask_out if mask_out is not None else torch.empty((H, W), dtype=torch.uint8, device=self.e.device)
+            cov = cov_out if cov_out is not None else torch.empty(1, dtype=torch.float64, device=self.e.device)
             rc = self.e._lib.vfi_hud_update(self.e._h, _ptr(rgb), H, W, _ptr(self.ring), self.hist_len,
                                             C.byref(self.count), self.var_threshold, _ptr(mask), _ptr(cov), _stream())
         self.e._check(rc, "vfi_hud_update")

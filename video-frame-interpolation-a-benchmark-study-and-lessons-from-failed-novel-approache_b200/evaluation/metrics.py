@@ -63,6 +63,64 @@ def psnr_ssim_batch(pred, gt, device=None):
     return np.array([_psnr_from_sse(int(s), n) for s in sse.tolist()], dtype=np.float64), ss.cpu().numpy(), sse
 
 
+def evaluate_sharded(pred, gt, rank: int = 0, world: int = 1, group=None, chunk: int = 64, device=None) -> dict:
+    """Extra (not in the reference): PSNR / SSIM means of n frame pairs sharded by frame index over `world` ranks
+    (BASELINE.json config 5; the means the reference forms at evaluation/metrics.py:208-258 from its per-frame values).
+    pred, gt: (n,H,W,3) uint8 -- numpy or CUDA tensors holding the WHOLE set (each rank touches only its contiguous
+    range; evaluate_range takes producers instead when no rank can hold the whole set).  Each rank runs the fused
+    PSNR+SSIM kernel (vfi_psnr_ssim_u8) over its range `chunk` pairs at a time, and ONE all-reduce(SUM) of
+    {sum psnr over finite values, sum ssim, n, n identical (psnr = inf), sum of integer SSE} ends the job (float64
+    vector; the integer entries stay exact below 2^53).  Returns the whole-set means and sums on every rank."""
+    from .. import sharding
+    e = Engine.get(device)
+    lo, hi = sharding.shard_range(pred.shape[0], rank, world)
+    part = evaluate_range(lambda a, b: pred[a:b], lambda a, b: gt[a:b], lo, hi, chunk, e)
+    return reduce_sums(part, (lo, hi), group, e.device)
+
+
+def reduce_sums(part, rng=None, group=None, device=None) -> dict:
+    """The job's one collective: all-reduce(SUM) of a rank's evaluate_range() vector, then the means."""
+    from .. import sharding
+    vec = torch.tensor(part, dtype=torch.float64, device=device if device is not None else 'cpu')
+    return _finish_sums(sharding.reduce_counters(vec, group).tolist(), rng)
+
+
+def evaluate_range(pred_fn, gt_fn, lo: int, hi: int, chunk: int = 64, engine=None, device=None):
+    """Sums over frame pairs [lo, hi): [sum psnr (finite), sum ssim, n, n_inf, sum sse] as Python floats/ints.
+    The per-frame PSNR is formed on the host from the exact integer SSE with the reference's own float64 expression
+    (evaluation/metrics.py:311-315), so the sum is over bit-identical per-frame values."""
+    e = engine or Engine.get(device)
+    s_psnr = s_ssim = 0.0
+    n_tot = n_inf = sse_tot = 0
+    pending = []
+    for a in range(lo, hi, chunk):
+        b = min(hi, a + chunk)
+        p, g = pred_fn(a, b), gt_fn(a, b)
+        sse, _, ss = e.psnr_ssim(p, g)
+        pending.append((sse, ss, int(np.prod(p.shape[1:]))))
+    for sse, ss, elems in pending:                    # one device->host read per chunk, after everything is queued
+        sse = sse.tolist()
+        for v in sse:
+            ps = _psnr_from_sse(int(v), elems)
+            if np.isinf(ps):
+                n_inf += 1
+            else:
+                s_psnr += ps
+            sse_tot += int(v)
+        s_ssim += float(ss.sum(dtype=torch.float64))
+        n_tot += len(sse)
+    assert sse_tot < 2 ** 53
+    return [s_psnr, s_ssim, float(n_tot), float(n_inf), float(sse_tot)]
+
+
+def _finish_sums(vec, rng=None) -> dict:
+    s_psnr, s_ssim, n, n_inf, sse = vec
+    n, n_inf = int(n), int(n_inf)
+    return {'range': rng, 'n': n, 'n_identical': n_inf, 'sse_sum': int(sse), 'psnr_sum': s_psnr, 'ssim_sum': s_ssim,
+            'psnr': float('inf') if n_inf else (s_psnr / n if n else float('nan')),     # np.mean with an inf entry is inf
+            'ssim': s_ssim / n if n else float('nan')}
+
+
 @dataclasses.dataclass
 class QualityResults:
     psnr: float

@@ -96,6 +96,13 @@ class AdaptiveRouter:
             self._engine = Engine.get(self._device)      # None -> the current CUDA device
         return self._engine
 
+    def reset(self) -> None:
+        """Forget the HUD history and mask (a fresh router with the same thresholds): a new clip starts."""
+        self._hud = None
+        self._hud_mask_dev = None
+        self.hud_mask = None
+        self._last = {}
+
     def _hud_state(self) -> HudState:
         if self._hud is None:
             self._hud = HudState(self.engine, self.hud_history_frames, self.hud_variance_threshold)
@@ -335,6 +342,124 @@ class AdaptivePipeline(BaseModel):
         routes = sharding.gather_flags(torch.tensor(local, dtype=torch.int8, device=dev), n_pairs, rank, world, group)
         whole = RoutingStats(*vec)
         return {'range': (lo, hi), 'routes': routes.cpu().numpy(), 'stats': whole.to_dict()}
+
+    def process_clip_batched(self, frames, num_frames: int = 3, rank: int = 0, world: int = 1, group=None,
+                             batch: int = 8, out=None, on_batch=None, n_pairs: Optional[int] = None, base: int = 0) -> dict:
+        """Extra (not in the reference): process_clip at device speed.  Same per-pair semantics as interpolate()
+        (:369-411: cut -> copies of frame0; else RIFE with the HUD composite when coverage > 0.01; the route
+        recommendation is computed and counted either way), evaluated `batch` pairs at a time on a DEVICE-RESIDENT
+        clip: one scene-cut SSIM launch for the shard, then per batch one Farneback + flow-statistics pass, one
+        Laplacian pass, the (sequential) HUD pushes of the non-cut pairs each writing its own mask slice, ONE
+        device->host read of the 8 x {mean, max, std, laplacian, coverage} scalars for the decision tree, and one
+        IFNet call over the batch with the per-pair masks.  Sharding, HUD warm-up replay and the end-of-clip
+        all-reduce / all-gather are those of process_clip.
+        frames: (n_pairs+1, H, W, 3) uint8 CUDA tensor (a numpy / host tensor is uploaded whole).  A rank that holds only
+        its part of the clip passes frames = clip[base : ...] with `base` and the clip's `n_pairs` (it needs the frames from
+        16 pairs before its range, for the HUD warm-up replay across cuts, to one past its last pair).
+        out: optional (hi-lo, T, H, W, 3) uint8 CUDA tensor for the shard's frames; on_batch(j0, frames_dev, analyses).
+        Returns {'range', 'routes', 'cuts', 'hud_coverage' (clip order), 'stats', 'analyses' (this shard)}."""
+        from ... import sharding
+        self.ensure_loaded()
+        if self.enable_vfimamba:
+            raise RuntimeError("process_clip_batched runs the RIFE fast path only; use process_clip with VFIMamba loaded")
+        r, e = self.router, self.router.engine
+        dev = e.device
+        if not (isinstance(frames, torch.Tensor) and frames.is_cuda):
+            frames = e._u8(frames)
+        if n_pairs is None:
+            n_pairs = base + frames.shape[0] - 1
+        H, W = int(frames.shape[1]), int(frames.shape[2])
+        F = lambda a, b: frames[a - base:b - base]          # clip frames [a, b)
+        lo, hi = sharding.shard_range(n_pairs, rank, world)
+        ts = self._rife.get_default_timestamps(num_frames)
+        T = len(ts)
+        prec = _abi.PRECISION_BF16 if self._rife.precision == 'bf16' else _abi.PRECISION_FP32
+        scale = 0.5 if self._rife.uhd_mode else 1.0
+        code = {'rife': _abi.ROUTE_RIFE, 'vfimamba': _abi.ROUTE_VFIMAMBA, 'scene_change': _abi.ROUTE_SCENE_CHANGE}
+        scores = {}
+
+        def score_range(a, b):                      # scene-cut SSIM of pairs [a, b), one launch per <= 64 pairs
+            for s0 in range(a, b, 64):
+                s1 = min(b, s0 + 64)
+                sc = e.ssim(F(s0, s1), F(s0 + 1, s1 + 1), downscale=4).tolist()
+                scores.update(zip(range(s0, s1), sc))
+
+        def is_cut(j):
+            if j not in scores:
+                score_range(max(base, j - 15), j + 1)
+            return scores[j] < r.scene_change_threshold
+
+        analyses, local_routes, local_cov = [], [], []
+        if lo < hi:
+            score_range(lo, hi)
+            _, replay = sharding.warmup_start(lo, is_cut)
+            for j in replay:
+                r._detect_hud_dev(frames[j - base], None)
+            hud = r._hud_state()
+            masks = torch.zeros((batch, H, W), dtype=torch.uint8, device=dev)
+            covs = torch.zeros((batch,), dtype=torch.float64, device=dev)
+            for j0 in range(lo, hi, batch):
+                nb = min(batch, hi - j0)
+                f0, f1 = F(j0, j0 + nb), F(j0 + 1, j0 + nb + 1)
+                cut = [is_cut(j) for j in range(j0, j0 + nb)]
+                st = lv = None
+                if not all(cut):
+                    st = e.farneback(f0, f1, want_flow=False, want_stats=True, **FARNEBACK)
+                    lv = e.laplacian_var(f0)
+                ready = [False] * nb
+                for k in range(nb):
+                    if cut[k]:
+                        continue                                    # cut pairs return before detect_hud (:244-254)
+                    hud.update(f0[k], mask_out=masks[k], cov_out=covs[k:k + 1])
+                    ready[k] = len(hud) >= 5
+                if any(ready):                                      # router.hud_mask = the newest mask, as after analyze()
+                    r._hud_mask_dev, r.hud_mask = masks[max(k for k in range(nb) if ready[k])].clone(), None
+                if st is not None:
+                    host = torch.cat([st.reshape(-1), lv, covs[:nb]]).tolist()      # the batch's one device->host read
+                    st_h, lv_h, cov_h = host[:3 * nb], host[3 * nb:4 * nb], host[4 * nb:]
+                batch_an = []
+                for k in range(nb):
+                    sc = scores[j0 + k]
+                    if cut[k]:
+                        a = ContentAnalysis(0, 0, 0, False, True, 0, 'scene_change', 1.0 - sc)
+                        masks[k].zero_()
+                    else:
+                        mean, mx, sd = st_h[3 * k:3 * k + 3]
+                        cov = cov_h[k] if ready[k] else 0.0
+                        route, conf, hp, _ = _abi.route_decide(sc, mean, mx, sd, lv_h[k], r.scene_change_threshold,
+                                                               r.particle_threshold, r.motion_threshold_low,
+                                                               r.motion_threshold_high)
+                        a = ContentAnalysis(motion_mean=mean, motion_max=mx, motion_std=sd, has_particles=hp,
+                                            is_scene_change=False, hud_coverage=cov,
+                                            recommended_model=_abi.ROUTE_NAMES[route], confidence=conf)
+                        if not (ready[k] and cov > 0.01):
+                            masks[k].zero_()                        # no composite (:398)
+                    self.stats.add('scene_change' if cut[k] else 'rife')   # VFIMamba disabled: RIFE runs the non-cut pairs
+                    batch_an.append(a)
+                    local_routes.append(code[a.recommended_model])
+                    local_cov.append(a.hud_coverage)
+                dst = out[j0 - lo:j0 - lo + nb] if out is not None else None
+                if not all(cut):
+                    res = e.infer(f0, f1, ts, scale, prec, hud_mask=masks[:nb], out=dst)
+                else:
+                    res = dst if dst is not None else torch.empty((nb, T, H, W, 3), dtype=torch.uint8, device=dev)
+                for k in range(nb):
+                    if cut[k]:
+                        res[k] = f0[k]                              # n copies of frame0 (:383-385), broadcast over T
+                analyses += batch_an
+                if on_batch is not None:
+                    on_batch(j0, res, batch_an)
+        # the recommendation counters (what RoutingStats would hold with VFIMamba enabled is the route histogram)
+        vec = torch.tensor([len(local_routes)] + [sum(1 for c in local_routes if c == k) for k in
+                                                  (_abi.ROUTE_RIFE, _abi.ROUTE_VFIMAMBA, _abi.ROUTE_SCENE_CHANGE)],
+                           dtype=torch.int64, device=dev)
+        vec = sharding.reduce_counters(vec, group).tolist()
+        routes = sharding.gather_flags(torch.tensor(local_routes, dtype=torch.int8, device=dev), n_pairs, rank, world, group)
+        cov = sharding.gather_flags(torch.tensor(local_cov, dtype=torch.float64, device=dev), n_pairs, rank, world, group)
+        routes = routes.cpu().numpy()
+        return {'range': (lo, hi), 'routes': routes, 'cuts': (routes == _abi.ROUTE_SCENE_CHANGE),
+                'hud_coverage': cov.cpu().numpy(), 'analyses': analyses,
+                'stats': {'total': vec[0], 'recommended_rife': vec[1], 'recommended_vfimamba': vec[2], 'scene_change': vec[3]}}
 
     def get_stats(self) -> dict:
         return self.stats.to_dict()

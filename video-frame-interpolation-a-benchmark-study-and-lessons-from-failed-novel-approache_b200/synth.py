@@ -37,39 +37,66 @@ def _scene(rng, H, W):
     return sc
 
 
-def gen_clip(n_pairs, H=1080, W=1920, seed=0, cut_every=60, fast=(120, 150), hud=True):
-    """Return uint8 RGB frames (n_pairs + 1, H, W, 3); pair j = (frames[j], frames[j+1])."""
+def _scene_start(i, cut_every):
+    return (i // cut_every) * cut_every if cut_every else 0
+
+
+def _fast_steps(lo, hi, fast):
+    """Number of frame indices j in (lo, hi] with fast[0] < j <= fast[1]."""
+    if not fast:
+        return 0
+    return max(0, min(hi, fast[1]) - max(lo, fast[0]))
+
+
+def _render(sc, pan, fshift, x, y, hud_pat, out):
+    H, W = out.shape[:2]
+    fine = np.roll(sc["fine"], (int(pan[1]), int(pan[0])), (0, 1))
+    coarse = np.roll(sc["coarse"], (0, fshift), (0, 1))
+    for c in range(3):
+        ax = 2 * np.pi * sc["fx"][c][:, None] * (x[None, :] - pan[0])
+        ay = 2 * np.pi * sc["fy"][c][:, None] * (y[None, :] - pan[1]) + sc["ph"][c][:, None]
+        L = np.concatenate([sc["A"][c][:, None] * np.sin(ay), sc["A"][c][:, None] * np.cos(ay)], 0)
+        R = np.concatenate([np.cos(ax), np.sin(ax)], 0)
+        img = 128.0 + L.T @ R + fine
+        img = img * (1 - sc["win"]) + (128.0 + coarse) * sc["win"]
+        out[:, :, c] = np.clip(np.rint(img), 0, 255).astype(np.uint8)
+    if hud_pat is not None:
+        out[:hud_pat.shape[0], :hud_pat.shape[1]] = hud_pat
+
+
+def gen_clip(n_pairs, H=1080, W=1920, seed=0, cut_every=60, fast=(120, 150), hud=True, start=0, threads=None, out=None):
+    """Return uint8 RGB frames (n_pairs + 1, H, W, 3) = clip frames start .. start + n_pairs; pair j of the returned
+    array is clip pair start + j.  Every frame is a pure function of its clip index (scene = the last multiple of
+    `cut_every`, pan = velocity x frames since the scene began, fast-window shift = 36 px per frame inside `fast`), so a
+    rank can generate just its own shard, and frames render on `threads` host threads (default: all cores, <= 16)."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
     x = np.arange(W, dtype=np.float32)
     y = np.arange(H, dtype=np.float32)
     hud_h, hud_w = max(8, int(H * 0.08)), max(8, int(W * 0.12))
     hy, hx = np.mgrid[0:hud_h, 0:hud_w]
     hud_pat = np.stack([40 + 170 * (((hx // 6) + (hy // 6)) % 2), 200 - 120 * ((hx // 9) % 2),
-                        60 + 100 * ((hy // 5) % 2)], -1).astype(np.uint8)
-    frames = np.empty((n_pairs + 1, H, W, 3), np.uint8)
-    sc = None
-    pan = np.zeros(2, np.int64)
-    fshift = 0
-    for i in range(n_pairs + 1):
-        if sc is None or (cut_every and i % cut_every == 0 and i > 0):
-            sc = _scene(np.random.default_rng(seed * 1000003 + i + 17), H, W)
-            pan = np.zeros(2, np.int64)
-            fshift = 0
-        elif i > 0:
-            pan = pan + sc["vel"]
-            if fast and fast[0] < i <= fast[1]:
-                fshift += 36
-        fine = np.roll(sc["fine"], (int(pan[1]), int(pan[0])), (0, 1))
-        coarse = np.roll(sc["coarse"], (0, fshift), (0, 1))
-        for c in range(3):
-            ax = 2 * np.pi * sc["fx"][c][:, None] * (x[None, :] - pan[0])
-            ay = 2 * np.pi * sc["fy"][c][:, None] * (y[None, :] - pan[1]) + sc["ph"][c][:, None]
-            L = np.concatenate([sc["A"][c][:, None] * np.sin(ay), sc["A"][c][:, None] * np.cos(ay)], 0)
-            R = np.concatenate([np.cos(ax), np.sin(ax)], 0)
-            img = 128.0 + L.T @ R + fine
-            img = img * (1 - sc["win"]) + (128.0 + coarse) * sc["win"]
-            frames[i, :, :, c] = np.clip(np.rint(img), 0, 255).astype(np.uint8)
-        if hud:
-            frames[i, :hud_h, :hud_w] = hud_pat
+                        60 + 100 * ((hy // 5) % 2)], -1).astype(np.uint8) if hud else None
+    frames = out if out is not None else np.empty((n_pairs + 1, H, W, 3), np.uint8)
+    idx = list(range(start, start + n_pairs + 1))
+    scenes = {}
+    for s0 in sorted({_scene_start(i, cut_every) for i in idx}):
+        scenes[s0] = _scene(np.random.default_rng(seed * 1000003 + s0 + 17), H, W)
+
+    def one(k):
+        i = idx[k]
+        s0 = _scene_start(i, cut_every)
+        sc = scenes[s0]
+        pan = sc["vel"].astype(np.int64) * (i - s0)
+        _render(sc, pan, 36 * _fast_steps(s0, i, fast), x, y, hud_pat, frames[k])
+
+    nt = threads if threads is not None else min(16, os.cpu_count() or 1)
+    if nt > 1 and len(idx) > 1:
+        with ThreadPoolExecutor(nt) as ex:
+            list(ex.map(one, range(len(idx))))
+    else:
+        for k in range(len(idx)):
+            one(k)
     return frames
 
 
