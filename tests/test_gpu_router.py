@@ -213,3 +213,55 @@ def test_clip_streamer_equals_batch_api():
             assert np.array_equal(st.result(slot).numpy(), want[b0])
     slot, b0 = pending.pop(0)
     assert np.array_equal(st.result(slot).numpy(), want[b0])
+
+
+@pytest.mark.parametrize("rank,world,batch", [(0, 1, 8), (0, 1, 5), (1, 2, 8), (2, 3, 4)])
+def test_process_clip_batched_equals_per_pair_path(engine, clip_and_gold, rank, world, batch):
+    """The device-resident batched clip path (one statistics read and one IFNet call per batch, per-pair HUD masks) gives
+    the per-pair path's routes, HUD coverage and FRAMES (interpolate(): cut -> copies of frame0, HUD composite) bit for bit,
+    for a whole clip and for a shard that starts mid-clip and holds only its part of the frames (`base`)."""
+    from vfi_b200 import sharding
+    clip, g = clip_and_gold
+    n = len(clip) - 1
+    lo, hi = sharding.shard_range(n, rank, world)
+    base = max(0, lo - 16)
+    p = AdaptivePipeline(enable_vfimamba=False)
+    p.load()
+    dev = torch.from_numpy(clip[base:hi + 1]).cuda()
+    out = torch.empty((hi - lo, 3) + clip.shape[1:], dtype=torch.uint8, device="cuda")
+    res = p.process_clip_batched(dev, 3, rank, world, batch=batch, out=out, n_pairs=n, base=base)
+    assert res["range"] == (lo, hi)
+    assert res["routes"][:hi - lo].tolist() == g["rows"][lo:hi, 6].astype(int).tolist()
+    assert res["hud_coverage"][:hi - lo].tolist() == g["rows"][lo:hi, 5].tolist()
+    assert [a.is_scene_change for a in res["analyses"]] == g["rows"][lo:hi, 4].astype(bool).tolist()
+    assert p.get_stats()["total"] == hi - lo
+    # frames: against the per-pair path fed the same history
+    q = AdaptivePipeline(enable_vfimamba=False)
+    q.load()
+    want = {}
+    q.process_clip(clip, 3, rank=rank, world=world, on_pair=lambda j, mids, a: want.__setitem__(j, np.stack(mids)))
+    got = out.cpu().numpy()
+    for j in range(lo, hi):
+        assert np.array_equal(got[j - lo], want[j]), j
+    if world == 1:
+        assert res["stats"]["scene_change"] == int((g["rows"][:, 4] == 1).sum())
+        assert res["stats"]["recommended_vfimamba"] == int((g["rows"][:, 6] == 1).sum())
+
+
+def test_evaluate_sharded_sums(engine):
+    """Sharded PSNR/SSIM evaluator: a rank's partial sums over its range are the sums of the per-frame reference values
+    (integer SSE exactly), and the ranges of all ranks tile the set."""
+    from vfi_b200.evaluation import metrics as M
+    fr = gen_clip(10, 180, 320, seed=21, cut_every=0, fast=None)
+    pred = noisy_copy(fr, seed=5)
+    pred[3] = fr[3]                                                     # one identical pair -> psnr inf, counted apart
+    whole = M.evaluate_sharded(pred, fr, chunk=4)
+    ps = [metrics_ref.psnr_simple(pred[i], fr[i]) for i in range(11)]
+    ss = [metrics_ref.ssim_simple(pred[i], fr[i]) for i in range(11)]
+    sse = sum(int(((pred[i].astype(np.int64) - fr[i]) ** 2).sum()) for i in range(11))
+    assert whole["n"] == 11 and whole["n_identical"] == 1 and whole["sse_sum"] == sse and whole["psnr"] == float("inf")
+    assert abs(whole["psnr_sum"] - sum(p for p in ps if np.isfinite(p))) < 1e-9
+    assert abs(whole["ssim"] - np.mean(ss)) < 1e-9
+    parts = [M.evaluate_range(lambda a, b: pred[a:b], lambda a, b: fr[a:b], *M_range, 3) for M_range in ((0, 4), (4, 8), (8, 11))]
+    tot = np.sum(np.array(parts), axis=0)
+    assert tot[2] == 11 and tot[3] == 1 and int(tot[4]) == sse and abs(tot[1] - whole["ssim_sum"]) < 1e-9

@@ -220,70 +220,128 @@ __global__ void fb_matrices_kernel(const float* __restrict__ R, const float2* __
 }
 
 // ---- box blur of M + 2x2 solve (+ next UpdateMatrices) --------------------------------------------------------------
-#define BS_T 32
-__global__ void __launch_bounds__(256) fb_blur_solve_kernel(const float* __restrict__ Min, const float* __restrict__ R,
-                                                            float* __restrict__ Mout /*null on the last iteration*/,
-                                                            float2* __restrict__ flow /*null unless last iteration*/, int h, int w, int m) {
-  extern __shared__ double tile[];  // [5][BS_T + 2m][BS_T + 2m + 1]
-  __shared__ float2 fl[BS_T][BS_T + 1];
-  const int pair = blockIdx.z, x0 = blockIdx.x * BS_T, y0 = blockIdx.y * BS_T;
-  const int tw = BS_T + 2 * m, ts = tw + 1, win = 2 * m + 1;
+// A CTA owns a strip of BS_COLS output columns and a segment of rows and walks DOWN it (OpenCV's own structure,
+// FarnebackUpdateFlow_Blur: vertical running sums per column, then horizontal running sums, both in double):
+//   V phase  thread = column of the strip + its 2m halo columns (clamped = OpenCV's replicated border): the five fp64
+//            vertical window sums are kept in registers and updated per row with the entering / leaving row of M (read
+//            from global memory: the leaving row is an L1/L2 hit, it entered 2m+1 rows earlier); BS_R rows are written to
+//            a shared-memory tile per block barrier;
+//   H phase  thread = (row, run of 8 columns): horizontal sliding sums over the tile (positions skewed by one double per
+//            8 so that the 16 runs of a row hit distinct banks), the 2x2 solve, flow to shared memory;
+//   S phase  thread = column again: coalesced flow store (last iteration) or the next UpdateMatrices into Mout.
+// The row segmentation depends only on the level's height, never on the batch: a pair's flow is bit-identical alone or
+// in a batch.
+#define BS_COLS 128
+#define BS_THREADS (BS_COLS + 2 * FB_MAX_M + 2)            // 160
+#define BS_POS(x) ((x) + ((x) >> (RUN == 8 ? 3 : 2)))      // one double of skew per run
+#define BS_STRIDE (BS_THREADS + BS_THREADS / RUN)          // doubles per (row, plane)
+template <int BS_R, int RUN, bool FUSE>
+__global__ void __launch_bounds__(BS_THREADS) fb_blur_solve_kernel(const float* __restrict__ Min, const float* __restrict__ R,
+                                                                   float* __restrict__ Mout /*null on the last iteration*/,
+                                                                   float2* __restrict__ flow /*null unless last iteration*/, int h, int w, int m,
+                                                                   int rows_per_seg) {
+  extern __shared__ double tile[];  // [BS_R][5][BS_STRIDE]
+  __shared__ float2 fl[BS_R][BS_COLS];
+  const int t = threadIdx.x, pair = blockIdx.z, x0 = blockIdx.x * BS_COLS;
+  const int y0 = blockIdx.y * rows_per_seg, y1 = min(h, y0 + rows_per_seg);
+  const int win = 2 * m + 1;
   const size_t plane = (size_t)h * w;
   const float* Mi = Min + (size_t)pair * 5 * plane;
-  for (int e = threadIdx.x; e < 5 * tw * tw; e += blockDim.x) {
-    const int c = e / (tw * tw), r = e - c * tw * tw, ly = r / tw, lx = r - ly * tw;
-    const int gy = min(max(y0 + ly - m, 0), h - 1), gx = min(max(x0 + lx - m, 0), w - 1);  // clamped window (vsum init / border copy)
-    tile[(c * tw + ly) * ts + lx] = (double)Mi[c * plane + (size_t)gy * w + gx];
-  }
-  __syncthreads();
-  // vertical sliding sums, in place: after this tile[c][y][x] = sum of rows y .. y+2m of the input
-  for (int e = threadIdx.x; e < 5 * tw; e += blockDim.x) {
-    const int c = e / tw, lx = e - c * tw;
-    double* col = tile + (size_t)c * tw * ts + lx;
-    double S = 0.0;
-    for (int j = 0; j < win; j++) S += col[j * ts];
-    for (int y = 0; y < BS_T; y++) {
-      const double old = col[y * ts];
-      col[y * ts] = S;
-      if (y + 1 < BS_T) S += col[(y + win) * ts] - old;
+  const bool vcol = t < BS_COLS + 2 * m;
+  const int gx = min(max(x0 + t - m, 0), w - 1);
+  double S[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  if (vcol) {
+    for (int j = -m; j <= m; j++) {
+      const size_t o = (size_t)min(max(y0 + j, 0), h - 1) * w + gx;
+#pragma unroll
+      for (int c = 0; c < 5; c++) S[c] += (double)Mi[c * plane + o];
     }
   }
-  __syncthreads();
-  {
-    // horizontal sliding sums over 4 consecutive outputs, then the solve
-    const int ly = threadIdx.x >> 3, sx = (threadIdx.x & 7) * 4;
-    double g[5];
+  const int tp = BS_POS(t);
+  constexpr int RUNS = BS_COLS / RUN;
+  const int hr = t / RUNS, hx = (t % RUNS) * RUN;          // H-phase role (threads 0 .. BS_R * RUNS - 1)
+  const float* R0 = R + (size_t)(2 * pair) * 5 * plane;
+  const double scale = 1.0 / ((double)win * (double)win);
+  for (int yb = y0; yb < y1; yb += BS_R) {
+    const int nr = min(BS_R, y1 - yb);
+    if (vcol) {
+      float en[BS_R][5], le[BS_R][5];
 #pragma unroll
-    for (int c = 0; c < 5; c++) {
-      const double* rowp = tile + ((size_t)c * tw + ly) * ts + sx;
-      double S = 0.0;
-      for (int j = 0; j < win; j++) S += rowp[j];
-      g[c] = S;
-    }
-    const double scale = 1.0 / ((double)win * (double)win);
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      const double g11 = g[0] * scale, g12 = g[1] * scale, g22 = g[2] * scale, h1 = g[3] * scale, h2 = g[4] * scale;
-      const double idet = 1.0 / (g11 * g22 - g12 * g12 + 1e-3);
-      fl[ly][sx + i] = make_float2((float)((g11 * h2 - g12 * h1) * idet), (float)((g22 * h1 - g12 * h2) * idet));
-      if (i < 3) {
+      for (int r = 0; r < BS_R; r++) {                     // the batch's loads first: 2 x 5 x BS_R independent requests
+        const size_t oe = (size_t)min(yb + r + m + 1, h - 1) * w + gx, ol = (size_t)max(yb + r - m, 0) * w + gx;
 #pragma unroll
         for (int c = 0; c < 5; c++) {
-          const double* rowp = tile + ((size_t)c * tw + ly) * ts + sx + i;
-          g[c] += rowp[win] - rowp[0];
+          en[r][c] = r < nr ? Mi[c * plane + oe] : 0.f;
+          le[r][c] = r < nr ? Mi[c * plane + ol] : 0.f;
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < BS_R; r++) {
+#pragma unroll
+        for (int c = 0; c < 5; c++) {
+          tile[(r * 5 + c) * BS_STRIDE + tp] = S[c];
+          S[c] += (double)en[r][c] - (double)le[r][c];
         }
       }
     }
+    __syncthreads();
+    if (t < BS_R * RUNS && hr < nr) {
+      double g[5];
+      const double* base = tile + (size_t)hr * 5 * BS_STRIDE;
+#pragma unroll
+      for (int c = 0; c < 5; c++) {
+        const double* rowp = base + c * BS_STRIDE;
+        double a = 0.0;
+        for (int j = 0; j < win; j++) a += rowp[BS_POS(hx + j)];
+        g[c] = a;
+      }
+#pragma unroll
+      for (int i = 0; i < RUN; i++) {
+        const double g11 = g[0] * scale, g12 = g[1] * scale, g22 = g[2] * scale, h1 = g[3] * scale, h2 = g[4] * scale;
+        const double idet = 1.0 / (g11 * g22 - g12 * g12 + 1e-3);
+        fl[hr][hx + i] = make_float2((float)((g11 * h2 - g12 * h1) * idet), (float)((g22 * h1 - g12 * h2) * idet));
+        if (i < RUN - 1) {
+#pragma unroll
+          for (int c = 0; c < 5; c++) {
+            const double* rowp = base + c * BS_STRIDE;
+            g[c] += rowp[BS_POS(hx + i + win)] - rowp[BS_POS(hx + i)];
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (t < BS_COLS && x0 + t < w) {
+      const int x = x0 + t;
+      for (int r = 0; r < nr; r++) {
+        const int y = yb + r;
+        const float2 f = fl[r][t];
+        if (flow) flow[(size_t)pair * plane + (size_t)y * w + x] = f;
+        if (FUSE && Mout) fb_matrix_px(R0, R0 + 5 * plane, plane, w, h, x, y, f.x, f.y, Mout + (size_t)pair * 5 * plane);
+      }
+    }
   }
-  __syncthreads();
+}
+static int bs_rows_per_seg(int h) { return h >= 1024 ? 128 : h >= 512 ? 64 : 32; }   // a function of the level only
+// UpdateMatrices from a flow field of the level's own size (the unfused variant of the blur kernel's S phase)
+__global__ void fb_matrices_flow_kernel(const float* __restrict__ R, const float2* __restrict__ flow, float* __restrict__ M, int h, int w) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, pair = blockIdx.z;
+  if (x >= w) return;
+  const size_t plane = (size_t)h * w;
+  const float2 f = flow[(size_t)pair * plane + (size_t)y * w + x];
   const float* R0 = R + (size_t)(2 * pair) * 5 * plane;
-  for (int e = threadIdx.x; e < BS_T * BS_T; e += blockDim.x) {
-    const int ly = e >> 5, lx = e & 31, x = x0 + lx, y = y0 + ly;
-    if (x >= w || y >= h) continue;
-    const float2 f = fl[ly][lx];
-    if (flow) flow[(size_t)pair * plane + (size_t)y * w + x] = f;
-    if (Mout) fb_matrix_px(R0, R0 + 5 * plane, plane, w, h, x, y, f.x, f.y, Mout + (size_t)pair * 5 * plane);
-  }
+  fb_matrix_px(R0, R0 + 5 * plane, plane, w, h, x, y, f.x, f.y, M + (size_t)pair * 5 * plane);
+}
+static int fb_variant() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VFI_FB_VARIANT"); v = e ? atoi(e) : 0; }
+  return v;
+}
+template <int BS_R, int RUN, bool FUSE>
+static void bs_launch(dim3 grid, cudaStream_t s, const float* Mi, const float* R, float* Mo, float2* fl, int hh, int w, int m, int rps) {
+  const size_t smem = (size_t)BS_R * 5 * (BS_THREADS + BS_THREADS / RUN) * sizeof(double);
+  static bool set = false;
+  if (!set) { cudaFuncSetAttribute(fb_blur_solve_kernel<BS_R, RUN, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); set = true; }
+  fb_blur_solve_kernel<BS_R, RUN, FUSE><<<grid, BS_THREADS, smem, s>>>(Mi, R, Mo, fl, hh, w, m, rps);
 }
 
 int cv_round(double v) { return (int)nearbyint(v); }
@@ -374,8 +432,6 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
   prepare_poly(poly_n, poly_sigma, P);
   const int m = winsize / 2;
   const size_t px = (size_t)H * W;
-  const size_t smem = (size_t)5 * (BS_T + 2 * m) * (BS_T + 2 * m + 1) * sizeof(double);
-  VFI_CUDA(h, cudaFuncSetAttribute(fb_blur_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int chunk = std::min(n, 8);
   Carve cv{nullptr, 0};
   for (int pass = 0; pass < 2; pass++) {
@@ -389,6 +445,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
     float* M1 = cv.take<float>((size_t)chunk * 5 * px);
     float2* fA = cv.take<float2>((size_t)chunk * px);
     float2* fB = cv.take<float2>((size_t)chunk * px);
+    float2* tmpf = cv.take<float2>((size_t)chunk * px);
     if (pass == 0) { if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc; continue; }
     for (int n0 = 0; n0 < n; n0 += chunk) {
       const int nn = std::min(chunk, n - n0);
@@ -421,7 +478,22 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
         float2* cur = (k == 0 && flow_out) ? reinterpret_cast<float2*>(flow_out) + (size_t)n0 * px : (prev == fA ? fB : fA);
         for (int i = 0; i < iterations; i++) {
           const bool last = i == iterations - 1;
-          fb_blur_solve_kernel<<<dim3(cdiv(w, BS_T), cdiv(hh, BS_T), nn), 256, smem, s>>>(Mi, R, last ? nullptr : Mo, last ? cur : nullptr, hh, w, m);
+          const int rps = bs_rows_per_seg(hh);
+          const dim3 grid(cdiv(w, BS_COLS), cdiv(hh, rps), nn);
+          const int var = fb_variant();
+          if (var == 0 || var == 1) {
+            // shipped: blur + solve (flow only), then UpdateMatrices as its own full-occupancy launch -- fused behind the
+            // solve it ran at the blur kernel's low occupancy and cost more than both launches together (A/B on B200:
+            // 0.71 ms per 1080p pair fused, 0.57 unfused)
+            if (var == 0) bs_launch<4, 8, false>(grid, s, Mi, R, nullptr, last ? cur : tmpf, hh, w, m, rps);
+            else bs_launch<8, 8, false>(grid, s, Mi, R, nullptr, last ? cur : tmpf, hh, w, m, rps);
+            if (!last) {
+              VFI_LAUNCHED(h);
+              fb_matrices_flow_kernel<<<dim3(cdiv(w, 128), hh, nn), 128, 0, s>>>(R, tmpf, Mo, hh, w);
+            }
+          } else if (var == 2) bs_launch<4, 4, true>(grid, s, Mi, R, last ? nullptr : Mo, last ? cur : nullptr, hh, w, m, rps);
+          else if (var == 3) bs_launch<4, 8, true>(grid, s, Mi, R, last ? nullptr : Mo, last ? cur : nullptr, hh, w, m, rps);
+          else bs_launch<8, 8, true>(grid, s, Mi, R, last ? nullptr : Mo, last ? cur : nullptr, hh, w, m, rps);
           VFI_LAUNCHED(h);
           std::swap(Mi, Mo);
         }
