@@ -87,6 +87,18 @@ int vfi_ifnet_infer(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int
                     const float* timesteps, int T, float scale, int precision,
                     const uint8_t* hud_mask, uint8_t* out, float* out_f32, float* flow_out, void* stream);
 
+/* The same with the conventions of the reference's experiment runner, scripts/run_experiments.py:365-386
+ * (rife_interpolate; duplicated at gui/benchmark_proper.py:90-101):
+ *   VFI_FLAG_BGR              frames in and out are BGR (cv2 order); the network sees RGB (:381-382 flip, :386 flip back)
+ *   VFI_FLAG_PAD_REFLECT_EDGE the bottom/right padding is cv2.BORDER_REFLECT (border pixel repeated, :379-380) instead
+ *                             of the reflect-101 of models/base.py:203-225
+ * With scale 0.5 the padding multiple is 128, as :373-375 computes it.  flags = 0 is vfi_ifnet_infer. */
+#define VFI_FLAG_BGR 1
+#define VFI_FLAG_PAD_REFLECT_EDGE 2
+int vfi_ifnet_infer_ex(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int B, int H, int W,
+                       const float* timesteps, int T, float scale, int precision, int flags,
+                       const uint8_t* hud_mask, uint8_t* out, float* out_f32, float* flow_out, void* stream);
+
 /* The fused backward-warp + sigmoid-blend kernel on its own (IFNet.forward tail:
  * warp(img0,flow[:, :2]), warp(img1,flow[:, 2:4]), sigmoid(mask), blend -- reached through
  * rife_wrapper.py:146).  img0/img1: N x H x W x 3 uint8; flow: N x H x W x 4 float;
@@ -99,6 +111,12 @@ int vfi_warp_blend(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, cons
  * psnr_out: n x double (inf when sse == 0).  Either may be NULL.                          */
 int vfi_psnr_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t elems,
                 unsigned long long* sse_out, double* psnr_out, void* stream);
+
+/* The five integer moments behind the experiment runner's GLOBAL (single-window) metrics, scripts/run_experiments.py:292-312
+ * calc_psnr / calc_ssim (every published number of the study; duplicated at gui/benchmark_proper.py:31-44): for n pairs of
+ * `elems` uint8 values, out[5*i + 0..4] = sum a, sum b, sum a^2, sum b^2, sum a*b (int64, exact).  The float64 formulas
+ * are finished on the host with the reference's own expressions.                                                        */
+int vfi_moments_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t elems, long long* out, void* stream);
 
 /* compute_ssim_simple (evaluation/metrics.py:318-335; skimage structural_similarity on the
  * cv2 gray images, 7x7 uniform window) when downscale == 1; AdaptiveRouter.detect_scene_change's
@@ -129,6 +147,25 @@ int vfi_flow_stats(vfi_handle* h, const float* flow, int n, int H, int W, double
 int vfi_farneback(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int n, int H, int W, int channels,
                   double pyr_scale, int levels, int winsize, int iterations, int poly_n, double poly_sigma,
                   float* flow_out, double* stats_out, void* stream);
+
+/* The experiment runner's motion-threshold router, scripts/run_experiments.py:848-874 (the "adaptive" method every
+ * adaptive_* result of the study used): cv2.resize(gray, (480, 270)) of both frames -> vfi_farneback(0.5, 1, 15, 1, 5, 1.1)
+ * -> mean |flow| > motion_thresh ? RIFE : cv2.addWeighted(prev, 1-t, curr, t, 0).
+ *   vfi_resize_gray_u8 : cv2.resize(cv2.cvtColor(src, COLOR_{RGB,BGR}2GRAY), (dw, dh)), INTER_LINEAR uint8 fixed point,
+ *                        bit-exact.  src: n x H x W x channels (3: RGB, or BGR when bgr != 0; 1: already gray); dst: n x dh x dw.
+ *   vfi_add_weighted_u8: cv2.addWeighted(a, alpha, b, beta, 0) on uint8 (float multiply-add, round half to even,
+ *                        saturate); bit-exact whenever a*alpha and b*beta are exact in float (t = k/4, as the runner uses). */
+int vfi_resize_gray_u8(vfi_handle* h, const uint8_t* src, int n, int H, int W, int channels, int bgr, int dh, int dw,
+                       uint8_t* dst, void* stream);
+int vfi_add_weighted_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, size_t elems, double alpha, double beta,
+                        uint8_t* out, void* stream);
+
+/* cv2.Canny(gray, low, high) (aperture 3, L1 gradient) -- the edge-density term of the MCAR complexity score,
+ * scripts/run_experiments.py:466-468 (`np.mean(edges > 0)`).  gray: n x H x W uint8.  edges_out: nullable, n x H x W uint8
+ * (255 / 0, bit-exact with OpenCV); density_out: nullable, n x double = edge pixels / (H*W).  Synchronises `stream`
+ * (the hysteresis runs to its fixed point under host control).                                                       */
+int vfi_canny_u8(vfi_handle* h, const uint8_t* gray, int n, int H, int W, double low, double high,
+                 uint8_t* edges_out, double* density_out, void* stream);
 
 /* detect_particles' frequency term (adaptive_pipeline.py:180-183): variance of the 3x3
  * Laplacian (reflect-101) of the gray image.  rgb: n x H x W x 3; out: n x double.        */

@@ -8,6 +8,7 @@ LIB_PATH = os.path.join(_HERE, "libvfi_b200.so")
 
 OK, E_ARG, E_CUDA, E_STATE, E_NOMEM = 0, -1, -2, -3, -4
 PRECISION_FP32, PRECISION_BF16 = 0, 1
+FLAG_BGR, FLAG_PAD_REFLECT_EDGE = 1, 2
 ROUTE_RIFE, ROUTE_VFIMAMBA, ROUTE_SCENE_CHANGE = 0, 1, 2
 ROUTE_NAMES = ("rife", "vfimamba", "scene_change")
 IFNET_PARAMS = 5664776
@@ -24,6 +25,11 @@ SIGNATURES = {
     "vfi_set_option": (_i, [_vp, C.c_char_p, _i]),
     "vfi_ifnet_load_weights": (_i, [_vp, _vp, _sz, _vp]),
     "vfi_ifnet_infer": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _f, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vfi_ifnet_infer_ex": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _i, _f, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "vfi_moments_u8": (_i, [_vp, _vp, _vp, _i, _sz, _vp, _vp]),
+    "vfi_resize_gray_u8": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "vfi_add_weighted_u8": (_i, [_vp, _vp, _vp, _sz, _d, _d, _vp, _vp]),
+    "vfi_canny_u8": (_i, [_vp, _vp, _i, _i, _i, _d, _d, _vp, _vp, _vp]),
     "vfi_warp_blend": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "vfi_psnr_u8": (_i, [_vp, _vp, _vp, _i, _sz, _vp, _vp, _vp]),
     "vfi_ssim_gray_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),

@@ -240,7 +240,14 @@ static int run_conv(vfi_handle* h, const Layer& L, const void* in, const void* r
 extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int B, int H, int W,
                                const float* timesteps, int T, float scale, int precision, const uint8_t* hud_mask,
                                uint8_t* out, float* out_f32, float* flow_out, void* stream) {
+  return vfi_ifnet_infer_ex(h, img0, img1, B, H, W, timesteps, T, scale, precision, 0, hud_mask, out, out_f32, flow_out, stream);
+}
+extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer_ex(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int B, int H, int W,
+                                  const float* timesteps, int T, float scale, int precision, int flags, const uint8_t* hud_mask,
+                                  uint8_t* out, float* out_f32, float* flow_out, void* stream) {
   if (!h) return VFI_E_ARG;
+  if (flags & ~(VFI_FLAG_BGR | VFI_FLAG_PAD_REFLECT_EDGE)) VFI_FAIL(h, VFI_E_ARG, "unknown flags 0x%x", flags);
+  const int bgr = (flags & VFI_FLAG_BGR) ? 1 : 0, edge = (flags & VFI_FLAG_PAD_REFLECT_EDGE) ? 1 : 0;
   if (!h->weights_loaded) VFI_FAIL(h, VFI_E_STATE, "IFNet weights not loaded");
   if (!img0 || !img1 || !out || !timesteps || B < 1 || T < 1 || T > 64 || H < 2 || W < 2)
     VFI_FAIL(h, VFI_E_ARG, "bad argument");
@@ -254,7 +261,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
   const size_t esz = bf ? 2 : 4;
   const int mult = 64 * inv > 32 ? 64 * inv : 32;
   const int Hp = (H + mult - 1) / mult * mult, Wp = (W + mult - 1) / mult * mult;
-  if (Hp - H >= H || Wp - W >= W) VFI_FAIL(h, VFI_E_ARG, "frame too small for reflect padding to %d", mult);
+  if (Hp - H >= H + edge || Wp - W >= W + edge) VFI_FAIL(h, VFI_E_ARG, "frame too small for reflect padding to %d", mult);
   // consecutive pairs of one clip (img1 is img0 shifted by one frame): frame b+1 is both pair b's second and pair
   // b+1's first frame -- pad it and run the Head on it once
   const bool clipmode = B > 1 && img1 == img0 + (size_t)H * W * 3;
@@ -324,9 +331,9 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
     }
     if ((rc = k_build_taps(h, taps, sl, 5, Hp, Wp, s))) return rc;
     // to_tensor + reflect pad, both frames of every pair
-    if ((rc = k_pad_rgbx(h, img0, imgs, B, H, W, Hp, Wp, s))) return rc;
-    if (clipmode) rc = k_pad_rgbx(h, img1 + (size_t)(B - 1) * H * W * 3, imgs + (size_t)B * px * 4, 1, H, W, Hp, Wp, s);
-    else rc = k_pad_rgbx(h, img1, imgs + (size_t)B * px * 4, B, H, W, Hp, Wp, s);
+    if ((rc = k_pad_rgbx(h, img0, imgs, B, H, W, Hp, Wp, s, edge, bgr))) return rc;
+    if (clipmode) rc = k_pad_rgbx(h, img1 + (size_t)(B - 1) * H * W * 3, imgs + (size_t)B * px * 4, 1, H, W, Hp, Wp, s, edge, bgr);
+    else rc = k_pad_rgbx(h, img1, imgs + (size_t)B * px * 4, B, H, W, Hp, Wp, s, edge, bgr);
     if (rc) return rc;
     // Head (encode) once per image, shared by all T timesteps
     if ((rc = k_head_cnn0(h, h->layers[0], imgs, ht0, NI, Hp, Wp, bf, s))) return rc;
@@ -375,7 +382,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer(vfi_handle
       if (bf && i < 4) lows.push_planes(lowp[i], sc, Hp, Wp, taps + (size_t)i * (Hp + Wp));
       else lows.push(low[i], sc, lc, Hp, Wp, taps + (size_t)i * (Hp + Wp));
     }
-    if ((rc = k_final_blend(h, imgs, lows, flow_pre, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s))) return rc;
+    if ((rc = k_final_blend(h, imgs, lows, flow_pre, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s, bgr))) return rc;
   }
   return VFI_OK;
 }

@@ -175,7 +175,7 @@ int vfi_ws_reserve(vfi_handle* h, size_t bytes);
 int vfi_red_reserve(vfi_handle* h, size_t bytes);
 
 // ---- elementwise.cu -----------------------------------------------------------------------
-int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s);
+int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s, int edge = 0, int bgr = 0);
 int k_head_cnn0(vfi_handle* h, const Layer& L, const uint8_t* imgs, void* out, int NI, int Hp, int Wp, bool bf, cudaStream_t s);
 // The lastconv outputs of the blocks run so far.  low[k] = [N, Hp/s[k], Wp/s[k], 4*c4[k]] fp32 (flow 4, mask 1,
 // feat 8).  The reference's full-resolution flow / mask / feat tensors (IFBlock.forward's F.interpolate(scale) and
@@ -226,7 +226,7 @@ int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet
 // flow_pre (nullable): [N,Hp,Wp,4] fp32 flow already summed over every level of `lows` but the last (full-resolution) one
 int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const float* flow_pre, const uint8_t* hud,
                   const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp, int Wp,
-                  cudaStream_t s);
+                  cudaStream_t s, int bgr = 0);
 // finest block at scale 1.0: gather fused with conv0[0] (tcgen05), bf16 only
 int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
                     const float* tsteps_dev, bf16* out, float* flow_sum, int B, int I1, int T, int Hp, int Wp,

@@ -139,28 +139,31 @@ __device__ __forceinline__ void sample_feat_px(const T* __restrict__ feats, cons
 
 // ------------------------------------------------------------------------------------------
 // to_tensor + pad_to_multiple(reflect) (models/base.py:175-186, :203-225) kept in uint8: RGB -> RGBX
+// edge: 0 = torch 'reflect' / cv2 BORDER_REFLECT_101 (models/base.py:203-225), 1 = cv2.BORDER_REFLECT, the border pixel
+// repeated (scripts/run_experiments.py:377-380); bgr: the caller's frames are BGR (run_experiments.py:381-382 flips them
+// for the network): the padded copy is RGB either way
 __global__ void pad_rgbx_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int B, int H, int W,
-                                int Hp, int Wp) {
+                                int Hp, int Wp, int edge, int bgr) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   size_t total = (size_t)B * Hp * Wp;
   if (i >= total) return;
   int x = (int)(i % Wp);
   int y = (int)((i / Wp) % Hp);
   int b = (int)(i / ((size_t)Wp * Hp));
-  int sx = x < W ? x : 2 * (W - 1) - x;
-  int sy = y < H ? y : 2 * (H - 1) - y;
+  int sx = x < W ? x : 2 * (W - 1) + edge - x;
+  int sy = y < H ? y : 2 * (H - 1) + edge - y;
   const uint8_t* p = src + (((size_t)b * H + sy) * W + sx) * 3;
-  reinterpret_cast<uchar4*>(dst)[i] = make_uchar4(p[0], p[1], p[2], 0);
+  reinterpret_cast<uchar4*>(dst)[i] = bgr ? make_uchar4(p[2], p[1], p[0], 0) : make_uchar4(p[0], p[1], p[2], 0);
 }
 // the same for W % 4 == 0 and a 4-byte aligned source: a thread turns 12 source bytes (three aligned words) into four
 // RGBX pixels (one 16-byte store); only the reflected border falls back to byte loads
 __global__ void pad_rgbx4_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int B, int H, int W, int Hp,
-                                 int Wp) {
+                                 int Wp, int edge, int bgr) {
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const int Wq = Wp >> 2;
   if (i >= (size_t)B * Hp * Wq) return;
   const int x = (int)(i % Wq) * 4, y = (int)((i / Wq) % Hp), b = (int)(i / ((size_t)Wq * Hp));
-  const int sy = y < H ? y : 2 * (H - 1) - y;
+  const int sy = y < H ? y : 2 * (H - 1) + edge - y;
   const uint8_t* row = src + ((size_t)b * H + sy) * W * 3;
   uint4 o;
   if (x + 3 < W) {
@@ -174,21 +177,22 @@ __global__ void pad_rgbx4_kernel(const uint8_t* __restrict__ src, uint8_t* __res
     uint32_t v[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-      const int xx = x + k, sx = xx < W ? xx : 2 * (W - 1) - xx;
+      const int xx = x + k, sx = xx < W ? xx : 2 * (W - 1) + edge - xx;
       const uint8_t* p = row + (size_t)sx * 3;
       v[k] = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
     }
     o = make_uint4(v[0], v[1], v[2], v[3]);
   }
+  if (bgr) { o.x = __byte_perm(o.x, 0, 0x4012); o.y = __byte_perm(o.y, 0, 0x4012); o.z = __byte_perm(o.z, 0, 0x4012); o.w = __byte_perm(o.w, 0, 0x4012); }
   reinterpret_cast<uint4*>(dst)[i] = o;
 }
-int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s) {
+int k_pad_rgbx(vfi_handle* h, const uint8_t* src, uint8_t* dst, int B, int H, int W, int Hp, int Wp, cudaStream_t s, int edge, int bgr) {
   ProfScope _ps(h, PC_PAD, s);
   size_t total = (size_t)B * Hp * Wp;
   if ((W & 3) == 0 && (Wp & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0)
-    pad_rgbx4_kernel<<<cdiv(total / 4, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp);
+    pad_rgbx4_kernel<<<cdiv(total / 4, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp, edge, bgr);
   else
-    pad_rgbx_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp);
+    pad_rgbx_kernel<<<cdiv(total, 256), 256, 0, s>>>(src, dst, B, H, W, Hp, Wp, edge, bgr);
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -760,7 +764,7 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
                                                                  uint8_t* __restrict__ out,
                                                                  float* __restrict__ out_f32,
                                                                  float* __restrict__ flow_out, int B, int I1, int Tn, int H,
-                                                                 int W, int Hp, int Wp) {
+                                                                 int W, int Hp, int Wp, int bgr) {
   extern __shared__ float4 tl_sm[];
   __shared__ __align__(16) uint8_t s_rgb[TL_H][TL_W * 3];  // the tile's u8 result, stored row-wise as 32-bit words
   const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
@@ -810,6 +814,7 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
       uchar4 sp = __ldg(reinterpret_cast<const uchar4*>(hsrc) + (size_t)y * Wp + x);
       r = sp.x; g = sp.y; bl = sp.z;
     }
+    if (bgr) { const uint8_t sw = r; r = bl; bl = sw; }           // the caller's frames are BGR: uint8 result in its order
     s_rgb[yl][3 * xl] = r; s_rgb[yl][3 * xl + 1] = g; s_rgb[yl][3 * xl + 2] = bl;
   }
   __syncthreads();
@@ -832,7 +837,7 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
 }
 int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const float* flow_pre, const uint8_t* hud,
                   const float* tsteps_dev, uint8_t* out, float* out_f32, float* flow_out, int B, int I1, int T, int H, int W, int Hp,
-                  int Wp, cudaStream_t s) {
+                  int Wp, cudaStream_t s, int bgr) {
   ProfScope _ps(h, PC_BLEND, s);
   const size_t smem = tl_smem_bytes(lows, 2);
   const dim3 grid((W + TL_W - 1) / TL_W, (H + TL_H - 1) / TL_H, B * T);
@@ -843,14 +848,14 @@ int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const 
     last.push(lows.p[lows.n - 1], 1, lows.c4[lows.n - 1] * 4, Hp, Wp);
     if (lows.c4[lows.n - 1] == 1)  // fp16 texels
       final_blend_kernel<2><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
-                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp);
+                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, bgr);
     else if (lows.c4[lows.n - 1] == 2)
       final_blend_kernel<1><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
-                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp);
+                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, bgr);
     else VFI_FAIL(h, VFI_E_ARG, "final blend: pre-summed flow needs the compact last level");
   } else {
     final_blend_kernel<0><<<grid, TL_THREADS, smem, s>>>(imgs, lows, nullptr, hud, tsteps_dev, out, out_f32, flow_out, B,
-                                                             I1, T, H, W, Hp, Wp);
+                                                             I1, T, H, W, Hp, Wp, bgr);
   }
   VFI_LAUNCHED(h);
   return 0;

@@ -127,6 +127,58 @@ extern "C" __attribute__((visibility("default"))) int vfi_psnr_u8(vfi_handle* h,
 }
 
 // ---------------------------------------------------------------------------------------------
+// Global (single-window) moments of a uint8 pair: sum a, sum b, sum a^2, sum b^2, sum ab -- the integers behind
+// scripts/run_experiments.py:292-312 calc_psnr / calc_ssim.  16-byte loads, five dp4a per 4 bytes, u64 lane
+// accumulators, shuffle + smem block reduction, one integer atomic per block and moment.
+__global__ void moments_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, size_t elems,
+                               unsigned long long* __restrict__ acc5) {
+  __shared__ unsigned long long sh[32];
+  const int f = blockIdx.y;
+  const uint8_t* pa = a + (size_t)f * elems;
+  const uint8_t* pb = b + (size_t)f * elems;
+  unsigned long long m[5] = {0, 0, 0, 0, 0};
+  const bool aligned = ((((uintptr_t)pa) | ((uintptr_t)pb)) & 15) == 0;
+  const size_t nvec = aligned ? elems / 16 : 0;
+  const uint4* va = reinterpret_cast<const uint4*>(pa);
+  const uint4* vb = reinterpret_cast<const uint4*>(pb);
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+    const uint4 x = __ldg(va + i), y = __ldg(vb + i);
+    const uint32_t xs[4] = {x.x, x.y, x.z, x.w}, ys[4] = {y.x, y.y, y.z, y.w};
+    uint32_t s0 = 0, s1 = 0, s2 = 0, s3 = 0, s4 = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      s0 = __dp4a(xs[k], 0x01010101u, s0); s1 = __dp4a(ys[k], 0x01010101u, s1);
+      s2 = __dp4a(xs[k], xs[k], s2); s3 = __dp4a(ys[k], ys[k], s3); s4 = __dp4a(xs[k], ys[k], s4);
+    }
+    m[0] += s0; m[1] += s1; m[2] += s2; m[3] += s3; m[4] += s4;
+  }
+  for (size_t i = nvec * 16 + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < elems; i += (size_t)gridDim.x * blockDim.x) {
+    const unsigned long long x = pa[i], y = pb[i];
+    m[0] += x; m[1] += y; m[2] += x * x; m[3] += y * y; m[4] += x * y;
+  }
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    const unsigned long long v = block_sum(m[k], sh);
+    if (threadIdx.x == 0 && v) atomicAdd(acc5 + 5 * f + k, v);
+  }
+}
+extern "C" __attribute__((visibility("default"))) int vfi_moments_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t elems,
+                                                                       long long* out, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!a || !b || !out || n < 1 || elems < 1 || n > 65535) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  if (elems > ((size_t)1 << 46)) VFI_FAIL(h, VFI_E_ARG, "too many elements for exact int64 moments");
+  VFI_ENTER(h, stream);
+  cudaStream_t s = (cudaStream_t)stream;
+  VFI_CUDA(h, cudaMemsetAsync(out, 0, (size_t)n * 5 * 8, s));
+  int bx = (int)std::min<size_t>(PSNR_BLOCKS_PER_FRAME, (elems / 16 + 255) / 256 + 1);
+  if (n >= 64) bx = std::min(bx, 32);
+  ProfScope ps(h, PC_REDUCE, s);
+  moments_kernel<<<dim3(bx, n), 256, 0, s>>>(a, b, elems, reinterpret_cast<unsigned long long*>(out));
+  VFI_LAUNCHED(h);
+  return VFI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // SSIM (skimage structural_similarity, 2-D uint8, win 7 uniform, sample covariance, data_range 255;
 // SURVEY App. B.2) on the cv2 gray image (DS = 1: evaluation/metrics.py:318-335) or on its x0.25
 // INTER_LINEAR thumbnail (DS = 4: adaptive_pipeline.py:149-158, = 2x2 centre average, App. B.1).
@@ -753,5 +805,237 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
   VFI_LAUNCHED(h);
   coverage_finish_kernel<<<1, 1, 0, s>>>(cnt, (double)npix, coverage_out);
   VFI_LAUNCHED(h);
+  return VFI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The experiment runner's motion-threshold router (scripts/run_experiments.py:848-874): gray thumbnails and the linear
+// blend it falls back to.
+//   resize_gray : cv2.resize(cv2.cvtColor(frame, *2GRAY), (dw, dh)) -- INTER_LINEAR, uint8 fixed point (lin_tap above)
+//   add_weighted: cv2.addWeighted(a, alpha, b, beta, 0) for uint8: saturate_cast<uchar>(cvRound(a*alpha + b*beta)) in float
+template <int CH, bool BGR>
+__device__ __forceinline__ int gray_src(const uint8_t* __restrict__ img, int W, int y, int x) {
+  if (CH == 1) return img[(size_t)y * W + x];
+  const uint8_t* q = img + ((size_t)y * W + x) * 3;
+  return BGR ? gray_u8(q[2], q[1], q[0]) : gray_u8(q[0], q[1], q[2]);
+}
+template <int CH, bool BGR>
+__global__ void resize_gray_kernel(const uint8_t* __restrict__ src, int H, int W, int dh, int dw, double sy, double sx,
+                                   uint8_t* __restrict__ dst) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= dw) return;
+  const uint8_t* img = src + (size_t)blockIdx.z * H * W * CH;
+  int v;
+  if (dh == H && dw == W) v = gray_src<CH, BGR>(img, W, y, x);
+  else {
+    const LinTap tx = lin_tap(x, sx, W, true), ty = lin_tap(y, sy, H, false);
+    const int h0 = gray_src<CH, BGR>(img, W, ty.s0, tx.s0) * tx.a0 + gray_src<CH, BGR>(img, W, ty.s0, tx.s1) * tx.a1;
+    const int h1 = gray_src<CH, BGR>(img, W, ty.s1, tx.s0) * tx.a0 + gray_src<CH, BGR>(img, W, ty.s1, tx.s1) * tx.a1;
+    v = (((ty.a0 * (h0 >> 4)) >> 16) + ((ty.a1 * (h1 >> 4)) >> 16) + 2) >> 2;
+  }
+  dst[((size_t)blockIdx.z * dh + y) * dw + x] = (uint8_t)v;
+}
+extern "C" __attribute__((visibility("default"))) int vfi_resize_gray_u8(vfi_handle* h, const uint8_t* src, int n, int H, int W, int channels,
+                                                                           int bgr, int dh, int dw, uint8_t* dst, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!src || !dst || n < 1 || n > 65535 || H < 1 || W < 1 || dh < 1 || dw < 1 || dh > 65535 || (channels != 1 && channels != 3))
+    VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  VFI_ENTER(h, stream);
+  cudaStream_t s = (cudaStream_t)stream;
+  const double sx = 1.0 / ((double)dw / (double)W), sy = 1.0 / ((double)dh / (double)H);   // as cv::resize computes them
+  const dim3 grid(cdiv(dw, 128), dh, n);
+  ProfScope ps(h, PC_REDUCE, s);
+  if (channels == 1) resize_gray_kernel<1, false><<<grid, 128, 0, s>>>(src, H, W, dh, dw, sy, sx, dst);
+  else if (bgr) resize_gray_kernel<3, true><<<grid, 128, 0, s>>>(src, H, W, dh, dw, sy, sx, dst);
+  else resize_gray_kernel<3, false><<<grid, 128, 0, s>>>(src, H, W, dh, dw, sy, sx, dst);
+  VFI_LAUNCHED(h);
+  return VFI_OK;
+}
+__global__ void add_weighted_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, size_t elems, float alpha, float beta,
+                                    uint8_t* __restrict__ out) {
+  const bool aligned = ((((uintptr_t)a) | ((uintptr_t)b) | ((uintptr_t)out)) & 15) == 0;
+  const size_t nvec = aligned ? elems / 16 : 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x) {
+    const uint4 x = __ldg(reinterpret_cast<const uint4*>(a) + i), y = __ldg(reinterpret_cast<const uint4*>(b) + i);
+    const uint32_t xs[4] = {x.x, x.y, x.z, x.w}, ys[4] = {y.x, y.y, y.z, y.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      uint32_t w = 0;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const float v = fmaf((float)((xs[k] >> (8 * j)) & 0xff), alpha, __fmul_rn((float)((ys[k] >> (8 * j)) & 0xff), beta));
+        w |= (uint32_t)min(max(__float2int_rn(v), 0), 255) << (8 * j);
+      }
+      o[k] = w;
+    }
+    reinterpret_cast<uint4*>(out)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+  for (size_t i = nvec * 16 + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < elems; i += (size_t)gridDim.x * blockDim.x) {
+    const float v = fmaf((float)a[i], alpha, __fmul_rn((float)b[i], beta));
+    out[i] = (uint8_t)min(max(__float2int_rn(v), 0), 255);
+  }
+}
+extern "C" __attribute__((visibility("default"))) int vfi_add_weighted_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, size_t elems,
+                                                                            double alpha, double beta, uint8_t* out, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!a || !b || !out || elems < 1) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  VFI_ENTER(h, stream);
+  cudaStream_t s = (cudaStream_t)stream;
+  ProfScope ps(h, PC_BLEND, s);
+  const int blocks = (int)std::min<size_t>((size_t)h->sm_count * 16, (elems / 16 + 255) / 256 + 1);
+  add_weighted_kernel<<<blocks, 256, 0, s>>>(a, b, elems, (float)alpha, (float)beta, out);
+  VFI_LAUNCHED(h);
+  return VFI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// cv2.Canny(gray, low, high) (aperture 3, L1 gradient) -- the edge-density term of the MCAR complexity score,
+// scripts/run_experiments.py:466-468.  OpenCV's algorithm (imgproc/canny.cpp), all integer, so the edge map is bit-exact:
+//   Sobel 3x3 dx, dy (BORDER_REPLICATE), mag = |dx| + |dy| (0 outside the image);
+//   non-maximum suppression along the gradient direction quantised with tan(22.5 deg) in 15-bit fixed point;
+//   label 2 (strong: local maximum, mag > high), 0 (weak: local maximum, low < mag <= high), 1 (no edge);
+//   hysteresis: weak pixels 8-connected to a strong one become strong -- tile-local fixed point in shared memory,
+//   relaunched until no tile changes (the result does not depend on the order).
+#define CN_T 32
+__global__ void __launch_bounds__(256) canny_nms_kernel(const uint8_t* __restrict__ gray, int H, int W, int low, int high,
+                                                        uint8_t* __restrict__ label) {
+  __shared__ uint8_t g[CN_T + 4][CN_T + 4];
+  __shared__ short sdx[CN_T + 2][CN_T + 2], sdy[CN_T + 2][CN_T + 2];
+  __shared__ int mg[CN_T + 2][CN_T + 2];
+  const uint8_t* img = gray + (size_t)blockIdx.z * H * W;
+  const int x0 = blockIdx.x * CN_T, y0 = blockIdx.y * CN_T;
+  for (int e = threadIdx.x; e < (CN_T + 4) * (CN_T + 4); e += blockDim.x) {
+    const int ly = e / (CN_T + 4), lx = e - ly * (CN_T + 4);
+    const int gy = min(max(y0 + ly - 2, 0), H - 1), gx = min(max(x0 + lx - 2, 0), W - 1);   // BORDER_REPLICATE
+    g[ly][lx] = img[(size_t)gy * W + gx];
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < (CN_T + 2) * (CN_T + 2); e += blockDim.x) {
+    const int ly = e / (CN_T + 2), lx = e - ly * (CN_T + 2);
+    const int gy = y0 + ly - 1, gx = x0 + lx - 1;
+    int dx = 0, dy = 0, m = 0;
+    if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+      const int a = g[ly][lx], b = g[ly][lx + 1], c = g[ly][lx + 2];
+      const int d = g[ly + 1][lx], f = g[ly + 1][lx + 2];
+      const int p = g[ly + 2][lx], q = g[ly + 2][lx + 1], r = g[ly + 2][lx + 2];
+      dx = (c - a) + 2 * (f - d) + (r - p);
+      dy = (p - a) + 2 * (q - b) + (r - c);
+      m = abs(dx) + abs(dy);
+    }
+    sdx[ly][lx] = (short)dx; sdy[ly][lx] = (short)dy; mg[ly][lx] = m;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < CN_T * CN_T; e += blockDim.x) {
+    const int ly = (e >> 5) + 1, lx = (e & 31) + 1;
+    const int gy = y0 + ly - 1, gx = x0 + lx - 1;
+    if (gy >= H || gx >= W) continue;
+    const int m = mg[ly][lx];
+    uint8_t lab = 1;
+    if (m > low) {
+      const int xs = sdx[ly][lx], ys = sdy[ly][lx];
+      const int ax = abs(xs), ay = abs(ys) << 15;
+      const int tg22x = ax * 13573;
+      bool ismax;
+      if (ay < tg22x) ismax = m > mg[ly][lx - 1] && m >= mg[ly][lx + 1];
+      else {
+        const int tg67x = tg22x + (ax << 16);
+        if (ay > tg67x) ismax = m > mg[ly - 1][lx] && m >= mg[ly + 1][lx];
+        else {
+          const int sg = (xs ^ ys) < 0 ? -1 : 1;
+          ismax = m > mg[ly - 1][lx - sg] && m > mg[ly + 1][lx + sg];
+        }
+      }
+      if (ismax) lab = m > high ? 2 : 0;
+    }
+    label[((size_t)blockIdx.z * H + gy) * W + gx] = lab;
+  }
+}
+__global__ void __launch_bounds__(256) canny_hyst_kernel(uint8_t* __restrict__ label, int H, int W, int* __restrict__ changed) {
+  __shared__ uint8_t t[CN_T + 2][CN_T + 2];
+  __shared__ int again, any;
+  uint8_t* lab = label + (size_t)blockIdx.z * H * W;
+  const int x0 = blockIdx.x * CN_T, y0 = blockIdx.y * CN_T;
+  for (int e = threadIdx.x; e < (CN_T + 2) * (CN_T + 2); e += blockDim.x) {
+    const int ly = e / (CN_T + 2), lx = e - ly * (CN_T + 2);
+    const int gy = y0 + ly - 1, gx = x0 + lx - 1;
+    t[ly][lx] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? lab[(size_t)gy * W + gx] : 1;
+  }
+  if (threadIdx.x == 0) any = 0;
+  __syncthreads();
+  for (;;) {
+    if (threadIdx.x == 0) again = 0;
+    __syncthreads();
+    for (int e = threadIdx.x; e < CN_T * CN_T; e += blockDim.x) {
+      const int ly = (e >> 5) + 1, lx = (e & 31) + 1;
+      if (t[ly][lx] == 0) {
+        const bool s = t[ly - 1][lx - 1] == 2 || t[ly - 1][lx] == 2 || t[ly - 1][lx + 1] == 2 || t[ly][lx - 1] == 2 ||
+                       t[ly][lx + 1] == 2 || t[ly + 1][lx - 1] == 2 || t[ly + 1][lx] == 2 || t[ly + 1][lx + 1] == 2;
+        if (s) { t[ly][lx] = 2; again = 1; }       // monotone 0 -> 2: racing readers only see it earlier or later
+      }
+    }
+    __syncthreads();
+    if (!again) break;
+    if (threadIdx.x == 0) any = 1;
+    __syncthreads();
+  }
+  if (any) {
+    for (int e = threadIdx.x; e < CN_T * CN_T; e += blockDim.x) {
+      const int ly = (e >> 5) + 1, lx = (e & 31) + 1;
+      const int gy = y0 + ly - 1, gx = x0 + lx - 1;
+      if (gy < H && gx < W && t[ly][lx] == 2) lab[(size_t)gy * W + gx] = 2;
+    }
+    if (threadIdx.x == 0) *changed = 1;
+  }
+}
+__global__ void canny_finish_kernel(const uint8_t* __restrict__ label, size_t px, uint8_t* __restrict__ edges, unsigned long long* __restrict__ cnt) {
+  __shared__ unsigned long long sh[32];
+  const int f = blockIdx.y;
+  unsigned long long c = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < px; i += (size_t)gridDim.x * blockDim.x) {
+    const bool e = label[(size_t)f * px + i] == 2;
+    if (edges) edges[(size_t)f * px + i] = e ? 255 : 0;
+    c += e;
+  }
+  c = block_sum(c, sh);
+  if (threadIdx.x == 0 && c) atomicAdd(cnt + f, c);
+}
+__global__ void canny_density_kernel(const unsigned long long* cnt, int n, double px, double* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (double)cnt[i] / px;
+}
+extern "C" __attribute__((visibility("default"))) int vfi_canny_u8(vfi_handle* h, const uint8_t* gray, int n, int H, int W, double low, double high,
+                                                                     uint8_t* edges_out, double* density_out, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!gray || (!edges_out && !density_out) || n < 1 || n > 4096 || H < 1 || W < 1) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  VFI_ENTER(h, stream);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (low > high) std::swap(low, high);
+  const int ilow = (int)floor(low), ihigh = (int)floor(high);
+  const size_t px = (size_t)H * W;
+  if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * px + (size_t)n * 8 + 256))) return rc;
+  uint8_t* label = (uint8_t*)h->red;
+  unsigned long long* cnt = (unsigned long long*)(label + (((size_t)n * px + 63) & ~(size_t)63));
+  int* changed = (int*)(cnt + n);
+  const dim3 grid(cdiv(W, CN_T), cdiv(H, CN_T), n);
+  ProfScope ps(h, PC_REDUCE, s);
+  canny_nms_kernel<<<grid, 256, 0, s>>>(gray, H, W, ilow, ihigh, label);
+  VFI_LAUNCHED(h);
+  for (int it = 0; it < 4096; it++) {          // each pass moves the frontier at least one tile; stops at the fixed point
+    VFI_CUDA(h, cudaMemsetAsync(changed, 0, sizeof(int), s));
+    canny_hyst_kernel<<<grid, 256, 0, s>>>(label, H, W, changed);
+    VFI_LAUNCHED(h);
+    int host = 0;
+    VFI_CUDA(h, cudaMemcpyAsync(&host, changed, sizeof(int), cudaMemcpyDeviceToHost, s));
+    VFI_CUDA(h, cudaStreamSynchronize(s));
+    if (!host) break;
+  }
+  VFI_CUDA(h, cudaMemsetAsync(cnt, 0, (size_t)n * 8, s));
+  canny_finish_kernel<<<dim3(std::min<size_t>(296, cdiv(px, 1024)), n), 256, 0, s>>>(label, px, edges_out, cnt);
+  VFI_LAUNCHED(h);
+  if (density_out) {
+    canny_density_kernel<<<cdiv(n, 128), 128, 0, s>>>(cnt, n, (double)px, density_out);
+    VFI_LAUNCHED(h);
+  }
   return VFI_OK;
 }

@@ -104,9 +104,10 @@ class Engine:
         self.weights_loaded = True
 
     def infer(self, img0, img1, timesteps, scale=1.0, precision=_abi.PRECISION_BF16, hud_mask=None,
-              want_float=False, want_flow=False, out=None):
+              want_float=False, want_flow=False, out=None, flags=0):
         """img0/img1: (B,H,W,3) or (H,W,3) uint8 (numpy or torch).  Returns uint8 (B,T,H,W,3) on the GPU
-        (plus float frames / final flow when asked)."""
+        (plus float frames / final flow when asked).  flags: _abi.FLAG_BGR | _abi.FLAG_PAD_REFLECT_EDGE (the
+        conventions of scripts/run_experiments.py:365-386)."""
         img0, img1 = self._u8(img0), self._u8(img1)
         if img0.dim() == 3:
             img0, img1 = img0[None], img1[None]
@@ -119,10 +120,10 @@ class Engine:
             of = torch.empty((B, T, H, W, 3), dtype=torch.float32, device=self.device) if want_float else None
             fl = torch.empty((B, T, H, W, 4), dtype=torch.float32, device=self.device) if want_flow else None
             hm = self._u8(hud_mask) if hud_mask is not None else None
-            rc = self._lib.vfi_ifnet_infer(self._h, _ptr(img0), _ptr(img1), B, H, W, C.cast(ts, C.c_void_p), T,
-                                           float(scale), int(precision), _ptr(hm), _ptr(out), _ptr(of), _ptr(fl),
-                                           _stream())
-        self._check(rc, "vfi_ifnet_infer")
+            rc = self._lib.vfi_ifnet_infer_ex(self._h, _ptr(img0), _ptr(img1), B, H, W, C.cast(ts, C.c_void_p), T,
+                                              float(scale), int(precision), int(flags), _ptr(hm), _ptr(out), _ptr(of),
+                                              _ptr(fl), _stream())
+        self._check(rc, "vfi_ifnet_infer_ex")
         res = (out,)
         if want_float:
             res += (of,)
@@ -167,6 +168,16 @@ class Engine:
             rc = self._lib.vfi_psnr_u8(self._h, _ptr(a), _ptr(b), n, elems, _ptr(sse), _ptr(ps), _stream())
         self._check(rc, "vfi_psnr_u8")
         return sse, ps
+
+    def moments(self, a, b):
+        """Exact global moments per pair: (n,5) int64 = sum a, sum b, sum a^2, sum b^2, sum ab over every byte."""
+        a, b = self._u8(a), self._u8(b)
+        n = a.shape[0]
+        with torch.cuda.device(self.device):
+            out = torch.empty((n, 5), dtype=torch.int64, device=self.device)
+            rc = self._lib.vfi_moments_u8(self._h, _ptr(a), _ptr(b), n, a[0].numel(), _ptr(out), _stream())
+        self._check(rc, "vfi_moments_u8")
+        return out
 
     def ssim(self, a, b, downscale=1):
         a, b = self._u8(a), self._u8(b)
@@ -219,6 +230,42 @@ class Engine:
         if want_flow and want_stats:
             return flow, st
         return flow if want_flow else st
+
+    def resize_gray(self, img, dsize, bgr=False):
+        """cv2.resize(cv2.cvtColor(img, *2GRAY), dsize) on the device.  img: (n,H,W,3) or (n,H,W) uint8; dsize = (dw, dh)."""
+        img = self._u8(img)
+        ch = 3 if img.dim() == 4 else 1
+        n, H, W = img.shape[:3]
+        dw, dh = int(dsize[0]), int(dsize[1])
+        with torch.cuda.device(self.device):
+            out = torch.empty((n, dh, dw), dtype=torch.uint8, device=self.device)
+            rc = self._lib.vfi_resize_gray_u8(self._h, _ptr(img), n, H, W, ch, 1 if bgr else 0, dh, dw, _ptr(out), _stream())
+        self._check(rc, "vfi_resize_gray_u8")
+        return out
+
+    def add_weighted(self, a, alpha, b, beta, out=None):
+        """cv2.addWeighted(a, alpha, b, beta, 0) for uint8 arrays of one shape, on the device."""
+        a, b = self._u8(a), self._u8(b)
+        with torch.cuda.device(self.device):
+            if out is None:
+                out = torch.empty_like(a)
+            rc = self._lib.vfi_add_weighted_u8(self._h, _ptr(a), _ptr(b), a.numel(), float(alpha), float(beta), _ptr(out), _stream())
+        self._check(rc, "vfi_add_weighted_u8")
+        return out
+
+    def canny(self, gray, low=100, high=200, want_edges=True):
+        """cv2.Canny(gray, low, high) on the device.  gray: (n,H,W) uint8 -> (edges (n,H,W) uint8 | None, density (n,) f64)."""
+        gray = self._u8(gray)
+        n, H, W = gray.shape
+        with torch.cuda.device(self.device):
+            edges = torch.empty((n, H, W), dtype=torch.uint8, device=self.device) if want_edges else None
+            dens = torch.empty(n, dtype=torch.float64, device=self.device)
+            rc = self._lib.vfi_canny_u8(self._h, _ptr(gray), n, H, W, float(low), float(high), _ptr(edges), _ptr(dens), _stream())
+        self._check(rc, "vfi_canny_u8")
+        return edges, dens
+
+    def canny_density(self, gray, low=100, high=200):
+        return self.canny(gray, low, high, want_edges=False)[1]
 
     def laplacian_var(self, rgb):
         rgb = self._u8(rgb)
