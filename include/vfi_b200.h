@@ -91,8 +91,9 @@ int vfi_ifnet_infer(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int
  * (rife_interpolate; duplicated at gui/benchmark_proper.py:90-101):
  *   VFI_FLAG_BGR              frames in and out are BGR (cv2 order); the network sees RGB (:381-382 flip, :386 flip back)
  *   VFI_FLAG_PAD_REFLECT_EDGE the bottom/right padding is cv2.BORDER_REFLECT (border pixel repeated, :379-380) instead
- *                             of the reflect-101 of models/base.py:203-225
- * With scale 0.5 the padding multiple is 128, as :373-375 computes it.  flags = 0 is vfi_ifnet_infer. */
+ *                             of the reflect-101 of models/base.py:203-225, and the
+ *                             padding multiple is 128 at every scale, as :373-375 computes it
+ * flags = 0 is vfi_ifnet_infer. */
 #define VFI_FLAG_BGR 1
 #define VFI_FLAG_PAD_REFLECT_EDGE 2
 int vfi_ifnet_infer_ex(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int B, int H, int W,

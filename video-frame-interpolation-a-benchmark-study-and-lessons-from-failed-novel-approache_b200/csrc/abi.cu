@@ -259,7 +259,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer_ex(vfi_han
   cudaStream_t s = (cudaStream_t)stream;
   const bool bf = precision == VFI_PRECISION_BF16;
   const size_t esz = bf ? 2 : 4;
-  const int mult = 64 * inv > 32 ? 64 * inv : 32;
+  // run_experiments.py:373-375 pads to multiples of 128 at every scale; the wrapper (base.py:203-225) to max(32, 64/scale)
+  const int mult = edge ? std::max(128, 64 * inv) : (64 * inv > 32 ? 64 * inv : 32);
   const int Hp = (H + mult - 1) / mult * mult, Wp = (W + mult - 1) / mult * mult;
   if (Hp - H >= H + edge || Wp - W >= W + edge) VFI_FAIL(h, VFI_E_ARG, "frame too small for reflect padding to %d", mult);
   // consecutive pairs of one clip (img1 is img0 shifted by one frame): frame b+1 is both pair b's second and pair
