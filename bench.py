@@ -156,13 +156,23 @@ def measure_aux(eng, clip_dev, H, W, hbm):
             fn()
         torch.cuda.synchronize()
         reps = 10
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(reps):
-            fn()
-        e1.record()
-        torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / (reps * per_call)
+        if per_call == 1 and name.startswith("hud"):
+            # one small launch per call: back-to-back calls from Python are host-bound (~25 us of interpreter + allocator per
+            # call), so the kernel itself is timed with the library's own events around its launch
+            eng.profile_read()
+            eng.profile(True)
+            for _ in range(reps):
+                fn()
+            ms = eng.profile_read()["reduce"][0] / (reps * per_call)
+            eng.profile(False)
+        else:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / (reps * per_call)
         gbps = bytes_per_frame / (ms / 1000.0) / 1e9
         out[name] = {"ms_per_frame": ms, "bound": "hbm", "achieved": gbps, "peak": hbm, "unit": "GB/s", "frac": gbps / hbm,
                      "algorithmic_bytes_per_frame": bytes_per_frame, "what": what}

@@ -114,6 +114,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_psnr_u8(vfi_handle* h,
   if (!a || !b || n < 1 || elems < 1 || n > 65535) VFI_FAIL(h, VFI_E_ARG, "bad argument");
   VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
+  ProfScope ps(h, PC_REDUCE, s);
   if (int rc = vfi_red_reserve(h, (size_t)65536 * 8)) return rc;
   unsigned long long* acc = (unsigned long long*)h->red;
   VFI_CUDA(h, cudaMemsetAsync(acc, 0, (size_t)n * 8, s));
@@ -370,6 +371,136 @@ __global__ void __launch_bounds__(SF_COLS) ssim_full_kernel(const uint8_t* __res
     if (t == 0) part_sse[pi] = s;
   }
 }
+// Fast path (W % 4 == 0, 4-byte aligned frames): NO shared memory and NO block barrier.  A warp owns a strip of 128 input
+// columns (120 output windows; lane = 4 adjacent columns, read as three aligned 32-bit words per image and row) and a
+// segment of rows and walks down it.  Per row and lane: cv2 gray of the 4 + 4 pixels (two dp4a each: the 14-bit
+// coefficients split into 7-bit halves), the SSE of the 12 byte pairs (vabsdiffu4 + dp4a), the vertical 7-row running sums of
+// (a | b << 16), a^2 + b^2, ab per column -- the leaving row comes from a 7-deep ring of packed grays held in REGISTERS
+// (the row loop is unrolled by 7, so the ring index is static) -- then the horizontal 7-column sums from the lane's own
+// four columns and six more fetched from lanes +1 / +2 by shuffle, and the SSIM rational of four windows in fp64
+// (the integer -> double conversions ride on the fp64 adder through the 2^52 magic constant).
+#define SW_OUT 120
+__device__ __forceinline__ int gray_dp4a(unsigned px) {   // px = r | g << 8 | b << 16 (byte 3 ignored)
+  return (int)(((__dp4a(px, 0x001D964Cu, 0u) << 7) + __dp4a(px, 0x00172346u, 16384u)) >> 15);
+}
+__device__ __forceinline__ double ssim_window_fast(int pk, int q, int ab) {
+  const int A = pk & 0xffff, B = (unsigned)pk >> 16;
+  const int AB = A * B, t3 = A * A + B * B;
+  const double c1 = 6.5025 * 2401.0, c2 = 58.5225 * 2352.0;
+  const double two52 = 4503599627370496.0, two31 = 2147483648.0;
+  // as_double(0x43300000 : u) = 2^52 + u exactly, so (that - 2^52) is the exact conversion on the fp64 adder (the I2F
+  // unit is 4x slower); the constants are added afterwards: folding them into the 2^52 constant would round them to 0.5
+  const double n1 = (__hiloint2double(0x43300000, 2 * AB) - two52) + c1;
+  const double n2 = (__hiloint2double(0x43300000, (2 * (49 * ab - AB)) ^ 0x80000000) - (two52 + two31)) + c2;
+  const double d1 = (__hiloint2double(0x43300000, t3) - two52) + c1;
+  const double d2 = (__hiloint2double(0x43300000, 49 * q - t3) - two52) + c2;
+  // 1 / den: MUFU.RCP64H seed (~20 bits) + two Newton steps (relative error ~1e-16); den >= C1 * C2 * n^3 (n - 1) > 0
+  const double den = d1 * d2;
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(den));
+  r = fma(r, fma(-den, r, 1.0), r);
+  r = fma(r, fma(-den, r, 1.0), r);
+  return (n1 * n2) * r;
+}
+template <bool SSE>
+__global__ void __launch_bounds__(128, 6) ssim_warp_kernel(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int H, int W,
+                                                        int rows_per_seg, int strips, double* __restrict__ part_ssim,
+                                                        unsigned long long* __restrict__ part_sse) {
+  const int lane = threadIdx.x & 31, sx = blockIdx.x * 4 + (threadIdx.x >> 5), f = blockIdx.z;
+  if (sx >= strips) return;
+  const int x = sx * SW_OUT + lane * 4;
+  const bool xin = x < W;
+  const int oh = H - 6;
+  const int y0 = blockIdx.y * rows_per_seg, y1 = min(oh, y0 + rows_per_seg);
+  const bool last_seg = y1 == oh;
+  const int yend = y1 + 6;                                  // input rows y0 .. yend-1
+  const int wpr = (W * 3) >> 2;                             // 32-bit words per image row
+  const uint32_t* pa = reinterpret_cast<const uint32_t*>(a + ((size_t)f * H * W + x) * 3);
+  const uint32_t* pb = reinterpret_cast<const uint32_t*>(b + ((size_t)f * H * W + x) * 3);
+  const bool own = xin && (lane < SW_OUT / 4 || sx == strips - 1);
+  bool valid[4];
+#pragma unroll
+  for (int c = 0; c < 4; c++) valid[c] = lane < SW_OUT / 4 && x + c + 6 < W;
+  int pk[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0}, ab[4] = {0, 0, 0, 0};
+  uint32_t ring_a[7] = {0, 0, 0, 0, 0, 0, 0}, ring_b[7] = {0, 0, 0, 0, 0, 0, 0};
+  double acc = 0.0;
+  unsigned long long sse = 0;
+  uint32_t na[3], nb[3];                                    // the NEXT row's words: loads run one row ahead
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    na[k] = xin ? __ldg(pa + (size_t)y0 * wpr + k) : 0u;
+    nb[k] = xin ? __ldg(pb + (size_t)y0 * wpr + k) : 0u;
+  }
+  for (int r0 = y0; r0 < yend; r0 += 7) {
+#pragma unroll
+    for (int j = 0; j < 7; j++) {
+      const int r = r0 + j;
+      if (r >= yend) break;                                 // warp-uniform
+      uint32_t wa[1][3], wb[1][3];
+      constexpr int J = 0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) { wa[0][k] = na[k]; wb[0][k] = nb[k]; }
+      {
+        const bool ld = xin && r + 1 < yend;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          na[k] = ld ? __ldg(pa + (size_t)(r + 1) * wpr + k) : 0u;
+          nb[k] = ld ? __ldg(pb + (size_t)(r + 1) * wpr + k) : 0u;
+        }
+      }
+      if (SSE && own && (r < y0 + rows_per_seg || last_seg)) {
+        uint32_t e = 0;
+#pragma unroll
+        for (int k = 0; k < 3; k++) { const uint32_t d = __vabsdiffu4(wa[J][k], wb[J][k]); e = __dp4a(d, d, e); }
+        sse += e;
+      }
+      const uint32_t pxa[4] = {wa[J][0], __byte_perm(wa[J][0], wa[J][1], 0x0543), __byte_perm(wa[J][1], wa[J][2], 0x0432), wa[J][2] >> 8};
+      const uint32_t pxb[4] = {wb[J][0], __byte_perm(wb[J][0], wb[J][1], 0x0543), __byte_perm(wb[J][1], wb[J][2], 0x0432), wb[J][2] >> 8};
+      const uint32_t oa4 = ring_a[j], ob4 = ring_b[j];
+      uint32_t na4 = 0, nb4 = 0;
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        const int ga = gray_dp4a(pxa[c]), gb = gray_dp4a(pxb[c]);
+        const int oa = (oa4 >> (8 * c)) & 0xff, ob = (ob4 >> (8 * c)) & 0xff;
+        pk[c] += (ga | (gb << 16)) - (oa | (ob << 16));
+        q[c] += ga * ga + gb * gb - oa * oa - ob * ob;
+        ab[c] += ga * gb - oa * ob;
+        na4 |= (uint32_t)ga << (8 * c); nb4 |= (uint32_t)gb << (8 * c);
+      }
+      ring_a[j] = na4; ring_b[j] = nb4;
+      if (r - y0 >= 6) {                                    // 7-row window complete: output row r - 6
+        int e0[10], e1[10], e2[10];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+          e0[c] = pk[c]; e1[c] = q[c]; e2[c] = ab[c];
+          e0[4 + c] = __shfl_down_sync(0xffffffffu, pk[c], 1); e1[4 + c] = __shfl_down_sync(0xffffffffu, q[c], 1);
+          e2[4 + c] = __shfl_down_sync(0xffffffffu, ab[c], 1);
+        }
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+          e0[8 + c] = __shfl_down_sync(0xffffffffu, pk[c], 2); e1[8 + c] = __shfl_down_sync(0xffffffffu, q[c], 2);
+          e2[8 + c] = __shfl_down_sync(0xffffffffu, ab[c], 2);
+        }
+        int hp = 0, hq = 0, hab = 0;
+#pragma unroll
+        for (int i = 0; i < 7; i++) { hp += e0[i]; hq += e1[i]; hab += e2[i]; }
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+          const double sw = ssim_window_fast(hp, hq, hab);
+          acc += valid[c] ? sw : 0.0;                         // select, not a branch (a garbage window may give NaN: dropped)
+          if (c < 3) { hp += e0[c + 7] - e0[c]; hq += e1[c + 7] - e1[c]; hab += e2[c + 7] - e2[c]; }
+        }
+      }
+    }
+  }
+  acc = warp_sum(acc);
+  const size_t pi = ((size_t)f * gridDim.y + blockIdx.y) * strips + sx;
+  if (lane == 0) part_ssim[pi] = acc;
+  if (SSE) {
+    sse = warp_sum(sse);
+    if (lane == 0) part_sse[pi] = sse;
+  }
+}
 __global__ void ssim_full_finish_kernel(const double* __restrict__ part_ssim, const unsigned long long* __restrict__ part_sse, int per,
                                         double denom, size_t elems, double* __restrict__ ssim_out,
                                         unsigned long long* __restrict__ sse_out, double* __restrict__ psnr_out) {
@@ -393,6 +524,26 @@ __global__ void ssim_full_finish_kernel(const double* __restrict__ part_ssim, co
 static int ssim_full_launch(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, int H, int W, bool want_sse,
                             double* ssim_out, unsigned long long* sse_out, double* psnr_out, cudaStream_t s) {
   const int oh = H - 6, ow = W - 6;
+  ProfScope ps(h, PC_REDUCE, s);
+  if ((W & 3) == 0 && ((((uintptr_t)a) | ((uintptr_t)b)) & 3) == 0) {
+    // warp-walking kernel: aim at ~40 warps per SM; at least 48 output rows per segment so the 6-row halo stays cheap
+    const int strips = cdiv(ow, SW_OUT);
+    int segs = std::max(1, std::min(cdiv(oh, 48), cdiv(40 * h->sm_count, strips * n)));
+    const int rps = cdiv(oh, segs);
+    segs = cdiv(oh, rps);
+    const int per = strips * segs;
+    if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * per * 16 + 64))) return rc;
+    double* part = (double*)h->red;
+    unsigned long long* parte = (unsigned long long*)(part + (size_t)n * per);
+    const dim3 grid(cdiv(strips, 4), segs, n);
+    if (want_sse) ssim_warp_kernel<true><<<grid, 128, 0, s>>>(a, b, H, W, rps, strips, part, parte);
+    else ssim_warp_kernel<false><<<grid, 128, 0, s>>>(a, b, H, W, rps, strips, part, nullptr);
+    VFI_LAUNCHED(h);
+    ssim_full_finish_kernel<<<n, 256, 0, s>>>(part, want_sse ? parte : nullptr, per, (double)oh * (double)ow, (size_t)H * W * 3, ssim_out,
+                                              sse_out, psnr_out);
+    VFI_LAUNCHED(h);
+    return VFI_OK;
+  }
   const int strips = cdiv(ow, SF_OUT);
   // enough CTAs for ~6 per SM when the batch is small; at least 32 output rows per CTA so the 6-row halo stays cheap
   int segs = std::max(1, std::min(cdiv(oh, 32), cdiv(6 * h->sm_count, strips * n)));
@@ -431,6 +582,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_ssim_gray_u8(vfi_handl
   VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   if (downscale == 1) return ssim_full_launch(h, a, b, n, H, W, false, out, nullptr, nullptr, s);
+  ProfScope ps(h, PC_REDUCE, s);
   dim3 grid(cdiv(ww - 6, SS_T), cdiv(hh - 6, SS_T), n);
   const int per = grid.x * grid.y;
   if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * per * 8))) return rc;
@@ -453,7 +605,24 @@ __global__ void flow_stats_kernel(const float* __restrict__ flow, size_t npix, d
   const float2* p = reinterpret_cast<const float2*>(flow) + (size_t)f * npix;
   double s = 0.0, s2 = 0.0;
   float mx = 0.f;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < npix; i += (size_t)gridDim.x * blockDim.x) {
+  // two pixels per 16-byte load, four loads in flight per thread; the per-pixel arithmetic is numpy's (float32 magnitude)
+  const size_t n4 = ((npix & 1) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) ? npix / 2 : 0;
+  const float4* p4 = reinterpret_cast<const float4*>(p);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < n4; i0 += 4 * stride) {
+    float4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = i0 + k * stride < n4 ? __ldg(p4 + i0 + k * stride) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const float m0 = sqrtf(__fadd_rn(__fmul_rn(v[k].x, v[k].x), __fmul_rn(v[k].y, v[k].y)));
+      const float m1 = sqrtf(__fadd_rn(__fmul_rn(v[k].z, v[k].z), __fmul_rn(v[k].w, v[k].w)));
+      s += (double)m0 + (double)m1;
+      s2 += (double)m0 * (double)m0 + (double)m1 * (double)m1;
+      mx = fmaxf(mx, fmaxf(m0, m1));
+    }
+  }
+  for (size_t i = 2 * n4 + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < npix; i += stride) {
     float2 v = __ldg(p + i);
     float m = sqrtf(__fadd_rn(__fmul_rn(v.x, v.x), __fmul_rn(v.y, v.y)));
     s += (double)m;
@@ -563,6 +732,65 @@ __global__ void __launch_bounds__(LP_WARPS * 32) laplacian_kernel(const uint8_t*
     o[0] = bs; o[1] = bs2;
   }
 }
+// Fast path (W % 4 == 0, 4-byte aligned frames): a lane owns 4 adjacent columns read as three aligned 32-bit words per row
+// (gray by dp4a, as in ssim_warp_kernel); lanes 1..30 of a warp own 120 columns, lanes 0 and 31 carry the neighbouring
+// strips' edge columns.  The previous / current / next gray rows live in registers as packed bytes; a row costs three loads,
+// four grays and two shuffles per lane.  Reflect-101 needs no extra loads: column -1 is column 1 (the lane's own second
+// gray), column W is column W - 2 (its own third), rows -1 / H are rows 1 / H - 2.
+#define LW_OUT 120
+__device__ __forceinline__ uint32_t lw_gray_row(const uint32_t* __restrict__ p, size_t wpr, int H, int y, bool xin) {
+  if (!xin) return 0u;
+  y = y < 0 ? -y : (y >= H ? 2 * (H - 1) - y : y);
+  y = max(0, min(y, H - 1));
+  const uint32_t* q = p + (size_t)y * wpr;
+  const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2);
+  return (uint32_t)gray_dp4a(w0) | ((uint32_t)gray_dp4a(__byte_perm(w0, w1, 0x0543)) << 8) |
+         ((uint32_t)gray_dp4a(__byte_perm(w1, w2, 0x0432)) << 16) | ((uint32_t)gray_dp4a(w2 >> 8) << 24);
+}
+__global__ void __launch_bounds__(128) laplacian_warp_kernel(const uint8_t* __restrict__ rgb, int H, int W, int rows_per_seg, int strips,
+                                                             long long* __restrict__ partial) {
+  const int lane = threadIdx.x & 31, sx = blockIdx.x * 4 + (threadIdx.x >> 5), f = blockIdx.z;
+  if (sx >= strips) return;
+  const int x = sx * LW_OUT + (lane - 1) * 4;               // lane 0: the four columns left of the strip
+  const bool xin = x >= 0 && x < W;
+  const bool owns = xin && lane >= 1 && lane <= LW_OUT / 4;
+  const bool first_col = x == 0, last_col = x + 4 == W;
+  const size_t wpr = (size_t)(W * 3) >> 2;
+  const uint32_t* p = reinterpret_cast<const uint32_t*>(rgb + ((size_t)f * H * W + (xin ? x : 0)) * 3);
+  const int y0 = blockIdx.y * rows_per_seg, y1 = min(H, y0 + rows_per_seg);
+  int s = 0;
+  unsigned long long s2 = 0;
+  uint32_t gp = lw_gray_row(p, wpr, H, y0 - 1, xin), gc = lw_gray_row(p, wpr, H, y0, xin);
+  for (int y = y0; y < y1; y += 4) {
+    uint32_t gn[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) gn[j] = lw_gray_row(p, wpr, H, y + 1 + j, xin && y + j < y1);
+    uint32_t e2 = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      if (y + j >= y1) break;
+      int l = (int)(__shfl_up_sync(0xffffffffu, gc, 1) >> 24), r = (int)(__shfl_down_sync(0xffffffffu, gc, 1) & 0xff);
+      if (first_col) l = (gc >> 8) & 0xff;                  // column -1 = column 1
+      if (last_col) r = (gc >> 16) & 0xff;                  // column W = column W - 2
+      if (owns) {
+        const int c0 = gc & 0xff, c1 = (gc >> 8) & 0xff, c2 = (gc >> 16) & 0xff, c3 = gc >> 24;
+        const int v0 = (int)(gp & 0xff) + (int)(gn[j] & 0xff) + l + c1 - 4 * c0;
+        const int v1 = (int)((gp >> 8) & 0xff) + (int)((gn[j] >> 8) & 0xff) + c0 + c2 - 4 * c1;
+        const int v2 = (int)((gp >> 16) & 0xff) + (int)((gn[j] >> 16) & 0xff) + c1 + c3 - 4 * c2;
+        const int v3 = (int)(gp >> 24) + (int)(gn[j] >> 24) + c2 + r - 4 * c3;
+        s += v0 + v1 + v2 + v3;
+        e2 += (uint32_t)(v0 * v0 + v1 * v1 + v2 * v2 + v3 * v3);   // |v| <= 1020: four rows of four stay below 2^32
+      }
+      gp = gc; gc = gn[j];
+    }
+    s2 += e2;
+  }
+  const long long ws = warp_sum((long long)s), ws2 = warp_sum((long long)s2);
+  if (lane == 0) {
+    long long* o = partial + 2 * (((size_t)f * gridDim.y + blockIdx.y) * strips + sx);
+    o[0] = ws; o[1] = ws2;
+  }
+}
 __global__ void laplacian_finish_kernel(const long long* __restrict__ partial, int per, double npix, double* __restrict__ out) {
   __shared__ long long shl[32];
   const int f = blockIdx.x;
@@ -580,14 +808,18 @@ extern "C" __attribute__((visibility("default"))) int vfi_laplacian_var(vfi_hand
   if (!rgb || !out || n < 1 || n > 4096 || H < 2 || W < 2) VFI_FAIL(h, VFI_E_ARG, "bad argument");
   VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
-  const int strips = cdiv(W, LP_WARPS * LP_COLS);
-  int segs = std::max(cdiv(H, LP_MAX_ROWS), std::min(cdiv(H, 16), cdiv(8 * h->sm_count, strips * n)));
+  ProfScope ps(h, PC_REDUCE, s);
+  const bool fast = (W & 3) == 0 && W >= 8 && (((uintptr_t)rgb) & 3) == 0;
+  const int strips = fast ? cdiv(W, LW_OUT) : cdiv(W, LP_WARPS * LP_COLS);
+  // per-lane 32-bit row sums: at most 2^20 rows per segment would overflow nothing, but keep segments short enough to fill the GPU
+  int segs = std::max(cdiv(H, LP_MAX_ROWS), std::min(cdiv(H, 16), cdiv((fast ? 32 : 8) * h->sm_count, strips * n)));
   const int rps = cdiv(H, segs);
   segs = cdiv(H, rps);
   const int per = strips * segs;
   if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, (size_t)n * per * 16))) return rc;
   long long* partial = (long long*)h->red;
-  laplacian_kernel<<<dim3(strips, segs, n), LP_WARPS * 32, 0, s>>>(rgb, H, W, rps, partial);
+  if (fast) laplacian_warp_kernel<<<dim3(cdiv(strips, 4), segs, n), 128, 0, s>>>(rgb, H, W, rps, strips, partial);
+  else laplacian_kernel<<<dim3(strips, segs, n), LP_WARPS * 32, 0, s>>>(rgb, H, W, rps, partial);
   VFI_LAUNCHED(h);
   laplacian_finish_kernel<<<n, 256, 0, s>>>(partial, per, (double)H * W, out);
   VFI_LAUNCHED(h);
@@ -628,21 +860,32 @@ __global__ void hud_var_kernel(const uint8_t* __restrict__ ring, HudSlots sl, do
 // the 48 x 48 region around it (the three morphology steps reach 2 + 4 + 2 pixels) as 48 row bit-words: a horizontal
 // step is shifts and ORs of one word, a vertical step ORs neighbouring rows, erosion is dilation of the complement, and
 // "out-of-image samples are ignored" is a mask on each step's input.
-#define HM_T 32
+#define HM_TW 32     // tile width: the 48-pixel region (tile + 2 x 8 halo) is one 64-bit word per row
+#define HM_TH 128    // tile height: tall tiles amortise the per-CTA cell / flag set-up (4x fewer CTAs than 32 x 32)
 #define HM_R 8
-#define HM_N (HM_T + 2 * HM_R)
-#define HM_CELLS 50  // small-mask cells a 48-pixel span can touch when the frame is at least 320 x 180 (ratio >= 1);
-                     // smaller frames (nearest UPsampling of the thumbnail grid) take the unstaged path
+#define HM_NX (HM_TW + 2 * HM_R)   // 48 region columns (bits)
+#define HM_NY (HM_TH + 2 * HM_R)   // 144 region rows (one thread each in the morphology steps)
+#define HM_CX 50     // small-mask cells a 48-pixel span can touch when the frame is at least 320 x 180 (ratio >= 1);
+#define HM_CY 146    // ... and a 144-pixel span; smaller frames (nearest UPsampling of the thumbnail grid) take the unstaged path
 // np.var(last five thumbnails) < thr with numpy's operation order; `newest` >= 0 replaces the ring read of the fifth
 // (newest) thumbnail: the fused kernel computes that value itself while another CTA may still be writing it to the ring
 __device__ __forceinline__ bool hud_flag_at(const uint8_t* __restrict__ ring, const int* idx, double thr, int i, int newest = -1) {
+  int xi[5];
+  int S = 0, Q = 0;
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    xi[k] = (k == 4 && newest >= 0) ? newest : (int)ring[(size_t)idx[k] * HUD_W * HUD_H + i];
+    S += xi[k]; Q += xi[k] * xi[k];
+  }
+  // 25 * var = 5 * sum(x^2) - (sum x)^2 exactly; numpy's float64 result is within a few ulp of the true variance, so the
+  // comparison can only differ from the exact one when the true variance sits (almost) on the threshold: decide those
+  // rare cases with numpy's own operation order, everything else with two integer multiplies
+  const double v25 = (double)(5 * Q - S * S), t25 = 25.0 * thr;
+  if (fabs(v25 - t25) > 1e-6 * (t25 > 1.0 ? t25 : 1.0)) return v25 < t25;
   double x[5];
   double sum = 0.0;
 #pragma unroll
-  for (int k = 0; k < 5; k++) {
-    x[k] = (k == 4 && newest >= 0) ? (double)newest : (double)ring[(size_t)idx[k] * HUD_W * HUD_H + i];
-    sum = __dadd_rn(sum, x[k]);
-  }
+  for (int k = 0; k < 5; k++) { x[k] = (double)xi[k]; sum = __dadd_rn(sum, x[k]); }
   const double mean = __ddiv_rn(sum, 5.0);
   double acc = 0.0;
 #pragma unroll
@@ -652,7 +895,7 @@ __device__ __forceinline__ bool hud_flag_at(const uint8_t* __restrict__ ring, co
 __device__ __forceinline__ void hm_dilate(unsigned long long* a, unsigned long long* tmp, const bool rowin, unsigned long long inx,
                                           int r, bool complement) {
   const int t = threadIdx.x;
-  if (t < HM_N) {
+  if (t < HM_NY) {
     unsigned long long w = a[t];
     if (complement) w = ~w;
     w = rowin ? (w & inx) : 0ull;
@@ -661,64 +904,70 @@ __device__ __forceinline__ void hm_dilate(unsigned long long* a, unsigned long l
     tmp[t] = hz;
   }
   __syncthreads();
-  if (t < HM_N) {
+  if (t < HM_NY) {
     unsigned long long v = 0ull;
     for (int k = -r; k <= r; k++)
-      if (t + k >= 0 && t + k < HM_N) v |= tmp[t + k];
+      if (t + k >= 0 && t + k < HM_NY) v |= tmp[t + k];
     a[t] = complement ? ~v : v;
   }
   __syncthreads();
 }
 // FUSED (frames of at least 320 x 180): the launch also IS detect_hud's thumbnail step.  Every CTA computes the new frame's
 // thumbnail values for the cells it needs straight from the RGB frame (never reading the ring slot being written), the CTA
-// whose 32 x 32 tile holds a cell's first pixel stores it into the ring, and the last CTA to finish turns the count into the
+// whose tile holds a cell's first pixel stores it into the ring, and the last CTA to finish turns the count into the
 // coverage and re-arms the two counters: one launch per frame instead of thumbnail + memset + mask + coverage.
-__device__ __forceinline__ int hud_first_px(int c, double ratio, double inv, int n) {  // smallest g with min(floor(g * inv), last) == c
-  int g = max(0, min(n - 1, (int)ceil((double)c * ratio)));
-  while (g > 0 && (int)floor(__dmul_rn((double)(g - 1), inv)) >= c) g--;
-  while (g < n - 1 && (int)floor(__dmul_rn((double)g, inv)) < c) g++;
-  return g;
-}
+// the pixel whose tile's CTA stores cell c of the new thumbnail: every CTA evaluates the same formula, the pixel lies in
+// cell c - 1 or c, and a tile's 8-pixel halo always reaches the next cell's first pixel, so exactly one CTA that staged
+// cell c owns it
+__device__ __forceinline__ int hud_owner_px(int c, double ratio, int n) { return max(0, min(n - 1, (int)floor(__dmul_rn((double)c, ratio)))); }
 template <bool FUSED>
 __global__ void __launch_bounds__(256) hud_mask_kernel(uint8_t* __restrict__ ring, HudSlots sl, double thr,
                                                        uint8_t* __restrict__ dst, int H, int W, double ify, double ifx,
                                                        unsigned long long* __restrict__ cnt, const uint8_t* __restrict__ rgb,
                                                        double rsy, double rsx, double* __restrict__ coverage_out) {
-  __shared__ unsigned long long rows[HM_N], tmp[HM_N];
-  __shared__ uint8_t flag[HM_CELLS][HM_CELLS];
-  const int tx0 = blockIdx.x * HM_T, ty0 = blockIdx.y * HM_T;
+  __shared__ unsigned long long rows[HM_NY], tmp[HM_NY];
+  __shared__ uint8_t flag[HM_CY][HM_CX];
+  const int tx0 = blockIdx.x * HM_TW, ty0 = blockIdx.y * HM_TH;
   const int ox = tx0 - HM_R, oy = ty0 - HM_R;
-  const int x_lo = max(ox, 0), x_hi = min(ox + HM_N - 1, W - 1), y_lo = max(oy, 0), y_hi = min(oy + HM_N - 1, H - 1);
+  const int x_lo = max(ox, 0), x_hi = min(ox + HM_NX - 1, W - 1), y_lo = max(oy, 0), y_hi = min(oy + HM_NY - 1, H - 1);
   const int cx0 = min((int)floor(__dmul_rn((double)x_lo, ifx)), HUD_W - 1), cx1 = min((int)floor(__dmul_rn((double)x_hi, ifx)), HUD_W - 1);
   const int cy0 = min((int)floor(__dmul_rn((double)y_lo, ify)), HUD_H - 1), cy1 = min((int)floor(__dmul_rn((double)y_hi, ify)), HUD_H - 1);
   const int ncx = cx1 - cx0 + 1, ncy = cy1 - cy0 + 1;
-  const bool staged = ncx <= HM_CELLS && ncy <= HM_CELLS;
+  const bool staged = ncx <= HM_CX && ncy <= HM_CY;
   if (staged)
     for (int e = threadIdx.x; e < ncx * ncy; e += blockDim.x) {
       const int cy = e / ncx, cx = e - cy * ncx, ax = cx0 + cx, ay = cy0 + cy;
       int newest = -1;
       if (FUSED) {
         newest = resized_gray(rgb, W, lin_tap(ax, rsx, W, true), lin_tap(ay, rsy, H, false));
-        const int fx = hud_first_px(ax, rsx, ifx, W), fy = hud_first_px(ay, rsy, ify, H);
-        if (fx >= tx0 && fx < tx0 + HM_T && fy >= ty0 && fy < ty0 + HM_T)
+        const int fx = hud_owner_px(ax, rsx, W), fy = hud_owner_px(ay, rsy, H);
+        if (fx >= tx0 && fx < tx0 + HM_TW && fy >= ty0 && fy < ty0 + HM_TH)
           ring[(size_t)sl.idx[4] * HUD_W * HUD_H + ay * HUD_W + ax] = (uint8_t)newest;
       }
       flag[cy][cx] = hud_flag_at(ring, sl.idx, thr, ay * HUD_W + ax, newest) ? 1 : 0;
     }
+  // region column / row -> staged cell index (or -1 outside the image): the double multiply + floor once per column / row
+  __shared__ short colcell[HM_NX], rowcell[HM_NY];
+  if (threadIdx.x < HM_NX) {
+    const int gx = ox + (int)threadIdx.x;
+    colcell[threadIdx.x] = (gx >= 0 && gx < W) ? (short)(min((int)floor(__dmul_rn((double)gx, ifx)), HUD_W - 1) - cx0) : (short)-1;
+  }
+  if (threadIdx.x < HM_NY) {
+    const int gy = oy + (int)threadIdx.x;
+    rowcell[threadIdx.x] = (gy >= 0 && gy < H) ? (short)(min((int)floor(__dmul_rn((double)gy, ify)), HUD_H - 1) - cy0) : (short)-1;
+  }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int t = warp; t < HM_N; t += 8) {
-    const int gy = oy + t;
-    const bool yin = gy >= 0 && gy < H;
-    const int cya = yin ? min((int)floor(__dmul_rn((double)gy, ify)), HUD_H - 1) : 0, cy = cya - cy0;
+  for (int t = warp; t < HM_NY; t += 8) {
+    const int cy = rowcell[t];
     unsigned int half[2];
 #pragma unroll
     for (int hh = 0; hh < 2; hh++) {
-      const int c = lane + 32 * hh, gx = ox + c;
+      const int c = lane + 32 * hh;
       bool bit = false;
-      if (yin && c < HM_N && gx >= 0 && gx < W) {
-        const int cxa = min((int)floor(__dmul_rn((double)gx, ifx)), HUD_W - 1);
-        bit = staged ? flag[cy][cxa - cx0] != 0 : hud_flag_at(ring, sl.idx, thr, cya * HUD_W + cxa);
+      if (cy >= 0 && c < HM_NX) {
+        const int cc = colcell[c];
+        if (cc >= 0) bit = staged ? flag[cy][cc] != 0 : hud_flag_at(ring, sl.idx, thr, (cy + cy0) * HUD_W + cc + cx0);
       }
       half[hh] = __ballot_sync(0xffffffffu, bit);
     }
@@ -732,22 +981,25 @@ __global__ void __launch_bounds__(256) hud_mask_kernel(uint8_t* __restrict__ rin
     inx = ((c_hi == 63 ? 0ull : (1ull << (c_hi + 1))) - 1ull) & ~((1ull << c_lo) - 1ull);
   }
   const int gy_t = oy + (int)threadIdx.x;
-  const bool rowin = threadIdx.x < HM_N && gy_t >= 0 && gy_t < H;
+  const bool rowin = threadIdx.x < HM_NY && gy_t >= 0 && gy_t < H;
   hm_dilate(rows, tmp, rowin, inx, 2, false);  // MORPH_CLOSE: dilate 5x5 ...
   hm_dilate(rows, tmp, rowin, inx, 4, true);   // ... erode 5x5, then MORPH_OPEN's erode 5x5: together erode 9x9
   hm_dilate(rows, tmp, rowin, inx, 2, false);  // ... dilate 5x5
-  // store the tile (4 pixels per thread) and count it
-  const int yl = threadIdx.x >> 3, xq = (threadIdx.x & 7) * 4;
-  const int y = ty0 + yl, x = tx0 + xq;
+  // store the tile (4 pixels per thread and step, 32 rows per step) and count it
   unsigned int c4 = 0;
-  if (y < H && x < W) {
-    const unsigned long long w = rows[HM_R + yl] >> (HM_R + xq);
-    uint8_t v[4];
+  const int xq = (threadIdx.x & 7) * 4, x = tx0 + xq;
 #pragma unroll
-    for (int k = 0; k < 4; k++) { v[k] = (x + k < W) ? (uint8_t)((w >> k) & 1ull) : 0; c4 += v[k]; }
-    uint8_t* o = dst + (size_t)y * W + x;
-    if (x + 3 < W && ((W & 3) == 0)) *reinterpret_cast<uchar4*>(o) = make_uchar4(v[0], v[1], v[2], v[3]);
-    else for (int k = 0; k < 4 && x + k < W; k++) o[k] = v[k];
+  for (int step = 0; step < HM_TH / 32; step++) {
+    const int yl = (threadIdx.x >> 3) + 32 * step, y = ty0 + yl;
+    if (y < H && x < W) {
+      const unsigned long long w = rows[HM_R + yl] >> (HM_R + xq);
+      uint8_t v[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) { v[k] = (x + k < W) ? (uint8_t)((w >> k) & 1ull) : 0; c4 += v[k]; }
+      uint8_t* o = dst + (size_t)y * W + x;
+      if (x + 3 < W && ((W & 3) == 0)) *reinterpret_cast<uchar4*>(o) = make_uchar4(v[0], v[1], v[2], v[3]);
+      else for (int k = 0; k < 4 && x + k < W; k++) o[k] = v[k];
+    }
   }
   __shared__ unsigned long long sh[32];
   const unsigned long long c = block_sum((unsigned long long)c4, sh);
@@ -775,6 +1027,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
   VFI_ENTER(h, stream);
   cudaStream_t s = (cudaStream_t)stream;
   const size_t npix = (size_t)H * W;
+  ProfScope ps(h, PC_REDUCE, s);
   if (int rc = vfi_red_reserve(h, std::max((size_t)65536 * 8, npix + HUD_W * HUD_H + 4096))) return rc;
   const long long c = *count;
   // cv2.resize(gray, (320, 180)): inv_scale = dsize / ssize, scale = 1 / inv_scale (doubles, as OpenCV computes them)
@@ -783,7 +1036,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
   for (int k = 0; k < 5; k++) sl.idx[k] = (int)(((c - 4 + k) % hist_len + hist_len) % hist_len);  // oldest -> newest of the last five
   const double ifx = 1.0 / ((double)W / (double)HUD_W), ify = 1.0 / ((double)H / (double)HUD_H);
   if (c + 1 >= 5 && W >= HUD_W && H >= HUD_H) {  // steady state: one launch (thumbnail + mask + coverage)
-    hud_mask_kernel<true><<<dim3(cdiv(W, HM_T), cdiv(H, HM_T)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx,
+    hud_mask_kernel<true><<<dim3(cdiv(W, HM_TW), cdiv(H, HM_TH)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx,
                                                                              h->hud_cnt, rgb, rsy, rsx, coverage_out);
     VFI_LAUNCHED(h);
     *count = c + 1;
@@ -800,7 +1053,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_hud_update(vfi_handle*
   }
   unsigned long long* cnt = (unsigned long long*)h->red;
   VFI_CUDA(h, cudaMemsetAsync(cnt, 0, 8, s));
-  hud_mask_kernel<false><<<dim3(cdiv(W, HM_T), cdiv(H, HM_T)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx, cnt,
+  hud_mask_kernel<false><<<dim3(cdiv(W, HM_TW), cdiv(H, HM_TH)), 256, 0, s>>>(hist_ring, sl, var_threshold, mask_out, H, W, ify, ifx, cnt,
                                                                             nullptr, 0.0, 0.0, nullptr);
   VFI_LAUNCHED(h);
   coverage_finish_kernel<<<1, 1, 0, s>>>(cnt, (double)npix, coverage_out);
