@@ -44,6 +44,12 @@ typedef struct vfi_handle vfi_handle;
 int vfi_create(int device, vfi_handle** out);
 void vfi_destroy(vfi_handle* h);
 const char* vfi_last_error(vfi_handle* h);
+/* Stream-ordering fence: makes `stream` wait for the handle's previous call (if that ran on another stream) and records it as
+ * the handle's latest user; launches nothing.  Calls captured into a CUDA graph (cudaStreamBeginCapture on `stream` around
+ * vfi_ifnet_infer: the single-pair latency path of RIFEModel.interpolate) skip this bookkeeping, so the graph's owner
+ * brackets every replay with vfi_fence before and after. */
+int vfi_fence(vfi_handle* h, void* stream);
+
 /* number of kernels this handle has launched since creation (bench.py "gpu_launches") */
 long long vfi_launch_count(vfi_handle* h);
 

@@ -126,6 +126,14 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   VFI_FAIL(h, VFI_E_ARG, "unknown option %s", key);
 }
 
+// Orders `stream` into the handle's call sequence without launching anything: waits (on the device) for the handle's previous
+// call when that ran on another stream, and marks `stream` as the latest user.  Bracket a CUDA-graph replay of captured
+// calls with two fences (captured calls record no cross-stream bookkeeping themselves).
+extern "C" __attribute__((visibility("default"))) int vfi_fence(vfi_handle* h, void* stream) {
+  if (!h) return VFI_E_ARG;
+  VFI_ENTER(h, stream);
+  return VFI_OK;
+}
 extern "C" __attribute__((visibility("default"))) const char* vfi_last_error(vfi_handle* h) { return h ? h->err.c_str() : "null handle"; }
 extern "C" __attribute__((visibility("default"))) long long vfi_launch_count(vfi_handle* h) { return h ? h->launches : 0; }
 extern "C" __attribute__((visibility("default"))) size_t vfi_device_bytes(vfi_handle* h) {

@@ -115,14 +115,18 @@ struct ProfScope {
 // not move the thread's CUDA device behind PyTorch's back), and orders this call after the handle's previous call when
 // that one ran on another stream.
 struct CallScope {
-  vfi_handle* h; cudaStream_t s; int prev_dev = -1; bool ok = true;
+  vfi_handle* h; cudaStream_t s; int prev_dev = -1; bool ok = true, capturing = false;
   CallScope(vfi_handle* h_, cudaStream_t s_) : h(h_), s(s_) {
     if (cudaGetDevice(&prev_dev) != cudaSuccess) prev_dev = -1;
     if (prev_dev != h->device && cudaSetDevice(h->device) != cudaSuccess) { ok = false; return; }
-    if (h->scratch_used && h->scratch_stream != s) cudaStreamWaitEvent(s, h->scratch_ev, 0);
+    // a call being captured into a CUDA graph (RIFEModel's single-pair path) records no cross-stream bookkeeping: the
+    // graph owner replays it on one stream and orders it against other users of the handle itself
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    capturing = cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone;
+    if (!capturing && h->scratch_used && h->scratch_stream != s) cudaStreamWaitEvent(s, h->scratch_ev, 0);
   }
   ~CallScope() {
-    if (ok) { cudaEventRecord(h->scratch_ev, s); h->scratch_stream = s; h->scratch_used = true; }
+    if (ok && !capturing) { cudaEventRecord(h->scratch_ev, s); h->scratch_stream = s; h->scratch_used = true; }
     if (prev_dev >= 0 && prev_dev != h->device) cudaSetDevice(prev_dev);
   }
 };

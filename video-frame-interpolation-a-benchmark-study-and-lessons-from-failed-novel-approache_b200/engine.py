@@ -36,6 +36,8 @@ class Engine:
             raise _abi.VFIError(f"vfi_create(device={device}) failed ({rc}): needs an sm_100 (B200) GPU")
         self._h = h
         self.weights_loaded = False
+        self._graph_launches = 0      # kernels launched by CUDA-graph replays (the library counts them at capture only)
+        self._ts_last = None          # timesteps the handle's device copy holds (set by the last eager infer)
 
     @staticmethod
     def get(device=None):
@@ -62,7 +64,11 @@ class Engine:
 
     @property
     def launches(self):
-        return int(self._lib.vfi_launch_count(self._h))
+        return int(self._lib.vfi_launch_count(self._h)) + self._graph_launches
+
+    def fence(self):
+        """Order the current stream into the handle's call sequence (vfi_fence): before and after a graph replay."""
+        self._check(self._lib.vfi_fence(self._h, _stream()), "vfi_fence")
 
     def device_bytes(self):
         """Device memory owned by the library handle (workspace + scratch + packed weights): invisible to torch's stats."""
@@ -124,6 +130,7 @@ class Engine:
                                               float(scale), int(precision), int(flags), _ptr(hm), _ptr(out), _ptr(of),
                                               _ptr(fl), _stream())
         self._check(rc, "vfi_ifnet_infer_ex")
+        self._ts_last = tuple(float(t) for t in timesteps)
         res = (out,)
         if want_float:
             res += (of,)
