@@ -80,3 +80,36 @@ def test_single_process_paths_need_no_group():
     v = torch.tensor([1, 2, 3])
     assert sharding.reduce_counters(v.clone()).tolist() == [1, 2, 3]
     assert sharding.gather_flags(torch.tensor([0, 2, 1], dtype=torch.int8), 3, 0, 1).tolist() == [0, 2, 1]
+
+
+def _sum_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import vfi_b200  # noqa: F401
+    from vfi_b200 import sharding
+    from vfi_b200.evaluation import metrics as M
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = sharding.shard_range(10, rank, world)
+    # a rank's evaluate_range() vector: [sum psnr, sum ssim, n, n_inf, sum sse] over its frames (synthetic per-frame values)
+    psnr = [30.0 + i for i in range(lo, hi)]
+    part = [sum(psnr), sum(0.9 + 0.001 * i for i in range(lo, hi)), float(hi - lo), float(rank == 0), float(sum(1000 * i for i in range(lo, hi)))]
+    res = M.reduce_sums(part, (lo, hi), None, "cpu")
+    cov = sharding.gather_flags(torch.tensor([0.5 * i for i in range(lo, hi)], dtype=torch.float64), 10, rank, world)
+    np.savez(os.path.join(out_dir, f"s{rank}.npz"), n=res["n"], sse=res["sse_sum"], psnr_sum=res["psnr_sum"], ssim=res["ssim"],
+             inf=res["n_identical"], cov=cov.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_metric_sums_all_reduce(tmp_path, world):
+    """Config 5's one collective (evaluation.metrics.reduce_sums) and the float64 flag gather over gloo: every rank ends
+    with the whole-set sums (integer entries exact) and the clip-order coverage vector."""
+    mp.spawn(_sum_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        p = np.load(tmp_path / f"s{r}.npz")
+        assert int(p["n"]) == 10 and int(p["sse"]) == sum(1000 * i for i in range(10)) and int(p["inf"]) == 1
+        assert abs(float(p["psnr_sum"]) - sum(30.0 + i for i in range(10))) < 1e-9
+        assert abs(float(p["ssim"]) - np.mean([0.9 + 0.001 * i for i in range(10)])) < 1e-12
+        assert p["cov"].tolist() == [0.5 * i for i in range(10)]

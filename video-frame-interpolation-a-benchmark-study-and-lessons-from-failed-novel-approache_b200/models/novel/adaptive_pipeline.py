@@ -344,7 +344,8 @@ class AdaptivePipeline(BaseModel):
         return {'range': (lo, hi), 'routes': routes.cpu().numpy(), 'stats': whole.to_dict()}
 
     def process_clip_batched(self, frames, num_frames: int = 3, rank: int = 0, world: int = 1, group=None,
-                             batch: int = 8, out=None, on_batch=None, n_pairs: Optional[int] = None, base: int = 0) -> dict:
+                             batch: int = 8, out=None, on_batch=None, n_pairs: Optional[int] = None, base: int = 0,
+                             collect: bool = True) -> dict:
         """Extra (not in the reference): process_clip at device speed.  Same per-pair semantics as interpolate()
         (:369-411: cut -> copies of frame0; else RIFE with the HUD composite when coverage > 0.01; the route
         recommendation is computed and counted either way), evaluated `batch` pairs at a time on a DEVICE-RESIDENT
@@ -357,6 +358,7 @@ class AdaptivePipeline(BaseModel):
         its part of the clip passes frames = clip[base : ...] with `base` and the clip's `n_pairs` (it needs the frames from
         16 pairs before its range, for the HUD warm-up replay across cuts, to one past its last pair).
         out: optional (hi-lo, T, H, W, 3) uint8 CUDA tensor for the shard's frames; on_batch(j0, frames_dev, analyses).
+        collect=False skips the end-of-clip collectives (this rank's counters and flags only, padded with -1).
         Returns {'range', 'routes', 'cuts', 'hud_coverage' (clip order), 'stats', 'analyses' (this shard)}."""
         from ... import sharding
         self.ensure_loaded()
@@ -453,9 +455,14 @@ class AdaptivePipeline(BaseModel):
         vec = torch.tensor([len(local_routes)] + [sum(1 for c in local_routes if c == k) for k in
                                                   (_abi.ROUTE_RIFE, _abi.ROUTE_VFIMAMBA, _abi.ROUTE_SCENE_CHANGE)],
                            dtype=torch.int64, device=dev)
-        vec = sharding.reduce_counters(vec, group).tolist()
-        routes = sharding.gather_flags(torch.tensor(local_routes, dtype=torch.int8, device=dev), n_pairs, rank, world, group)
-        cov = sharding.gather_flags(torch.tensor(local_cov, dtype=torch.float64, device=dev), n_pairs, rank, world, group)
+        if collect:
+            vec = sharding.reduce_counters(vec, group).tolist()
+            routes = sharding.gather_flags(torch.tensor(local_routes, dtype=torch.int8, device=dev), n_pairs, rank, world, group)
+            cov = sharding.gather_flags(torch.tensor(local_cov, dtype=torch.float64, device=dev), n_pairs, rank, world, group)
+        else:
+            vec = vec.tolist()
+            routes = torch.tensor(local_routes, dtype=torch.int8, device=dev)
+            cov = torch.tensor(local_cov, dtype=torch.float64, device=dev)
         routes = routes.cpu().numpy()
         return {'range': (lo, hi), 'routes': routes, 'cuts': (routes == _abi.ROUTE_SCENE_CHANGE),
                 'hud_coverage': cov.cpu().numpy(), 'analyses': analyses,
