@@ -122,6 +122,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!strcmp(key, "v2_pm")) { h->opt_v2_pm = value; return VFI_OK; }
   if (!strcmp(key, "v2_tma")) { h->opt_v2_tma = value; return VFI_OK; }
   if (!strcmp(key, "l2_chunk_mb")) { h->opt_l2_chunk_mb = value; return VFI_OK; }
+  if (!strcmp(key, "gc_persistent")) { h->opt_gc_persistent = value; return VFI_OK; }
+  if (!strcmp(key, "gc_ablate")) { h->opt_gc_ablate = value; return VFI_OK; }
   if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }
   VFI_FAIL(h, VFI_E_ARG, "unknown option %s", key);
 }

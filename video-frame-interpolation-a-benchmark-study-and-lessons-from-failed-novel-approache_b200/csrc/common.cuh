@@ -94,6 +94,8 @@ struct vfi_handle {
   int opt_fuse_gather = 1;      // vfi_set_option("fuse_gather"): finest block's gather fused with conv0[0]
   int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps
   int opt_v2_ablate = 0;        // debug only: see V2Params::ablate
+  int opt_gc_persistent = 1;    // vfi_set_option("gc_persistent"): persistent, phase-overlapped form of the fused finest-block gather
+  int opt_gc_ablate = 0;        // debug only: gather_conv0a phases off (1 staging, 2 gather, 4 MMA + epilogue, 8 flow evaluation)
   int opt_conv_v2 = 1;          // vfi_set_option("conv_v2"): resident-weight halo-tile conv kernel where it applies
   // optional per-kernel-class timing (vfi_profile_enable): event pairs around every launch
   bool profile = false;

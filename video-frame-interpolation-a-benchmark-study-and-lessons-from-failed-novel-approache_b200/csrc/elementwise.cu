@@ -970,11 +970,13 @@ __device__ __forceinline__ Tap ld_tap(const Tap* p) {
 // levels are one flat array of 33-float4 rows, so entry e is simply staged row e / 33, column e % 33; the x taps come
 // from the per-call tables (k_build_taps), the level of a row from the host-computed row starts.
 template <int TW, int NT>
-__device__ __forceinline__ void flat_stage(const LowSet& L, const GcRows& R, int n, int ox, int oy, int Hp, int Wp, float4* sm) {
+__device__ __forceinline__ void flat_stage(const LowSet& L, const GcRows& R, int n, int ox, int oy, int Hp, int Wp, float4* sm,
+                                           int tid = -1) {
   constexpr int GC_TW_ = TW, GC_TAB_ = 5 * TW, GC_THREADS_ = NT;
+  if (tid < 0) tid = (int)threadIdx.x;     // NT threads with ids 0 .. NT-1 cooperate (a subset of the CTA's warps may stage)
   RowTap* ytab = reinterpret_cast<RowTap*>(sm);
   const float oyf = (float)max(oy, 0) + 0.5f;
-  for (int e = threadIdx.x; e < L.n * GC_TW_; e += GC_THREADS_) {
+  for (int e = tid; e < L.n * GC_TW_; e += GC_THREADS_) {
     const int k = e / GC_TW_, yl = e - k * GC_TW_;
     const Tap ty = ld_tap(L.yt[k] + min(max(oy + yl, 0), Hp - 1));
     const int r_lo = (int)fmaxf(L.rs[k] * oyf - 0.5f, 0.f);
@@ -986,7 +988,7 @@ __device__ __forceinline__ void flat_stage(const LowSet& L, const GcRows& R, int
   }
   const int total = R.start[5] * GC_TW_;
 #pragma unroll 2
-  for (int e = threadIdx.x; e < total; e += GC_THREADS_) {
+  for (int e = tid; e < total; e += GC_THREADS_) {
     const int u = e / GC_TW_, col = e - u * GC_TW_;
     int k = 0;
 #pragma unroll
@@ -1025,7 +1027,7 @@ __global__ void __launch_bounds__(GC_THREADS, 2)
 gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
                      const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
                      bf16* __restrict__ out, float4* __restrict__ flow_sum, const __grid_constant__ GcRows grows, int B, int I1, int Tn, int Hp,
-                     int Wp, float slope, int stage_bytes) {
+                     int Wp, float slope, int stage_bytes, int ablate) {
   using namespace umma;
   extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
   __shared__ uint64_t mma_bar;
@@ -1042,7 +1044,7 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   // stage only the flow rows (incl. the halo row / column); mask / feat of the finest coarse level are interpolated
   // straight from global memory (L1 / L2 resident: one 64 B texel serves four pixels), which leaves room for the A tile
   // beside the staging area at two CTAs per SM and lets a pixel go from evaluation to its A chunks in one pass
-  flat_stage<GC_TW, GC_THREADS>(lows, grows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
+  if (!(ablate & 1)) flat_stage<GC_TW, GC_THREADS>(lows, grows, n, tx0 - 1, ty0 - 1, Hp, Wp, tl_sm);
   if (threadIdx.x >= GC_THREADS - 2 * GC_TW) {  // the last warps: they have the fewest staging entries
     const int e = threadIdx.x - (GC_THREADS - 2 * GC_TW), ax = e / GC_TW, j = e - ax * GC_TW;
     const int kl = lows.n - 1;
@@ -1076,8 +1078,8 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
     uint4 u[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) u[j] = make_uint4(0u, 0u, 0u, 0u);
-    if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
-      const float4 fl = flat_eval<GC_TW>(lows, tl_sm, lx, ly);
+    if (gy >= 0 && gx >= 0 && !(ablate & 2)) {  // else: outside the image = the convolution's zero padding
+      const float4 fl = (ablate & 8) ? make_float4(0.5f, 0.25f, -0.5f, -0.25f) : flat_eval<GC_TW>(lows, tl_sm, lx, ly);
       // the flow of blocks 0..3 at this pixel, for the final blend (tile-interior pixels: each written exactly once)
       if (fsum && ly > 0 && lx > 0) fsum[gy * Wp + gx] = fl;
       // mask + 8 feature channels: bilinear x2 of texel channels 4..12
@@ -1117,6 +1119,10 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   __syncthreads();
 
   // ---- phase 3: 2 sub-tiles (output columns 0-7, 8-15) x 9 taps x 2 k-steps of tcgen05.mma, then the epilogue ----
+  if (ablate & 4) {
+    if (warp == 0) { tc_after(); tmem_dealloc(tmem_base, 32); }
+    return;
+  }
   if (warp == 0) {
     const uint32_t leader = elect_one();
     constexpr uint32_t IDESC = idesc_bf16_m128(16);
@@ -1172,6 +1178,167 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
   }
 }
 
+// Persistent form of the kernel above (2 CTAs per SM loop over the tiles): barriers, TMEM and the 9 KB of weights are set
+// up once per CTA, and while warps 0-3 issue tile i's MMAs and run its epilogue, warps 4-11 already stage the flow rows of
+// tile i+1 -- the two latency-bound phases overlap instead of adding (phase ablation on B200, 24 items of 1080p: set-up
+// 0.37 ms + staging 0.41 + gather 1.22 + MMA / epilogue 0.33 = the one-tile kernel's 2.28 ms).
+template <typename T>
+__global__ void __launch_bounds__(GC_THREADS, 2)
+gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
+                       const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
+                       bf16* __restrict__ out, float4* __restrict__ flow_sum, const __grid_constant__ GcRows grows, int B, int I1, int Tn, int Hp,
+                       int Wp, float slope, int stage_bytes, int tiles_x, int tiles_y, int num_tiles) {
+  using namespace umma;
+  extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
+  __shared__ uint64_t mma_bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ Tap mtab[2][GC_TW];
+  uint8_t* a_s = reinterpret_cast<uint8_t*>(tl_sm) + stage_bytes;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint8_t* w_s = a_s + GC_A_BYTES;
+  constexpr int ablate = 0;
+  (void)ablate;
+  if (threadIdx.x == 0) { bar_init(&mma_bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, 32);
+  for (int i = threadIdx.x; i < GC_W_BYTES / 16; i += GC_THREADS)
+    reinterpret_cast<uint4*>(w_s)[i] = __ldg(reinterpret_cast<const uint4*>(wpack) + i);
+  const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it (16-channel texels: c4 == 4)
+  int tile = blockIdx.x;
+  // stage tile `t` (flow rows + the mask / feat tap tables) with the NT threads whose ids are tid = 0 .. NT-1
+  auto stage = [&](int t, auto nt_tag, int tid) {
+    constexpr int NT = decltype(nt_tag)::value;
+    const int tx = t % tiles_x, ty = (t / tiles_x) % tiles_y, nn = t / (tiles_x * tiles_y);
+    flat_stage<GC_TW, NT>(lows, grows, nn, tx * TL_W - 1, ty * TL_H - 1, Hp, Wp, tl_sm, tid);
+    if (tid >= NT - 2 * GC_TW) {
+      const int e = tid - (NT - 2 * GC_TW), ax = e / GC_TW, j = e - ax * GC_TW;
+      const Tap* src = ax ? lows.yt[kl] + max(ty * TL_H - 1 + j, 0) : lows.xt[kl] + max(tx * TL_W - 1 + j, 0);
+      reinterpret_cast<int4*>(&mtab[ax][j])[0] = __ldg(reinterpret_cast<const int4*>(src));
+    }
+  };
+  if (tile < num_tiles) stage(tile, std::integral_constant<int, GC_THREADS>{}, (int)threadIdx.x);
+  fence_async_smem();
+  tc_before();
+  __syncthreads();
+  tc_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int plane = Hp * Wp;
+  const uint32_t* img32 = reinterpret_cast<const uint32_t*>(imgs);
+  const int mWl = lows.Wl[kl];
+  const bf16 *mfp = lows.mf[kl], *f7p = lows.f7[kl];
+  for (int it = 0; tile < num_tiles; tile += gridDim.x, it++) {
+    const int tx0 = (tile % tiles_x) * TL_W, ty0 = ((tile / tiles_x) % tiles_y) * TL_H, n = tile / (tiles_x * tiles_y);
+    const int b = n / Tn;
+    const float t = tsteps[n - b * Tn];
+    const int base0 = b * plane, base1 = (I1 + b) * plane;
+    const int mtb = n * lows.Hl[kl] * mWl;
+    float4* fsum = flow_sum ? flow_sum + (size_t)n * plane : nullptr;
+    // Work units: region rows 0..32 with lane = column 1..32 (one image row per warp instruction: two or three cache
+    // lines per tap instead of the five a row-straddling warp touches), then the halo column (lx = 0) in two more units.
+    constexpr int GC_UNITS = GC_TW + 2;
+  #pragma unroll 1
+    for (int unit = warp; unit < GC_UNITS; unit += GC_THREADS / 32) {
+      int ly, lx;
+      if (unit < GC_TW) { ly = unit; lx = lane + 1; }
+      else { ly = (unit - GC_TW) * 32 + lane; lx = 0; if (ly >= GC_TW) continue; }
+      const int gy = ty0 - 1 + ly, gx = tx0 - 1 + lx;  // global pixel
+      uint4 u[4];
+  #pragma unroll
+      for (int j = 0; j < 4; j++) u[j] = make_uint4(0u, 0u, 0u, 0u);
+      if (gy >= 0 && gx >= 0) {  // else: outside the image = the convolution's zero padding
+        const float4 fl = flat_eval<GC_TW>(lows, tl_sm, lx, ly);
+        // the flow of blocks 0..3 at this pixel, for the final blend (tile-interior pixels: each written exactly once)
+        if (fsum && ly > 0 && lx > 0) fsum[gy * Wp + gx] = fl;
+        // mask + 8 feature channels: bilinear x2 of texel channels 4..12
+        const Tap ty = mtab[1][ly], tx = mtab[0][lx];
+        const int r0 = mtb + ty.i0 * mWl, r1 = mtb + ty.i1 * mWl;
+        const float w00 = ty.h * tx.h, w01 = ty.h * tx.l, w10 = ty.l * tx.h, w11 = ty.l * tx.l;
+        float mf[9];
+        {
+          float a[9], c[9];
+          mf9_load(mfp, f7p, r0 + tx.i0, a);
+          mf9_load(mfp, f7p, r0 + tx.i1, c);
+  #pragma unroll
+          for (int i = 0; i < 9; i++) mf[i] = w00 * a[i] + w01 * c[i];
+          mf9_load(mfp, f7p, r1 + tx.i0, a);
+          mf9_load(mfp, f7p, r1 + tx.i1, c);
+  #pragma unroll
+          for (int i = 0; i < 9; i++) mf[i] += w10 * a[i] + w11 * c[i];
+        }
+        const Bil b0 = bil_setup((float)gx + fl.x, (float)gy + fl.y, Wp, Hp, base0);
+        const Bil b1 = bil_setup((float)gx + fl.z, (float)gy + fl.w, Wp, Hp, base1);
+        float c0[3], c1[3], v0[4], v1[4];
+        sample_rgbx(img32, b0, c0);
+        sample_rgbx(img32, b1, c1);
+        sample_feat_px<T>(feats, b0, v0);
+        sample_feat_px<T>(feats, b1, v1);
+        // channel order of the block input: warped img0 (3), img1 (3), f0 (4), f1 (4), timestep, mask, feat (8), flow (4)
+        u[0] = make_uint4(pk_bf16(c0[0], c0[1]), pk_bf16(c0[2], c1[0]), pk_bf16(c1[1], c1[2]), pk_bf16(v0[0], v0[1]));
+        u[1] = make_uint4(pk_bf16(v0[2], v0[3]), pk_bf16(v1[0], v1[1]), pk_bf16(v1[2], v1[3]), pk_bf16(t, mf[0]));
+        u[2] = make_uint4(pk_bf16(mf[1], mf[2]), pk_bf16(mf[3], mf[4]), pk_bf16(mf[5], mf[6]), pk_bf16(mf[7], mf[8]));
+        u[3] = make_uint4(pk_bf16(fl.x, fl.y), pk_bf16(fl.z, fl.w), 0u, 0u);
+      }
+      const uint32_t pix = gc_pix_index(ly, lx);
+  #pragma unroll
+      for (int j = 0; j < 4; j++) *reinterpret_cast<uint4*>(a_s + ((size_t)j * GC_CS + pix) * 16) = u[j];
+    }
+    fence_async_smem();
+    __syncthreads();               // the A tile is complete; the staging area and the tap tables are free again
+    if (warp == 0) {
+      const uint32_t leader = elect_one();
+      constexpr uint32_t IDESC = idesc_bf16_m128(16);
+      const uint64_t ad0 = desc_ns(s_u32(a_s), GC_CS * 16, GC_PW * 16);
+      const uint64_t bd0 = desc_ns(s_u32(w_s), 16 * 16, 128);
+  #pragma unroll
+      for (int tap = 0; tap < 9; tap++) {
+  #pragma unroll
+        for (int k = 0; k < 2; k++) {
+  #pragma unroll
+          for (int j = 0; j < 2; j++) {
+            const int ky = tap / 3, kx = tap % 3;
+            const int pl = (ky != 1 ? 2 : 0) + (kx != 1 ? 1 : 0);
+            const uint32_t a_off = (uint32_t)(pl * GC_PLANE + (ky != 0 ? 1 : 0) * GC_PW + (kx != 0 ? 1 : 0) + 8 * j + 2 * k * GC_CS);
+            const uint32_t b_off = (uint32_t)((tap * 4 + 2 * k) * 16);
+            mma_bf16_elect(leader, tmem_base + (uint32_t)(j * 16), ad0 + a_off, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
+          }
+        }
+      }
+      if (leader) commit_to(&mma_bar);
+      __syncwarp();
+    }
+    if (warp < 4) {
+      bar_wait(&mma_bar, (uint32_t)(it & 1));
+      tc_after();
+      const int m = warp * 32 + lane;
+      const int Ho = Hp >> 1, Wo = Wp >> 1;
+      const int oy = (ty0 >> 1) + (m >> 3);
+      float v[2][16];
+      ld16(tmem_base + ((uint32_t)(warp * 32) << 16), v[0]);
+      ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + 16, v[1]);
+  #pragma unroll
+      for (int j = 0; j < 2; j++) {
+        const int ox = (tx0 >> 1) + 8 * j + (m & 7);
+  #pragma unroll
+        for (int c = 0; c < 16; c++) {
+          float x = v[j][c] + __ldg(bias + c);
+          v[j][c] = x > 0.f ? x : x * slope;
+        }
+        // conv0's second conv is stride 2 too: write its four phase planes [N, 4, Ho/2, Wo/2, 16]
+        const size_t opix = ((((size_t)n * 4 + (oy & 1) * 2 + (ox & 1)) * (Ho >> 1) + (oy >> 1)) * (Wo >> 1) + (ox >> 1));
+        uint4 o0, o1;
+        o0.x = pk_bf16(v[j][0], v[j][1]); o0.y = pk_bf16(v[j][2], v[j][3]); o0.z = pk_bf16(v[j][4], v[j][5]); o0.w = pk_bf16(v[j][6], v[j][7]);
+        o1.x = pk_bf16(v[j][8], v[j][9]); o1.y = pk_bf16(v[j][10], v[j][11]); o1.z = pk_bf16(v[j][12], v[j][13]); o1.w = pk_bf16(v[j][14], v[j][15]);
+        st_v8(out + opix * 16, o0, o1);
+      }
+    }
+    if (warp >= 4 && tile + (int)gridDim.x < num_tiles)
+      stage(tile + (int)gridDim.x, std::integral_constant<int, GC_THREADS - 128>{}, (int)threadIdx.x - 128);
+    tc_before();
+    __syncthreads();               // next tile staged; this tile's MMAs complete (the epilogue waited for them), TMEM read out
+    tc_after();
+  }
+  if (warp == 0) tmem_dealloc(tmem_base, 32);
+}
+
 // Lb0 = the block's conv0[0] layer (28 -> 16, stride 2).  Output: its activation as the phase planes of [N, Hp/2, Wp/2, 16].
 int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
                     const float* tsteps_dev, bf16* out, float* flow_sum, int B, int I1, int T, int Hp, int Wp,
@@ -1187,9 +1354,19 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
   const size_t smem = un + GC_A_BYTES + GC_W_BYTES;
   VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   if (smem > 112 * 1024) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: shared memory budget");
+  if (h->opt_gc_persistent && !h->opt_gc_ablate) {
+    VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_p_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    const int tiles_x = Wp / TL_W, tiles_y = Hp / TL_H, num_tiles = tiles_x * tiles_y * B * T;
+    gather_conv0a_p_kernel<bf16><<<std::min(num_tiles, 2 * h->sm_count), GC_THREADS, smem, s>>>(
+        imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out, reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, Hp, Wp,
+        h->slope, (int)un, tiles_x, tiles_y, num_tiles);
+    VFI_LAUNCHED(h);
+    return 0;
+  }
   const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
   gather_conv0a_kernel<bf16><<<grid, GC_THREADS, smem, s>>>(imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out,
-                                                          reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, Hp, Wp, h->slope, (int)un);
+                                                          reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, Hp, Wp, h->slope, (int)un,
+                                                          h->opt_gc_ablate);
   VFI_LAUNCHED(h);
   return 0;
 }
