@@ -174,6 +174,12 @@ int vfi_add_weighted_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, size_
 int vfi_canny_u8(vfi_handle* h, const uint8_t* gray, int n, int H, int W, double low, double high,
                  uint8_t* edges_out, double* density_out, void* stream);
 
+/* MCAR tier 2, scripts/run_experiments.py:498-503 / :526-531: cv2.remap(src, x + flow_x * t, y + flow_y * t, cv2.INTER_LINEAR)
+ * for a uint8 image (H x W x channels, BORDER_CONSTANT 0) and a dense flow field (H x W x 2 float, e.g. vfi_farneback's
+ * flow_out); OpenCV's 5-bit fixed-point bilinear path, bit-exact.  Follow with vfi_add_weighted_u8(dst, 1-t, curr, t). */
+int vfi_remap_flow_u8(vfi_handle* h, const uint8_t* src, const float* flow, double t, int H, int W, int channels,
+                      uint8_t* dst, void* stream);
+
 /* detect_particles' frequency term (adaptive_pipeline.py:180-183): variance of the 3x3
  * Laplacian (reflect-101) of the gray image.  rgb: n x H x W x 3; out: n x double.        */
 int vfi_laplacian_var(vfi_handle* h, const uint8_t* rgb, int n, int H, int W, double* out, void* stream);

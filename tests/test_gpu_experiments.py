@@ -133,3 +133,33 @@ def test_rife_interpolate_call_site(engine, golden, weights):
     c = engine.infer(np.ascontiguousarray(small[0][..., ::-1])[None], np.ascontiguousarray(small[1][..., ::-1])[None], [0.5], 0.5,
                      _abi.PRECISION_FP32, flags=_abi.FLAG_PAD_REFLECT_EDGE)[0, 0].cpu().numpy()
     assert not np.array_equal(a, b) and np.array_equal(a, c[..., ::-1])
+
+
+@pytest.mark.parametrize("H,W", [(270, 480), (203, 317)])
+def test_remap_flow_bit_exact_and_mcar_tiers(engine, H, W):
+    """MCAR tier 2 (run_experiments.py:498-503): cv2.remap(prev, x + u t, y + v t, INTER_LINEAR) bit-exact with OpenCV's
+    fixed-point path for a real Farneback field and for large / out-of-frame displacements; then the three tiers."""
+    rgb = gen_clip(1, H, W, seed=6, cut_every=0, fast=(0, 2))
+    bgr = np.ascontiguousarray(rgb[..., ::-1])
+    g = [cv2.cvtColor(f, cv2.COLOR_BGR2GRAY) for f in bgr]
+    flow = cv2.calcOpticalFlowFarneback(g[0], g[1], None, 0.5, 1, 15, 1, 5, 1.1, 0)
+    rng = np.random.default_rng(0)
+    wild = (rng.standard_normal(flow.shape) * 40).astype(np.float32)          # leaves the frame: BORDER_CONSTANT zeros
+    y, x = np.mgrid[0:H, 0:W].astype(np.float32)
+    for fl in (flow, wild):
+        for t in (0.25, 0.5, 0.75):
+            want = cv2.remap(bgr[0], x + fl[..., 0] * t, y + fl[..., 1] * t, cv2.INTER_LINEAR)
+            assert np.array_equal(engine.remap_flow(bgr[0], fl, t).cpu().numpy(), want)
+    gray1 = cv2.remap(g[0], x + flow[..., 0] * 0.5, y + flow[..., 1] * 0.5, cv2.INTER_LINEAR)
+    assert np.array_equal(engine.remap_flow(g[0], flow, 0.5).cpu().numpy(), gray1)
+    # tiers: thresholds placed around the pair's complexity
+    c, dflow = rx.estimate_motion_complexity(g[0], g[1])
+    lin, tier = rx.mcar_interpolate_cached(bgr[0], bgr[1], 0.5, c, dflow, 0.5, c + 0.1, c + 0.2)
+    assert tier == "linear" and np.array_equal(lin, cv2.addWeighted(bgr[0], 0.5, bgr[1], 0.5, 0))
+    fw, tier = rx.mcar_interpolate_cached(bgr[0], bgr[1], 0.25, c, dflow, 0.5, c - 0.01, c + 0.2)
+    ref_flow = dflow.cpu().numpy()
+    want = cv2.addWeighted(cv2.remap(bgr[0], x + ref_flow[..., 0] * 0.25, y + ref_flow[..., 1] * 0.25, cv2.INTER_LINEAR), 0.75, bgr[1], 0.25, 0)
+    assert tier == "flow" and np.array_equal(fw, want)
+    rx.RIFEModel._instance = engine
+    rf, tier, c2 = rx.mcar_interpolate(bgr[0], bgr[1], 0.5, 1.0, -2.0, -1.0)
+    assert tier == "rife" and rf.shape == bgr[0].shape and abs(c2 - c) < 1e-12

@@ -1292,3 +1292,39 @@ extern "C" __attribute__((visibility("default"))) int vfi_canny_u8(vfi_handle* h
   }
   return VFI_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// MCAR tier 2 (scripts/run_experiments.py:498-503, :526-531): cv2.remap(prev, x + flow_x * t, y + flow_y * t, INTER_LINEAR)
+// on uint8 frames (BORDER_CONSTANT 0).  OpenCV's fixed-point path restated exactly: the float32 map coordinate is rounded to
+// 1/32 pixel (cvRound(v * 32): half to even), the four bilinear weights are the 5-bit fractions' products scaled to 2^15
+// ((32-a)(32-b), a(32-b), (32-a)b, ab times 32: they sum to 2^15 with no correction), result = (sum + 2^14) >> 15.
+__global__ void remap_flow_kernel(const uint8_t* __restrict__ src, const float2* __restrict__ flow, float t, int H, int W, int C,
+                                  uint8_t* __restrict__ dst) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const float2 f = __ldg(flow + (size_t)y * W + x);
+  const float mx = __fadd_rn((float)x, __fmul_rn(f.x, t)), my = __fadd_rn((float)y, __fmul_rn(f.y, t));
+  const int sx = __float2int_rn(__fmul_rn(mx, 32.f)), sy = __float2int_rn(__fmul_rn(my, 32.f));
+  const int ix = sx >> 5, iy = sy >> 5, a = sx & 31, b = sy & 31;
+  const int w00 = (32 - a) * (32 - b), w01 = a * (32 - b), w10 = (32 - a) * b, w11 = a * b;
+  const bool x0 = (unsigned)ix < (unsigned)W, x1 = (unsigned)(ix + 1) < (unsigned)W;
+  const bool y0 = (unsigned)iy < (unsigned)H, y1 = (unsigned)(iy + 1) < (unsigned)H;
+  const uint8_t* p = src + ((ptrdiff_t)iy * W + ix) * C;
+  uint8_t* o = dst + ((size_t)y * W + x) * C;
+  for (int c = 0; c < C; c++) {
+    const int p00 = (x0 && y0) ? p[c] : 0, p01 = (x1 && y0) ? p[C + c] : 0;
+    const int p10 = (x0 && y1) ? p[(size_t)W * C + c] : 0, p11 = (x1 && y1) ? p[(size_t)W * C + C + c] : 0;
+    o[c] = (uint8_t)(((p00 * w00 + p01 * w01 + p10 * w10 + p11 * w11) * 32 + 16384) >> 15);
+  }
+}
+extern "C" __attribute__((visibility("default"))) int vfi_remap_flow_u8(vfi_handle* h, const uint8_t* src, const float* flow, double t, int H, int W,
+                                                                          int channels, uint8_t* dst, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!src || !flow || !dst || H < 1 || W < 1 || H > 65535 || channels < 1 || channels > 4) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  VFI_ENTER(h, stream);
+  cudaStream_t s = (cudaStream_t)stream;
+  ProfScope ps(h, PC_BLEND, s);
+  remap_flow_kernel<<<dim3(cdiv(W, 128), H), 128, 0, s>>>(src, reinterpret_cast<const float2*>(flow), (float)t, H, W, channels, dst);
+  VFI_LAUNCHED(h);
+  return VFI_OK;
+}

@@ -274,6 +274,19 @@ class Engine:
     def canny_density(self, gray, low=100, high=200):
         return self.canny(gray, low, high, want_edges=False)[1]
 
+    def remap_flow(self, img, flow, t):
+        """cv2.remap(img, x + flow[...,0]*t, y + flow[...,1]*t, INTER_LINEAR) on the device.  img (H,W,C) uint8, flow (H,W,2) f32."""
+        img = self._u8(img)
+        flow = flow.to(self.device, torch.float32).contiguous() if isinstance(flow, torch.Tensor) else \
+            torch.from_numpy(np.ascontiguousarray(flow, dtype=np.float32)).to(self.device)
+        H, W = img.shape[:2]
+        ch = img.shape[2] if img.dim() == 3 else 1
+        with torch.cuda.device(self.device):
+            out = torch.empty_like(img)
+            rc = self._lib.vfi_remap_flow_u8(self._h, _ptr(img), _ptr(flow), float(t), H, W, ch, _ptr(out), _stream())
+        self._check(rc, "vfi_remap_flow_u8")
+        return out
+
     def laplacian_var(self, rgb):
         rgb = self._u8(rgb)
         n, H, W, _ = rgb.shape

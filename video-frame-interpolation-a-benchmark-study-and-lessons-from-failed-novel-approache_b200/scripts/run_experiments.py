@@ -9,7 +9,8 @@ kernels -- the call sites that produced every published number of the study (SUR
                                     (vfi_ifnet_infer_ex with VFI_FLAG_BGR | VFI_FLAG_PAD_REFLECT_EDGE)
   adaptive_interpolate   :848-874   the evaluated "adaptive" method: 480x270 gray thumbnails -> calc_motion ->
                                     motion > thresh ? RIFE x3 : cv2.addWeighted x3
-  estimate_motion_complexity / mcar_tier :449-476, :479-520   MCAR score (mean/20, std/15, Canny edge density) and tiers
+  estimate_motion_complexity / mcar_interpolate(_cached) :449-537   MCAR score (mean/20, std/15, Canny edge density) and its
+                                    three tiers: addWeighted, cv2.remap flow warp + addWeighted (vfi_remap_flow_u8), RIFE
 
 Frames are BGR uint8 (H,W,3), as the runner holds them (cv2.VideoCapture order).  No CPU fallback.
 """
@@ -115,16 +116,16 @@ def adaptive_interpolate(prev, curr, motion_thresh: float, rife_scale: float = 0
     return [eng.add_weighted(a, 1 - t, b, t).cpu().numpy() for t in ts], False, motion
 
 
-def estimate_motion_complexity(prev_gray: np.ndarray, curr_gray: np.ndarray):
+def estimate_motion_complexity(prev_gray, curr_gray):
     """:449-476 -- (complexity in [0,1], flow).  Farneback + |flow| mean/std on the device; Canny edge density on the
     device (vfi_canny_density)."""
     eng = Engine.get(None)
-    flow, st = eng.farneback(prev_gray[None], curr_gray[None], pyr_scale=0.5, levels=1, winsize=15, iterations=1,
+    flow, st = eng.farneback(eng._u8(prev_gray)[None], eng._u8(curr_gray)[None], pyr_scale=0.5, levels=1, winsize=15, iterations=1,
                              poly_n=5, poly_sigma=1.1, want_flow=True, want_stats=True)
     mean, _, std = st[0].tolist()
     mean_motion = min(1.0, mean / 20.0)
     motion_var = min(1.0, std / 15.0)
-    edge_density = float(eng.canny_density(curr_gray[None], 100, 200)[0]) * 2.0
+    edge_density = float(eng.canny_density(eng._u8(curr_gray)[None], 100, 200)[0]) * 2.0
     complexity = min(1.0, 0.5 * mean_motion + 0.3 * motion_var + 0.2 * edge_density)
     return complexity, flow[0]
 
@@ -136,3 +137,25 @@ def mcar_tier(complexity: float, threshold_low: float = 0.3, threshold_high: flo
     if complexity < threshold_high:
         return 'flow'
     return 'rife'
+
+
+def mcar_interpolate_cached(prev, curr, t, complexity, flow, rife_scale=0.5, threshold_low=0.3, threshold_high=0.7):
+    """:513-537 -- one MCAR frame from a precomputed complexity and flow: (frame, tier).  flow: the device tensor
+    estimate_motion_complexity returned (or a host array)."""
+    eng = Engine.get(None)
+    tier = mcar_tier(complexity, threshold_low, threshold_high)
+    if tier == 'linear':
+        return eng.add_weighted(prev, 1 - t, curr, t).cpu().numpy(), tier
+    if tier == 'flow':
+        warped = eng.remap_flow(np.ascontiguousarray(prev), flow, t)
+        return eng.add_weighted(warped, 1 - t, curr, t).cpu().numpy(), tier
+    return rife_interpolate(prev, curr, t, rife_scale), tier
+
+
+def mcar_interpolate(prev, curr, t, rife_scale=0.5, threshold_low=0.3, threshold_high=0.7):
+    """:479-510 -- (frame, tier, complexity); the grays are cv2's BGR2GRAY computed on the device."""
+    eng = Engine.get(None)
+    g = eng.resize_gray(np.stack([prev, curr]), (prev.shape[1], prev.shape[0]), bgr=True)
+    complexity, flow = estimate_motion_complexity(g[0], g[1])
+    frame, tier = mcar_interpolate_cached(prev, curr, t, complexity, flow, rife_scale, threshold_low, threshold_high)
+    return frame, tier, complexity
