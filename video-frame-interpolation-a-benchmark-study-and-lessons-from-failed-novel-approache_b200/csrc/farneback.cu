@@ -101,15 +101,33 @@ __global__ void fb_blur_v_kernel(const float* __restrict__ A, float* __restrict_
   I[((size_t)blockIdx.z * h + y) * w + x] = t.a1 == 0.f ? v[0] : v[0] * t.a0 + v[1] * t.a1;
 }
 
+// Level 0 (no resize, 3-tap kernel): both passes in one launch, same operation order as fb_blur_h then fb_blur_v
+// (horizontal taps first, then vertical), so the plane is bit-identical; each thread reads its 3 x 3 gray bytes (L1 hits).
+__global__ void fb_blur3_kernel(const uint8_t* __restrict__ gray, float* __restrict__ I, int H, int W, float k0, float k1) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= W) return;
+  const uint8_t* g = gray + (size_t)blockIdx.z * H * W;
+  const int xl = refl101(x - 1, W), xr = refl101(x + 1, W);
+  float a[3];
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const uint8_t* row = g + (size_t)refl101(y - 1 + j, H) * W;
+    a[j] = k0 * (float)row[x] + k1 * ((float)row[xl] + (float)row[xr]);
+  }
+  I[((size_t)blockIdx.z * H + y) * W + x] = k0 * a[1] + k1 * (a[0] + a[2]);
+}
+
 // ---- polynomial expansion -----------------------------------------------------------------------------------------
 #define PE_TW 64
 #define PE_TH 16
+template <int PN>   // poly_n as a compile-time constant: the tile index divisions and the tap loops unroll
 __global__ void __launch_bounds__(256) fb_polyexp_kernel(const float* __restrict__ I, float* __restrict__ R, int h, int w, FbPoly P) {
-  __shared__ float src[PE_TH + 2 * FB_MAX_N][PE_TW + 2 * FB_MAX_N];
-  __shared__ float row[3][PE_TH][PE_TW + 2 * FB_MAX_N];
-  const int n = P.n, x0 = blockIdx.x * PE_TW, y0 = blockIdx.y * PE_TH;
+  __shared__ float src[PE_TH + 2 * PN][PE_TW + 2 * PN];
+  __shared__ float row[3][PE_TH][PE_TW + 2 * PN];
+  constexpr int n = PN;
+  const int x0 = blockIdx.x * PE_TW, y0 = blockIdx.y * PE_TH;
   const float* img = I + (size_t)blockIdx.z * h * w;
-  const int sw = PE_TW + 2 * n, sh = PE_TH + 2 * n;
+  constexpr int sw = PE_TW + 2 * n, sh = PE_TH + 2 * n;
   for (int e = threadIdx.x; e < sw * sh; e += blockDim.x) {
     const int ly = e / sw, lx = e - ly * sw;
     const int gy = min(max(y0 + ly - n, 0), h - 1), gx = min(max(x0 + lx - n, 0), w - 1);  // replicate, as OpenCV's row buffer
@@ -119,6 +137,7 @@ __global__ void __launch_bounds__(256) fb_polyexp_kernel(const float* __restrict
   for (int e = threadIdx.x; e < PE_TH * sw; e += blockDim.x) {
     const int ly = e / sw, lx = e - ly * sw;
     float t0 = src[ly + n][lx] * P.g[0], t1 = 0.f, t2 = 0.f;
+#pragma unroll
     for (int k = 1; k <= n; k++) {
       const float s0 = src[ly + n - k][lx], s1 = src[ly + n + k][lx], p = s0 + s1;
       t0 = t0 + P.g[k] * p;
@@ -135,6 +154,7 @@ __global__ void __launch_bounds__(256) fb_polyexp_kernel(const float* __restrict
     if (y0 + ly >= h || x0 + lx >= w) continue;
     const float g0 = P.g[0];
     double b1 = row[0][ly][x] * g0, b2 = 0, b3 = row[1][ly][x] * g0, b4 = 0, b5 = row[2][ly][x] * g0, b6 = 0;
+#pragma unroll
     for (int k = 1; k <= n; k++) {
       const float p0 = row[0][ly][x + k], m0 = row[0][ly][x - k], p1 = row[1][ly][x + k], m1 = row[1][ly][x - k];
       const float p2 = row[2][ly][x + k], m2 = row[2][ly][x - k];
@@ -157,14 +177,12 @@ __global__ void __launch_bounds__(256) fb_polyexp_kernel(const float* __restrict
 }
 
 // ---- FarnebackUpdateMatrices for one pixel ------------------------------------------------------------------------
-__device__ __forceinline__ void fb_matrix_px(const float* __restrict__ R0, const float* __restrict__ R1, size_t plane, int w,
-                                             int h, int x, int y, float dx, float dy, float* __restrict__ M) {
+__device__ __forceinline__ void fb_matrix_core(const float* __restrict__ R1, size_t plane, int w, int h, int x, int y, float dx, float dy,
+                                               float q0, float q1, float q2, float q3, float q4, float* __restrict__ m5) {
   float fx = (float)x + dx, fy = (float)y + dy;
   const int x1 = (int)floorf(fx), y1 = (int)floorf(fy);
   fx -= (float)x1; fy -= (float)y1;
-  const size_t o = (size_t)y * w + x;
   float r2, r3, r4, r5, r6;
-  const float q0 = R0[o], q1 = R0[o + plane], q2 = R0[o + 2 * plane], q3 = R0[o + 3 * plane], q4 = R0[o + 4 * plane];
   if ((unsigned)x1 < (unsigned)(w - 1) && (unsigned)y1 < (unsigned)(h - 1)) {
     const float a00 = (1.f - fx) * (1.f - fy), a01 = fx * (1.f - fy), a10 = (1.f - fx) * fy, a11 = fx * fy;
     const float* p = R1 + (size_t)y1 * w + x1;
@@ -191,23 +209,52 @@ __device__ __forceinline__ void fb_matrix_px(const float* __restrict__ R0, const
                         (y >= h - B ? border[h - y - 1] : 1.f);
     r2 *= scale; r3 *= scale; r4 *= scale; r5 *= scale; r6 *= scale;
   }
-  M[o] = r4 * r4 + r6 * r6;
-  M[o + plane] = (r4 + r5) * r6;
-  M[o + 2 * plane] = r5 * r5 + r6 * r6;
-  M[o + 3 * plane] = r4 * r2 + r6 * r3;
-  M[o + 4 * plane] = r6 * r2 + r5 * r3;
+  m5[0] = r4 * r4 + r6 * r6;
+  m5[1] = (r4 + r5) * r6;
+  m5[2] = r5 * r5 + r6 * r6;
+  m5[3] = r4 * r2 + r6 * r3;
+  m5[4] = r6 * r2 + r5 * r3;
 }
+__device__ __forceinline__ void fb_matrix_px(const float* __restrict__ R0, const float* __restrict__ R1, size_t plane, int w,
+                                             int h, int x, int y, float dx, float dy, float* __restrict__ M) {
+  const size_t o = (size_t)y * w + x;
+  float m5[5];
+  fb_matrix_core(R1, plane, w, h, x, y, dx, dy, R0[o], R0[o + plane], R0[o + 2 * plane], R0[o + 3 * plane], R0[o + 4 * plane], m5);
+#pragma unroll
+  for (int c = 0; c < 5; c++) M[o + c * plane] = m5[c];
+}
+// four adjacent pixels (x % 4 == 0, w % 4 == 0): the five coefficient planes of frame 0 come in and the five matrix planes go
+// out as 16-byte accesses (10 instead of 40 LSU instructions; the 20 bilinear taps per pixel stay scalar gathers)
+__device__ __forceinline__ void fb_matrix_px4(const float* __restrict__ R0, const float* __restrict__ R1, size_t plane, int w, int h,
+                                              int x, int y, const float2* fl4, float* __restrict__ M) {
+  const size_t o = (size_t)y * w + x;
+  float4 q[5], m[5];
+#pragma unroll
+  for (int c = 0; c < 5; c++) q[c] = *reinterpret_cast<const float4*>(R0 + o + c * plane);
+  float* mf = reinterpret_cast<float*>(m);
+  const float* qf = reinterpret_cast<const float*>(q);
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    float m5[5];
+    fb_matrix_core(R1, plane, w, h, x + i, y, fl4[i].x, fl4[i].y, qf[i], qf[4 + i], qf[8 + i], qf[12 + i], qf[16 + i], m5);
+#pragma unroll
+    for (int c = 0; c < 5; c++) mf[4 * c + i] = m5[c];
+  }
+#pragma unroll
+  for (int c = 0; c < 5; c++) *reinterpret_cast<float4*>(M + o + c * plane) = m[c];
+}
+
 
 // first UpdateMatrices of a level: flow = resize(previous level's flow, INTER_LINEAR) * (1 / pyr_scale), zero at the coarsest level
 __global__ void fb_matrices_kernel(const float* __restrict__ R, const float2* __restrict__ prev, int hp, int wp, float up,
-                                   float* __restrict__ M, int h, int w) {
+                                   float* __restrict__ M, int h, int w, double sx, double sy) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, pair = blockIdx.z;
   if (x >= w) return;
   const size_t plane = (size_t)h * w;
   float dx = 0.f, dy = 0.f;
   if (prev) {
     const float2* pf = prev + (size_t)pair * hp * wp;
-    const FTap tx = ftap(x, 1.0 / ((double)w / (double)wp), wp, true), ty = ftap(y, 1.0 / ((double)h / (double)hp), hp, false);
+    const FTap tx = ftap(x, sx, wp, true), ty = ftap(y, sy, hp, false);   // sx, sy = 1 / (w / wp), 1 / (h / hp): computed once on the host
     const float2 a = pf[(size_t)ty.s0 * wp + tx.s0], b = pf[(size_t)ty.s0 * wp + tx.s1];
     const float2 c = pf[(size_t)ty.s1 * wp + tx.s0], d = pf[(size_t)ty.s1 * wp + tx.s1];
     const float h0x = a.x * tx.a0 + b.x * tx.a1, h1x = c.x * tx.a0 + d.x * tx.a1;
@@ -330,6 +377,16 @@ __global__ void fb_matrices_flow_kernel(const float* __restrict__ R, const float
   const float2 f = flow[(size_t)pair * plane + (size_t)y * w + x];
   const float* R0 = R + (size_t)(2 * pair) * 5 * plane;
   fb_matrix_px(R0, R0 + 5 * plane, plane, w, h, x, y, f.x, f.y, M + (size_t)pair * 5 * plane);
+}
+__global__ void fb_matrices_flow4_kernel(const float* __restrict__ R, const float2* __restrict__ flow, float* __restrict__ M, int h, int w) {
+  const int x = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y, pair = blockIdx.z;
+  if (x >= w) return;
+  const size_t plane = (size_t)h * w;
+  const float4* fp = reinterpret_cast<const float4*>(flow + (size_t)pair * plane + (size_t)y * w + x);
+  const float4 fa = fp[0], fb = fp[1];
+  const float2 fl4[4] = {make_float2(fa.x, fa.y), make_float2(fa.z, fa.w), make_float2(fb.x, fb.y), make_float2(fb.z, fb.w)};
+  const float* R0 = R + (size_t)(2 * pair) * 5 * plane;
+  fb_matrix_px4(R0, R0 + 5 * plane, plane, w, h, x, y, fl4, M + (size_t)pair * 5 * plane);
 }
 static int fb_variant() {
   static int v = -1;
@@ -465,13 +522,20 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
         const int w = cv_round(W * scale), hh = cv_round(H * scale);
         FbKern kk;
         gaussian_kernel(smooth, sigma, kk);
-        fb_blur_h_kernel<<<dim3(cdiv(w, 128), H, 2 * nn), 128, 0, s>>>(gray, A, H, W, w, 1.0 / ((double)w / (double)W), kk);
+        if (w == W && hh == H && kk.r == 1 && fb_variant() != 9) {
+          fb_blur3_kernel<<<dim3(cdiv(W, 128), H, 2 * nn), 128, 0, s>>>(gray, I, H, W, kk.k[0], kk.k[1]);
+          VFI_LAUNCHED(h);
+        } else {
+          fb_blur_h_kernel<<<dim3(cdiv(w, 128), H, 2 * nn), 128, 0, s>>>(gray, A, H, W, w, 1.0 / ((double)w / (double)W), kk);
+          VFI_LAUNCHED(h);
+          fb_blur_v_kernel<<<dim3(cdiv(w, 128), hh, 2 * nn), 128, 0, s>>>(A, I, H, hh, w, 1.0 / ((double)hh / (double)H), kk);
+          VFI_LAUNCHED(h);
+        }
+        if (poly_n == 5) fb_polyexp_kernel<5><<<dim3(cdiv(w, PE_TW), cdiv(hh, PE_TH), 2 * nn), 256, 0, s>>>(I, R, hh, w, P);
+        else fb_polyexp_kernel<7><<<dim3(cdiv(w, PE_TW), cdiv(hh, PE_TH), 2 * nn), 256, 0, s>>>(I, R, hh, w, P);
         VFI_LAUNCHED(h);
-        fb_blur_v_kernel<<<dim3(cdiv(w, 128), hh, 2 * nn), 128, 0, s>>>(A, I, H, hh, w, 1.0 / ((double)hh / (double)H), kk);
-        VFI_LAUNCHED(h);
-        fb_polyexp_kernel<<<dim3(cdiv(w, PE_TW), cdiv(hh, PE_TH), 2 * nn), 256, 0, s>>>(I, R, hh, w, P);
-        VFI_LAUNCHED(h);
-        fb_matrices_kernel<<<dim3(cdiv(w, 128), hh, nn), 128, 0, s>>>(R, prev, hp, wp, (float)(1. / pyr_scale), M0, hh, w);
+        fb_matrices_kernel<<<dim3(cdiv(w, 128), hh, nn), 128, 0, s>>>(R, prev, hp, wp, (float)(1. / pyr_scale), M0, hh, w,
+                                                                      prev ? 1.0 / ((double)w / (double)wp) : 1.0, prev ? 1.0 / ((double)hh / (double)hp) : 1.0);
         VFI_LAUNCHED(h);
         float* Mi = M0;
         float* Mo = M1;
@@ -489,7 +553,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
             else bs_launch<8, 8, false>(grid, s, Mi, R, nullptr, last ? cur : tmpf, hh, w, m, rps);
             if (!last) {
               VFI_LAUNCHED(h);
-              fb_matrices_flow_kernel<<<dim3(cdiv(w, 128), hh, nn), 128, 0, s>>>(R, tmpf, Mo, hh, w);
+              if ((w & 3) == 0 && var == 0) fb_matrices_flow4_kernel<<<dim3(cdiv(w / 4, 64), hh, nn), 64, 0, s>>>(R, tmpf, Mo, hh, w);
+              else fb_matrices_flow_kernel<<<dim3(cdiv(w, 128), hh, nn), 128, 0, s>>>(R, tmpf, Mo, hh, w);
             }
           } else if (var == 2) bs_launch<4, 4, true>(grid, s, Mi, R, last ? nullptr : Mo, last ? cur : nullptr, hh, w, m, rps);
           else if (var == 3) bs_launch<4, 8, true>(grid, s, Mi, R, last ? nullptr : Mo, last ? cur : nullptr, hh, w, m, rps);
