@@ -43,7 +43,7 @@ def peaks():
 def ncu_traffic(pattern):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes, average over the step's launches whose kernel name
     matches `pattern`) from the newest committed ncu launch list of this workload (profiles/r0N_launches_final.txt:
-    one 8-pair x 3-timestep 1080p step); None if no such file."""
+    one step of the default batch, 30 pairs x 3 timesteps of 1080p frames); None if no such file."""
     import glob
     import re
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r0*_launches_final.txt")))
@@ -319,7 +319,7 @@ def rife_roofline(eng, step, psteps, B, T, Hp, Wp, n_images, with_traffic):
                           "design_what": "what this design moves: RGBX taps of both frames 8, blocks 0-3 flow (fp32) 16, last "
                                          "block's flow delta + mask (fp16 texel) 16, u8 out 3"})
     hbm_entry("gather_conv0a", 8 + 16 + 8.5 + 1.5 + 16 + 8, "RGBX taps 8, Head feature taps 16, block-3 planes 8.5 "
-              "(34 B / 4 px), coarser flows 1.5, summed flow out 16, conv0[0] output 8 (32 B / 4 px)", r"gather_conv0a_kernel")
+              "(34 B / 4 px), coarser flows 1.5, summed flow out 16, conv0[0] output 8 (32 B / 4 px)", r"gather_conv0a(_p)?_kernel")
     hbm_entry("gather", (8 + 16 + 3 + 16) + (8 + 16 + 2 + 16) / 4.0 + (8 + 16 + 2 + 16) / 16.0 + 1,
               "blocks 0-3: taps + coarse inputs + 64 B per output pixel of the block input (s = 2: every pixel "
               "sampled; s = 4, 8, 16: 1/4, 1/16, 1/64 of them)", r"gather_(s2|lo|tile)?_?kernel")
