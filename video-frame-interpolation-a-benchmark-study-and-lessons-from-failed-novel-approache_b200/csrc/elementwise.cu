@@ -1205,9 +1205,8 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
   const int kl = lows.n - 1;  // finest coarse level: mask / feat come from it (16-channel texels: c4 == 4)
   int tile = blockIdx.x;
   // stage tile `t` (flow rows + the mask / feat tap tables) with the NT threads whose ids are tid = 0 .. NT-1
-  auto stage = [&](int t, auto nt_tag, int tid) {
+  auto stage = [&](int tx, int ty, int nn, auto nt_tag, int tid) {
     constexpr int NT = decltype(nt_tag)::value;
-    const int tx = t % tiles_x, ty = (t / tiles_x) % tiles_y, nn = t / (tiles_x * tiles_y);
     flat_stage<GC_TW, NT>(lows, grows, nn, tx * TL_W - 1, ty * TL_H - 1, Hp, Wp, tl_sm, tid);
     if (tid >= NT - 2 * GC_TW) {
       const int e = tid - (NT - 2 * GC_TW), ax = e / GC_TW, j = e - ax * GC_TW;
@@ -1215,7 +1214,11 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
       reinterpret_cast<int4*>(&mtab[ax][j])[0] = __ldg(reinterpret_cast<const int4*>(src));
     }
   };
-  if (tile < num_tiles) stage(tile, std::integral_constant<int, GC_THREADS>{}, (int)threadIdx.x);
+  // tile -> (tx, ty, n) once; afterwards the mixed-radix coordinates advance by the (decomposed) grid stride: no integer
+  // divisions in the loop (they were 6 % of the kernel's instructions)
+  int ctx = tile % tiles_x, cty = (tile / tiles_x) % tiles_y, cn = tile / (tiles_x * tiles_y);
+  const int g = (int)gridDim.x, gsx = g % tiles_x, gsy = (g / tiles_x) % tiles_y, gsn = g / (tiles_x * tiles_y);
+  if (tile < num_tiles) stage(ctx, cty, cn, std::integral_constant<int, GC_THREADS>{}, (int)threadIdx.x);
   fence_async_smem();
   tc_before();
   __syncthreads();
@@ -1225,8 +1228,12 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
   const uint32_t* img32 = reinterpret_cast<const uint32_t*>(imgs);
   const int mWl = lows.Wl[kl];
   const bf16 *mfp = lows.mf[kl], *f7p = lows.f7[kl];
-  for (int it = 0; tile < num_tiles; tile += gridDim.x, it++) {
-    const int tx0 = (tile % tiles_x) * TL_W, ty0 = ((tile / tiles_x) % tiles_y) * TL_H, n = tile / (tiles_x * tiles_y);
+  for (int it = 0; tile < num_tiles; tile += g, it++) {
+    const int tx0 = ctx * TL_W, ty0 = cty * TL_H, n = cn;
+    // the next tile of this CTA
+    ctx += gsx; cty += gsy; cn += gsn;
+    if (ctx >= tiles_x) { ctx -= tiles_x; cty++; }
+    if (cty >= tiles_y) { cty -= tiles_y; cn++; }
     const int b = n / Tn;
     const float t = tsteps[n - b * Tn];
     const int base0 = b * plane, base1 = (I1 + b) * plane;
@@ -1331,7 +1338,7 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
       }
     }
     if (warp >= 4 && tile + (int)gridDim.x < num_tiles)
-      stage(tile + (int)gridDim.x, std::integral_constant<int, GC_THREADS - 128>{}, (int)threadIdx.x - 128);
+      stage(ctx, cty, cn, std::integral_constant<int, GC_THREADS - 128>{}, (int)threadIdx.x - 128);
     tc_before();
     __syncthreads();               // next tile staged; this tile's MMAs complete (the epilogue waited for them), TMEM read out
     tc_after();
