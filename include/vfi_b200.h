@@ -125,6 +125,19 @@ int vfi_psnr_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t
  * are finished on the host with the reference's own expressions.                                                        */
 int vfi_moments_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t elems, long long* out, void* stream);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that may not call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as
+ * vfi_psnr_u8, but the per-pair SSE accumulators live in a static __device__ array inside the library instead of the
+ * handle's cudaMalloc'd scratch: the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   limit  : n <= VFI_NOALLOC_MAX_PAIRS frame pairs per call (32 KB of device memory held by every GPU that loads the
+ *            library, until exit); larger n is rejected with VFI_E_ARG -- split the call or use vfi_psnr_u8.
+ *   sharing: every call on a device uses the same array, which keeps the previous call's sums; each call clears the entries
+ *            it uses on `stream` first.  Calls that overlap on the GPU (different streams without ordering) race: serialise them.
+ *   set-up : the array's device address is looked up once per device on the first call (make that call outside a capture). */
+#define VFI_NOALLOC_MAX_PAIRS 4096
+int vfi_psnr_u8_noalloc(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t elems,
+                        unsigned long long* sse_out, double* psnr_out, void* stream);
+
 /* compute_ssim_simple (evaluation/metrics.py:318-335; skimage structural_similarity on the
  * cv2 gray images, 7x7 uniform window) when downscale == 1; AdaptiveRouter.detect_scene_change's
  * score (adaptive_pipeline.py:140-160: gray, x0.25 INTER_LINEAR, SSIM) when downscale == 4.

@@ -12,6 +12,7 @@ FLAG_BGR, FLAG_PAD_REFLECT_EDGE = 1, 2
 ROUTE_RIFE, ROUTE_VFIMAMBA, ROUTE_SCENE_CHANGE = 0, 1, 2
 ROUTE_NAMES = ("rife", "vfimamba", "scene_change")
 IFNET_PARAMS = 5664776
+NOALLOC_MAX_PAIRS = 4096
 PROFILE_CLASSES = ("pad", "head_cnn0", "conv_tcgen05", "conv_direct", "deconv_direct", "gather", "gather_conv0a",
                    "warp_blend", "reduce", "misc")
 
@@ -34,6 +35,7 @@ SIGNATURES = {
     "vfi_remap_flow_u8": (_i, [_vp, _vp, _vp, _d, _i, _i, _i, _vp, _vp]),
     "vfi_warp_blend": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "vfi_psnr_u8": (_i, [_vp, _vp, _vp, _i, _sz, _vp, _vp, _vp]),
+    "vfi_psnr_u8_noalloc": (_i, [_vp, _vp, _vp, _i, _sz, _vp, _vp, _vp]),
     "vfi_ssim_gray_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "vfi_psnr_ssim_u8": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "vfi_flow_stats": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp]),

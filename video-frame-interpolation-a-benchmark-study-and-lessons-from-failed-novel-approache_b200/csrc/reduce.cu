@@ -1328,3 +1328,60 @@ extern "C" __attribute__((visibility("default"))) int vfi_remap_flow_u8(vfi_hand
   VFI_LAUNCHED(h);
   return VFI_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// vfi_psnr_u8 without any allocation (no counterpart in the reference).
+// vfi_psnr_u8 keeps its per-pair SSE accumulators in the handle's cudaMalloc'd scratch (vfi_red_reserve); callers that may
+// not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) use this variant instead: the
+// accumulators live in a file-scope __device__ array of VFI_NOALLOC_MAX_PAIRS entries (32 KB, held by every GPU that loads the
+// library until exit).  In HOST code `g_noalloc_sse` is only a stand-in for the symbol, not a device address: the address is
+// resolved once per device, with that device current, by cudaGetSymbolAddress and cached.  Every call shares the array and
+// finds the previous call's sums in it: the entries it uses are cleared first (cudaMemsetAsync on `stream`), and calls that
+// overlap on the GPU (different streams, no ordering) race on it.
+static __device__ __align__(256) unsigned long long g_noalloc_sse[VFI_NOALLOC_MAX_PAIRS];
+static unsigned long long* g_noalloc_ptr[64] = {nullptr};   // per device: the array's DEVICE address
+
+extern "C" __attribute__((visibility("default"))) int vfi_psnr_u8_noalloc(vfi_handle* h, const uint8_t* a, const uint8_t* b, int n, size_t elems,
+                                                                            unsigned long long* sse_out, double* psnr_out, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!a || !b || n < 1 || elems < 1 || (!sse_out && !psnr_out)) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  if (n > VFI_NOALLOC_MAX_PAIRS)
+    VFI_FAIL(h, VFI_E_ARG, "vfi_psnr_u8_noalloc: %d frame pairs exceed the static scratch of %d; split the call or use vfi_psnr_u8", n,
+             VFI_NOALLOC_MAX_PAIRS);
+  if (h->device < 0 || h->device >= 64) VFI_FAIL(h, VFI_E_ARG, "device index %d out of range", h->device);
+  // the handle's device current for the call, the caller's restored afterwards; the handle's own scratch is not touched, so
+  // none of its cross-stream ordering is needed
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+  if (prev != h->device && cudaSetDevice(h->device) != cudaSuccess) { cudaGetLastError(); VFI_FAIL(h, VFI_E_CUDA, "cudaSetDevice(%d) failed", h->device); }
+  int rc = VFI_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned long long* acc = g_noalloc_ptr[h->device];
+  if (!acc) {   // set-up, once per device (do the first call outside a graph capture)
+    const cudaError_t e = cudaGetSymbolAddress((void**)&acc, g_noalloc_sse);
+    if (e != cudaSuccess || !acc) {
+      cudaGetLastError();
+      char msg[256];
+      snprintf(msg, sizeof(msg), "cudaGetSymbolAddress(g_noalloc_sse) failed: %s", cudaGetErrorString(e));
+      h->err = msg;
+      rc = VFI_E_CUDA;
+    } else {
+      g_noalloc_ptr[h->device] = acc;
+    }
+  }
+  if (rc == VFI_OK) {
+    cudaError_t e = cudaMemsetAsync(acc, 0, (size_t)n * sizeof(unsigned long long), s);   // the last call's sums are still there
+    if (e == cudaSuccess) {
+      int bx = (int)std::min<size_t>(PSNR_BLOCKS_PER_FRAME, (elems / 16 + 255) / 256 + 1);
+      if (n >= 64) bx = std::min(bx, 32);
+      psnr_sse_kernel<<<dim3(bx, n), 256, 0, s>>>(a, b, elems, acc);
+      h->launches++;
+      psnr_finish_kernel<<<cdiv(n, 128), 128, 0, s>>>(acc, elems, n, sse_out, psnr_out);
+      h->launches++;
+      e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) { h->err = std::string("vfi_psnr_u8_noalloc: ") + cudaGetErrorString(e); rc = VFI_E_CUDA; }
+  }
+  if (prev >= 0 && prev != h->device) cudaSetDevice(prev);
+  return rc;
+}

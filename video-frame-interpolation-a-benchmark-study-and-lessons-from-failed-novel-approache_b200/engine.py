@@ -176,6 +176,17 @@ class Engine:
         self._check(rc, "vfi_psnr_u8")
         return sse, ps
 
+    def psnr_sse_noalloc(self, a, b, sse_out, psnr_out=None):
+        """vfi_psnr_u8_noalloc: vfi_psnr_u8 with the accumulators in the library's static device array -- nothing is
+        allocated, here or in the library.  a, b: contiguous uint8 CUDA tensors (n, ...) on this device; sse_out (n,) int64 and
+        psnr_out (n,) float64 (optional) are the caller's CUDA tensors.  n <= _abi.NOALLOC_MAX_PAIRS; overlapping calls race."""
+        for t in (a, b, sse_out) + ((psnr_out,) if psnr_out is not None else ()):
+            if not (isinstance(t, torch.Tensor) and t.is_cuda and t.is_contiguous()):
+                raise TypeError("psnr_sse_noalloc takes contiguous CUDA tensors (it does not copy or allocate)")
+        rc = self._lib.vfi_psnr_u8_noalloc(self._h, _ptr(a), _ptr(b), a.shape[0], a[0].numel(), _ptr(sse_out), _ptr(psnr_out),
+                                           _stream())
+        self._check(rc, "vfi_psnr_u8_noalloc")
+
     def moments(self, a, b):
         """Exact global moments per pair: (n,5) int64 = sum a, sum b, sum a^2, sum b^2, sum ab over every byte."""
         a, b = self._u8(a), self._u8(b)
