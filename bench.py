@@ -678,6 +678,11 @@ def main():
     ms_e2e = cx.timed(step_e2e, e2e_steps, 3, after=streamer.join)   # ends when the last result has reached pinned host memory
     e2e = world * frames_per_step * e2e_steps / (ms_e2e / 1000.0)
     del streamer
+    # the same leg with the optional planar YUV 4:2:0 result format (half the device -> host bytes): secondary figure
+    streamer = model.clip_streamer(B, H, W, TIMESTEPS, depth=e2e_depth, output="yuv420")
+    ms_yuv = cx.timed(step_e2e, e2e_steps, 3, after=streamer.join)
+    e2e_yuv = world * frames_per_step * e2e_steps / (ms_yuv / 1000.0)
+    del streamer
 
     # ---- the other BASELINE.json configs, sharded over the same ranks ----
     other = {}
@@ -717,6 +722,9 @@ def main():
                        "l2_policy": "inputs+activations per step (>1 GB) exceed the 126 MB L2; batches rotate through the pool"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int((B + 1) * H * W * 3),
                     "d2h_bytes_per_step": int(B * T * H * W * 3), "steps": e2e_steps,
+                    "yuv420_output": {"value": e2e_yuv, "unit": UNIT, "d2h_bytes_per_step": int(B * T * H * W * 3 // 2),
+                                      "what": "same call with clip_streamer(output='yuv420'): results come down as cv2-exact I420 frames "
+                                              "(1.5 B/px); the RGB figure above is the headline (the reference's result format)"},
                     "api": "RIFEModel.clip_streamer().submit (B+1 pinned host uint8 frames in, B x T pinned host uint8 frames out per step; upload / kernels / download on three streams, %d slots)" % e2e_depth},
             "gpu_launches": int(launches),
             "clocks": sampler.summary(),

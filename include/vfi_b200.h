@@ -187,6 +187,13 @@ int vfi_add_weighted_u8(vfi_handle* h, const uint8_t* a, const uint8_t* b, size_
 int vfi_canny_u8(vfi_handle* h, const uint8_t* gray, int n, int H, int W, double low, double high,
                  uint8_t* edges_out, double* density_out, void* stream);
 
+/* Optional planar YUV 4:2:0 (I420) RESULT format: cv2.cvtColor(frame, COLOR_RGB2YUV_I420) (COLOR_BGR2YUV_I420 when bgr != 0),
+ * bit-exact (BT.601 limited range, chroma of the top-left pixel of each 2 x 2 block).  The experiment runner hands every
+ * interpolated frame to a libx264 encoder (scripts/run_experiments.py:861-868 `ff_proc.stdin.write(mid.tobytes())`), which
+ * converts to yuv420p; converting on the device halves the device -> host bytes of an interpolated frame (1.5 B/px, not 3).
+ *   src: n x H x W x 3 uint8 (H, W even); dst: n x (H*3/2) x W uint8 = per frame Y (H x W), U (H/2 x W/2), V (H/2 x W/2). */
+int vfi_rgb_to_yuv420_u8(vfi_handle* h, const uint8_t* src, int n, int H, int W, int bgr, uint8_t* dst, void* stream);
+
 /* MCAR tier 2, scripts/run_experiments.py:498-503 / :526-531: cv2.remap(src, x + flow_x * t, y + flow_y * t, cv2.INTER_LINEAR)
  * for a uint8 image (H x W x channels, BORDER_CONSTANT 0) and a dense flow field (H x W x 2 float, e.g. vfi_farneback's
  * flow_out); OpenCV's 5-bit fixed-point bilinear path, bit-exact.  Follow with vfi_add_weighted_u8(dst, 1-t, curr, t). */

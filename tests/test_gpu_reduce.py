@@ -157,3 +157,25 @@ def test_warp_blend_vs_oracle(engine, H, W):
     want = want[0].permute(1, 2, 0).numpy()
     assert float(np.abs(of[0].cpu().numpy() - want).max()) <= 2e-5
     assert np.abs(out[0].cpu().numpy().astype(int) - (want * 255).clip(0, 255).astype(np.uint8).astype(int)).max() <= 1
+
+
+@pytest.mark.parametrize("H,W", [(1080, 1920), (360, 640), (6, 10), (270, 482), (2, 2)])
+def test_yuv420_bit_exact_vs_cv2(engine, H, W):
+    """vfi_rgb_to_yuv420_u8 = cv2.cvtColor(COLOR_RGB2YUV_I420 / COLOR_BGR2YUV_I420), bit for bit (aligned fast path: W % 4 == 0;
+    byte path otherwise)."""
+    rgb = np.random.default_rng(H + W).integers(0, 256, (3, H, W, 3), dtype=np.uint8)
+    got = engine.to_yuv420(rgb).cpu().numpy()
+    assert got.shape == (3, H * 3 // 2, W)
+    for i in range(3):
+        assert np.array_equal(got[i], cv2.cvtColor(rgb[i], cv2.COLOR_RGB2YUV_I420))
+    assert np.array_equal(engine.to_yuv420(rgb[0], bgr=True).cpu().numpy(), cv2.cvtColor(rgb[0], cv2.COLOR_BGR2YUV_I420))
+    ext = np.zeros((2, H, W, 3), np.uint8)
+    ext[1] = 255                                                        # black / white: Y 16 / 235, chroma 128
+    e = engine.to_yuv420(ext).cpu().numpy()
+    assert e[0, :H].max() == 16 and e[1, :H].min() == 235 and (e[:, H:] == 128).all()
+
+
+def test_yuv420_rejects_odd_sizes(engine):
+    from vfi_b200 import _abi
+    with pytest.raises(_abi.VFIError, match="even frame sizes"):
+        engine.to_yuv420(np.zeros((1, 5, 8, 3), np.uint8))

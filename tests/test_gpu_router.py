@@ -265,3 +265,25 @@ def test_evaluate_sharded_sums(engine):
     parts = [M.evaluate_range(lambda a, b: pred[a:b], lambda a, b: fr[a:b], *M_range, 3) for M_range in ((0, 4), (4, 8), (8, 11))]
     tot = np.sum(np.array(parts), axis=0)
     assert tot[2] == 11 and tot[3] == 1 and int(tot[4]) == sse and abs(tot[1] - whole["ssim_sum"]) < 1e-9
+
+
+def test_clip_streamer_yuv420_output():
+    """output='yuv420': every result frame is cv2's I420 conversion of the RGB result, at half the download bytes."""
+    import cv2
+    m = RIFEModel()
+    m.load()
+    ts = [0.25, 0.5, 0.75]
+    clip = gen_clip(6, 96, 160, seed=12, cut_every=0, fast=None)
+    host = torch.from_numpy(clip).pin_memory()
+    rgb = m.clip_streamer(pairs=3, H=96, W=160, timestamps=ts)
+    yuv = m.clip_streamer(pairs=3, H=96, W=160, timestamps=ts, output="yuv420")
+    assert yuv.d2h_bytes * 2 == rgb.d2h_bytes
+    for b in range(2):
+        want = rgb.result(rgb.submit(host[3 * b:3 * b + 4])).numpy().copy()
+        got = yuv.result(yuv.submit(host[3 * b:3 * b + 4])).numpy()
+        assert got.shape == (3, 3, 144, 160)
+        for p in range(3):
+            for k in range(3):
+                assert np.array_equal(got[p, k], cv2.cvtColor(want[p, k], cv2.COLOR_RGB2YUV_I420))
+    with pytest.raises(ValueError):
+        m.clip_streamer(pairs=1, H=95, W=160, timestamps=ts, output="yuv420")

@@ -33,6 +33,7 @@ SIGNATURES = {
     "vfi_add_weighted_u8": (_i, [_vp, _vp, _vp, _sz, _d, _d, _vp, _vp]),
     "vfi_canny_u8": (_i, [_vp, _vp, _i, _i, _i, _d, _d, _vp, _vp, _vp]),
     "vfi_remap_flow_u8": (_i, [_vp, _vp, _vp, _d, _i, _i, _i, _vp, _vp]),
+    "vfi_rgb_to_yuv420_u8": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "vfi_warp_blend": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "vfi_psnr_u8": (_i, [_vp, _vp, _vp, _i, _sz, _vp, _vp, _vp]),
     "vfi_psnr_u8_noalloc": (_i, [_vp, _vp, _vp, _i, _sz, _vp, _vp, _vp]),

@@ -1330,6 +1330,77 @@ extern "C" __attribute__((visibility("default"))) int vfi_remap_flow_u8(vfi_hand
 }
 
 // ---------------------------------------------------------------------------------------------
+// Planar YUV 4:2:0 (I420) result format: cv2.cvtColor(frame, COLOR_RGB2YUV_I420 / COLOR_BGR2YUV_I420) restated exactly
+// (OpenCV imgproc color_yuv: ITU-R BT.601 limited range, 20-bit fixed point, chroma taken from the TOP-LEFT pixel of each
+// 2 x 2 block, no averaging; pinned against cv2 4.13 by tests/test_gpu_reduce.py).  1.5 bytes per pixel instead of 3: the
+// format the experiment runner's encoder wants (scripts/run_experiments.py pipes raw frames into libx264, which converts to
+// yuv420p), and half the device -> host bytes of the end-to-end path, which is host-link bound at 4 and 8 GPUs per box.
+// Layout per frame, as cv2 returns it: (H * 3 / 2) x W bytes = Y plane H x W, U plane (H/2) x (W/2), V plane (H/2) x (W/2).
+#define YUV_SHIFT 20
+__device__ __forceinline__ int yuv_y(int r, int g, int b) { return (269484 * r + 528482 * g + 102760 * b + (16 << YUV_SHIFT) + (1 << (YUV_SHIFT - 1))) >> YUV_SHIFT; }
+__device__ __forceinline__ int yuv_u(int r, int g, int b) { return (-155188 * r - 305135 * g + 460324 * b + (128 << YUV_SHIFT) + (1 << (YUV_SHIFT - 1))) >> YUV_SHIFT; }
+__device__ __forceinline__ int yuv_v(int r, int g, int b) { return (460324 * r - 385875 * g - 74448 * b + (128 << YUV_SHIFT) + (1 << (YUV_SHIFT - 1))) >> YUV_SHIFT; }
+// FAST (W % 4 == 0, 4-byte aligned frames): a thread converts 4 x 2 pixels from six aligned 32-bit words into two 32-bit
+// luma stores and one 16-bit store per chroma plane; otherwise a thread converts one 2 x 2 block with byte accesses.
+template <bool FAST, bool BGR>
+__global__ void rgb_to_i420_kernel(const uint8_t* __restrict__ src, int H, int W, uint8_t* __restrict__ dst) {
+  const int f = blockIdx.z, y = (blockIdx.y * blockDim.y + threadIdx.y) * 2;
+  const int x = (blockIdx.x * blockDim.x + threadIdx.x) * (FAST ? 4 : 2);
+  if (x >= W || y >= H) return;
+  const uint8_t* img = src + (size_t)f * H * W * 3;
+  uint8_t* Y = dst + (size_t)f * H * W * 3 / 2;
+  uint8_t* U = Y + (size_t)H * W;
+  uint8_t* V = U + (size_t)(H / 2) * (W / 2);
+  constexpr int NP = FAST ? 4 : 2;
+  int uu[NP / 2], vv[NP / 2];
+#pragma unroll
+  for (int j = 0; j < 2; j++) {
+    uint32_t px[NP];
+    const uint8_t* row = img + ((size_t)(y + j) * W + x) * 3;
+    if (FAST) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(row);
+      const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+      px[0] = w0; px[1] = __byte_perm(w0, w1, 0x0543); px[2] = __byte_perm(w1, w2, 0x0432); px[NP - 1] = w2 >> 8;
+    } else {
+#pragma unroll
+      for (int i = 0; i < NP; i++) px[i] = (uint32_t)row[3 * i] | ((uint32_t)row[3 * i + 1] << 8) | ((uint32_t)row[3 * i + 2] << 16);
+    }
+    uint32_t yw = 0;
+#pragma unroll
+    for (int i = 0; i < NP; i++) {
+      const int c0 = px[i] & 0xff, c1 = (px[i] >> 8) & 0xff, c2 = (px[i] >> 16) & 0xff;
+      const int r = BGR ? c2 : c0, b = BGR ? c0 : c2;
+      yw |= (uint32_t)yuv_y(r, c1, b) << (8 * i);
+      if (j == 0 && (i & 1) == 0) { uu[i / 2] = yuv_u(r, c1, b); vv[i / 2] = yuv_v(r, c1, b); }
+    }
+    uint8_t* yo = Y + (size_t)(y + j) * W + x;
+    if (FAST) *reinterpret_cast<uint32_t*>(yo) = yw;
+    else { yo[0] = (uint8_t)(yw & 0xff); yo[1] = (uint8_t)(yw >> 8); }
+  }
+  const size_t co = (size_t)(y / 2) * (W / 2) + x / 2;
+  if (FAST) {
+    *reinterpret_cast<uint16_t*>(U + co) = (uint16_t)(uu[0] | (uu[NP / 2 - 1] << 8));
+    *reinterpret_cast<uint16_t*>(V + co) = (uint16_t)(vv[0] | (vv[NP / 2 - 1] << 8));
+  } else { U[co] = (uint8_t)uu[0]; V[co] = (uint8_t)vv[0]; }
+}
+extern "C" __attribute__((visibility("default"))) int vfi_rgb_to_yuv420_u8(vfi_handle* h, const uint8_t* src, int n, int H, int W, int bgr,
+                                                                             uint8_t* dst, void* stream) {
+  if (!h) return VFI_E_ARG;
+  if (!src || !dst || n < 1 || n > 65535 || H < 2 || W < 2) VFI_FAIL(h, VFI_E_ARG, "bad argument");
+  if ((H & 1) || (W & 1)) VFI_FAIL(h, VFI_E_ARG, "4:2:0 needs even frame sizes, got %dx%d", H, W);
+  VFI_ENTER(h, stream);
+  cudaStream_t s = (cudaStream_t)stream;
+  ProfScope ps(h, PC_MISC, s);
+  // per-frame plane offsets stay 4-byte aligned when H * W * 3 / 2 is a multiple of 4: W % 4 == 0 and H even
+  const bool fast = (W & 3) == 0 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 3) == 0;
+  const dim3 block(32, 4), grid(cdiv(W / (fast ? 4 : 2), 32), cdiv(H / 2, 4), n);
+  if (fast) { if (bgr) rgb_to_i420_kernel<true, true><<<grid, block, 0, s>>>(src, H, W, dst); else rgb_to_i420_kernel<true, false><<<grid, block, 0, s>>>(src, H, W, dst); }
+  else { if (bgr) rgb_to_i420_kernel<false, true><<<grid, block, 0, s>>>(src, H, W, dst); else rgb_to_i420_kernel<false, false><<<grid, block, 0, s>>>(src, H, W, dst); }
+  VFI_LAUNCHED(h);
+  return VFI_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // vfi_psnr_u8 without any allocation (no counterpart in the reference).
 // vfi_psnr_u8 keeps its per-pair SSE accumulators in the handle's cudaMalloc'd scratch (vfi_red_reserve); callers that may
 // not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) use this variant instead: the

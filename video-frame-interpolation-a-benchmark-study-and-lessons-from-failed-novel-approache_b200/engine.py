@@ -298,6 +298,18 @@ class Engine:
         self._check(rc, "vfi_remap_flow_u8")
         return out
 
+    def to_yuv420(self, frames, bgr=False, out=None):
+        """cv2.cvtColor(f, COLOR_RGB2YUV_I420) of every frame on the device.  frames: (..., H, W, 3) uint8 -> (..., H*3//2, W)."""
+        frames = self._u8(frames)
+        H, W = frames.shape[-3], frames.shape[-2]
+        n = frames.numel() // (H * W * 3)
+        with torch.cuda.device(self.device):
+            if out is None:
+                out = torch.empty(tuple(frames.shape[:-3]) + (H * 3 // 2, W), dtype=torch.uint8, device=self.device)
+            rc = self._lib.vfi_rgb_to_yuv420_u8(self._h, _ptr(frames), n, H, W, 1 if bgr else 0, _ptr(out), _stream())
+        self._check(rc, "vfi_rgb_to_yuv420_u8")
+        return out
+
     def laplacian_var(self, rgb):
         rgb = self._u8(rgb)
         n, H, W, _ = rgb.shape

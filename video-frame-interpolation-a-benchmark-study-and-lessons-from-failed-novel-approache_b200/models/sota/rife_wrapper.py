@@ -175,10 +175,11 @@ class RIFEModel(BaseModel):
         out = self._engine.infer(frames0, frames1, list(timestamps), scale, prec, hud_mask=hud_masks)
         return out if device_out else out.cpu().numpy()
 
-    def clip_streamer(self, pairs: int, H: int, W: int, timestamps, depth: int = 2) -> "ClipStreamer":
-        """Extra (not in the reference): pipelined clip interpolation, see ClipStreamer."""
+    def clip_streamer(self, pairs: int, H: int, W: int, timestamps, depth: int = 2, output: str = 'rgb') -> "ClipStreamer":
+        """Extra (not in the reference): pipelined clip interpolation, see ClipStreamer.  output='yuv420': the results come
+        down as planar I420 frames (cv2 COLOR_RGB2YUV_I420, (H*3/2, W) uint8 each) -- half the device -> host bytes."""
         self.ensure_loaded()
-        return ClipStreamer(self, pairs, H, W, list(timestamps), depth)
+        return ClipStreamer(self, pairs, H, W, list(timestamps), depth, output)
 
     def upscale(self, frame: np.ndarray, scale: float = 1.333) -> np.ndarray:
         """RIFE does no SR: Lanczos on the host exactly as the reference (rife_wrapper.py:156-164)."""
@@ -269,8 +270,12 @@ class ClipStreamer:
         out = st.result(slot)                # (pairs, T, H, W, 3) uint8 pinned host tensor (valid until the slot is reused)
     """
 
-    def __init__(self, model: "RIFEModel", pairs: int, H: int, W: int, timestamps, depth: int = 2):
-        self.m, self.B, self.ts, self.depth = model, pairs, timestamps, depth
+    def __init__(self, model: "RIFEModel", pairs: int, H: int, W: int, timestamps, depth: int = 2, output: str = 'rgb'):
+        if output not in ('rgb', 'yuv420'):
+            raise ValueError("output must be 'rgb' or 'yuv420'")
+        if output == 'yuv420' and (H % 2 or W % 2):
+            raise ValueError("yuv420 output needs even frame sizes")
+        self.m, self.B, self.ts, self.depth, self.output = model, pairs, timestamps, depth, output
         dev = model.device
         T = len(timestamps)
         self.prec = _abi.PRECISION_BF16 if model.precision == 'bf16' else _abi.PRECISION_FP32
@@ -279,13 +284,15 @@ class ClipStreamer:
             self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
             self.in_dev = [torch.empty((pairs + 1, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(depth)]
             self.out_dev = [torch.empty((pairs, T, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(depth)]
-            self.out_host = [torch.empty((pairs, T, H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(depth)]
+            res_shape = (pairs, T, H, W, 3) if output == 'rgb' else (pairs, T, H * 3 // 2, W)
+            self.yuv_dev = [torch.empty(res_shape, dtype=torch.uint8, device=dev) for _ in range(depth)] if output == 'yuv420' else None
+            self.out_host = [torch.empty(res_shape, dtype=torch.uint8).pin_memory() for _ in range(depth)]
             self.ev_in = [torch.cuda.Event() for _ in range(depth)]
             self.ev_cmp = [torch.cuda.Event() for _ in range(depth)]
             self.ev_out = [torch.cuda.Event() for _ in range(depth)]
         self.k = 0
         self.h2d_bytes = (pairs + 1) * H * W * 3
-        self.d2h_bytes = pairs * T * H * W * 3
+        self.d2h_bytes = pairs * T * H * W * 3 // (1 if output == 'rgb' else 2)
 
     def submit(self, frames_host: torch.Tensor) -> int:
         i = self.k % self.depth
@@ -305,10 +312,12 @@ class ClipStreamer:
                 self.s_cmp.wait_event(self.ev_out[i])       # the previous result in this output slot has left
             self.m._engine.infer(self.in_dev[i][:-1], self.in_dev[i][1:], self.ts, self.scale, self.prec,
                                  out=self.out_dev[i])
+            if self.yuv_dev is not None:
+                self.m._engine.to_yuv420(self.out_dev[i], out=self.yuv_dev[i])
             self.ev_cmp[i].record(self.s_cmp)
         with torch.cuda.stream(self.s_out):
             self.s_out.wait_event(self.ev_cmp[i])
-            self.out_host[i].copy_(self.out_dev[i], non_blocking=True)
+            self.out_host[i].copy_(self.out_dev[i] if self.yuv_dev is None else self.yuv_dev[i], non_blocking=True)
             self.ev_out[i].record(self.s_out)
         self.k += 1
         return i
