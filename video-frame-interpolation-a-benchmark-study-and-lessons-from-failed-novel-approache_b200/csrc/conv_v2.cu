@@ -20,6 +20,7 @@
 
 #include <cuda.h>
 #include "common.cuh"
+#include "umma.cuh"
 #include <cuda_fp16.h>
 
 struct V2Params {
@@ -115,20 +116,7 @@ struct V2Cfg {
 };
 
 namespace {
-__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void bar_init(uint64_t* b, uint32_t cnt) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s_u32(b)), "r"(cnt) : "memory");
-}
-__device__ __forceinline__ void bar_wait(uint64_t* b, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred P1;\n\t"
-      "V2_WAIT:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
-      "@P1 bra V2_DONE;\n\t"
-      "bra V2_WAIT;\n\t"
-      "V2_DONE:\n\t}" ::"r"(s_u32(b)), "r"(parity)
-      : "memory");
-}
+using namespace umma;  // mbarrier / cp.async / tcgen05 wrappers and the no-swizzle descriptor shared with conv_s2.cu and the fused gathers
 // polling wait with back-off, for waits that are normally long (stage release, accumulator release): a warp parked here
 // must not compete with the epilogue warps for issue slots and the shared-memory pipe
 __device__ __forceinline__ void bar_wait_relaxed(uint64_t* b, uint32_t parity) {
@@ -144,19 +132,6 @@ __device__ __forceinline__ void bar_wait_relaxed(uint64_t* b, uint32_t parity) {
     if (!done) __nanosleep(200);
   } while (!done);
 }
-__device__ __forceinline__ void bar_arrive(uint64_t* b) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s_u32(b)) : "memory");
-}
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void commit_to(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s_u32(bar))
-               : "memory");
-}
 __device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                          uint32_t accumulate) {
   asm volatile(
@@ -165,34 +140,6 @@ __device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
-}
-// same, issued from a converged warp: `leader` is the elect.sync result, operands are warp-uniform
-__device__ __forceinline__ void mma_bf16_elect(uint32_t leader, uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
-                                               uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p, pe;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "setp.ne.b32 pe, %5, 0;\n\t"
-      "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader)
-      : "memory");
-}
-__device__ __forceinline__ uint32_t elect_one() {
-  uint32_t pred;
-  asm volatile("{\n\t.reg .pred pe;\n\telect.sync _|pe, 0xffffffff;\n\tselp.u32 %0, 1, 0, pe;\n\t}" : "=r"(pred));
-  return pred;
-}
-__device__ __forceinline__ void ld16(uint32_t taddr, float* v) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
 }
 // tcgen05.ld of N consecutive fp32 accumulator columns of this warp's 32 lanes; NO wait (caller issues wait::ld)
 template <int N>
@@ -230,20 +177,8 @@ __device__ __forceinline__ void st_global_v8(float* p, float a, float b, float c
                "f"(e), "f"(f), "f"(g), "f"(h)
                : "memory");
 }
-// no-swizzle K-major descriptor: start, LBO (K-direction core-matrix stride), SBO (8-row group stride), bytes
-__device__ __forceinline__ uint64_t desc_ns(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = (uint64_t)((saddr & 0x3FFFF) >> 4);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;  // descriptor version (sm_100)
-  return d;                // layout_type 0 = SWIZZLE_NONE, base_offset 0
-}
 __device__ __forceinline__ uint32_t idesc_bf16(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | (8u << 24);  // F32 acc, BF16 x BF16, M = 128
-}
-__device__ __forceinline__ uint32_t pk_bf16(float a, float b) {
-  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&t);
 }
 }  // namespace
 

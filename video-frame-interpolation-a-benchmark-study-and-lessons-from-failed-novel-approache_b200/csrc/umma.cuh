@@ -1,5 +1,5 @@
 // umma.cuh -- the PTX wrappers (mbarrier, cp.async, tcgen05 alloc / mma / commit / ld, no-swizzle smem descriptors) shared
-// by the resident-weight implicit-GEMM kernels (conv_s2.cu and the fused gather kernels of elementwise.cu; conv_v2.cu keeps its own copies with its trace hooks).  sm_100a only.
+// by the resident-weight implicit-GEMM kernels (conv_s2.cu and the fused gather kernels of elementwise.cu and conv_v2.cu).  sm_100a only.
 #pragma once
 #include "common.cuh"
 
