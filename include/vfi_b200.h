@@ -65,6 +65,10 @@ size_t vfi_device_bytes(vfi_handle* h);
  *   "v2_pm"         0: chunk-major halo tile (16-byte TMA box rows); 1: c = 64 layers use a pixel-major SWIZZLE_128B tile.
  *   "v2_res_global" 0: ResConv residual from the shared-memory tile; 1: from global memory.
  *   "l2_chunk_mb"   0: off; n: run each ResConv chain depth-first over item groups of n MB of activations.
+ *   "gc_persistent" 1: the fused finest-block gather is persistent (staging of tile i+1 overlaps tile i's MMAs / epilogue); 0: one tile per CTA.
+ *   "fuse_gather3"  0: block 3 runs gather_s2 + conv_s2; 1: its gather is fused with its conv0[0] like the finest block's
+ *                      (same results to the bf16 tolerance; measured 3 % slower per step on B200, kept as a variant).
+ *   "gc_ablate": debug only (phase ablation of the fused finest gather).
  *   "v2_ablate", "v2_trace": debug only (tools/bench_conv.py, tools/v2_trace.py). */
 int vfi_set_option(vfi_handle* h, const char* key, int value);
 

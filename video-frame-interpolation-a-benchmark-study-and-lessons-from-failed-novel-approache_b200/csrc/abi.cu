@@ -122,6 +122,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!strcmp(key, "v2_pm")) { h->opt_v2_pm = value; return VFI_OK; }
   if (!strcmp(key, "v2_tma")) { h->opt_v2_tma = value; return VFI_OK; }
   if (!strcmp(key, "l2_chunk_mb")) { h->opt_l2_chunk_mb = value; return VFI_OK; }
+  if (!strcmp(key, "fuse_gather3")) { h->opt_fuse_gather3 = value; return VFI_OK; }
   if (!strcmp(key, "gc_persistent")) { h->opt_gc_persistent = value; return VFI_OK; }
   if (!strcmp(key, "gc_ablate")) { h->opt_gc_ablate = value; return VFI_OK; }
   if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }
@@ -362,6 +363,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer_ex(vfi_han
       if (fused && i == 4) {
         if ((rc = k_gather_conv0a(h, Lb[0], imgs, feats, lows, tdev, (bf16*)a0, flow3, B, I1, T, Hp, Wp, s))) return rc;
         flow_pre = flow3;
+      } else if (fused && h->opt_fuse_gather3 && i == 3 && sc == 2 && Lb[0].ws2 && Lb[0].cout == 32 && Hp % 64 == 0 && Wp % 32 == 0) {
+        if ((rc = k_gather_s2_conv0a(h, Lb[0], imgs, feats, lows, tdev, (bf16*)a0, B, I1, T, Hp, Wp, s))) return rc;
       } else {
         if ((rc = k_gather(h, imgs, feats, lows, tdev, xin, B, I1, T, Hp, Wp, sc, bf, bf, s))) return rc;
         if ((rc = run_conv(h, Lb[0], xin, nullptr, a0, N, hs, wsz, bf, bf, s))) return rc;

@@ -94,6 +94,8 @@ struct vfi_handle {
   int opt_fuse_gather = 1;      // vfi_set_option("fuse_gather"): finest block's gather fused with conv0[0]
   int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps
   int opt_v2_ablate = 0;        // debug only: see V2Params::ablate
+  int opt_fuse_gather3 = 0;     // vfi_set_option("fuse_gather3"): block 3's (s = 2) gather fused with its conv0[0].  OFF: measured 3 % SLOWER
+                                // per step than gather_s2 + conv_s2 (18 instead of 24 resident warps on a latency-bound gather)
   int opt_gc_persistent = 1;    // vfi_set_option("gc_persistent"): persistent, phase-overlapped form of the fused finest-block gather
   int opt_gc_ablate = 0;        // debug only: gather_conv0a phases off (1 staging, 2 gather, 4 MMA + epilogue, 8 flow evaluation)
   int opt_conv_v2 = 1;          // vfi_set_option("conv_v2"): resident-weight halo-tile conv kernel where it applies
@@ -223,6 +225,9 @@ struct LowSet {
     mf[n - 1] = pl.mf; f7[n - 1] = pl.f7;
   }
 };
+// block 3 (s = 2) input gather fused with its conv0[0] (csrc/elementwise.cu)
+int k_gather_s2_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
+                       const float* tsteps_dev, bf16* out, int B, int I1, int T, int Hp, int Wp, cudaStream_t s);
 // tap tables of `n` levels: level k at out + k * (Wp + Hp), columns first
 int k_build_taps(vfi_handle* h, Tap* out, const int* scales, int n, int Hp, int Wp, cudaStream_t s);
 int k_gather(vfi_handle* h, const uint8_t* imgs, const void* feats, const LowSet& lows, const float* tsteps_dev,

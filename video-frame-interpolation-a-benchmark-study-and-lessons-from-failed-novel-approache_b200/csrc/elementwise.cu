@@ -1471,6 +1471,265 @@ static int launch_gather_s2(vfi_handle* h, const uint8_t* imgs, const bf16* feat
 // Block-input gather at s >= 4 (bf16 mode, LowPlanes levels): gather_kernel<bf16, false> with the per-call tap tables
 // instead of per-thread source-index arithmetic, 32-bit indexing, and mask / feat fetched once per output with the
 // mean weights of the 2 x 2 sampled positions (which share their source cell: the last level is at least 2s coarse).
+// ------------------------------------------------------------------------------------------
+// Block 3 at scale 1.0 (s = 2): block-input gather FUSED with conv0's first stride-2 convolution (28 -> 32 channels), the
+// way gather_conv0a_p_kernel does it for the finest block.  The 28-channel half-resolution block input (64 B per pixel,
+// 3 GB written and read back per 90 items of 1080p) never goes to HBM.
+//   tile     : 8 x 16 conv outputs (one M = 128 MMA tile) <- 17 x 33 half-resolution input pixels (stride 2, pad 1) <- the
+//              34 x 66 full-resolution pixels whose four warped samples each of them averages (gather_s2_kernel's arithmetic)
+//   A (smem) : conv_s2.cu's four phase-plane windows [Cin/8][plane][17 rows][9 cols][8 ch], written straight by the gather
+//   B (smem) : [tap][Cin/8][32][8] bf16 (18 KB), resident; D: 32 TMEM columns
+//   persistent, 288 threads (561 pixels in two rounds), 2 CTAs per SM; warps 0-3 issue the MMAs and run the epilogue of tile
+//   i while warps 4-8 stage the flow rows of tile i+1.
+#define G3_THREADS 288
+#ifndef G3_UNROLL
+#define G3_UNROLL 2
+#endif
+constexpr int kG3Unroll = G3_UNROLL;   // samples of a pixel in flight together (the kernel runs 18 warps per SM: ILP instead of occupancy)
+#define G3_RW 17          // region width  (half-resolution pixels)
+#define G3_RH 33          // region height
+#define G3_FW 34          // flow region width  (full-resolution pixels)
+#define G3_FH 66          // flow region height
+#define G3_PW 9           // phase-plane window width
+#define G3_PLANE 156      // plane stride (16-byte units): >= 17 * 9, == 4 mod 8
+#define G3_CS 626         // chunk stride: >= 4 * G3_PLANE, == 2 mod 8
+#define G3_A_BYTES (4 * G3_CS * 16)
+#define G3_W_BYTES (9 * 32 * 32 * 2)
+#define G3_TAB (5 * G3_FH)
+__host__ __device__ __forceinline__ int g3_rows(int s) { return G3_FH / s + 3; }   // source rows a 66-row span can touch (+1 spare)
+static size_t g3_stage_bytes(const LowSet& lows, GcRows* R) {
+  int rows = 0;
+  for (int k = 0; k < 5; k++) {
+    R->start[k] = rows;
+    if (k < lows.n) rows += g3_rows(lows.s[k]);
+  }
+  R->start[5] = rows;
+  return ((size_t)G3_TAB + (size_t)rows * G3_FW) * sizeof(float4);
+}
+// flat_stage for a G3_FW x G3_FH region with origin (ox, oy): per-level row table (one entry per region row) followed by the
+// x-interpolated, pre-scaled flow rows of every coarse level (G3_FW float4 per row)
+template <int NT>
+__device__ __forceinline__ void rect_stage(const LowSet& L, const GcRows& R, int n, int ox, int oy, int Hp, int Wp, float4* sm, int tid) {
+  RowTap* ytab = reinterpret_cast<RowTap*>(sm);
+  const float oyf = (float)max(oy, 0) + 0.5f;
+  for (int e = tid; e < L.n * G3_FH; e += NT) {
+    const int k = e / G3_FH, yl = e - k * G3_FH;
+    const Tap ty = ld_tap(L.yt[k] + min(max(oy + yl, 0), Hp - 1));
+    const int r_lo = (int)fmaxf(L.rs[k] * oyf - 0.5f, 0.f);
+    const int off = G3_TAB + R.start[k] * G3_FW;
+    RowTap t;
+    t.o0 = (off + (ty.i0 - r_lo) * G3_FW) * 16; t.o1 = (off + (ty.i1 - r_lo) * G3_FW) * 16;  // byte offsets
+    t.hy = ty.h; t.ly = ty.l;
+    ytab[e] = t;
+  }
+  const int total = R.start[5] * G3_FW;
+#pragma unroll 2
+  for (int e = tid; e < total; e += NT) {
+    const int u = e / G3_FW, col = e - u * G3_FW;
+    int k = 0;
+#pragma unroll
+    for (int j = 1; j < 5; j++) k += (j < L.n && u >= R.start[j]) ? 1 : 0;
+    const int Hl = L.Hl[k], Wl = L.Wl[k], c4 = L.c4[k];
+    const int r_lo = (int)fmaxf(L.rs[k] * oyf - 0.5f, 0.f);
+    const int ry = min(r_lo + u - R.start[k], Hl - 1);
+    const Tap tx = ld_tap(L.xt[k] + min(max(ox + col, 0), Wp - 1));
+    const float4* row = reinterpret_cast<const float4*>(L.p[k]) + ((size_t)n * Hl + ry) * Wl * c4;
+    const float4 a = __ldg(row + tx.i0 * c4), b = __ldg(row + tx.i1 * c4);
+    const float fs = L.fs[k];
+    sm[G3_TAB + e] = make_float4((tx.h * a.x + tx.l * b.x) * fs, (tx.h * a.y + tx.l * b.y) * fs,
+                                 (tx.h * a.z + tx.l * b.z) * fs, (tx.h * a.w + tx.l * b.w) * fs);
+  }
+}
+__device__ __forceinline__ float4 rect_eval(const LowSet& L, const float4* sm, int lx, int ly) {
+  const RowTap* ytab = reinterpret_cast<const RowTap*>(sm);
+  float4 fl = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    if (k < L.n) {
+      const RowTap t = ytab[k * G3_FH + ly];
+      const char* col = reinterpret_cast<const char*>(sm + lx);
+      const float4 a = *reinterpret_cast<const float4*>(col + t.o0), c = *reinterpret_cast<const float4*>(col + t.o1);
+      fl.x = fmaf(t.ly, c.x, fmaf(t.hy, a.x, fl.x)); fl.y = fmaf(t.ly, c.y, fmaf(t.hy, a.y, fl.y));
+      fl.z = fmaf(t.ly, c.z, fmaf(t.hy, a.z, fl.z)); fl.w = fmaf(t.ly, c.w, fmaf(t.hy, a.w, fl.w));
+    }
+  }
+  return fl;
+}
+
+__device__ __forceinline__ uint32_t g3_pix_index(int ly, int lx) {
+  // region-local (ly, lx) in [0, 33) x [0, 17): half-resolution pixel (hy0 - 1 + ly, hx0 - 1 + lx); hy0, hx0 are even
+  const int py = (ly + 1) & 1, px = (lx + 1) & 1;
+  const int pr = (ly + 1) >> 1, pc = (lx + 1) >> 1;
+  return (uint32_t)((py * 2 + px) * G3_PLANE + pr * G3_PW + pc);
+}
+__global__ void __launch_bounds__(G3_THREADS, 2)
+gather_s2_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const bf16* __restrict__ feats, const __grid_constant__ LowSet lows,
+                          const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
+                          bf16* __restrict__ out, const __grid_constant__ GcRows grows, int B, int I1, int Tn, int Hp, int Wp,
+                          float slope, int stage_bytes, int tiles_x, int tiles_y, int num_tiles) {
+  using namespace umma;
+  extern __shared__ float4 tl_sm[];  // row table + staged flow rows | A tile | weights
+  __shared__ uint64_t mma_bar;
+  __shared__ uint32_t tmem_slot;
+  uint8_t* a_s = reinterpret_cast<uint8_t*>(tl_sm) + stage_bytes;
+  uint8_t* w_s = a_s + G3_A_BYTES;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) { bar_init(&mma_bar, 1); fence_barrier_init(); }
+  if (warp == 0) tmem_alloc(&tmem_slot, 32);
+  for (int i = threadIdx.x; i < G3_W_BYTES / 16; i += G3_THREADS)
+    reinterpret_cast<uint4*>(w_s)[i] = __ldg(reinterpret_cast<const uint4*>(wpack) + i);
+  int tile = blockIdx.x;
+  int ctx = tile % tiles_x, cty = (tile / tiles_x) % tiles_y, cn = tile / (tiles_x * tiles_y);
+  const int g = (int)gridDim.x, gsx = g % tiles_x, gsy = (g / tiles_x) % tiles_y, gsn = g / (tiles_x * tiles_y);
+  // full-resolution origin of tile (tx, ty)'s flow region: two pixels left of / above its 32 x 64 full-resolution footprint
+  if (tile < num_tiles) rect_stage<G3_THREADS>(lows, grows, cn, ctx * 32 - 2, cty * 64 - 2, Hp, Wp, tl_sm, (int)threadIdx.x);
+  fence_async_smem();
+  tc_before();
+  __syncthreads();
+  tc_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int plane = Hp * Wp;
+  const uint32_t* img32 = reinterpret_cast<const uint32_t*>(imgs);
+  const int kl = lows.n - 1, mWl = lows.Wl[kl];
+  const bf16 *mfp = lows.mf[kl], *f7p = lows.f7[kl];
+  const Tap *mxt = lows.xt[kl], *myt = lows.yt[kl];
+  for (int it = 0; tile < num_tiles; tile += g, it++) {
+    const int hx0 = ctx * 16, hy0 = cty * 32, n = cn;      // half-resolution tile origin
+    ctx += gsx; cty += gsy; cn += gsn;                       // the next tile of this CTA
+    if (ctx >= tiles_x) { ctx -= tiles_x; cty++; }
+    if (cty >= tiles_y) { cty -= tiles_y; cn++; }
+    const int b = n / Tn;
+    const float t = tsteps[n - b * Tn];
+    const int base0 = b * plane, base1 = (I1 + b) * plane;
+    const int mtb = n * lows.Hl[kl] * mWl;
+#pragma unroll 1
+    for (int e = threadIdx.x; e < G3_RW * G3_RH; e += G3_THREADS) {
+      const int ly = e / G3_RW, lx = e - ly * G3_RW;
+      const int hx = hx0 - 1 + lx, hy = hy0 - 1 + ly;        // half-resolution pixel
+      uint4 u[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) u[j] = make_uint4(0u, 0u, 0u, 0u);
+      if (hx >= 0 && hy >= 0) {                               // else: the convolution's zero padding
+        const int gx = 2 * hx, gy = 2 * hy;                   // top-left of the pixel's 2 x 2 full-resolution positions
+        float mf[9];
+        {
+          const Tap xa = ld_tap(mxt + gx), xb = ld_tap(mxt + gx + 1), ya = ld_tap(myt + gy), yb = ld_tap(myt + gy + 1);
+          const float hxw = 0.5f * (xa.h + xb.h), lxw = 0.5f * (xa.l + xb.l), hyw = 0.5f * (ya.h + yb.h), lyw = 0.5f * (ya.l + yb.l);
+          const int r0 = mtb + ya.i0 * mWl, r1 = mtb + ya.i1 * mWl;
+          const float w00 = hyw * hxw, w01 = hyw * lxw, w10 = lyw * hxw, w11 = lyw * lxw;
+          float a[9], c[9];
+          mf9_load(mfp, f7p, r0 + xa.i0, a);
+          mf9_load(mfp, f7p, r0 + xa.i1, c);
+#pragma unroll
+          for (int i = 0; i < 9; i++) mf[i] = w00 * a[i] + w01 * c[i];
+          mf9_load(mfp, f7p, r1 + xa.i0, a);
+          mf9_load(mfp, f7p, r1 + xa.i1, c);
+#pragma unroll
+          for (int i = 0; i < 9; i++) mf[i] += w10 * a[i] + w11 * c[i];
+        }
+        float c0[3] = {0.f, 0.f, 0.f}, c1[3] = {0.f, 0.f, 0.f}, v0[4] = {0.f, 0.f, 0.f, 0.f}, v1[4] = {0.f, 0.f, 0.f, 0.f};
+        float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll kG3Unroll
+        for (int d = 0; d < 4; d++) {                         // same visiting order and sums as gather_s2_kernel
+          const int dx = d & 1, dy = d >> 1;
+          const float4 fl = rect_eval(lows, tl_sm, 2 * lx + dx, 2 * ly + dy);
+          const Bil b0 = bil_setup((float)(gx + dx) + fl.x, (float)(gy + dy) + fl.y, Wp, Hp, base0);
+          const Bil b1 = bil_setup((float)(gx + dx) + fl.z, (float)(gy + dy) + fl.w, Wp, Hp, base1);
+          float r[4];
+          sample_rgbx(img32, b0, r);
+          c0[0] += r[0]; c0[1] += r[1]; c0[2] += r[2];
+          sample_rgbx(img32, b1, r);
+          c1[0] += r[0]; c1[1] += r[1]; c1[2] += r[2];
+          sample_feat_px<bf16>(feats, b0, r);
+          v0[0] += r[0]; v0[1] += r[1]; v0[2] += r[2]; v0[3] += r[3];
+          sample_feat_px<bf16>(feats, b1, r);
+          v1[0] += r[0]; v1[1] += r[1]; v1[2] += r[2]; v1[3] += r[3];
+          fs.x += fl.x; fs.y += fl.y; fs.z += fl.z; fs.w += fl.w;
+        }
+        const float q = 0.25f, qf = 0.125f;  // mean of the four positions; the flow also scales by 1/s = 1/2
+        u[0] = make_uint4(pk_bf16(c0[0] * q, c0[1] * q), pk_bf16(c0[2] * q, c1[0] * q), pk_bf16(c1[1] * q, c1[2] * q), pk_bf16(v0[0] * q, v0[1] * q));
+        u[1] = make_uint4(pk_bf16(v0[2] * q, v0[3] * q), pk_bf16(v1[0] * q, v1[1] * q), pk_bf16(v1[2] * q, v1[3] * q), pk_bf16(t, mf[0]));
+        u[2] = make_uint4(pk_bf16(mf[1], mf[2]), pk_bf16(mf[3], mf[4]), pk_bf16(mf[5], mf[6]), pk_bf16(mf[7], mf[8]));
+        u[3] = make_uint4(pk_bf16(fs.x * qf, fs.y * qf), pk_bf16(fs.z * qf, fs.w * qf), 0u, 0u);
+      }
+      const uint32_t pix = g3_pix_index(ly, lx);
+#pragma unroll
+      for (int j = 0; j < 4; j++) *reinterpret_cast<uint4*>(a_s + ((size_t)j * G3_CS + pix) * 16) = u[j];
+    }
+    fence_async_smem();
+    __syncthreads();               // the A tile is complete; the staging area is free again
+    if (warp == 0) {
+      const uint32_t leader = elect_one();
+      constexpr uint32_t IDESC = idesc_bf16_m128(32);
+      const uint64_t ad0 = desc_ns(s_u32(a_s), G3_CS * 16, G3_PW * 16);
+      const uint64_t bd0 = desc_ns(s_u32(w_s), 32 * 16, 128);
+#pragma unroll
+      for (int tap = 0; tap < 9; tap++) {
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+          const int ky = tap / 3, kx = tap % 3;
+          const int pl = (ky != 1 ? 2 : 0) + (kx != 1 ? 1 : 0);
+          const uint32_t a_off = (uint32_t)(pl * G3_PLANE + (ky != 0 ? 1 : 0) * G3_PW + (kx != 0 ? 1 : 0) + 2 * k * G3_CS);
+          const uint32_t b_off = (uint32_t)((tap * 4 + 2 * k) * 32);
+          mma_bf16_elect(leader, tmem_base, ad0 + a_off, bd0 + b_off, IDESC, (tap | k) ? 1u : 0u);
+        }
+      }
+      if (leader) commit_to(&mma_bar);
+      __syncwarp();
+    }
+    if (warp < 4) {
+      bar_wait(&mma_bar, (uint32_t)(it & 1));
+      tc_after();
+      const int m = warp * 32 + lane;
+      const int Ho = Hp >> 2, Wo = Wp >> 2;                   // conv0[0]'s output grid (quarter resolution)
+      const int oy = (hy0 >> 1) + (m >> 3), ox = (hx0 >> 1) + (m & 7);
+      float v[32];
+      ld16(tmem_base + ((uint32_t)(warp * 32) << 16), v);
+      ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + 16, v + 16);
+#pragma unroll
+      for (int c = 0; c < 32; c++) {
+        const float x = v[c] + __ldg(bias + c);
+        v[c] = x > 0.f ? x : x * slope;
+      }
+      // conv0's second conv is stride 2 too: write its four phase planes [N, 4, Ho/2, Wo/2, 32]
+      const size_t opix = ((((size_t)n * 4 + (oy & 1) * 2 + (ox & 1)) * (Ho >> 1) + (oy >> 1)) * (Wo >> 1) + (ox >> 1));
+      uint4 o[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        o[j] = make_uint4(pk_bf16(v[8 * j], v[8 * j + 1]), pk_bf16(v[8 * j + 2], v[8 * j + 3]), pk_bf16(v[8 * j + 4], v[8 * j + 5]),
+                          pk_bf16(v[8 * j + 6], v[8 * j + 7]));
+      st_v8(out + opix * 32, o[0], o[1]);
+      st_v8(out + opix * 32 + 16, o[2], o[3]);
+    }
+    if (warp >= 4 && tile + g < num_tiles)
+      rect_stage<G3_THREADS - 128>(lows, grows, cn, ctx * 32 - 2, cty * 64 - 2, Hp, Wp, tl_sm, (int)threadIdx.x - 128);
+    tc_before();
+    __syncthreads();               // next tile staged; this tile's accumulator read out
+    tc_after();
+  }
+  if (warp == 0) tmem_dealloc(tmem_base, 32);
+}
+// Lb0 = block 3's conv0[0] (28 -> 32, stride 2).  Output: its activation as the phase planes of [N, Hp/4, Wp/4, 32].
+int k_gather_s2_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const void* feats, const LowSet& lows,
+                       const float* tsteps_dev, bf16* out, int B, int I1, int T, int Hp, int Wp, cudaStream_t s) {
+  ProfScope _ps(h, PC_GATHER, s);
+  if (!Lb0.ws2 || Lb0.cin_pad != 32 || Lb0.cout != 32) VFI_FAIL(h, VFI_E_STATE, "gather_s2_conv0a: layer not packed");
+  if (Hp % 64 || Wp % 32) VFI_FAIL(h, VFI_E_ARG, "gather_s2_conv0a: padded size must be a multiple of 64 x 32");
+  for (int k = 0; k < lows.n; k++)
+    if (lows.s[k] < 4) VFI_FAIL(h, VFI_E_ARG, "gather_s2_conv0a: coarse levels only");
+  if (lows.n < 1 || !lows.mf[lows.n - 1] || !lows.xt[0]) VFI_FAIL(h, VFI_E_ARG, "gather_s2_conv0a: needs tap tables and plane-stored coarse levels");
+  GcRows grows;
+  const size_t un = (g3_stage_bytes(lows, &grows) + 127) & ~(size_t)127;
+  const size_t smem = un + G3_A_BYTES + G3_W_BYTES;
+  if (smem > 110 * 1024) VFI_FAIL(h, VFI_E_ARG, "gather_s2_conv0a: shared memory budget");
+  VFI_CUDA(h, cudaFuncSetAttribute(gather_s2_conv0a_p_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
+  const int tiles_x = Wp / 32, tiles_y = Hp / 64, num_tiles = tiles_x * tiles_y * B * T;
+  gather_s2_conv0a_p_kernel<<<std::min(num_tiles, 2 * h->sm_count), G3_THREADS, smem, s>>>(
+      imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out, grows, B, I1, T, Hp, Wp, h->slope, (int)un, tiles_x, tiles_y, num_tiles);
+  VFI_LAUNCHED(h);
+  return 0;
+}
+
 __global__ void __launch_bounds__(128) gather_lo_kernel(const uint8_t* __restrict__ imgs, const bf16* __restrict__ feats,
                                                         const __grid_constant__ LowSet lows, const float* __restrict__ tsteps,
                                                         bf16* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, int s,
