@@ -104,16 +104,19 @@ __global__ void __launch_bounds__(S2_THREADS, 1) conv_s2_kernel(const __grid_con
     // critical path (see conv_v2.cu)
     const int depth = P.nstages - 2 < 1 ? 1 : (P.nstages - 2 > 3 ? 3 : P.nstages - 2);
     int it = 0;
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
-      const int st = it % P.nstages;
-      const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
-      const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+    TileWalk tw((int)blockIdx.x, (int)gridDim.x, P.tiles_x, P.tiles_y);   // no per-tile integer divisions (umma.cuh)
+    StageWalk sw(P.nstages), pub(P.nstages);                               // pub: the stage published `depth` iterations later
+    for (; tw.tile < P.num_tiles; tw.next(), sw.next(), it++) {
+      const int st = sw.st;
+      const uint32_t ph = sw.ph;
+      const int tx = tw.tx, ty = tw.ty, n = tw.n;
       const int c0 = tx * 8 * KW - 1, r0 = ty * 16 - 1;  // plane coordinates of the window origin
       if (it >= depth) {
         if (depth == 3) cp_wait<2>(); else if (depth == 2) cp_wait<1>(); else cp_wait<0>();
         fence_async_smem();
         __syncwarp();
-        if (lane == 0) bar_arrive(&full_bar[(it - depth) % P.nstages]);
+        if (lane == 0) bar_arrive(&full_bar[pub.st]);
+        pub.next();
       }
       bar_wait(&empty_bar[st], ph ^ 1);
       const uint32_t dst = s_u32(a_s + (size_t)st * C::A_BYTES);
@@ -143,9 +146,10 @@ __global__ void __launch_bounds__(S2_THREADS, 1) conv_s2_kernel(const __grid_con
     constexpr int KSTEPS = CIN / 16;
     const uint64_t bd0 = desc_ns(s_u32(w_s), B_LBO, B_SBO);
     int it = 0;
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
-      const int st = it % P.nstages;
-      const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
+    StageWalk sw(P.nstages);
+    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, sw.next(), it++) {
+      const int st = sw.st;
+      const uint32_t ph = sw.ph;
       const int as = it & 1;
       bar_wait(&tempty_bar[as], (uint32_t)(((it >> 1) & 1) ^ 1));
       bar_wait(&full_bar[st], ph);
@@ -181,9 +185,10 @@ __global__ void __launch_bounds__(S2_THREADS, 1) conv_s2_kernel(const __grid_con
     const int ly = m >> 3, lx = m & 7;
     const float4* bias4 = reinterpret_cast<const float4*>(bias_s);
     int it = 0;
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+    TileWalk tw((int)blockIdx.x, (int)gridDim.x, P.tiles_x, P.tiles_y);
+    for (; tw.tile < P.num_tiles; tw.next(), it++) {
       const int as = it & 1;
-      const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+      const int tx = tw.tx, ty = tw.ty, n = tw.n;
       const int y = ty * 16 + ly;
       bar_wait(&tfull_bar[as], (uint32_t)((it >> 1) & 1));
       tc_after();

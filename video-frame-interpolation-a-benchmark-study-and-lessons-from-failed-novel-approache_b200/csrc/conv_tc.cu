@@ -18,6 +18,7 @@
 #include <map>
 
 #include "common.cuh"
+#include "umma.cuh"
 
 // ---------------------------------------------------------------------------------------------
 struct TcParams {
@@ -155,8 +156,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x) {
-        int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+      umma::TileWalk tw((int)blockIdx.x, (int)gridDim.x, P.tiles_x, P.tiles_y);   // no per-tile integer divisions (umma.cuh)
+      for (; tw.tile < P.num_tiles; tw.next()) {
+        const int tx = tw.tx, ty = tw.ty, n = tw.n;
         int x0 = tx * P.tw, y0 = ty * P.th;
         for (int s = 0; s < P.nsteps; s++) {
           const TcStep& st = P.steps[s];
@@ -209,11 +211,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int lg = warp & 3;  // TMEM lane group this warp may access
     const int m = lg * 32 + lane;
     int it = 0;
-    for (int tile = blockIdx.x; tile < P.num_tiles; tile += gridDim.x, it++) {
+    const int my = m / P.tw, mx = m % P.tw;   // this thread's pixel inside a tile: loop invariant
+    umma::TileWalk tw((int)blockIdx.x, (int)gridDim.x, P.tiles_x, P.tiles_y);
+    for (; tw.tile < P.num_tiles; tw.next(), it++) {
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
-      int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
-      const int y = ty * P.th + m / P.tw, x = tx * P.tw + m % P.tw;
+      const int tx = tw.tx, ty = tw.ty, n = tw.n;
+      const int y = ty * P.th + my, x = tx * P.tw + mx;
       const bool valid = (y < P.Ho) && (x < P.Wo);
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();

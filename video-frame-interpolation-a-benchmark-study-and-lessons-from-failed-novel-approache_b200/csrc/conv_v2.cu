@@ -247,10 +247,12 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     // ================= producer (TMA): one thread, NCHUNK tensor boxes per tile =================
     if (threadIdx.x == 0) {
       int it = 0;
-      for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
-        const int st = it % P.nstages;
-        const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
-        const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+      TileWalk tw(tile0, tile_step, P.tiles_x, P.tiles_y);
+      StageWalk sw(P.nstages);
+      for (; tw.tile < P.num_tiles; tw.next(), sw.next(), it++) {
+        const int st = sw.st;
+        const uint32_t ph = sw.ph;
+        const int tx = tw.tx, ty = tw.ty, n = tw.n;
         V2_TRACE(0, it, 0);  // wants stage
         if (P.ablate & 256) bar_wait(&empty_bar[st], ph ^ 1); else bar_wait_relaxed(&empty_bar[st], ph ^ 1);
         V2_TRACE(0, it, 1);  // got stage
@@ -312,10 +314,12 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     // hand-shake off the MMA warp's critical path (with no slack, load / MMA / epilogue times ADD instead of overlap).
     const int depth = P.nstages - 2 < 1 ? 1 : (P.nstages - 2 > V2_DEPTH ? V2_DEPTH : P.nstages - 2);
     int it = 0;
-    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
-      const int st = it % P.nstages;
-      const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
-      const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+    TileWalk tw(tile0, tile_step, P.tiles_x, P.tiles_y);
+    StageWalk sw(P.nstages);
+    for (; tw.tile < P.num_tiles; tw.next(), sw.next(), it++) {
+      const int st = sw.st;
+      const uint32_t ph = sw.ph;
+      const int tx = tw.tx, ty = tw.ty, n = tw.n;
       const int gx0 = tx * 8 * KW - 1, gy0 = ty * 16 - 1;
       if (it >= depth) {
         // publish the oldest in-flight tile BEFORE claiming a new stage, so publishing never waits on a stage release
@@ -372,9 +376,10 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     constexpr int KSTEPS = CIN / 16;
     const uint64_t bd0 = desc_ns(s_u32(w_s), B_LBO, B_SBO);
     int it = 0;
-    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
-      const int st = it % P.nstages;
-      const uint32_t ph = (uint32_t)((it / P.nstages) & 1);
+    StageWalk sw(P.nstages);
+    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, sw.next(), it++) {
+      const int st = sw.st;
+      const uint32_t ph = sw.ph;
       const int as = it % C::NACC;
       if (leader) V2_TRACE(1, it, 0);
       if (P.ablate & 512) bar_wait(&tempty_bar[as], (uint32_t)(((it / C::NACC) & 1) ^ 1)); else bar_wait_relaxed(&tempty_bar[as], (uint32_t)(((it / C::NACC) & 1) ^ 1));
@@ -434,9 +439,10 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     const int ly = m >> 3, lx = m & 7;
     const float* bias_r = P.bias_c + pr * 40;
     int it = 0;
-    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
+    TileWalk tw(tile0, tile_step, P.tiles_x, P.tiles_y);
+    for (; tw.tile < P.num_tiles; tw.next(), it++) {
       const int as = it % C::NACC;
-      const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+      const int tx = tw.tx, ty = tw.ty, n = tw.n;
       const int y = ty * 16 + ly, x = (tx * KW + j) * 8 + lx;
       bar_wait(&tfull_bar[as], (uint32_t)((it / C::NACC) & 1));
       tc_after();
@@ -515,10 +521,12 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
     constexpr int NR = CH / 8;
     const bool tr = warp == PW_ + 1 && lane == 0;
     int it = 0;
-    for (int tile = tile0; tile < P.num_tiles; tile += tile_step, it++) {
-      const int st = it % P.nstages;
+    TileWalk tw(tile0, tile_step, P.tiles_x, P.tiles_y);
+    StageWalk sw(P.nstages);
+    for (; tw.tile < P.num_tiles; tw.next(), sw.next(), it++) {
+      const int st = sw.st;
       const int as = it % C::NACC;
-      const int tx = tile % P.tiles_x, ty = (tile / P.tiles_x) % P.tiles_y, n = tile / (P.tiles_x * P.tiles_y);
+      const int tx = tw.tx, ty = tw.ty, n = tw.n;
       const int y = ty * 16 + ly;
       // residual = centre pixels of the input halo tile: pull them into registers as soon as the tile has landed and
       // release the smem stage right away (the stage then only lives for load + MMA, not for the whole epilogue)
@@ -535,7 +543,7 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
           for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = ok ? __ldg(rp + ch) : make_uint4(0u, 0u, 0u, 0u);
         }
       } else if (use_res) {
-        if (!(P.ablate & 32)) bar_wait(&full_bar[st], (uint32_t)((it / P.nstages) & 1));
+        if (!(P.ablate & 32)) bar_wait(&full_bar[st], sw.ph);
         if (tr) V2_TRACE(2, it, 4);  // input tile visible
         const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * C::A_BYTES);
         if (active && !(P.ablate & 32))

@@ -100,4 +100,28 @@ constexpr int chunk_stride(int npix, int nchunk) {
   else if (nchunk == 2) { while (c % 8 != 4) c++; }
   return c;
 }
+// A persistent CTA's walk over its tiles (tile0, tile0 + step, ...) WITHOUT per-tile integer divisions: the linear index is
+// decoded to (tx, ty, n) once and the mixed-radix coordinates then advance by the decomposed step.  The three runtime
+// div / mod of the decode cost ~100-150 cycles each, dependent, in EVERY role of a warp-specialised kernel; with the
+// it % nstages of the stage ring they were ~860 cycles per tile on the epilogue warps' critical path (tools/v2_trace.py).
+struct TileWalk {
+  int tile, tx, ty, n, step, sx, sy, sn, tiles_x, tiles_y;
+  __device__ __forceinline__ TileWalk(int tile0, int step_, int tiles_x_, int tiles_y_)
+      : tile(tile0), step(step_), tiles_x(tiles_x_), tiles_y(tiles_y_) {
+    const int per = tiles_x * tiles_y;
+    tx = tile0 % tiles_x; ty = (tile0 / tiles_x) % tiles_y; n = tile0 / per;
+    sx = step_ % tiles_x; sy = (step_ / tiles_x) % tiles_y; sn = step_ / per;
+  }
+  __device__ __forceinline__ void next() {
+    tile += step; tx += sx; ty += sy; n += sn;
+    if (tx >= tiles_x) { tx -= tiles_x; ty++; }
+    if (ty >= tiles_y) { ty -= tiles_y; n++; }
+  }
+};
+// stage index and mbarrier phase parity of iteration it = 0, 1, ... of an nst-deep ring: st = it % nst, ph = (it / nst) & 1
+struct StageWalk {
+  int st, nst; uint32_t ph;
+  __device__ __forceinline__ explicit StageWalk(int nst_, int start = 0) : st(start % nst_), nst(nst_), ph((uint32_t)((start / nst_) & 1)) {}
+  __device__ __forceinline__ void next() { if (++st == nst) { st = 0; ph ^= 1u; } }
+};
 }  // namespace umma
