@@ -564,7 +564,9 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
             }
           }
         }
-        // the stage is refilled by TMA (async proxy): these generic-proxy reads must be ordered before that write
+        // the stage is refilled by TMA (async proxy): these generic-proxy reads must be ordered before that write.  REQUIRED: without
+        // this fence (v2_ablate bit 16, timing experiments only) tools/stress_determinism.py shows results changing from run to run
+        // (the mbarrier arrive / wait alone does not order the generic-proxy reads against the TMA write); it costs 4 % of a ResConv launch
         if (TMA && !(P.ablate & 16)) fence_async_smem();
         __syncwarp();
         if (lane == 0) bar_arrive(&empty_bar[st]);
