@@ -62,6 +62,13 @@ struct V2Params {
 #ifndef V2_PM_BASEOFF
 #define V2_PM_BASEOFF 0
 #endif
+#ifndef V2_EPI_GROUPS
+// 1: all 16 epilogue warps work on one tile, then all move to the next (one tile generation in flight).
+// 2: two groups of 8 warps take ALTERNATE tiles, each warp doing in two sequential halves what two warps do in mode 1: two
+//    generations in flight hide the epilogue's serial chain (wait -> residual LDS -> tcgen05.ld -> math -> stores), which
+//    tools/v2_trace.py shows to be the tile period of the c = 32 / 64 layers.  Not used by the final lastconv (EPI 2).
+#define V2_EPI_GROUPS 2
+#endif
 #ifndef V2_TMA_SLIM
 #define V2_TMA_SLIM 0  // 1: TMA instances run 576 threads (one producer warp) with bias / beta in registers (measured 2 % slower)
 #endif
@@ -218,8 +225,10 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
 
   // ---- one-time setup: barriers, TMEM, resident weights ----
   if (threadIdx.x == 0) {
-    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], ALL_TMA ? 1 : V2_PRODUCERS / 32 + (TJ > 0 ? 1 : 0)); bar_init(&empty_bar[i], (use_res && !P.res_global) ? 1 + V2_EPI_WARPS : 1); }
-    for (int i = 0; i < C::NACC; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], V2_EPI_WARPS); }
+    // epilogue warps that arrive per tile: all 16, or the 8 of the group that owns the tile
+    constexpr int EPI_ARRIVE = (V2_EPI_GROUPS == 2 && EPI != 2) ? V2_EPI_WARPS / 2 : V2_EPI_WARPS;
+    for (int i = 0; i < P.nstages; i++) { bar_init(&full_bar[i], ALL_TMA ? 1 : V2_PRODUCERS / 32 + (TJ > 0 ? 1 : 0)); bar_init(&empty_bar[i], (use_res && !P.res_global) ? 1 + EPI_ARRIVE : 1); }
+    for (int i = 0; i < C::NACC; i++) { bar_init(&tfull_bar[i], 1); bar_init(&tempty_bar[i], EPI_ARRIVE); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == PW_) {
@@ -485,6 +494,149 @@ conv_v2_kernel(const __grid_constant__ V2Params P, const __grid_constant__ CUten
               st_global_v8(row + (2 * q + jj) * lc, v[c0] + bias_r[c0], v[c0 + 1] + bias_r[c0 + 1], v[c0 + 2] + bias_r[c0 + 2],
                            v[c0 + 3] + bias_r[c0 + 3], v[c0 + 4] + bias_r[c0 + 4], 0.f, 0.f, 0.f);
             }
+        }
+      }
+    }
+  } else if constexpr (V2_EPI_GROUPS == 2) {
+    // ================= epilogue, two tile generations in flight: group = (epilogue warp index) / 8 owns tiles it = group,
+    // group + 2, ...; inside a group a warp (lane group lg, r2 = 0 / 1) does the work of mode 1's roles r2 and r2 + 2 as two
+    // sequential halves, so its register footprint is mode 1's.  The smem stage goes back after the second half's residual
+    // reads, the TMEM buffer after the second half's tcgen05.ld.
+    const int lg = warp & 3;
+    const int role4 = (warp - PW_ - 1) >> 2;     // 0..3
+    const int grp = role4 >> 1, r2 = role4 & 1;
+    constexpr int NSJ = KW >= 2 ? 2 : 1;
+    constexpr int Q = 4 / NSJ;
+    constexpr int CH = EPI == 1 ? 8 : (CN % Q == 0 && (CN / Q == 16 || CN / Q == 32)) ? CN / Q : 16;
+    constexpr int NSC = CN / CH;
+    static_assert(NSC <= Q && NSC * CH == CN, "epilogue slicing");
+    constexpr int NJ = KW / NSJ;
+    static_assert(CH == 8 || CH == 16 || CH == 32, "epilogue slice width");
+    constexpr int NR = CH / 8;
+    const int m = lg * 32 + lane;
+    const int ly = m >> 3, lx = m & 7;
+    int it = grp;
+    TileWalk tw(tile0 + grp * tile_step, 2 * tile_step, P.tiles_x, P.tiles_y);
+    StageWalk sw(P.nstages, grp);
+    for (; tw.tile < P.num_tiles; tw.next(), sw.next(), sw.next(), it += 2) {
+      const int st = sw.st;
+      const int as = it % C::NACC;
+      const uint32_t aph = (uint32_t)((it / C::NACC) & 1);
+      const int tx = tw.tx, ty = tw.ty, n = tw.n;
+      const int y = ty * 16 + ly;
+      const bool smem_res = use_res && !P.res_global;
+      if (smem_res) bar_wait(&full_bar[st], sw.ph);
+      const uint4* a_st = reinterpret_cast<const uint4*>(a_s + (size_t)st * C::A_BYTES);
+#pragma unroll
+      for (int half = 0; half < 2; half++) {
+        const int role = r2 + 2 * half;
+        const int jc = role % NSJ;
+        const int cb = (role / NSJ) * CH;
+        const bool active = role / NSJ < NSC;
+        const float* bias_r = P.bias_c + co0 + (active ? cb : 0);  // warp-uniform constant-bank reads
+        const float* beta_r = P.beta_c + co0 + (active ? cb : 0);
+        uint4 res[NJ * NR];
+        if (use_res && P.res_global) {
+          if (active)
+#pragma unroll
+          for (int jj = 0; jj < NJ; jj++) {
+            const int x = (tx * KW + jj * NSJ + jc) * 8 + lx;
+            const uint4* rp = reinterpret_cast<const uint4*>(P.in + (((size_t)n * P.H + y) * P.W + x) * CIN + co0 + cb);
+            const bool ok = (y < P.H) && (x < P.W);
+#pragma unroll
+            for (int ch = 0; ch < NR; ch++) res[jj * NR + ch] = ok ? __ldg(rp + ch) : make_uint4(0u, 0u, 0u, 0u);
+          }
+        } else if (use_res) {
+          if (active)
+#pragma unroll
+          for (int jj = 0; jj < NJ; jj++) {
+            const int pc = (ly + 1) * C::PITCH + 8 * (jj * NSJ + jc) + lx + 1;  // this thread's centre pixel
+#pragma unroll
+            for (int ch = 0; ch < NR; ch++) {
+              if constexpr (PM) {
+                const int c8 = (co0 + cb) / 8 + ch;
+                const uint32_t row = s_u32(a_s + (size_t)st * C::A_BYTES) + (uint32_t)((c8 >> 3) * C::NPIX * 128 + pc * 128);
+                const uint32_t ad = row + (uint32_t)(((c8 & 7) ^ ((row >> 7) & 7)) << 4);
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(res[jj * NR + ch].x), "=r"(res[jj * NR + ch].y), "=r"(res[jj * NR + ch].z), "=r"(res[jj * NR + ch].w)
+                             : "r"(ad));
+              } else {
+                res[jj * NR + ch] = a_st[((co0 + cb) / 8 + ch) * C::CS + pc];
+              }
+            }
+          }
+          if (half == 1) {   // both halves' residuals are in registers: hand the stage back (fence: see mode 1)
+            if (TMA) fence_async_smem();
+            __syncwarp();
+            if (lane == 0) bar_arrive(&empty_bar[st]);
+          }
+        }
+        if (half == 0) { bar_wait(&tfull_bar[as], aph); tc_after(); }
+        float v[NJ][CH];
+        if (active) {
+#pragma unroll
+          for (int jj = 0; jj < NJ; jj++)
+            ld_cols<CH>(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(as * C::ACC_STRIDE + (jj * NSJ + jc) * CN + cb), v[jj]);
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        }
+        if (half == 1) {     // the buffer's last read: back to the MMA warp
+          tc_before();
+          __syncwarp();
+          if (lane == 0) bar_arrive(&tempty_bar[as]);
+        }
+        if (active) {
+#pragma unroll
+          for (int jj = 0; jj < NJ; jj++) {
+            const int j = jj * NSJ + jc;
+            const int x = (tx * KW + j) * 8 + lx;
+            if ((y < P.H) && (x < P.W)) {
+#pragma unroll
+              for (int i = 0; i < CH; i++) v[jj][i] += bias_r[i];
+              if constexpr (EPI == 1) {
+                static_assert(EPI != 1 || (COUT == 16 && CH == 8), "Head deconv instance");
+                uint4 o;
+                o.x = pk_bf16(v[jj][0], v[jj][1]); o.y = pk_bf16(v[jj][2], v[jj][3]);
+                o.z = pk_bf16(v[jj][4], v[jj][5]); o.w = pk_bf16(v[jj][6], v[jj][7]);
+                *reinterpret_cast<uint4*>(P.out + (((size_t)n * 2 * P.H + 2 * y + (cb >> 3)) * (2 * P.W) + 2 * x) * 4) = o;
+              } else {
+                if (use_res) {
+#pragma unroll
+                  for (int ch = 0; ch < NR; ch++) {
+                    const uint4 r = res[jj * NR + ch];
+                    const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rr[q]));
+                      const int i = ch * 8 + 2 * q;
+                      v[jj][i] = fmaf(v[jj][i], beta_r[i], f.x);
+                      v[jj][i + 1] = fmaf(v[jj][i + 1], beta_r[i + 1], f.y);
+                    }
+                  }
+                }
+                if (P.act) {
+#pragma unroll
+                  for (int i = 0; i < CH; i++) v[jj][i] = v[jj][i] > 0.f ? v[jj][i] : v[jj][i] * P.slope;
+                }
+                bf16* op = P.out + (((size_t)n * P.H + y) * P.W + x) * COUT + co0 + cb;
+                if constexpr (CH >= 16) {
+#pragma unroll
+                  for (int c = 0; c < CH; c += 16) {
+                    uint4 o0, o1;
+                    o0.x = pk_bf16(v[jj][c], v[jj][c + 1]); o0.y = pk_bf16(v[jj][c + 2], v[jj][c + 3]);
+                    o0.z = pk_bf16(v[jj][c + 4], v[jj][c + 5]); o0.w = pk_bf16(v[jj][c + 6], v[jj][c + 7]);
+                    o1.x = pk_bf16(v[jj][c + 8], v[jj][c + 9]); o1.y = pk_bf16(v[jj][c + 10], v[jj][c + 11]);
+                    o1.z = pk_bf16(v[jj][c + 12], v[jj][c + 13]); o1.w = pk_bf16(v[jj][c + 14], v[jj][c + 15]);
+                    st_v8(op + c, o0, o1);
+                  }
+                } else {
+                  uint4 o;
+                  o.x = pk_bf16(v[jj][0], v[jj][1]); o.y = pk_bf16(v[jj][2], v[jj][3]);
+                  o.z = pk_bf16(v[jj][4], v[jj][5]); o.w = pk_bf16(v[jj][6], v[jj][7]);
+                  *reinterpret_cast<uint4*>(op) = o;
+                }
+              }
+            }
+          }
         }
       }
     }
