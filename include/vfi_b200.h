@@ -62,7 +62,7 @@ size_t vfi_device_bytes(vfi_handle* h);
  *                      kernel (csrc/conv_v2.cu) and the stride-2 ones on csrc/conv_s2.cu; 0: TMA-per-tap kernel.
  *   "v2_tma"        1: conv_v2 halo tiles arrive by TMA tensor boxes; 0: by cp.async producer warps.
  *   "fuse_gather"   1: the finest block's input gather is fused with conv0[0] (and hands the summed flow to the blend).
- *   "v2_pm"         0: chunk-major halo tile (16-byte TMA box rows); 1: c = 64 layers use a pixel-major SWIZZLE_128B tile.
+ *   "v2_pm"         1: c = 64 layers use a pixel-major SWIZZLE_128B halo tile (one 128-byte-row TMA box); 0: chunk-major tile (16-byte rows).
  *   "v2_res_global" 0: ResConv residual from the shared-memory tile; 1: from global memory.
  *   "l2_chunk_mb"   0: off; n: run each ResConv chain depth-first over item groups of n MB of activations.
  *   "gc_persistent" 1: the fused finest-block gather is persistent (staging of tile i+1 overlaps tile i's MMAs / epilogue); 0: one tile per CTA.

@@ -58,15 +58,15 @@ def test_parity_uhd_scales(engine, oracle_model, prec, scale, H, W):
     _check(engine, oracle_model, fr[0], fr[1], [0.5], scale, prec)
 
 
-@pytest.mark.parametrize("opts", [{"v2_tma": 0}, {"fuse_gather": 0}, {"conv_v2": 0}, {"v2_res_global": 1}, {"l2_chunk_mb": 1}, {"v2_pm": 1},
+@pytest.mark.parametrize("opts", [{"v2_tma": 0}, {"fuse_gather": 0}, {"conv_v2": 0}, {"v2_res_global": 1}, {"l2_chunk_mb": 1}, {"v2_pm": 0},
                                   {"fuse_gather3": 1}, {"gc_persistent": 0}],
                          ids=lambda o: ",".join(f"{k}={v}" for k, v in o.items()))
 def test_parity_of_every_kernel_variant(engine, oracle_model, opts):
     """vfi_set_option only chooses between kernels that compute the same thing: each non-default path (cp.async
     producers, unfused finest gather + tiled blend, TMA-per-tap convs, residual from global memory, depth-first
-    ResConv chain, pixel-major swizzled c = 64 tiles, block 3's gather fused with its conv0[0], the one-tile-per-CTA form of the
+    ResConv chain, chunk-major c = 64 tiles, block 3's gather fused with its conv0[0], the one-tile-per-CTA form of the
     fused finest gather) meets the bf16 tolerance against the oracle on its own."""
-    defaults = {"v2_tma": 1, "fuse_gather": 1, "conv_v2": 1, "v2_res_global": 0, "l2_chunk_mb": 0, "v2_pm": 0, "fuse_gather3": 0,
+    defaults = {"v2_tma": 1, "fuse_gather": 1, "conv_v2": 1, "v2_res_global": 0, "l2_chunk_mb": 0, "v2_pm": 1, "fuse_gather3": 0,
                 "gc_persistent": 1}
     fr = gen_clip(2, 160, 224, seed=11, cut_every=0, fast=None)
     try:

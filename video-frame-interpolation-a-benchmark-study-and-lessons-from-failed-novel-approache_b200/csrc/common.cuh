@@ -88,8 +88,9 @@ struct vfi_handle {
                                 // activations (in + out) fit this many MB, so a layer reads what the previous one left in L2; 0 = off
                                 // (measured slower at every size: +15 us of fill / drain per extra launch outweighs the L2 hits)
   int opt_v2_res_global = 0;    // vfi_set_option("v2_res_global"): ResConv residual read from global memory, not the smem tile (slower)
-  int opt_v2_pm = 0;            // vfi_set_option("v2_pm"): pixel-major 128-byte-swizzled halo tiles for c = 64 (one wide TMA box per
-                                // tile, tap-shifted SWIZZLE_128B descriptors); same speed as the chunk-major tile, kept as a variant
+  int opt_v2_pm = 1;            // vfi_set_option("v2_pm"): pixel-major 128-byte-swizzled halo tiles for c = 64 (one wide TMA box per
+                                // tile, tap-shifted SWIZZLE_128B descriptors).  Same speed as the chunk-major tile while the epilogue chain
+                                // bound the layer (round 1); 1.5 % of the conv class faster since the two-group epilogue (round 2): default
   int opt_v2_tma = 1;           // vfi_set_option("v2_tma"): conv_v2 halo tiles by TMA (one thread) instead of cp.async producers
   int opt_fuse_gather = 1;      // vfi_set_option("fuse_gather"): finest block's gather fused with conv0[0]
   int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps
