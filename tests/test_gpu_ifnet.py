@@ -178,13 +178,13 @@ def test_conv_v2_halo_tile_kernel(engine, weights, layer, Hin, Win):
     scale = max(1.0, ref.abs().max().item())
     assert (y2 - ref).abs().max().item() <= 1.5e-2 * scale
     assert (y2 - y1).abs().max().item() <= 1.0e-2 * scale          # same operands, different accumulation order + bf16 store
-    if li["cin"] == 64:     # the pixel-major (SWIZZLE_128B, tap-shifted descriptors) and cp.async-fed variants: same MMAs, same bits
-        for opt in ("v2_pm", "v2_tma"):
+    if li["cin"] == 64:     # the chunk-major (default: pixel-major SWIZZLE_128B, tap-shifted descriptors) and cp.async-fed variants:
+        for opt in ("v2_pm", "v2_tma"):   # same MMAs, same bits
             try:
-                engine.set_option(opt, 1 if opt == "v2_pm" else 0)
+                engine.set_option(opt, 0)
                 y3 = engine.debug_conv(layer, _abi.PRECISION_BF16, x, None)
             finally:
-                engine.set_option(opt, 0 if opt == "v2_pm" else 1)
+                engine.set_option(opt, 1)   # both default to 1
             assert torch.equal(y3, y2), opt
 
 
