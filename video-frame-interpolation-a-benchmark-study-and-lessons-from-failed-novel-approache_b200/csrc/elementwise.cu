@@ -969,7 +969,7 @@ __device__ __forceinline__ Tap ld_tap(const Tap* p) {
 // to the region's columns and pre-multiplied by the level's flow scale (a power of two: exact).  The staged rows of all
 // levels are one flat array of 33-float4 rows, so entry e is simply staged row e / 33, column e % 33; the x taps come
 // from the per-call tables (k_build_taps), the level of a row from the host-computed row starts.
-template <int TW, int NT>
+template <int TW, int NT, int UNR = 2>
 __device__ __forceinline__ void flat_stage(const LowSet& L, const GcRows& R, int n, int ox, int oy, int Hp, int Wp, float4* sm,
                                            int tid = -1) {
   constexpr int GC_TW_ = TW, GC_TAB_ = 5 * TW, GC_THREADS_ = NT;
@@ -987,7 +987,7 @@ __device__ __forceinline__ void flat_stage(const LowSet& L, const GcRows& R, int
     ytab[e] = t;
   }
   const int total = R.start[5] * GC_TW_;
-#pragma unroll 4   // loads in flight per thread: 2 -> 4 took 2.8 % off the fused finest gather, 8 made it 8 % slower (B200)
+#pragma unroll UNR   // loads in flight per thread: 4 takes 2.8 % off the persistent fused finest gather (8: 8 % slower); 2 elsewhere
   for (int e = tid; e < total; e += GC_THREADS_) {
     const int u = e / GC_TW_, col = e - u * GC_TW_;
     int k = 0;
@@ -1207,7 +1207,7 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
   // stage tile `t` (flow rows + the mask / feat tap tables) with the NT threads whose ids are tid = 0 .. NT-1
   auto stage = [&](int tx, int ty, int nn, auto nt_tag, int tid) {
     constexpr int NT = decltype(nt_tag)::value;
-    flat_stage<GC_TW, NT>(lows, grows, nn, tx * TL_W - 1, ty * TL_H - 1, Hp, Wp, tl_sm, tid);
+    flat_stage<GC_TW, NT, 4>(lows, grows, nn, tx * TL_W - 1, ty * TL_H - 1, Hp, Wp, tl_sm, tid);
     if (tid >= NT - 2 * GC_TW) {
       const int e = tid - (NT - 2 * GC_TW), ax = e / GC_TW, j = e - ax * GC_TW;
       const Tap* src = ax ? lows.yt[kl] + max(ty * TL_H - 1 + j, 0) : lows.xt[kl] + max(tx * TL_W - 1 + j, 0);
