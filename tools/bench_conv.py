@@ -1,6 +1,9 @@
 #!/usr/bin/env python
 """Time single conv layers through vfi_debug_conv with the library's per-class event timers (conversions excluded).
-    python tools/bench_conv.py [ablate-mask ...]"""
+    python tools/bench_conv.py [ablate-mask ...]
+The producer / MMA-warp masks (1, 2, 64, 128, 256, 512) act in every build; the EPILOGUE masks (4, 8, 16, 32, ...) exist only in the
+single-group epilogue: build csrc with `make NVCC="nvcc -DV2_EPI_GROUPS=1"` for the phase matrix of DESIGN.md section 4b (the shipped
+two-group epilogue carries no ablation branches)."""
 import os
 import sys
 
