@@ -69,7 +69,11 @@ size_t vfi_device_bytes(vfi_handle* h);
  *   "fuse_gather3"  0: block 3 runs gather_s2 + conv_s2; 1: its gather is fused with its conv0[0] like the finest block's
  *                      (same results to the bf16 tolerance; measured 3 % slower per step on B200, kept as a variant).
  *   "gc_ablate": debug only (phase ablation of the fused finest gather).
- *   "v2_ablate", "v2_trace": debug only (tools/bench_conv.py, tools/v2_trace.py). */
+ *   "v2_ablate", "v2_trace": debug only (tools/bench_conv.py, tools/v2_trace.py).
+ *   "ws_guard"      debug only: 1 makes vfi_ifnet_infer_ex and vfi_farneback fill their workspace with a byte pattern, leave a 4 KiB gap after every
+ *                      intermediate buffer they carve from it, and fail with VFI_E_CUDA if a kernel wrote into a gap (one extra
+ *                      memset, one check kernel and a stream synchronise per call, so not under stream capture; 2 = the check's self-test: it
+ *                      overwrites one gap byte itself and the call must fail; tests/test_gpu_bounds.py). */
 int vfi_set_option(vfi_handle* h, const char* key, int value);
 
 /* IFNet weights.  Replaces Model.load_model(dir, -1) (models/sota/rife_wrapper.py:102-103,

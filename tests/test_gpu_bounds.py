@@ -143,3 +143,74 @@ def test_the_guard_itself_catches_a_one_byte_overrun(guarded):
         guarded.check("self-test")
     guarded.buffers.clear()
     assert t.shape == (7,) and float(t.sum()) == 0.0
+
+
+# ---- the library's OWN intermediate buffers: vfi_set_option("ws_guard", 1) (csrc/abi.cu ws_guard_check) ------------------------
+# Every buffer vfi_ifnet_infer_ex carves from its workspace is followed by a 4 KiB pattern gap that a device kernel checks after
+# the blend; the workspace is pattern-filled first, so equal frames with and without the guard also show that no kernel reads
+# workspace bytes it (or an earlier kernel of the same call) did not write.
+KERNEL_VARIANTS = [{}, {"gc_persistent": 0}, {"fuse_gather3": 1}, {"fuse_gather": 0}, {"v2_tma": 0}, {"v2_pm": 0}, {"conv_v2": 0}]
+OPTION_DEFAULTS = {"gc_persistent": 1, "fuse_gather3": 0, "fuse_gather": 1, "v2_tma": 1, "v2_pm": 1, "conv_v2": 1}
+
+
+def _infer_guarded(engine, a, b, ts, scale, precision, **kw):
+    want = engine.infer(a, b, ts, scale, precision, **kw).clone()
+    engine.set_option("ws_guard", 1)
+    try:
+        got = engine.infer(a, b, ts, scale, precision, **kw)          # raises VFIError if a gap byte changed
+    finally:
+        engine.set_option("ws_guard", 0)
+    assert torch.equal(got, want), "frames depend on workspace bytes no kernel of the call wrote"
+
+
+@pytest.mark.parametrize("variant", KERNEL_VARIANTS, ids=lambda v: "-".join(f"{k}{x}" for k, x in v.items()) or "default")
+@pytest.mark.parametrize("H,W", [(45, 71), (129, 250), (270, 482)])
+def test_ifnet_workspace_buffers_stay_in_bounds_bf16(engine, H, W, variant):
+    a, b = _frames(2, H, W, 7), _frames(2, H, W, 8)
+    for k, v in variant.items():
+        engine.set_option(k, v)
+    try:
+        _infer_guarded(engine, a, b, [0.25, 0.5, 0.75], 1.0, _abi.PRECISION_BF16)
+        if min(H, W) >= 128:
+            _infer_guarded(engine, a, b, [0.5], 0.5, _abi.PRECISION_BF16, flags=_abi.FLAG_PAD_REFLECT_EDGE)
+        if min(H, W) >= 260:
+            _infer_guarded(engine, a, b, [0.5], 0.25, _abi.PRECISION_BF16)
+    finally:
+        for k in variant:
+            engine.set_option(k, OPTION_DEFAULTS[k])
+
+
+@pytest.mark.parametrize("H,W", [(45, 71), (270, 482)])
+def test_ifnet_workspace_buffers_stay_in_bounds_fp32_and_clip_mode(engine, H, W):
+    clip = _frames(4, H, W, 9)
+    _infer_guarded(engine, clip[:-1], clip[1:], [0.5], 1.0, _abi.PRECISION_FP32)       # consecutive pairs: shared Head images
+    _infer_guarded(engine, clip[:-1], clip[1:], [0.25, 0.5, 0.75], 1.0, _abi.PRECISION_BF16)
+    if min(H, W) >= 128:
+        _infer_guarded(engine, clip[:1], clip[1:2], [0.5], 0.5, _abi.PRECISION_FP32)
+
+
+def test_workspace_guard_self_test_fires(engine):
+    a, b = _frames(1, 129, 250, 10), _frames(1, 129, 250, 11)
+    engine.set_option("ws_guard", 2)                                   # the library overwrites one gap byte itself
+    try:
+        with pytest.raises(_abi.VFIError, match="workspace guard"):
+            engine.infer(a, b, [0.5], 1.0, _abi.PRECISION_BF16)
+    finally:
+        engine.set_option("ws_guard", 0)
+    engine.infer(a, b, [0.5], 1.0, _abi.PRECISION_BF16)                # and the handle is usable afterwards
+
+
+@pytest.mark.parametrize("H,W", [(100, 100), (129, 250), (270, 482), (360, 641)])
+def test_farneback_workspace_buffers_stay_in_bounds(engine, H, W):
+    a, b = _frames(3, H, W, 12), _frames(3, H, W, 13)
+    for kw in ({}, {"levels": 5, "iterations": 2}, {"poly_n": 7, "poly_sigma": 1.5, "winsize": 21}):
+        want_flow, want_stats = engine.farneback(a, b, want_flow=True, want_stats=True, **kw)
+        want_flow = want_flow.clone()
+        engine.set_option("ws_guard", 1)
+        try:
+            flow, stats = engine.farneback(a, b, want_flow=True, want_stats=True, **kw)   # raises VFIError if a gap byte changed
+            stats_only = engine.farneback(a, b, want_flow=False, want_stats=True, **kw)   # final flow lands in the workspace
+        finally:
+            engine.set_option("ws_guard", 0)
+        # the pattern-filled workspace changes nothing: no kernel reads bytes the call did not write
+        assert torch.equal(flow, want_flow) and torch.equal(stats, want_stats) and torch.equal(stats_only, want_stats)

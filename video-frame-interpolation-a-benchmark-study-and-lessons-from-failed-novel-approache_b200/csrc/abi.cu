@@ -126,6 +126,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!strcmp(key, "gc_persistent")) { h->opt_gc_persistent = value; return VFI_OK; }
   if (!strcmp(key, "gc_ablate")) { h->opt_gc_ablate = value; return VFI_OK; }
   if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }
+  if (!strcmp(key, "ws_guard")) { h->opt_ws_guard = value; return VFI_OK; }
   VFI_FAIL(h, VFI_E_ARG, "unknown option %s", key);
 }
 
@@ -228,15 +229,32 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_load_weights(vfi
 }
 
 // ---------------------------------------------------------------------------------------------
-struct Carve {
-  uint8_t* base; size_t off;
-  template <typename T> T* take(size_t n) {
-    off = (off + 1023) & ~(size_t)1023;
-    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
-    off += n * sizeof(T);
-    return p;
-  }
-};
+// Debug check behind vfi_set_option("ws_guard", 1) (tests/test_gpu_bounds.py): the workspace is filled with WS_GUARD_BYTE before
+// the schedule runs, every carved buffer is followed by a gap no kernel may write, and this kernel counts the gap bytes that
+// changed (bad[0]) and keeps the lowest gap index among them (bad[1]).
+__global__ void ws_guard_check_kernel(const uint8_t* __restrict__ ws, const unsigned long long* __restrict__ gaps, int ngaps,
+                                      unsigned long long* __restrict__ bad) {
+  const int g = blockIdx.x;
+  if (g >= ngaps) return;
+  const uint8_t* p = ws + gaps[2 * g];
+  const unsigned long long len = gaps[2 * g + 1];
+  unsigned long long mine = 0;
+  for (unsigned long long i = threadIdx.x; i < len; i += blockDim.x) mine += p[i] != WS_GUARD_BYTE;
+  if (mine) { atomicAdd(&bad[0], mine); atomicMin(&bad[1], (unsigned long long)g); }
+}
+int vfi_ws_guard_check(vfi_handle* h, const std::vector<unsigned long long>& gaps, unsigned long long* dev /* 2 + gaps */,
+                          cudaStream_t s) {
+  const int ngaps = (int)(gaps.size() / 2);
+  const unsigned long long init[2] = {0ull, ~0ull};
+  VFI_CUDA(h, cudaMemcpyAsync(dev, init, sizeof(init), cudaMemcpyHostToDevice, s));
+  VFI_CUDA(h, cudaMemcpyAsync(dev + 2, gaps.data(), gaps.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice, s));
+  ws_guard_check_kernel<<<ngaps, 256, 0, s>>>((const uint8_t*)h->ws, dev + 2, ngaps, dev);
+  unsigned long long bad[2];
+  VFI_CUDA(h, cudaMemcpyAsync(bad, dev, sizeof(bad), cudaMemcpyDeviceToHost, s));
+  VFI_CUDA(h, cudaStreamSynchronize(s));
+  if (bad[0]) VFI_FAIL(h, VFI_E_CUDA, "workspace guard: %llu byte(s) written past the end of carved buffer %llu (of %d)", bad[0], bad[1], ngaps);
+  return VFI_OK;
+}
 
 static int run_conv(vfi_handle* h, const Layer& L, const void* in, const void* res, void* out, int N, int Hin,
                     int Win, bool bf, bool out_phase, cudaStream_t s) {
@@ -301,10 +319,13 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer_ex(vfi_han
   const int last_c = !bf ? 16 : (fused && Lf[10].wv2) ? 4 : 8;
   const size_t px = (size_t)Hp * Wp;
   Carve cv{nullptr, 0};
+  std::vector<unsigned long long> guard_gaps;
+  if (h->opt_ws_guard) { cv.guard = WS_GUARD_BYTES; cv.gaps = &guard_gaps; }
   for (int pass = 0; pass < 2; pass++) {
     cv.off = 0;
     cv.base = pass ? (uint8_t*)h->ws : nullptr;
     if (pass == 0) { /* sizing pass */ }
+    if (cv.guard) cv.take<uint8_t>(0);                    // a gap before the first buffer too
     uint8_t* imgs = cv.take<uint8_t>(NI * px * 4);
     uint8_t* feats = cv.take<uint8_t>(NI * px * 4 * esz);
     uint8_t* ht0 = cv.take<uint8_t>(NI * (px / 4) * 16 * esz);
@@ -330,11 +351,18 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer_ex(vfi_han
     uint8_t* a0 = cv.take<uint8_t>(a0_e * esz);
     uint8_t* fa = cv.take<uint8_t>(f_e * esz);
     uint8_t* fb = cv.take<uint8_t>(f_e * esz);
+    const size_t guarded_bytes = cv.off;
+    unsigned long long* guard_dev = nullptr;
+    if (cv.guard) guard_dev = ws_guard_scratch(cv);        // the check's own counters + gap list, outside the guarded range
     if (pass == 0) {
       if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc;
       continue;
     }
     int rc;
+    if (cv.guard) {
+      if (guard_gaps.size() > 2 * WS_GUARD_MAX_GAPS) VFI_FAIL(h, VFI_E_ARG, "ws_guard: too many carved buffers");
+      VFI_CUDA(h, cudaMemsetAsync(h->ws, WS_GUARD_BYTE, guarded_bytes, s));
+    }
     if (T != h->t_n || memcmp(h->t_host, timesteps, T * sizeof(float))) {  // steady state (same timesteps every call): no copy
       memcpy(h->t_host, timesteps, T * sizeof(float));
       h->t_n = 0;  // invalid until the copy is enqueued
@@ -397,6 +425,11 @@ extern "C" __attribute__((visibility("default"))) int vfi_ifnet_infer_ex(vfi_han
       else lows.push(low[i], sc, lc, Hp, Wp, taps + (size_t)i * (Hp + Wp));
     }
     if ((rc = k_final_blend(h, imgs, lows, flow_pre, hud_mask, tdev, out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, s, bgr))) return rc;
+    if (cv.guard) {
+      // value 2 = the check's self-test: one byte of the fourth gap is overwritten on purpose and the call must fail
+      if (h->opt_ws_guard == 2) VFI_CUDA(h, cudaMemsetAsync((uint8_t*)h->ws + guard_gaps[2 * 3], 0, 1, s));
+      if ((rc = vfi_ws_guard_check(h, guard_gaps, guard_dev, s))) return rc;
+    }
   }
   return VFI_OK;
 }

@@ -95,6 +95,7 @@ struct vfi_handle {
   int opt_fuse_gather = 1;      // vfi_set_option("fuse_gather"): finest block's gather fused with conv0[0]
   int opt_v2_trace = 0;         // debug only: conv_v2 dumps CTA 0's pipeline time stamps
   int opt_v2_ablate = 0;        // debug only: see V2Params::ablate
+  int opt_ws_guard = 0;         // debug only: vfi_ifnet_infer_ex checks pattern gaps between its workspace buffers (abi.cu ws_guard_check)
   int opt_fuse_gather3 = 0;     // vfi_set_option("fuse_gather3"): block 3's (s = 2) gather fused with its conv0[0].  OFF: measured 3 % SLOWER
                                 // per step than gather_s2 + conv_s2 (18 instead of 24 resident warps on a latency-bound gather)
   int opt_gc_persistent = 1;    // vfi_set_option("gc_persistent"): persistent, phase-overlapped form of the fused finest-block gather
@@ -181,6 +182,37 @@ static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b)
 
 // arena helpers (abi.cu)
 int vfi_ws_reserve(vfi_handle* h, size_t bytes);
+// Carves the buffers of one call out of the handle's workspace (first pass with base = nullptr sizes it).  With
+// vfi_set_option("ws_guard") every buffer is followed by a pattern gap that vfi_ws_guard_check verifies after the call's kernels.
+#define WS_GUARD_BYTE 0xA5
+#define WS_GUARD_BYTES 4096
+#define WS_GUARD_MAX_GAPS 64
+struct Carve {
+  uint8_t* base; size_t off;
+  size_t guard = 0;                                      // vfi_set_option("ws_guard"): bytes of pattern kept after every buffer
+  std::vector<unsigned long long>* gaps = nullptr;       // (offset, length) of each guard gap, filled on the carving pass
+  template <typename T> T* take(size_t n) {
+    off = (off + 1023) & ~(size_t)1023;
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += n * sizeof(T);
+    if (guard) {
+      // the gap runs from the buffer's last byte to the next buffer's 1 KiB-aligned start
+      const size_t end = (off + guard + 1023) & ~(size_t)1023;
+      if (gaps && base) { gaps->push_back(off); gaps->push_back(end - off); }
+      off = end;
+    }
+    return p;
+  }
+};
+// device scratch of the check: 2 counters + the gap list; take it with cv.guard = 0, outside the guarded range
+inline unsigned long long* ws_guard_scratch(Carve& cv) {
+  const size_t g = cv.guard;
+  cv.guard = 0;
+  unsigned long long* p = cv.take<unsigned long long>(2 + 2 * WS_GUARD_MAX_GAPS);
+  cv.guard = g;
+  return p;
+}
+int vfi_ws_guard_check(vfi_handle* h, const std::vector<unsigned long long>& gaps, unsigned long long* dev, cudaStream_t s);
 int vfi_red_reserve(vfi_handle* h, size_t bytes);
 
 // ---- elementwise.cu -----------------------------------------------------------------------

@@ -455,16 +455,6 @@ void prepare_poly(int n, double sigma, FbPoly& P) {
   P.ig11 = inv[1][1]; P.ig03 = inv[0][3]; P.ig33 = inv[3][3]; P.ig55 = inv[5][5];
 }
 
-struct Carve {
-  uint8_t* base; size_t off;
-  template <typename T> T* take(size_t n) {
-    off = (off + 1023) & ~(size_t)1023;
-    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
-    off += n * sizeof(T);
-    return p;
-  }
-};
-
 }  // namespace
 
 extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* h, const uint8_t* img0, const uint8_t* img1, int n, int H, int W,
@@ -491,9 +481,12 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
   const size_t px = (size_t)H * W;
   const int chunk = std::min(n, 8);
   Carve cv{nullptr, 0};
+  std::vector<unsigned long long> guard_gaps;              // vfi_set_option("ws_guard"): pattern gaps around every buffer, checked below
+  if (h->opt_ws_guard) { cv.guard = WS_GUARD_BYTES; cv.gaps = &guard_gaps; }
   for (int pass = 0; pass < 2; pass++) {
     cv.off = 0;
     cv.base = pass ? (uint8_t*)h->ws : nullptr;
+    if (cv.guard) cv.take<uint8_t>(0);
     uint8_t* gray = cv.take<uint8_t>((size_t)chunk * 2 * px);
     float* A = cv.take<float>((size_t)chunk * 2 * px);
     float* I = cv.take<float>((size_t)chunk * 2 * px);
@@ -503,7 +496,10 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
     float2* fA = cv.take<float2>((size_t)chunk * px);
     float2* fB = cv.take<float2>((size_t)chunk * px);
     float2* tmpf = cv.take<float2>((size_t)chunk * px);
+    const size_t guarded_bytes = cv.off;
+    unsigned long long* guard_dev = cv.guard ? ws_guard_scratch(cv) : nullptr;
     if (pass == 0) { if (int rc = vfi_ws_reserve(h, cv.off + 4096)) return rc; continue; }
+    if (cv.guard) VFI_CUDA(h, cudaMemsetAsync(h->ws, WS_GUARD_BYTE, guarded_bytes, s));
     for (int n0 = 0; n0 < n; n0 += chunk) {
       const int nn = std::min(chunk, n - n0);
       ProfScope ps(h, PC_REDUCE, s);
@@ -567,6 +563,8 @@ extern "C" __attribute__((visibility("default"))) int vfi_farneback(vfi_handle* 
       if (stats_out)
         if (int rc = vfi_flow_stats_impl(h, reinterpret_cast<const float*>(prev), nn, H, W, stats_out + (size_t)3 * n0, s)) return rc;
     }
+    if (cv.guard)
+      if (int rc = vfi_ws_guard_check(h, guard_gaps, guard_dev, s)) return rc;
   }
   return VFI_OK;
 }
