@@ -76,9 +76,13 @@ __device__ __forceinline__ Bil bil_setup(float fx, float fy, int W, int H) {
 }
 // byte k of a packed RGBX word as float, exact, on the full-rate pipes (PRMT + FADD instead of the quarter-rate I2F):
 // 0x4B0000bb is the float 8388608 + bb
+// PRMT takes ONE immediate: with the literal 0x4B000000 in it the selector travels through a register and every byte costs
+// an extra MOV (a tenth of the blend kernel's instructions).  Read from constant memory the word lives in a register for the
+// whole kernel and the selector becomes the immediate.
+__constant__ uint32_t c_u8f_magic = 0x4B000000u;
 template <int K>
 __device__ __forceinline__ float u8f(uint32_t v) {
-  return __uint_as_float(__byte_perm(v, 0x4B000000u, 0x7440 | K)) - 8388608.0f;
+  return __uint_as_float(__byte_perm(v, c_u8f_magic, 0x7440 | K)) - 8388608.0f;
 }
 __device__ __forceinline__ void sample_rgbx(const uint8_t* img, const Bil& b, float* rgb) {
   const uint32_t* p = reinterpret_cast<const uint32_t*>(img);
