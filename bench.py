@@ -635,7 +635,7 @@ def main():
     with contextlib.redirect_stdout(sys.stderr):   # the wrapper prints "Loading RIFE ..." like the reference; stdout is the JSON line only
         model.load()
     eng = model._engine
-    for opt in ("l2_chunk_mb", "fuse_gather", "conv_v2", "v2_tma", "v2_res_global", "v2_pm", "gc_ablate", "gc_persistent", "fuse_gather3"):  # tuning knobs of the library (defaults are the shipped ones)
+    for opt in ("l2_chunk_mb", "fuse_gather", "conv_v2", "v2_tma", "v2_res_global", "v2_pm", "gc_ablate", "gc_persistent", "fuse_gather3", "t_fast"):  # tuning knobs of the library (defaults are the shipped ones)
         if os.environ.get("VFI_" + opt.upper()) is not None:
             eng.set_option(opt, int(os.environ["VFI_" + opt.upper()]))
     B, T = args.pairs, len(TIMESTEPS)

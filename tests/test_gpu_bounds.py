@@ -149,8 +149,8 @@ def test_the_guard_itself_catches_a_one_byte_overrun(guarded):
 # Every buffer vfi_ifnet_infer_ex carves from its workspace is followed by a 4 KiB pattern gap that a device kernel checks after
 # the blend; the workspace is pattern-filled first, so equal frames with and without the guard also show that no kernel reads
 # workspace bytes it (or an earlier kernel of the same call) did not write.
-KERNEL_VARIANTS = [{}, {"gc_persistent": 0}, {"fuse_gather3": 1}, {"fuse_gather": 0}, {"v2_tma": 0}, {"v2_pm": 0}, {"conv_v2": 0}]
-OPTION_DEFAULTS = {"gc_persistent": 1, "fuse_gather3": 0, "fuse_gather": 1, "v2_tma": 1, "v2_pm": 1, "conv_v2": 1}
+KERNEL_VARIANTS = [{}, {"gc_persistent": 0}, {"fuse_gather3": 1}, {"fuse_gather": 0}, {"v2_tma": 0}, {"v2_pm": 0}, {"conv_v2": 0}, {"t_fast": 0}]
+OPTION_DEFAULTS = {"gc_persistent": 1, "fuse_gather3": 0, "fuse_gather": 1, "v2_tma": 1, "v2_pm": 1, "conv_v2": 1, "t_fast": 1}
 
 
 def _infer_guarded(engine, a, b, ts, scale, precision, **kw):

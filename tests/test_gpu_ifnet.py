@@ -59,15 +59,15 @@ def test_parity_uhd_scales(engine, oracle_model, prec, scale, H, W):
 
 
 @pytest.mark.parametrize("opts", [{"v2_tma": 0}, {"fuse_gather": 0}, {"conv_v2": 0}, {"v2_res_global": 1}, {"l2_chunk_mb": 1}, {"v2_pm": 0},
-                                  {"fuse_gather3": 1}, {"gc_persistent": 0}],
+                                  {"fuse_gather3": 1}, {"gc_persistent": 0}, {"t_fast": 0}],
                          ids=lambda o: ",".join(f"{k}={v}" for k, v in o.items()))
 def test_parity_of_every_kernel_variant(engine, oracle_model, opts):
     """vfi_set_option only chooses between kernels that compute the same thing: each non-default path (cp.async
     producers, unfused finest gather + tiled blend, TMA-per-tap convs, residual from global memory, depth-first
     ResConv chain, chunk-major c = 64 tiles, block 3's gather fused with its conv0[0], the one-tile-per-CTA form of the
-    fused finest gather) meets the bf16 tolerance against the oracle on its own."""
+    fused finest gather, the item-major tile order of the gathers and the blend) meets the bf16 tolerance against the oracle on its own."""
     defaults = {"v2_tma": 1, "fuse_gather": 1, "conv_v2": 1, "v2_res_global": 0, "l2_chunk_mb": 0, "v2_pm": 1, "fuse_gather3": 0,
-                "gc_persistent": 1}
+                "gc_persistent": 1, "t_fast": 1}
     fr = gen_clip(2, 160, 224, seed=11, cut_every=0, fast=None)
     try:
         for k, v in opts.items():
@@ -78,6 +78,24 @@ def test_parity_of_every_kernel_variant(engine, oracle_model, opts):
         assert np.array_equal(two[1], one[0])
     finally:
         for k, v in defaults.items():
+            engine.set_option(k, v)
+
+
+@pytest.mark.parametrize("prec", [_abi.PRECISION_FP32, _abi.PRECISION_BF16])
+@pytest.mark.parametrize("other", [{}, {"gc_persistent": 0}, {"fuse_gather": 0}], ids=["default", "one-tile-gather", "unfused-gather"])
+def test_tile_order_changes_no_bit(engine, prec, other):
+    """"t_fast" only permutes the order in which the gathers and the blend visit their (tile, item) pairs (timestep-fastest, so a
+    pair's images are read once for all T items): frames and flow are identical to the item-major order, bit for bit."""
+    fr = gen_clip(3, 200, 300, seed=13, cut_every=0, fast=None)
+    try:
+        for k, v in other.items():
+            engine.set_option(k, v)
+        got = [t.clone() for t in engine.infer(fr[:3], fr[1:4], [0.25, 0.5, 0.75, 0.9], 1.0, prec, want_flow=True)]
+        engine.set_option("t_fast", 0)
+        want = engine.infer(fr[:3], fr[1:4], [0.25, 0.5, 0.75, 0.9], 1.0, prec, want_flow=True)
+        assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+    finally:
+        for k, v in {"t_fast": 1, "gc_persistent": 1, "fuse_gather": 1}.items():
             engine.set_option(k, v)
 
 

@@ -124,6 +124,7 @@ extern "C" __attribute__((visibility("default"))) int vfi_set_option(vfi_handle*
   if (!strcmp(key, "l2_chunk_mb")) { h->opt_l2_chunk_mb = value; return VFI_OK; }
   if (!strcmp(key, "fuse_gather3")) { h->opt_fuse_gather3 = value; return VFI_OK; }
   if (!strcmp(key, "gc_persistent")) { h->opt_gc_persistent = value; return VFI_OK; }
+  if (!strcmp(key, "t_fast")) { h->opt_t_fast = value; return VFI_OK; }
   if (!strcmp(key, "gc_ablate")) { h->opt_gc_ablate = value; return VFI_OK; }
   if (!strcmp(key, "v2_trace")) { h->opt_v2_trace = value; return VFI_OK; }
   if (!strcmp(key, "ws_guard")) { h->opt_ws_guard = value; return VFI_OK; }

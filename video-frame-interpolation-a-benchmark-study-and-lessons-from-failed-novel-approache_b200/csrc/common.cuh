@@ -99,6 +99,8 @@ struct vfi_handle {
   int opt_fuse_gather3 = 0;     // vfi_set_option("fuse_gather3"): block 3's (s = 2) gather fused with its conv0[0].  OFF: measured 3 % SLOWER
                                 // per step than gather_s2 + conv_s2 (18 instead of 24 resident warps on a latency-bound gather)
   int opt_gc_persistent = 1;    // vfi_set_option("gc_persistent"): persistent, phase-overlapped form of the fused finest-block gather
+  int opt_t_fast = 1;           // vfi_set_option("t_fast"): the gathers and the blend walk their tiles timestep-fastest, so the T items of a
+                                // pair share the pair's image reads in L2 (item-major order re-read every image from DRAM once per timestep)
   int opt_gc_ablate = 0;        // debug only: gather_conv0a phases off (1 staging, 2 gather, 4 MMA + epilogue, 8 flow evaluation)
   int opt_conv_v2 = 1;          // vfi_set_option("conv_v2"): resident-weight halo-tile conv kernel where it applies
   // optional per-kernel-class timing (vfi_profile_enable): event pairs around every launch

@@ -768,10 +768,12 @@ __global__ void __launch_bounds__(TL_THREADS) final_blend_kernel(const uint8_t* 
                                                                  uint8_t* __restrict__ out,
                                                                  float* __restrict__ out_f32,
                                                                  float* __restrict__ flow_out, int B, int I1, int Tn, int H,
-                                                                 int W, int Hp, int Wp, int bgr) {
+                                                                 int W, int Hp, int Wp, int bgr, int Tr) {
   extern __shared__ float4 tl_sm[];
   __shared__ __align__(16) uint8_t s_rgb[TL_H][TL_W * 3];  // the tile's u8 result, stored row-wise as 32-bit words
-  const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
+  // grid (tiles_x * Tr, tiles_y, items / Tr): Tr = T puts the T timesteps of a pair side by side (shared image reads in L2)
+  const int bxq = blockIdx.x / Tr;
+  const int n = blockIdx.z * Tr + (blockIdx.x - bxq * Tr), tx0 = bxq * TL_W, ty0 = blockIdx.y * TL_H;
   if (!PRE) {
     tile_stage<2>(lows, n, tx0, ty0, Hp, Wp, tl_sm);
     __syncthreads();
@@ -844,7 +846,8 @@ int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const 
                   int Wp, cudaStream_t s, int bgr) {
   ProfScope _ps(h, PC_BLEND, s);
   const size_t smem = tl_smem_bytes(lows, 2);
-  const dim3 grid((W + TL_W - 1) / TL_W, (H + TL_H - 1) / TL_H, B * T);
+  const int Tr = h->opt_t_fast ? T : 1;
+  const dim3 grid((W + TL_W - 1) / TL_W * Tr, (H + TL_H - 1) / TL_H, B * T / Tr);
   if (flow_pre) {
     if (lows.n < 1 || lows.s[lows.n - 1] != 1) VFI_FAIL(h, VFI_E_ARG, "final blend: pre-summed flow needs a full-resolution last level");
     LowSet last;
@@ -852,14 +855,14 @@ int k_final_blend(vfi_handle* h, const uint8_t* imgs, const LowSet& lows, const 
     last.push(lows.p[lows.n - 1], 1, lows.c4[lows.n - 1] * 4, Hp, Wp);
     if (lows.c4[lows.n - 1] == 1)  // fp16 texels
       final_blend_kernel<2><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
-                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, bgr);
+                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, bgr, Tr);
     else if (lows.c4[lows.n - 1] == 2)
       final_blend_kernel<1><<<grid, TL_THREADS, 0, s>>>(imgs, last, reinterpret_cast<const float4*>(flow_pre), hud, tsteps_dev,
-                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, bgr);
+                                                        out, out_f32, flow_out, B, I1, T, H, W, Hp, Wp, bgr, Tr);
     else VFI_FAIL(h, VFI_E_ARG, "final blend: pre-summed flow needs the compact last level");
   } else {
     final_blend_kernel<0><<<grid, TL_THREADS, smem, s>>>(imgs, lows, nullptr, hud, tsteps_dev, out, out_f32, flow_out, B,
-                                                             I1, T, H, W, Hp, Wp, bgr);
+                                                             I1, T, H, W, Hp, Wp, bgr, Tr);
   }
   VFI_LAUNCHED(h);
   return 0;
@@ -1191,7 +1194,7 @@ __global__ void __launch_bounds__(GC_THREADS, 2)
 gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
                        const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
                        bf16* __restrict__ out, float4* __restrict__ flow_sum, const __grid_constant__ GcRows grows, int B, int I1, int Tn, int Hp,
-                       int Wp, float slope, int stage_bytes, int tiles_x, int tiles_y, int num_tiles) {
+                       int Wp, float slope, int stage_bytes, int tiles_x, int tiles_y, int num_tiles, int tfast) {
   using namespace umma;
   extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
   __shared__ uint64_t mma_bar;
@@ -1220,8 +1223,15 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
   };
   // tile -> (tx, ty, n) once; afterwards the mixed-radix coordinates advance by the (decomposed) grid stride: no integer
   // divisions in the loop (they were 6 % of the kernel's instructions)
-  int ctx = tile % tiles_x, cty = (tile / tiles_x) % tiles_y, cn = tile / (tiles_x * tiles_y);
-  const int g = (int)gridDim.x, gsx = g % tiles_x, gsy = (g / tiles_x) % tiles_y, gsn = g / (tiles_x * tiles_y);
+  // Tile order (tfast): TIMESTEP fastest, then x, y, pair -- the T items of a pair warp the same two images (features and
+  // RGBX, 24 B per pixel and image), so the CTAs working side by side read one image region for all T timesteps while it is
+  // in L2; item-major order re-read every image from DRAM once per timestep (one item's reads + writes ~ the L2 size).
+  // tfast = 0 keeps the item-major order: the timestep digit then has radix 1 and the top digit is the item.
+  const int Tr = tfast ? Tn : 1;
+  int ct = tile % Tr, ctx = (tile / Tr) % tiles_x, cty = (tile / (Tr * tiles_x)) % tiles_y, ctop = tile / (Tr * tiles_x * tiles_y);
+  const int g = (int)gridDim.x, gst = g % Tr, gsx = (g / Tr) % tiles_x, gsy = (g / (Tr * tiles_x)) % tiles_y,
+            gstop = g / (Tr * tiles_x * tiles_y);
+  int cn = ctop * Tr + ct;                                 // item = pair * T + timestep
   if (tile < num_tiles) stage(ctx, cty, cn, std::integral_constant<int, GC_THREADS>{}, (int)threadIdx.x);
   fence_async_smem();
   tc_before();
@@ -1234,12 +1244,14 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
   const bf16 *mfp = lows.mf[kl], *f7p = lows.f7[kl];
   for (int it = 0; tile < num_tiles; tile += g, it++) {
     const int tx0 = ctx * TL_W, ty0 = cty * TL_H, n = cn;
-    // the next tile of this CTA
-    ctx += gsx; cty += gsy; cn += gsn;
-    if (ctx >= tiles_x) { ctx -= tiles_x; cty++; }
-    if (cty >= tiles_y) { cty -= tiles_y; cn++; }
-    const int b = n / Tn;
+    const int b = tfast ? ctop : n / Tn;
     const float t = tsteps[n - b * Tn];
+    // the next tile of this CTA
+    ct += gst; ctx += gsx; cty += gsy; ctop += gstop;
+    if (ct >= Tr) { ct -= Tr; ctx++; }
+    if (ctx >= tiles_x) { ctx -= tiles_x; cty++; }
+    if (cty >= tiles_y) { cty -= tiles_y; ctop++; }
+    cn = ctop * Tr + ct;
     const int base0 = b * plane, base1 = (I1 + b) * plane;
     const int mtb = n * lows.Hl[kl] * mWl;
     float4* fsum = flow_sum ? flow_sum + (size_t)n * plane : nullptr;
@@ -1370,7 +1382,7 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
     const int tiles_x = Wp / TL_W, tiles_y = Hp / TL_H, num_tiles = tiles_x * tiles_y * B * T;
     gather_conv0a_p_kernel<bf16><<<std::min(num_tiles, 2 * h->sm_count), GC_THREADS, smem, s>>>(
         imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out, reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, Hp, Wp,
-        h->slope, (int)un, tiles_x, tiles_y, num_tiles);
+        h->slope, (int)un, tiles_x, tiles_y, num_tiles, h->opt_t_fast);
     VFI_LAUNCHED(h);
     return 0;
   }
@@ -1394,9 +1406,12 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
 __global__ void __launch_bounds__(G2_THREADS, 3)
 gather_s2_kernel(const uint8_t* __restrict__ imgs, const bf16* __restrict__ feats, const __grid_constant__ LowSet lows,
                  const __grid_constant__ GcRows grows, const float* __restrict__ tsteps, bf16* __restrict__ out, int B, int I1,
-                 int Tn, int Hp, int Wp, int phase) {
+                 int Tn, int Hp, int Wp, int phase, int Tr) {
   extern __shared__ float4 tl_sm[];
-  const int n = blockIdx.z, tx0 = blockIdx.x * TL_W, ty0 = blockIdx.y * TL_H;
+  // grid (tiles_x * Tr, tiles_y, items / Tr): with Tr = T the T timesteps of a pair sit side by side in launch order and share
+  // the pair's image reads in L2 (see gather_conv0a_p_kernel); Tr = 1 is the item-major order
+  const int bxq = blockIdx.x / Tr;
+  const int n = blockIdx.z * Tr + (blockIdx.x - bxq * Tr), tx0 = bxq * TL_W, ty0 = blockIdx.y * TL_H;
   flat_stage<TL_W, G2_THREADS>(lows, grows, n, tx0, ty0, Hp, Wp, tl_sm);
   __syncthreads();
   const int b = n / Tn;
@@ -1465,8 +1480,9 @@ static int launch_gather_s2(vfi_handle* h, const uint8_t* imgs, const bf16* feat
                             bf16* out, int B, int I1, int T, int Hp, int Wp, bool phase, cudaStream_t s) {
   GcRows grows;
   const size_t smem = gc_stage_bytes(lows, &grows, TL_W);
-  const dim3 grid(Wp / TL_W, Hp / TL_H, B * T);
-  gather_s2_kernel<<<grid, G2_THREADS, smem, s>>>(imgs, feats, lows, grows, tsteps_dev, out, B, I1, T, Hp, Wp, phase ? 1 : 0);
+  const int Tr = h->opt_t_fast ? T : 1;
+  const dim3 grid(Wp / TL_W * Tr, Hp / TL_H, B * T / Tr);
+  gather_s2_kernel<<<grid, G2_THREADS, smem, s>>>(imgs, feats, lows, grows, tsteps_dev, out, B, I1, T, Hp, Wp, phase ? 1 : 0, Tr);
   VFI_LAUNCHED(h);
   return 0;
 }
@@ -1737,11 +1753,16 @@ int k_gather_s2_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, con
 __global__ void __launch_bounds__(128) gather_lo_kernel(const uint8_t* __restrict__ imgs, const bf16* __restrict__ feats,
                                                         const __grid_constant__ LowSet lows, const float* __restrict__ tsteps,
                                                         bf16* __restrict__ out, int B, int I1, int Tn, int Hp, int Wp, int s,
-                                                        int phase) {
+                                                        int phase, int Tr) {
   const int Hs = Hp / s, Ws = Wp / s;
-  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i >= (size_t)B * Tn * Hs * Ws) return;
-  const int X = (int)(i % Ws), Y = (int)((i / Ws) % Hs), n = (int)(i / ((size_t)Ws * Hs));
+  const size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i0 >= (size_t)B * Tn * Hs * Ws) return;
+  // thread order: x, then (Tr = T) the timestep, then y, then the pair -- a row of all T items before the next row, so the items
+  // of a pair share their image reads in L2; Tr = 1 is the item-major order.  i = the item-major index the output uses
+  const int X = (int)(i0 % Ws);
+  const size_t r = i0 / Ws, r2 = r / Tr;
+  const int Y = (int)(r2 % Hs), n = (int)(r2 / Hs) * Tr + (int)(r - r2 * Tr);
+  const size_t i = ((size_t)n * Hs + Y) * Ws + X;
   const int b = n / Tn;
   const float t = tsteps[n - b * Tn];
   const int plane = Hp * Wp;
@@ -1816,7 +1837,8 @@ __global__ void __launch_bounds__(128) gather_lo_kernel(const uint8_t* __restric
 static int launch_gather_lo(vfi_handle* h, const uint8_t* imgs, const bf16* feats, const LowSet& lows, const float* tsteps_dev,
                             bf16* out, int B, int I1, int T, int Hp, int Wp, int s_int, bool phase, cudaStream_t s) {
   const size_t total = (size_t)B * T * (Hp / s_int) * (Wp / s_int);
-  gather_lo_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, feats, lows, tsteps_dev, out, B, I1, T, Hp, Wp, s_int, phase ? 1 : 0);
+  gather_lo_kernel<<<cdiv(total, 128), 128, 0, s>>>(imgs, feats, lows, tsteps_dev, out, B, I1, T, Hp, Wp, s_int, phase ? 1 : 0,
+                                                    h->opt_t_fast ? T : 1);
   VFI_LAUNCHED(h);
   return 0;
 }
