@@ -69,7 +69,8 @@ size_t vfi_device_bytes(vfi_handle* h);
  *   "fuse_gather3"  0: block 3 runs gather_s2 + conv_s2; 1: its gather is fused with its conv0[0] like the finest block's
  *                      (same results to the bf16 tolerance; measured 3 % slower per step on B200, kept as a variant).
  *   "t_fast"        1: the gathers and the blend walk their tiles timestep-fastest (the T items of a pair side by side, so the pair's
- *                      images are read from DRAM once, not once per timestep); 0: item-major order.
+ *                      images are read from DRAM once, not once per timestep); 0: item-major order; 2: as 1 with the pairs next
+ *                      in the fused finest gather (timestep, pair, x, y: measured equal to 1).  Bit-identical results.
  *   "gc_ablate": debug only (phase ablation of the fused finest gather).
  *   "v2_ablate", "v2_trace": debug only (tools/bench_conv.py, tools/v2_trace.py).
  *   "ws_guard"      debug only: 1 makes vfi_ifnet_infer_ex and vfi_farneback fill their workspace with a byte pattern, leave a 4 KiB gap after every

@@ -91,9 +91,10 @@ def test_tile_order_changes_no_bit(engine, prec, other):
         for k, v in other.items():
             engine.set_option(k, v)
         got = [t.clone() for t in engine.infer(fr[:3], fr[1:4], [0.25, 0.5, 0.75, 0.9], 1.0, prec, want_flow=True)]
-        engine.set_option("t_fast", 0)
-        want = engine.infer(fr[:3], fr[1:4], [0.25, 0.5, 0.75, 0.9], 1.0, prec, want_flow=True)
-        assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+        for order in (0, 2):                                   # item-major; (timestep, pair, x, y) in the fused finest gather
+            engine.set_option("t_fast", order)
+            want = engine.infer(fr[:3], fr[1:4], [0.25, 0.5, 0.75, 0.9], 1.0, prec, want_flow=True)
+            assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1]), order
     finally:
         for k, v in {"t_fast": 1, "gc_persistent": 1, "fuse_gather": 1}.items():
             engine.set_option(k, v)

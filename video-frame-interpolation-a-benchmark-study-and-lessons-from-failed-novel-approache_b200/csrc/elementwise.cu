@@ -1189,12 +1189,14 @@ gather_conv0a_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ fea
 // up once per CTA, and while warps 0-3 issue tile i's MMAs and run its epilogue, warps 4-11 already stage the flow rows of
 // tile i+1 -- the two latency-bound phases overlap instead of adding (phase ablation on B200, 24 items of 1080p: set-up
 // 0.37 ms + staging 0.41 + gather 1.22 + MMA / epilogue 0.33 = the one-tile kernel's 2.28 ms).
-template <typename T>
+// ORDER: the tile order, a compile-time choice (the kernel sits at its 80-register cap; run-time digit roles cost spills)
+template <typename T, int ORDER>
 __global__ void __launch_bounds__(GC_THREADS, 2)
 gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ feats, const __grid_constant__ LowSet lows,
                        const float* __restrict__ tsteps, const bf16* __restrict__ wpack, const float* __restrict__ bias,
                        bf16* __restrict__ out, float4* __restrict__ flow_sum, const __grid_constant__ GcRows grows, int B, int I1, int Tn, int Hp,
-                       int Wp, float slope, int stage_bytes, int tiles_x, int tiles_y, int num_tiles, int tfast) {
+                       int Wp, float slope, int stage_bytes, int tiles_x, int tiles_y, int num_tiles) {
+  constexpr int tfast = ORDER;
   using namespace umma;
   extern __shared__ float4 tl_sm[];  // staged flow rows | A tile | weights
   __shared__ uint64_t mma_bar;
@@ -1227,10 +1229,13 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
   // RGBX, 24 B per pixel and image), so the CTAs working side by side read one image region for all T timesteps while it is
   // in L2; item-major order re-read every image from DRAM once per timestep (one item's reads + writes ~ the L2 size).
   // tfast = 0 keeps the item-major order: the timestep digit then has radix 1 and the top digit is the item.
+  // tfast = 2: (timestep, pair, x, y) -- in clip mode pair b's second frame is pair b + 1's first, so with the pairs side by
+  // side too each frame is read once instead of twice.
   const int Tr = tfast ? Tn : 1;
-  int ct = tile % Tr, ctx = (tile / Tr) % tiles_x, cty = (tile / (Tr * tiles_x)) % tiles_y, ctop = tile / (Tr * tiles_x * tiles_y);
-  const int g = (int)gridDim.x, gst = g % Tr, gsx = (g / Tr) % tiles_x, gsy = (g / (Tr * tiles_x)) % tiles_y,
-            gstop = g / (Tr * tiles_x * tiles_y);
+  const int R1 = tfast == 2 ? B : tiles_x, R2 = tfast == 2 ? tiles_x : tiles_y;   // radices of the digits after the timestep
+  int ct = tile % Tr, d1 = (tile / Tr) % R1, d2 = (tile / (Tr * R1)) % R2, d3 = tile / (Tr * R1 * R2);
+  const int g = (int)gridDim.x, gst = g % Tr, gs1 = (g / Tr) % R1, gs2 = (g / (Tr * R1)) % R2, gs3 = g / (Tr * R1 * R2);
+  int ctx = tfast == 2 ? d2 : d1, cty = tfast == 2 ? d3 : d2, ctop = tfast == 2 ? d1 : d3;
   int cn = ctop * Tr + ct;                                 // item = pair * T + timestep
   if (tile < num_tiles) stage(ctx, cty, cn, std::integral_constant<int, GC_THREADS>{}, (int)threadIdx.x);
   fence_async_smem();
@@ -1247,10 +1252,11 @@ gather_conv0a_p_kernel(const uint8_t* __restrict__ imgs, const T* __restrict__ f
     const int b = tfast ? ctop : n / Tn;
     const float t = tsteps[n - b * Tn];
     // the next tile of this CTA
-    ct += gst; ctx += gsx; cty += gsy; ctop += gstop;
-    if (ct >= Tr) { ct -= Tr; ctx++; }
-    if (ctx >= tiles_x) { ctx -= tiles_x; cty++; }
-    if (cty >= tiles_y) { cty -= tiles_y; ctop++; }
+    ct += gst; d1 += gs1; d2 += gs2; d3 += gs3;
+    if (ct >= Tr) { ct -= Tr; d1++; }
+    if (d1 >= R1) { d1 -= R1; d2++; }
+    if (d2 >= R2) { d2 -= R2; d3++; }
+    ctx = tfast == 2 ? d2 : d1; cty = tfast == 2 ? d3 : d2; ctop = tfast == 2 ? d1 : d3;
     cn = ctop * Tr + ct;
     const int base0 = b * plane, base1 = (I1 + b) * plane;
     const int mtb = n * lows.Hl[kl] * mWl;
@@ -1378,11 +1384,18 @@ int k_gather_conv0a(vfi_handle* h, const Layer& Lb0, const uint8_t* imgs, const 
   VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   if (smem > 112 * 1024) VFI_FAIL(h, VFI_E_ARG, "gather_conv0a: shared memory budget");
   if (h->opt_gc_persistent && !h->opt_gc_ablate) {
-    VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_p_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     const int tiles_x = Wp / TL_W, tiles_y = Hp / TL_H, num_tiles = tiles_x * tiles_y * B * T;
-    gather_conv0a_p_kernel<bf16><<<std::min(num_tiles, 2 * h->sm_count), GC_THREADS, smem, s>>>(
-        imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out, reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, Hp, Wp,
-        h->slope, (int)un, tiles_x, tiles_y, num_tiles, h->opt_t_fast);
+#define GC_P_LAUNCH(ORDER)                                                                                                        \
+  do {                                                                                                                            \
+    VFI_CUDA(h, cudaFuncSetAttribute(gather_conv0a_p_kernel<bf16, ORDER>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024)); \
+    gather_conv0a_p_kernel<bf16, ORDER><<<std::min(num_tiles, 2 * h->sm_count), GC_THREADS, smem, s>>>(                          \
+        imgs, (const bf16*)feats, lows, tsteps_dev, Lb0.ws2, Lb0.bias, out, reinterpret_cast<float4*>(flow_sum), grows, B, I1, T, \
+        Hp, Wp, h->slope, (int)un, tiles_x, tiles_y, num_tiles);                                                                  \
+  } while (0)
+    if (h->opt_t_fast == 0) GC_P_LAUNCH(0);
+    else if (h->opt_t_fast == 1) GC_P_LAUNCH(1);
+    else GC_P_LAUNCH(2);
+#undef GC_P_LAUNCH
     VFI_LAUNCHED(h);
     return 0;
   }
